@@ -1,0 +1,186 @@
+"""Pin the CPU oracle against outputs of the unmodified reference source
+(tests/golden/*.npz, produced by tests/golden/make_golden.py in the build
+container).  The reference has no tests of its own."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import barra_oracle as orc
+
+TOL = 1e-9   # north_star: <= 1e-9 relative in fp64
+
+
+def relerr(a, b, scale=None):
+    a = np.asarray(a, dtype=float)
+    b = np.asarray(b, dtype=float)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    nan_a, nan_b = np.isnan(a), np.isnan(b)
+    assert np.array_equal(nan_a, nan_b), "NaN pattern differs"
+    if a.size == 0 or nan_a.all():
+        return 0.0
+    if scale is None:
+        scale = np.nanmax(np.abs(b))
+    if scale == 0:
+        return float(np.nanmax(np.abs(a - b)))
+    return float(np.nanmax(np.abs(a - b)) / scale)
+
+
+@pytest.fixture(scope="module")
+def reg(golden_dir):
+    return np.load(os.path.join(golden_dir, "reg.npz"))
+
+
+@pytest.mark.parametrize("case", ["small", "csi", "n_lt_k", "nostyle_scale"])
+def test_reg_by_time(reg, case):
+    g = {k.split("__", 1)[1]: reg[k] for k in reg.files if k.startswith(case + "__")}
+    fr, spec, r2 = orc.reg_by_time(g["date_off"], g["cap"], g["ret"], g["ind"], g["style"], int(g["P"]))
+    # n_lt_k: N < K, the Gram is rank deficient and pinv's cutoff decides (SURVEY hard part 3)
+    tol = 1e-6 if case == "n_lt_k" else TOL
+    assert relerr(fr, g["factor_ret"]) < tol
+    # specific returns are measured against the return scale (they are ~0 when N < K)
+    assert relerr(spec, g["specific_ret"], scale=np.max(np.abs(g["ret"]))) < tol
+    assert np.max(np.abs(r2 - g["R2"])) < tol
+
+
+@pytest.mark.parametrize("case", ["small", "csi"])
+def test_cross_section_pieces(reg, case):
+    g = {k.split("__", 1)[1]: reg[k] for k in reg.files if k.startswith(case + "__")}
+    a, b = int(g["date_off"][0]), int(g["date_off"][1])
+    P = int(g["P"])
+    onehot = (g["ind"][a:b, None] == np.arange(P)[None, :]).astype(np.int64)
+    assert relerr(orc.style_factor_norm(g["style"][a:b], g["cap"][a:b]), g["style_norm0"]) < 1e-13
+    f, s, expo, r2 = orc.cross_section_reg(g["cap"][a:b], g["ret"][a:b], onehot, g["style"][a:b])
+    assert relerr(expo, g["exposure0"]) < TOL
+
+
+@pytest.fixture(scope="module")
+def risk(golden_dir):
+    return np.load(os.path.join(golden_dir, "risk.npz"))
+
+
+@pytest.mark.parametrize("q,tao", [(2, 10), (0, 252), (3, 40)])
+def test_newey_west(risk, q, tao):
+    fr = risk["nw_factor_ret"]
+    want, ok = risk[f"nw_q{q}_tao{tao}"], risk[f"nw_q{q}_tao{tao}_ok"]
+    got = orc.newey_west_by_time(fr, q, tao)
+    for t in range(len(fr)):
+        assert (got[t] is not None) == bool(ok[t])
+        if ok[t]:
+            assert relerr(got[t], want[t]) < 1e-12
+
+
+@pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
+def test_eigen_risk_adj(risk, T, M):
+    cov = risk["eig_cov_in"]
+    can = orc.eigen_risk_adj(cov, T, M, 1.4)
+    assert relerr(can, risk[f"eig_T{T}_M{M}_canonical"]) < TOL
+    lit = orc.eigen_risk_adj(cov, T, M, 1.4, eig=np.linalg.eig)
+    # literal mode reproduces the reference bit-for-bit on the SAME LAPACK build only;
+    # recorded, compared loosely (the gap to canonical is a property of the reference, F6)
+    assert relerr(lit, risk[f"eig_T{T}_M{M}_literal"]) < 1e-6
+
+
+def test_legacy_gauss_stream(risk):
+    for seed in (1, 2, 100):
+        want = risk[f"gauss_seed{seed}"]
+        got = orc.LegacyGauss(seed).standard_normal(64)
+        assert np.array_equal(got, want), "restated MT19937/polar stream must be bit-equal to numpy"
+        assert np.array_equal(np.random.RandomState(seed).standard_normal(64), want)
+    rs = np.random.RandomState(3)
+    got = rs.multivariate_normal(mean=3 * [0], cov=np.diag([3.0, 2.0, 0.5]), size=5)
+    assert np.array_equal(got, risk["mvn_seed3"])
+    # the structure the device path relies on: bm = sqrt(D0) * z for descending D0
+    z = np.random.RandomState(3).standard_normal((5, 3))
+    assert np.allclose(got, z * np.sqrt([3.0, 2.0, 0.5]), rtol=1e-15, atol=0)
+
+
+@pytest.mark.parametrize("n", [57, 300])
+def test_bayes_shrink(risk, n):
+    vol, cap = risk[f"bs{n}_vol"], risk[f"bs{n}_cap"]
+    codes, _ = orc.qcut_codes(cap, 10)
+    assert np.array_equal(codes, risk[f"bs{n}_codes_g10"])
+    assert relerr(orc.bayes_shrink(vol, cap, 10, 1), risk[f"bs{n}_out_g10_q1"]) < 1e-13
+    assert relerr(orc.bayes_shrink(vol, cap, 5, 0.5), risk[f"bs{n}_out_g5_q0.5"]) < 1e-13
+
+
+def test_bayes_shrink_duplicate_edges():
+    with pytest.raises(ValueError):
+        orc.bayes_shrink(np.ones(20), np.ones(20), 10, 1)
+
+
+def _lists(arr, ok):
+    return [arr[t] if ok[t] else None for t in range(len(ok))]
+
+
+def test_pipeline(golden_dir):
+    g = np.load(os.path.join(golden_dir, "pipeline.npz"))
+    P = int(g["P"])
+    fr, spec, r2 = orc.reg_by_time(g["date_off"], g["cap"], g["ret"], g["ind"], g["style"], P)
+    assert relerr(fr, g["factor_ret"]) < TOL
+    assert relerr(spec, g["specific_ret"]) < TOL
+    assert np.max(np.abs(r2 - g["R2"])) < TOL
+    T = fr.shape[0]
+    nw = orc.newey_west_by_time(g["factor_ret"], 2, 30)
+    assert [c is not None for c in nw] == list(g["nw_ok"])
+    for t in range(T):
+        if g["nw_ok"][t]:
+            assert relerr(nw[t], g["nw"][t]) < 1e-11
+    er = orc.eigen_risk_adj_by_time(_lists(g["nw"], g["nw_ok"]), T, 6, 1.4)
+    assert [c is not None for c in er] == list(g["er_ok"])
+    for t in range(T):
+        if g["er_ok"][t]:
+            assert relerr(er[t], g["er"][t]) < TOL
+    vr, lamb = orc.vol_regime_adj_by_time(g["factor_ret"], _lists(g["er"], g["er_ok"]), 12)
+    assert relerr(np.array(lamb), g["lamb"]) < 1e-12
+    for t in range(T):
+        assert (vr[t] is not None) == bool(g["vr_ok"][t])
+        if g["vr_ok"][t]:
+            assert relerr(vr[t], g["vr"][t]) < 1e-12
+    bs = orc.eigenfactor_bias_stat(_lists(g["nw"], g["nw_ok"])[40:], g["factor_ret"][40:], predlen=5)
+    assert relerr(bs, g["bias_stat_nw"]) < 1e-8
+
+
+@pytest.fixture(scope="module")
+def desc(golden_dir):
+    return np.load(os.path.join(golden_dir, "descriptors.npz"))
+
+
+def test_descriptors(desc):
+    s_all = desc["s"]
+    for s in np.unique(s_all):
+        sel = s_all == s
+        close = desc["close"][sel]
+        ret, lr = orc.prepare_returns(close)
+        assert relerr(ret, desc["ret"][sel]) < 1e-14
+        assert relerr(lr, desc["log_ret"][sel]) < 1e-14
+        mkt = desc["market_ret"][sel]
+        beta, hs = orc.beta_hsigma(ret, mkt)
+        assert relerr(beta, desc["BETA"][sel]) < TOL
+        assert relerr(hs, desc["HSIGMA"][sel]) < TOL
+        assert relerr(orc.dastd(ret - mkt), desc["DASTD"][sel]) < 1e-12
+        assert relerr(orc.cmra(lr), desc["CMRA"][sel]) < 1e-12
+
+
+def test_post_processing(desc):
+    d = desc["pp_date_idx"]
+    cols = ["DASTD", "CMRA", "HSIGMA", "BETA", "SIZE", "STOM", "STOQ", "STOA"]
+    wz = {}
+    for c in cols:
+        out = np.empty_like(desc[f"pp_in_{c}"])
+        for k in np.unique(d):
+            out[d == k] = orc.winsorize(desc[f"pp_in_{c}"][d == k], 2.5)
+        assert relerr(out, desc[f"pp_wz_{c}"]) < 1e-13, c
+        wz[c] = desc[f"pp_wz_{c}"]
+    vol = orc.composite([wz["DASTD"], wz["CMRA"], wz["HSIGMA"]], [0.7, 0.15, 0.15])
+    liq = orc.composite([wz["STOM"], wz["STOQ"], wz["STOA"]], [0.5, 0.25, 0.25])
+    assert relerr(vol, desc["pp_comp_volatility"]) < 1e-14
+    assert relerr(liq, desc["pp_comp_liquidity"]) < 1e-14
+    ov = np.empty_like(vol)
+    ol = np.empty_like(liq)
+    for k in np.unique(d):
+        m = d == k
+        ov[m] = orc.orthogonalize(desc["pp_comp_volatility"][m], np.column_stack([wz["BETA"][m], wz["SIZE"][m]]))
+        ol[m] = orc.orthogonalize(desc["pp_comp_liquidity"][m], wz["SIZE"][m])
+    assert relerr(ov, desc["pp_orth_volatility"]) < 1e-11
+    assert relerr(ol, desc["pp_orth_liquidity"]) < 1e-11
