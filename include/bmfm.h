@@ -1,0 +1,103 @@
+/*
+ * bmfm.h — C-ABI of the B200-native Barra risk-model path (libbmfm.so).
+ *
+ * The reference (Izumighj/LLM-Driven-Multi-factor-Model) is pure Python and
+ * has no FFI layer; its boundary is the Python API of Barra-master/mfm and
+ * Barra_factor_cal.  Each entry point below replaces the
+ * arithmetic of one reference function and is what a ctypes binding inside
+ * that function would call (INTEGRATION.md shows the stub).  Citations are
+ * file:line under the reference tree.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 for a bad argument
+ *     (BMFM_E_*), >0 = a cudaError_t from the CUDA runtime;
+ *     bmfm_last_error(ctx) gives the message.
+ *   - `*_dev` style pointers (no suffix) are DEVICE pointers owned by the
+ *     caller; the `_host` variants take HOST pointers and do the H2D/D2H copies
+ *     themselves on the context's stream (pinned memory recommended).
+ *   - all work is enqueued on the context's stream and is asynchronous for the
+ *     device-pointer entry points; `_host` variants synchronise before return.
+ *   - fp64 throughout; industry membership is an int32 index per row
+ *     (-1 or >= P: the row has no industry column set).
+ *   - one bmfm_ctx per host thread; a context is bound to one device.
+ */
+#ifndef BMFM_H
+#define BMFM_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bmfm_ctx bmfm_ctx;
+
+enum {
+  BMFM_OK = 0,
+  BMFM_E_ARG = -1,          /* NULL pointer / negative size */
+  BMFM_E_UNSUPPORTED = -2,  /* outside compiled limits (see bmfm_limits) */
+  BMFM_E_NOMEM = -3,
+  BMFM_E_STATE = -4
+};
+
+/* per-date status written by the *_by_time entry points */
+enum {
+  BMFM_ST_OK = 0,
+  BMFM_ST_SHORT = 1,     /* t <= q or t <= K: the reference raises, caller stores an empty DataFrame (utils.py:29, MFM.py:95-96) */
+  BMFM_ST_NOT_PSD = 2,   /* eigen_risk_adj PSD gate failed (utils.py:67-68) -> empty DataFrame */
+  BMFM_ST_NONFINITE = 3, /* non-finite Gram (e.g. last industry empty, CrossSection.py:70) -> numpy raises LinAlgError */
+  BMFM_ST_PINV = 4       /* informational: rank-deficient Gram, eigen-based pinv path was used (CrossSection.py:76) */
+};
+
+/* ---- context ------------------------------------------------------------ */
+/* stream: a cudaStream_t (as void*) to enqueue on; NULL = the default stream. */
+int bmfm_ctx_create(bmfm_ctx** out, int device, void* stream);
+int bmfm_ctx_destroy(bmfm_ctx* ctx);
+int bmfm_ctx_sync(bmfm_ctx* ctx);
+const char* bmfm_last_error(const bmfm_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+long long bmfm_launch_count(const bmfm_ctx* ctx);
+/* compiled limits: max styles Q, max industries P, max factors K */
+void bmfm_limits(int* max_Q, int* max_P, int* max_K);
+const char* bmfm_version(void);
+
+/* ---- part 1: cross-sectional regression ---------------------------------- */
+/*
+ * Replaces MFM.reg_by_time (Barra-master/mfm/MFM.py:48-76) and, per date,
+ * CrossSection.__init__ + CrossSection.reg (CrossSection.py:35-108) with
+ * style_factor_norm (CrossSection.py:12-20).
+ *
+ * Rows are grouped by date: date t owns rows [date_off[t], date_off[t+1]).
+ * Any row order inside a date is correct; the kernel is fastest when a date's
+ * rows are grouped by industry index.  Outputs keep the input row order.
+ *
+ *   date_off     int64  [T+1]
+ *   cap, ret     double [rows]
+ *   ind          int32  [rows]      industry index, -1 = none
+ *   style        double [rows * Q]  row-major
+ *   factor_ret   double [T * K]     K = 1 + P + Q, order country, industries, styles
+ *   specific_ret double [rows]
+ *   r2           double [T]
+ *   exposure     double [T * K * K] or NULL (pure-factor-portfolio exposure, CrossSection.py:104)
+ *   status       int32  [T]         BMFM_ST_*
+ *   max_rows_per_date  the largest date's row count (sizes the shared-memory
+ *                tile so a date is read from HBM once); 0 = unknown.
+ */
+int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                     const int64_t* date_off, const double* cap, const double* ret,
+                     const int32_t* ind, const double* style,
+                     double* factor_ret, double* specific_ret, double* r2,
+                     double* exposure, int32_t* status);
+
+/* Same, HOST pointers; copies inputs to the device, runs, copies results back. */
+int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
+                          const int64_t* date_off, const double* cap, const double* ret,
+                          const int32_t* ind, const double* style,
+                          double* factor_ret, double* specific_ret, double* r2,
+                          double* exposure, int32_t* status);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BMFM_H */

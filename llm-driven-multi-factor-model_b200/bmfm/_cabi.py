@@ -1,0 +1,147 @@
+"""ctypes binding of libbmfm.so (the C-ABI declared in include/bmfm.h).
+
+There is no CPU fallback: importing this module without the built library, or
+creating a context without a CUDA device, raises.  PyTorch is used only to own
+device memory and streams; the signatures below are plain pointers and sizes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbmfm.so")
+
+# status codes (include/bmfm.h)
+ST_OK, ST_SHORT, ST_NOT_PSD, ST_NONFINITE, ST_PINV = 0, 1, 2, 3, 4
+
+_lib = None
+_lock = threading.Lock()
+
+_P = C.c_void_p
+_I = C.c_int
+_D = C.c_double
+
+_SIGNATURES = {
+    "bmfm_ctx_create": ([C.POINTER(_P), _I, _P], _I),
+    "bmfm_ctx_destroy": ([_P], _I),
+    "bmfm_ctx_sync": ([_P], _I),
+    "bmfm_last_error": ([_P], C.c_char_p),
+    "bmfm_launch_count": ([_P], C.c_longlong),
+    "bmfm_limits": ([C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)], None),
+    "bmfm_version": ([], C.c_char_p),
+    "bmfm_reg_by_time": ([_P, _I, _I, _I, _I] + [_P] * 10, _I),
+    "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
+}
+
+
+def exported_symbols():
+    """Every symbol include/bmfm.h declares (checked by the CPU test-suite)."""
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """Load libbmfm.so once; raise loudly if it has not been built."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing: build it with "
+                    "`python llm-driven-multi-factor-model_b200/csrc/build.py` "
+                    "(there is no CPU fallback)")
+            L = C.CDLL(LIB_PATH)
+            for name, (argt, rest) in _SIGNATURES.items():
+                fn = getattr(L, name)   # AttributeError if the .so is stale
+                fn.argtypes = argt
+                fn.restype = rest
+            _lib = L
+    return _lib
+
+
+class BmfmError(RuntimeError):
+    pass
+
+
+def ptr(t):
+    """Device (or host) address of a torch tensor / numpy array, or NULL."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        assert t.is_contiguous()
+        return C.c_void_p(t.data_ptr())
+    assert t.flags["C_CONTIGUOUS"]
+    return C.c_void_p(t.ctypes.data)
+
+
+class Context:
+    """One bmfm_ctx bound to a CUDA device and (by default) torch's current stream."""
+
+    def __init__(self, device=None, stream="torch"):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise RuntimeError("bmfm needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        L = lib()
+        sp = None
+        if stream == "torch":
+            with torch.cuda.device(self.device):
+                sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        elif stream is not None:
+            sp = C.c_void_p(int(stream))
+        h = C.c_void_p()
+        rc = L.bmfm_ctx_create(C.byref(h), self.device, sp)
+        if rc != 0:
+            raise BmfmError(f"bmfm_ctx_create failed: {rc}")
+        self._h = h
+        self._L = L
+
+    def check(self, rc):
+        if rc != 0:
+            raise BmfmError(f"libbmfm error {rc}: {self._L.bmfm_last_error(self._h).decode()}")
+
+    def sync(self):
+        self.check(self._L.bmfm_ctx_sync(self._h))
+
+    @property
+    def launches(self):
+        return int(self._L.bmfm_launch_count(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.bmfm_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ part 1
+    def reg_by_time(self, T, P, Q, max_rows, date_off, cap, ret, ind, style,
+                    factor_ret, spec, r2, status, exposure=None):
+        self.check(self._L.bmfm_reg_by_time(self._h, T, P, Q, max_rows, ptr(date_off), ptr(cap), ptr(ret),
+                                            ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
+                                            ptr(exposure), ptr(status)))
+
+    def reg_by_time_host(self, T, P, Q, date_off, cap, ret, ind, style,
+                         factor_ret, spec, r2, status, exposure=None):
+        self.check(self._L.bmfm_reg_by_time_host(self._h, T, P, Q, ptr(date_off), ptr(cap), ptr(ret),
+                                                 ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
+                                                 ptr(exposure), ptr(status)))
+
+
+_default_ctx = {}
+
+
+def default_context():
+    """A per-device context on torch's current stream, created on first use."""
+    import torch
+
+    dev = torch.cuda.current_device() if torch.cuda.is_available() else -1
+    if dev not in _default_ctx:
+        _default_ctx[dev] = Context(dev if dev >= 0 else None)
+    return _default_ctx[dev]

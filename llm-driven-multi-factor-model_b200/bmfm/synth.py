@@ -121,8 +121,10 @@ def make_panel(T, N, P=31, Q=10, seed=20240002, ragged=0.0, scale_log10=(-1.0, 1
     ind = np.empty(N, dtype=np.int32)
     npref = min(P, N)
     ind[:npref] = np.arange(npref, dtype=np.int32)
-    if N > P:
+    if N > P and P > 0:
         ind[P:] = rng.integers(0, P, size=N - P, dtype=np.int32)
+    if P == 0:
+        ind[:] = -1
 
     mu = rng.normal(15.0, 1.5, size=N)
     walk = np.cumsum(rng.normal(0.0, 0.02, size=(T, N)), axis=0)
@@ -143,7 +145,7 @@ def make_panel(T, N, P=31, Q=10, seed=20240002, ragged=0.0, scale_log10=(-1.0, 1
     # returns from a factor structure on a cheaply standardised exposure
     sstd = (style - style.mean(axis=1, keepdims=True)) / style.std(axis=(1, 2), keepdims=True)
     f = rng.normal(0.0, 0.01, size=(T, K))
-    ret = f[:, :1] + f[:, 1:1 + P][:, ind] + np.einsum("tnq,tq->tn", sstd, f[:, 1 + P:])
+    ret = f[:, :1] + (f[:, 1:1 + P][:, ind] if P > 0 else 0.0) + np.einsum("tnq,tq->tn", sstd, f[:, 1 + P:])
     ret = ret + rng.normal(0.0, 0.02, size=(T, N))
 
     present = np.ones((T, N), dtype=bool)

@@ -1,0 +1,111 @@
+// Shared host/device helpers for libbmfm (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/bmfm.h"
+
+struct bmfm_ctx {
+  int device;
+  cudaStream_t stream;
+  bool own_stream;
+  int sm_count;
+  int max_smem_optin;
+  // grow-only device workspace (scratch beyond caller inputs/outputs)
+  void* ws;
+  size_t ws_bytes;
+  // grow-only staging buffers for the *_host entry points
+  void* stage[16];
+  size_t stage_bytes[16];
+  long long launches;
+  char err[512];
+};
+
+#define BMFM_CUDA(ctx, call)                                                        \
+  do {                                                                              \
+    cudaError_t e__ = (call);                                                       \
+    if (e__ != cudaSuccess) {                                                       \
+      snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d %s: %s", __FILE__, __LINE__,  \
+               #call, cudaGetErrorString(e__));                                     \
+      return (int)e__;                                                              \
+    }                                                                               \
+  } while (0)
+
+#define BMFM_ARG(ctx, cond, msg)                                                    \
+  do {                                                                              \
+    if (!(cond)) {                                                                  \
+      snprintf((ctx)->err, sizeof((ctx)->err), "bad argument: %s", msg);            \
+      return BMFM_E_ARG;                                                            \
+    }                                                                               \
+  } while (0)
+
+// host helpers (ctx.cu)
+int bmfm_ws_reserve(bmfm_ctx* ctx, size_t bytes);             // ctx->ws >= bytes
+int bmfm_stage_reserve(bmfm_ctx* ctx, int slot, size_t bytes);  // ctx->stage[slot] >= bytes
+static inline size_t bmfm_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+#ifdef __CUDACC__
+// ---- device helpers -------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
+}
+
+// Reduce NPAD (multiple of 32) per-lane values across the warp by recursive
+// halving: 5 exchange steps move NPAD/2 + NPAD/4 + ... values instead of 5*NPAD.
+// Afterwards slot i (< NPAD/32) of this lane holds the warp total of original
+// index reduce_scatter_index<NPAD>(i, lane).
+template <int NPAD>
+__device__ __forceinline__ void warp_reduce_scatter(double (&a)[NPAD], int lane) {
+  static_assert(NPAD % 32 == 0, "pad to a multiple of 32");
+#pragma unroll
+  for (int s = 0; s < 5; ++s) {
+    const int off = 16 >> s;
+    const int H = NPAD >> (s + 1);
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const double lo = a[i], hi = a[i + H];
+      const double send = upper ? lo : hi;
+      const double keep = upper ? hi : lo;
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+}
+template <int NPAD>
+__device__ __forceinline__ int reduce_scatter_index(int i, int lane) {
+  int idx = i;
+#pragma unroll
+  for (int s = 0; s < 5; ++s)
+    if (lane & (16 >> s)) idx += NPAD >> (s + 1);
+  return idx;
+}
+
+// cp.async (LDGSTS): element-granular global -> shared copies, any 4/8/16-byte alignment
+__device__ __forceinline__ void cp_async_4(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.wait_all;\n" ::: "memory");
+}
+// streaming store: results written once and not re-read by this kernel
+__device__ __forceinline__ void st_stream(double* p, double v) {
+  asm volatile("st.global.cs.f64 [%0], %1;\n" ::"l"(p), "d"(v) : "memory");
+}
+#endif

@@ -1,0 +1,125 @@
+// Context, workspace and the host-buffer (H2D / D2H) variants of the entry points.
+#include <stdlib.h>
+#include "bmfm_common.cuh"
+
+extern "C" const char* bmfm_version(void) { return "bmfm 0.1 (sm_100a)"; }
+
+extern "C" int bmfm_ctx_create(bmfm_ctx** out, int device, void* stream) {
+  if (!out) return BMFM_E_ARG;
+  *out = nullptr;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return (int)e;
+  bmfm_ctx* c = (bmfm_ctx*)calloc(1, sizeof(bmfm_ctx));
+  if (!c) return BMFM_E_NOMEM;
+  c->device = device;
+  // NULL = the default (legacy) stream, which is also torch's default stream
+  c->stream = (cudaStream_t)stream;
+  c->own_stream = false;
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+  cudaDeviceGetAttribute(&c->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  *out = c;
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_ctx_destroy(bmfm_ctx* c) {
+  if (!c) return BMFM_E_ARG;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  if (c->ws) cudaFree(c->ws);
+  for (int i = 0; i < 16; ++i)
+    if (c->stage[i]) cudaFree(c->stage[i]);
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  free(c);
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_ctx_sync(bmfm_ctx* c) {
+  if (!c) return BMFM_E_ARG;
+  BMFM_CUDA(c, cudaStreamSynchronize(c->stream));
+  return BMFM_OK;
+}
+
+extern "C" const char* bmfm_last_error(const bmfm_ctx* c) { return c ? c->err : "null context"; }
+extern "C" long long bmfm_launch_count(const bmfm_ctx* c) { return c ? c->launches : 0; }
+
+int bmfm_ws_reserve(bmfm_ctx* c, size_t bytes) {
+  if (c->ws_bytes >= bytes) return BMFM_OK;
+  BMFM_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->ws) BMFM_CUDA(c, cudaFree(c->ws));
+  c->ws = nullptr;
+  c->ws_bytes = 0;
+  BMFM_CUDA(c, cudaMalloc(&c->ws, bytes));
+  c->ws_bytes = bytes;
+  return BMFM_OK;
+}
+
+int bmfm_stage_reserve(bmfm_ctx* c, int slot, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  if (c->stage_bytes[slot] >= bytes) return BMFM_OK;
+  BMFM_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->stage[slot]) BMFM_CUDA(c, cudaFree(c->stage[slot]));
+  c->stage[slot] = nullptr;
+  c->stage_bytes[slot] = 0;
+  BMFM_CUDA(c, cudaMalloc(&c->stage[slot], bytes));
+  c->stage_bytes[slot] = bytes;
+  return BMFM_OK;
+}
+
+#define H2D(slot, src, bytes)                                                              \
+  do {                                                                                     \
+    int rc__ = bmfm_stage_reserve(ctx, slot, bytes);                                       \
+    if (rc__) return rc__;                                                                 \
+    if ((bytes) > 0)                                                                       \
+      BMFM_CUDA(ctx, cudaMemcpyAsync(ctx->stage[slot], src, bytes, cudaMemcpyHostToDevice, ctx->stream)); \
+  } while (0)
+#define DEVBUF(slot, bytes)                                  \
+  do {                                                       \
+    int rc__ = bmfm_stage_reserve(ctx, slot, bytes);         \
+    if (rc__) return rc__;                                   \
+  } while (0)
+#define D2H(dst, slot, bytes)                                                              \
+  do {                                                                                     \
+    if ((bytes) > 0)                                                                       \
+      BMFM_CUDA(ctx, cudaMemcpyAsync(dst, ctx->stage[slot], bytes, cudaMemcpyDeviceToHost, ctx->stream)); \
+  } while (0)
+
+extern "C" int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
+                                     const int64_t* date_off, const double* cap, const double* ret,
+                                     const int32_t* ind, const double* style,
+                                     double* factor_ret, double* specific_ret, double* r2,
+                                     double* exposure, int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && P >= 0 && Q >= 0 && date_off, "bad sizes");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t rows = (size_t)date_off[T];
+  const size_t K = 1 + (size_t)P + Q;
+  int max_rows = 0;
+  for (int t = 0; t < T; ++t) {
+    const int64_t n = date_off[t + 1] - date_off[t];
+    if (n > max_rows) max_rows = (int)n;
+  }
+  H2D(0, date_off, (T + 1) * sizeof(int64_t));
+  H2D(1, cap, rows * 8);
+  H2D(2, ret, rows * 8);
+  H2D(3, ind, rows * 4);
+  H2D(4, style, rows * Q * 8);
+  DEVBUF(5, T * K * 8);
+  DEVBUF(6, rows * 8);
+  DEVBUF(7, T * 8);
+  DEVBUF(8, T * 4);
+  if (exposure) DEVBUF(9, T * K * K * 8);
+  int rc = bmfm_reg_by_time(ctx, T, P, Q, max_rows, (const int64_t*)ctx->stage[0], (const double*)ctx->stage[1],
+                            (const double*)ctx->stage[2], (const int32_t*)ctx->stage[3],
+                            (const double*)ctx->stage[4], (double*)ctx->stage[5], (double*)ctx->stage[6],
+                            (double*)ctx->stage[7], exposure ? (double*)ctx->stage[9] : nullptr,
+                            (int32_t*)ctx->stage[8]);
+  if (rc) return rc;
+  D2H(factor_ret, 5, T * K * 8);
+  D2H(specific_ret, 6, rows * 8);
+  D2H(r2, 7, T * 8);
+  D2H(status, 8, T * 4);
+  if (exposure) D2H(exposure, 9, T * K * K * 8);
+  BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return BMFM_OK;
+}

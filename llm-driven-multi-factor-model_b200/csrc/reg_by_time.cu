@@ -1,0 +1,971 @@
+// Per-date constrained cross-sectional regression (part 1 of the Barra path).
+//
+// Replaces, for every date of the panel at once:
+//   MFM.reg_by_time                      Barra-master/mfm/MFM.py:48-76
+//   CrossSection.__init__ / .reg         Barra-master/mfm/CrossSection.py:35-108
+//   style_factor_norm                    Barra-master/mfm/CrossSection.py:12-20
+//
+// Design (B200): one CTA per date, grid-stride over dates.  A date's rows are
+// staged ONCE into shared memory with cp.async (the per-date tile of N=800
+// stocks x 100 B is 80 KB, two CTAs per SM), so HBM sees each input byte once:
+//   pass A   thread-per-row register accumulation of the structured weighted
+//            Gram: style x style (packed), style x ret, cap-weighted style sums
+//            and the moments of the scalar np.std — the one-hot block never
+//            becomes a dense matrix;
+//   buckets  per-industry sums (weights, w*ret, cap, w*style) by half-warp per
+//            industry segment when rows are grouped by industry, shared-memory
+//            atomics otherwise (any row order is correct);
+//   solve    the industry block of the normal equations is diagonal, so the
+//            K-1 = 41 unknowns reduce by block elimination to a Q x Q SPD
+//            system (Cholesky) plus a 2 x 2 for (country, multiplier) — solved
+//            by warp 0.  Dates whose reduced system is not safely definite are
+//            flagged and redone by the dense kernel below, which forms the
+//            reference's R^T G R explicitly and applies numpy's pinv semantics
+//            (eigen-decomposition, cutoff 1e-15 * max) — CrossSection.py:69-76;
+//   pass C   specific returns + R2 from the rows still resident in shared memory.
+// Dates larger than the tile are streamed tile by tile (pass C re-reads them).
+#include "bmfm_common.cuh"
+#include "jacobi.cuh"
+
+namespace bmfm {
+
+constexpr int REG_MAX_Q = 12;       // register-accumulator template range
+constexpr int REG_MAX_P = 63;       // P + 1 buckets <= 64
+constexpr int REG_NEED_DENSE = 100; // internal status: redo this date in the dense kernel
+
+struct RegParams {
+  int T, P, Q, K;
+  const long long* date_off;
+  const double* cap;
+  const double* ret;
+  const int* ind;
+  const double* style;
+  double* factor_ret;
+  double* spec;
+  double* r2;
+  double* exposure;
+  int* status;
+  int tile_rows;
+  int all_dense;  // dense kernel: process every date (exposure requested)
+};
+
+__host__ __device__ constexpr int round_up32(int x) { return (x + 31) / 32 * 32; }
+__host__ __device__ constexpr int na1_of(int Q) { return Q * (Q + 1) / 2 + Q; }
+__host__ __device__ constexpr int na1pad_of(int Q) { return na1_of(Q) == 0 ? 32 : round_up32(na1_of(Q)); }
+__host__ __device__ constexpr int na2_of(int Q) { return 3 * Q + 2; }
+__host__ __device__ constexpr int na2pad_of(int Q) { return round_up32(na2_of(Q)); }
+
+// byte offsets into dynamic shared memory
+struct RegSmem {
+  int style, cap, ret, w, ind, bucket, seg, acc, red, coef, fvec, solve, G, V, G0, cs, total;
+};
+
+__host__ __device__ inline int align16(int x) { return (x + 15) & ~15; }
+
+__host__ __device__ inline RegSmem reg_smem_layout(int tile_rows, int P, int Q, int nwarps, bool dense) {
+  RegSmem s;
+  const int NB = P + 1, BV = 3 + Q, K = 1 + P + Q;
+  const int ld = K | 1;
+  int o = 0;
+  s.style = o; o = align16(o + tile_rows * Q * 8);
+  s.cap = o;   o = align16(o + tile_rows * 8);
+  s.ret = o;   o = align16(o + tile_rows * 8);
+  s.w = o;     o = align16(o + tile_rows * 8);
+  s.ind = o;   o = align16(o + tile_rows * 4);
+  s.bucket = o; o = align16(o + NB * BV * 8);
+  s.seg = o;   o = align16(o + (3 * NB + 8) * 4);
+  s.acc = o;   o = align16(o + (na1pad_of(Q) + na2pad_of(Q)) * 8);
+  const int redw = na1pad_of(Q) > na2pad_of(Q) ? na1pad_of(Q) : na2pad_of(Q);
+  s.red = o;   o = align16(o + nwarps * redw * 8);
+  s.coef = o;  o = align16(o + (3 * Q + NB + 32) * 8);   // piv[Q] mp[Q] beta[Q] g[NB] misc[32]
+  s.fvec = o;  o = align16(o + (K + 2) * 8);
+  s.solve = o; o = align16(o + (Q * Q + 7 * Q + 2 * NB + 8) * 8);
+  s.G = s.V = s.G0 = s.cs = o;
+  if (dense) {
+    s.G = o;  o = align16(o + K * ld * 8);
+    s.V = o;  o = align16(o + K * ld * 8);
+    s.G0 = o; o = align16(o + K * ld * 8);
+    s.cs = o; o = align16(o + (4 * K + 16) * 8);
+  }
+  s.total = o;
+  return s;
+}
+
+__device__ __forceinline__ int bucket_of(int ind, int P) { return (ind >= 0 && ind < P) ? ind : P; }
+
+// ---- tile load: global -> shared, every byte once ---------------------------------------
+template <int Q>
+__device__ __forceinline__ void load_tile(const RegParams& p, long long a, int n, bool with_cap,
+                                          double* s_style, double* s_cap, double* s_ret, int* s_ind) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int e = tid; e < n; e += nt) {
+    if (with_cap) cp_async_8(&s_cap[e], p.cap + a + e);
+    cp_async_8(&s_ret[e], p.ret + a + e);
+    cp_async_4(&s_ind[e], p.ind + a + e);
+  }
+  if (Q > 0) {
+    const double* src = p.style + a * Q;
+    const int tot = n * Q;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+      const int n16 = tot >> 1;
+      for (int e = tid; e < n16; e += nt) cp_async_16(&s_style[2 * e], src + 2 * e);
+      if ((tot & 1) && tid == 0) cp_async_8(&s_style[tot - 1], src + tot - 1);
+    } else {
+      for (int e = tid; e < tot; e += nt) cp_async_8(&s_style[e], src + e);
+    }
+  }
+}
+
+template <int Q>
+__device__ __forceinline__ void load_row_styles(const double* s_style, int i, const double* piv, double (&d)[Q > 0 ? Q : 1]) {
+  if (Q == 0) return;
+  const double* row = s_style + (size_t)i * Q;
+  if (Q % 2 == 0) {
+#pragma unroll
+    for (int q = 0; q < Q; q += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(row + q);
+      d[q] = v.x - piv[q];
+      d[q + 1] = v.y - piv[q + 1];
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < Q; ++q) d[q] = row[q] - piv[q];
+  }
+}
+
+// ---- accumulation over one date (all tiles) ----------------------------------------------
+// On return (after the trailing __syncthreads):
+//   s_acc[0 .. NA1PAD)            S2 packed (q(q+1)/2 + r, r <= q) = sum w d_q d_r,  then BY[q] = sum w d_q y
+//   s_acc[NA1PAD ..)              CD[q] = sum cap d_q, D1[q] = sum d_q, D2[q] = sum d_q^2, Y1, Y2 (shifted ret moments)
+//   s_bucket[b*(3+Q) + v]         per bucket b: sum w, sum w y, sum cap, sum w d_q
+// with d_q = style_q - piv_q (piv = the date's first row: a cheap shift that removes the
+// cancellation a raw-moment formulation would have) and the LAST tile resident in shared memory.
+template <int Q>
+__device__ void accumulate_date(const RegParams& p, const RegSmem& L, unsigned char* smem, long long a, int n,
+                                int& ntiles_out) {
+  constexpr int NA1 = na1_of(Q), NA1PAD = na1pad_of(Q), NA2 = na2_of(Q), NA2PAD = na2pad_of(Q);
+  constexpr int QQ = Q > 0 ? Q : 1;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
+  const int P = p.P, NB = P + 1, BV = 3 + Q;
+  double* s_style = reinterpret_cast<double*>(smem + L.style);
+  double* s_cap = reinterpret_cast<double*>(smem + L.cap);
+  double* s_ret = reinterpret_cast<double*>(smem + L.ret);
+  double* s_w = reinterpret_cast<double*>(smem + L.w);
+  int* s_ind = reinterpret_cast<int*>(smem + L.ind);
+  double* s_bucket = reinterpret_cast<double*>(smem + L.bucket);
+  int* s_seg = reinterpret_cast<int*>(smem + L.seg);   // start[NB] end[NB] runs[NB] flag
+  double* s_acc = reinterpret_cast<double*>(smem + L.acc);
+  double* s_red = reinterpret_cast<double*>(smem + L.red);
+  double* s_piv = reinterpret_cast<double*>(smem + L.coef);   // piv[Q], then ypiv at misc
+  double* s_misc = s_piv + 3 * Q + NB;
+
+  const int tile_rows = p.tile_rows;
+  const int ntiles = (n + tile_rows - 1) / tile_rows;
+  ntiles_out = ntiles;
+
+  for (int e = tid; e < NB * BV; e += nt) s_bucket[e] = 0.0;
+  if (tid < Q) s_piv[tid] = p.style[a * Q + tid];
+  if (tid == 0) s_misc[0] = p.ret[a];   // ypiv
+  __syncthreads();
+  const double ypiv = s_misc[0];
+
+  double acc1[NA1PAD];
+  double acc2[NA2PAD];
+#pragma unroll
+  for (int i = 0; i < NA1PAD; ++i) acc1[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < NA2PAD; ++i) acc2[i] = 0.0;
+
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int r0 = tile * tile_rows;
+    const int m = min(tile_rows, n - r0);
+    if (tile > 0) __syncthreads();   // previous tile fully consumed
+    load_tile<Q>(p, a + r0, m, true, s_style, s_cap, s_ret, s_ind);
+    for (int e = tid; e < 3 * NB + 1; e += nt) s_seg[e] = 0;
+    cp_async_wait_all();
+    __syncthreads();
+
+    // pass A1: weighted style Gram + style x ret; also stores w = sqrt(cap)
+    for (int i = tid; i < m; i += nt) {
+      const double cap = s_cap[i];
+      const double w = sqrt(cap);
+      s_w[i] = w;
+      if (Q > 0) {
+        const double y = s_ret[i];
+        double d[QQ];
+        load_row_styles<Q>(s_style, i, s_piv, d);
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+          const double wd = w * d[q];
+#pragma unroll
+          for (int r = 0; r <= q; ++r) acc1[q * (q + 1) / 2 + r] = fma(wd, d[r], acc1[q * (q + 1) / 2 + r]);
+          acc1[Q * (Q + 1) / 2 + q] = fma(wd, y, acc1[Q * (Q + 1) / 2 + q]);
+        }
+      }
+    }
+    // pass A2: cap-weighted style sums (means of style_factor_norm), moments of the scalar std, ret moments
+    for (int i = tid; i < m; i += nt) {
+      const double cap = s_cap[i];
+      const double u = s_ret[i] - ypiv;
+      acc2[3 * Q] += u;
+      acc2[3 * Q + 1] = fma(u, u, acc2[3 * Q + 1]);
+      if (Q > 0) {
+        double d[QQ];
+        load_row_styles<Q>(s_style, i, s_piv, d);
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+          acc2[q] = fma(cap, d[q], acc2[q]);
+          acc2[Q + q] += d[q];
+          acc2[2 * Q + q] = fma(d[q], d[q], acc2[2 * Q + q]);
+        }
+      }
+    }
+    // industry runs inside the tile
+    int* seg_start = s_seg;
+    int* seg_end = s_seg + NB;
+    int* seg_runs = s_seg + 2 * NB;
+    int* seg_flag = s_seg + 3 * NB;
+    for (int i = tid; i < m; i += nt) {
+      const int b = bucket_of(s_ind[i], P);
+      const int bp = i > 0 ? bucket_of(s_ind[i - 1], P) : -1;
+      const int bn = i + 1 < m ? bucket_of(s_ind[i + 1], P) : -1;
+      if (b != bp) {
+        if (atomicAdd(&seg_runs[b], 1) > 0) *seg_flag = 1;   // a second run: rows not grouped
+        seg_start[b] = i;
+      }
+      if (b != bn) seg_end[b] = i + 1;
+    }
+    __syncthreads();   // s_w, runs visible
+    if (*seg_flag == 0) {
+      // grouped rows: a half-warp per bucket, lane = value column
+      const int v = tid & 15, grp = tid >> 4, ngrp = nt >> 4;
+      if (v < BV) {
+        for (int b = grp; b < NB; b += ngrp) {
+          if (seg_runs[b] == 0) continue;
+          const int lo = seg_start[b], hi = seg_end[b];
+          double sum = 0.0;
+          if (v == 0) {
+            for (int i = lo; i < hi; ++i) sum += s_w[i];
+          } else if (v == 1) {
+            for (int i = lo; i < hi; ++i) sum = fma(s_w[i], s_ret[i], sum);
+          } else if (v == 2) {
+            for (int i = lo; i < hi; ++i) sum += s_cap[i];
+          } else {
+            const int q = v - 3;
+            const double pv = s_piv[q];
+            for (int i = lo; i < hi; ++i) sum = fma(s_w[i], s_style[(size_t)i * Q + q] - pv, sum);
+          }
+          s_bucket[b * BV + v] += sum;
+        }
+      }
+    } else {
+      // arbitrary row order: shared-memory atomics (correct, slower)
+      for (int i = tid; i < m; i += nt) {
+        const int b = bucket_of(s_ind[i], P);
+        const double w = s_w[i];
+        atomicAdd(&s_bucket[b * BV + 0], w);
+        atomicAdd(&s_bucket[b * BV + 1], w * s_ret[i]);
+        atomicAdd(&s_bucket[b * BV + 2], s_cap[i]);
+        for (int q = 0; q < Q; ++q)
+          atomicAdd(&s_bucket[b * BV + 3 + q], w * (s_style[(size_t)i * Q + q] - s_piv[q]));
+      }
+    }
+  }
+
+  // CTA reduction of the register accumulators: warp recursive-halving, then across warps
+  warp_reduce_scatter<NA1PAD>(acc1, lane);
+#pragma unroll
+  for (int i = 0; i < NA1PAD / 32; ++i) s_red[warp * NA1PAD + reduce_scatter_index<NA1PAD>(i, lane)] = acc1[i];
+  __syncthreads();
+  for (int j = tid; j < NA1PAD; j += nt) {
+    double s = 0.0;
+    for (int w2 = 0; w2 < nwarps; ++w2) s += s_red[w2 * NA1PAD + j];
+    s_acc[j] = s;
+  }
+  __syncthreads();
+  warp_reduce_scatter<NA2PAD>(acc2, lane);
+#pragma unroll
+  for (int i = 0; i < NA2PAD / 32; ++i) s_red[warp * NA2PAD + reduce_scatter_index<NA2PAD>(i, lane)] = acc2[i];
+  __syncthreads();
+  for (int j = tid; j < NA2PAD; j += nt) {
+    double s = 0.0;
+    for (int w2 = 0; w2 < nwarps; ++w2) s += s_red[w2 * NA2PAD + j];
+    s_acc[NA1PAD + j] = s;
+  }
+  __syncthreads();
+  (void)NA1; (void)NA2;
+}
+
+// ---- fast solve: block elimination of the diagonal industry block (warp 0) -----------------
+// Minimise sum_i w_i (y_i - f_c - g_{p(i)} - beta . x_i)^2  s.t.  sum_p c_p g_p = 0,
+// x_i = d_i - m' (the sigma of style_factor_norm only rescales beta).  Eliminating g_p through
+// the diagonal block leaves  [w0 gs0' C; gs0 St t; C t' -D] (f_c, beta, mu') = (b0, bt, cy).
+// Equivalent to R pinv(R'GR) R'b of CrossSection.py:69-76 whenever R'GR is non-singular;
+// empty non-last industries (zero row/column of R'GR, pinv -> 0) are skipped the same way.
+// Returns 0 ok, REG_NEED_DENSE if a pivot is not safely positive, BMFM_ST_NONFINITE.
+template <int Q>
+__device__ int solve_fast_warp0(const RegParams& p, const RegSmem& L, unsigned char* smem, int n) {
+  const int lane = threadIdx.x & 31;
+  const int P = p.P, NB = P + 1, BV = 3 + Q, K = p.K;
+  constexpr int NA1PAD = na1pad_of(Q);
+  const double* s_bucket = reinterpret_cast<const double*>(smem + L.bucket);
+  const double* s_acc = reinterpret_cast<const double*>(smem + L.acc);
+  double* s_piv = reinterpret_cast<double*>(smem + L.coef);
+  double* s_mp = s_piv + Q;
+  double* s_beta = s_mp + Q;
+  double* s_g = s_beta + Q;
+  double* s_misc = s_g + NB;
+  double* s_f = reinterpret_cast<double*>(smem + L.fvec);
+  double* St = reinterpret_cast<double*>(smem + L.solve);   // Q*Q
+  double* rhs = St + Q * Q;                                 // 3*Q solved in place
+  double* org = rhs + 3 * Q;                                // 3*Q originals
+  double* diag0 = org + 3 * Q;                              // Q
+  double* winv = diag0 + Q;                                 // NB
+  const double* S2 = s_acc;
+  const double* BY = s_acc + Q * (Q + 1) / 2;
+  const double* CD = s_acc + NA1PAD;
+  const double* D1 = CD + Q;
+  const double* D2 = D1 + Q;
+#define BW(b) s_bucket[(b)*BV + 0]
+#define BWY(b) s_bucket[(b)*BV + 1]
+#define BC(b) s_bucket[(b)*BV + 2]
+#define BD(b, q) s_bucket[(b)*BV + 3 + (q)]
+  // industry sums
+  double sC = 0.0, Dm = 0.0, cy = 0.0;
+  for (int b = lane; b < P; b += 32) {
+    const double wv = BW(b);
+    const double wi = wv > 0.0 ? 1.0 / wv : 0.0;
+    winv[b] = wi;
+    const double c = wv > 0.0 ? BC(b) : 0.0;
+    sC += c;
+    Dm = fma(c * c, wi, Dm);
+    cy = fma(c * wi, BWY(b), cy);
+  }
+  sC = warp_sum(sC);
+  Dm = warp_sum(Dm);
+  cy = warp_sum(cy);
+  const double W0 = BW(P), b0 = BWY(P);
+  double capall = 0.0;
+  for (int b = lane; b < NB; b += 32) capall += BC(b);
+  capall = warp_sum(capall);
+  if (lane < Q) s_mp[lane] = CD[lane] / capall;
+  // scalar std of style_factor_norm: one mean and one variance over all n*Q entries
+  const double dn = (double)n;
+  double sigma = 1.0;
+  if (Q > 0) {
+    double v = lane < Q ? D1[lane] + dn * s_piv[lane] : 0.0;
+    const double mu = warp_sum(v) / (dn * Q);
+    double t2 = 0.0;
+    if (lane < Q) {
+      const double dq = s_piv[lane] - mu;
+      t2 = D2[lane] + 2.0 * dq * D1[lane] + dn * dq * dq;
+    }
+    sigma = sqrt(warp_sum(t2) / (dn * Q));
+  }
+  __syncwarp();
+  int fail = 0;
+  if (P > 0 && !(BC(P - 1) != 0.0)) fail = BMFM_ST_NONFINITE;   // -cap/0 in R (CrossSection.py:70)
+  // reduced matrices in d-units
+  for (int e = lane; e < Q * Q; e += 32) {
+    const int q = e / Q, r = e - q * Q;
+    const int hi = q > r ? q : r, lo = q > r ? r : q;
+    double a = S2[hi * (hi + 1) / 2 + lo];
+    for (int b = 0; b < P; ++b) a = fma(-BD(b, q) * winv[b], BD(b, r), a);
+    a += -s_mp[q] * BD(P, r) - s_mp[r] * BD(P, q) + s_mp[q] * s_mp[r] * W0;
+    St[e] = a;
+    if (q == r) diag0[q] = a;
+  }
+  if (lane < Q) {
+    const int q = lane;
+    double t = 0.0, bt = BY[q];
+    for (int b = 0; b < P; ++b) {
+      const double eb = BD(b, q) * winv[b];
+      if (winv[b] > 0.0) t = fma(eb - s_mp[q], BC(b), t);
+      bt = fma(-eb, BWY(b), bt);
+    }
+    bt -= s_mp[q] * b0;
+    const double gs0 = BD(P, q) - s_mp[q] * W0;
+    rhs[q] = org[q] = gs0;
+    rhs[Q + q] = org[Q + q] = t;
+    rhs[2 * Q + q] = org[2 * Q + q] = bt;
+  }
+  __syncwarp();
+  // Cholesky St = L L' (lower, in place), pivots checked against the original diagonal
+  for (int k = 0; k < Q; ++k) {
+    const double dk = St[k * Q + k];
+    if (!(dk > 1e-11 * diag0[k]) || !(diag0[k] > 0.0)) { if (!fail) fail = REG_NEED_DENSE; break; }
+    const double lkk = sqrt(dk);
+    __syncwarp();
+    if (lane == k) St[k * Q + k] = lkk;
+    if (lane > k && lane < Q) St[lane * Q + k] /= lkk;
+    __syncwarp();
+    const int mtr = Q - k - 1;
+    for (int e = lane; e < mtr * mtr; e += 32) {
+      const int i = k + 1 + e / mtr, j = k + 1 + e % mtr;
+      if (j <= i) St[i * Q + j] = fma(-St[i * Q + k], St[j * Q + k], St[i * Q + j]);
+    }
+    __syncwarp();
+  }
+  if (!fail) {
+    // three right-hand sides, lanes over (rhs, row)
+    for (int k = 0; k < Q; ++k) {
+      const double lkk = St[k * Q + k];
+      if (lane < 3) rhs[lane * Q + k] /= lkk;
+      __syncwarp();
+      for (int e = lane; e < 3 * Q; e += 32) {
+        const int r = e / Q, i = e - r * Q;
+        if (i > k) rhs[e] = fma(-St[i * Q + k], rhs[r * Q + k], rhs[e]);
+      }
+      __syncwarp();
+    }
+    for (int k = Q - 1; k >= 0; --k) {
+      const double lkk = St[k * Q + k];
+      if (lane < 3) rhs[lane * Q + k] /= lkk;
+      __syncwarp();
+      for (int e = lane; e < 3 * Q; e += 32) {
+        const int r = e / Q, i = e - r * Q;
+        if (i < k) rhs[e] = fma(-St[k * Q + i], rhs[r * Q + k], rhs[e]);
+      }
+      __syncwarp();
+    }
+    // 2x2 Schur system for (f_c, mu')
+    double g0x0 = 0, g0x1 = 0, g0x2 = 0, tx1 = 0, tx2 = 0;
+    if (lane < Q) {
+      g0x0 = org[lane] * rhs[lane];
+      g0x1 = org[lane] * rhs[Q + lane];
+      g0x2 = org[lane] * rhs[2 * Q + lane];
+      tx1 = org[Q + lane] * rhs[Q + lane];
+      tx2 = org[Q + lane] * rhs[2 * Q + lane];
+    }
+    g0x0 = warp_sum(g0x0); g0x1 = warp_sum(g0x1); g0x2 = warp_sum(g0x2);
+    tx1 = warp_sum(tx1); tx2 = warp_sum(tx2);
+    const double M00 = W0 - g0x0, M01 = sC - g0x1, M11 = -Dm - tx1;
+    const double r0 = b0 - g0x2, r1 = cy - tx2;
+    double fc, mu;
+    if (P > 0) {
+      const double det = M00 * M11 - M01 * M01;
+      if (!(fabs(det) > 1e-12 * (fabs(M00 * M11) + M01 * M01))) fail = REG_NEED_DENSE;
+      fc = (r0 * M11 - M01 * r1) / det;
+      mu = (M00 * r1 - M01 * r0) / det;
+    } else {
+      if (!(M00 > 1e-12 * W0)) fail = REG_NEED_DENSE;
+      fc = r0 / M00;
+      mu = 0.0;
+    }
+    double bsum = 0.0;
+    if (lane < Q) {
+      const double be = rhs[2 * Q + lane] - rhs[lane] * fc - rhs[Q + lane] * mu;
+      s_beta[lane] = be;
+      s_f[1 + P + lane] = be * sigma;
+      bsum = be * s_mp[lane];
+    }
+    bsum = warp_sum(bsum);
+    __syncwarp();
+    for (int b = lane; b < NB; b += 32) {
+      double g = 0.0;
+      if (b < P && winv[b] > 0.0) {
+        double eb = 0.0;
+        for (int q = 0; q < Q; ++q) eb = fma(BD(b, q) * winv[b] - s_mp[q], s_beta[q], eb);
+        g = BWY(b) * winv[b] - eb + mu * BC(b) * winv[b] - fc;
+      }
+      s_g[b] = g;
+      if (b < P) s_f[1 + b] = g;
+    }
+    if (lane == 0) {
+      s_f[0] = fc;
+      s_misc[1] = fc - bsum;   // c0: intercept on the pivot-shifted styles
+      s_misc[2] = sigma;
+    }
+    __syncwarp();
+    // any non-finite coefficient -> numpy would have raised / produced NaN
+    int bad = 0;
+    for (int k = lane; k < K; k += 32) bad |= !isfinite(s_f[k]);
+    bad = __any_sync(0xffffffffu, bad);
+    if (bad && fail != REG_NEED_DENSE) fail = BMFM_ST_NONFINITE;
+  }
+#undef BW
+#undef BWY
+#undef BC
+#undef BD
+  return __shfl_sync(0xffffffffu, fail, 0);
+}
+
+// ---- pass C: specific returns and R2 from coefficients in shared memory -------------------
+// spec_i = y_i - c0 - g[bucket_i] - sum_q beta_q d_iq   (CrossSection.py:105),
+// R2 = 1 - var(spec)/var(ret), np.var ddof 0 (CrossSection.py:106).
+template <int Q>
+__device__ void residual_date(const RegParams& p, const RegSmem& L, unsigned char* smem, long long a, int n,
+                              int ntiles, int t) {
+  constexpr int QQ = Q > 0 ? Q : 1;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
+  const int P = p.P, NB = P + 1;
+  constexpr int NA1PAD = na1pad_of(Q);
+  double* s_style = reinterpret_cast<double*>(smem + L.style);
+  double* s_cap = reinterpret_cast<double*>(smem + L.cap);
+  double* s_ret = reinterpret_cast<double*>(smem + L.ret);
+  int* s_ind = reinterpret_cast<int*>(smem + L.ind);
+  double* s_red = reinterpret_cast<double*>(smem + L.red);
+  const double* s_acc = reinterpret_cast<const double*>(smem + L.acc);
+  double* s_piv = reinterpret_cast<double*>(smem + L.coef);
+  double* s_beta = s_piv + 2 * Q;
+  double* s_g = s_beta + Q;
+  double* s_misc = s_g + NB;
+  const double c0 = s_misc[1];
+  double se = 0.0, see = 0.0;
+  for (int tile = ntiles - 1; tile >= 0; --tile) {
+    const int r0 = tile * p.tile_rows;
+    const int m = min(p.tile_rows, n - r0);
+    if (tile != ntiles - 1) {
+      __syncthreads();
+      load_tile<Q>(p, a + r0, m, false, s_style, s_cap, s_ret, s_ind);
+      cp_async_wait_all();
+      __syncthreads();
+    }
+    for (int i = tid; i < m; i += nt) {
+      double e = s_ret[i] - c0 - s_g[bucket_of(s_ind[i], P)];
+      if (Q > 0) {
+        double d[QQ];
+        load_row_styles<Q>(s_style, i, s_piv, d);
+#pragma unroll
+        for (int q = 0; q < Q; ++q) e = fma(-s_beta[q], d[q], e);
+      }
+      st_stream(p.spec + a + r0 + i, e);
+      se += e;
+      see = fma(e, e, see);
+    }
+  }
+  se = warp_sum(se);
+  see = warp_sum(see);
+  if (lane == 0) { s_red[2 * warp] = se; s_red[2 * warp + 1] = see; }
+  __syncthreads();
+  if (tid == 0) {
+    double a1 = 0.0, a2 = 0.0;
+    for (int w = 0; w < nwarps; ++w) { a1 += s_red[2 * w]; a2 += s_red[2 * w + 1]; }
+    const double dn = (double)n;
+    const double me = a1 / dn;
+    const double var_e = a2 / dn - me * me;
+    const double Y1 = s_acc[NA1PAD + 3 * Q], Y2 = s_acc[NA1PAD + 3 * Q + 1];
+    const double my = Y1 / dn;
+    const double var_y = Y2 / dn - my * my;
+    p.r2[t] = 1.0 - var_e / var_y;
+  }
+}
+
+// ---- dense solve: the reference's formulation, numpy pinv semantics (whole CTA) -----------
+// Builds G = X'WX and b = X'Wy from the same accumulators (standardised styles), applies the
+// constraint matrix R of CrossSection.py:69-71 (row P <- -cap_p/cap_last, column P deleted),
+// eigen-decomposes R'GR and keeps eigenvalues with |lambda| > 1e-15 * max|lambda| — numpy's
+// default pinv cutoff on singular values (CrossSection.py:76; :98 when P == 0).
+template <int Q>
+__device__ int solve_dense_cta(const RegParams& p, const RegSmem& L, unsigned char* smem, int n_rows, int t) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
+  const int P = p.P, NB = P + 1, BV = 3 + Q, K = p.K, ld = K | 1;
+  constexpr int NA1PAD = na1pad_of(Q);
+  const double* s_bucket = reinterpret_cast<const double*>(smem + L.bucket);
+  const double* s_acc = reinterpret_cast<const double*>(smem + L.acc);
+  double* s_piv = reinterpret_cast<double*>(smem + L.coef);
+  double* s_mp = s_piv + Q;
+  double* s_beta = s_mp + Q;
+  double* s_g = s_beta + Q;
+  double* s_misc = s_g + NB;
+  double* s_f = reinterpret_cast<double*>(smem + L.fvec);
+  double* G = reinterpret_cast<double*>(smem + L.G);
+  double* V = reinterpret_cast<double*>(smem + L.V);
+  double* G0 = reinterpret_cast<double*>(smem + L.G0);
+  double* cs = reinterpret_cast<double*>(smem + L.cs);    // K+2 rotation scratch
+  double* bvec = cs + K + 2;                               // K
+  double* rr = bvec + K;                                   // K
+  double* xr = rr + K;                                     // K (+ few)
+  double* SD = reinterpret_cast<double*>(smem + L.solve);  // Q
+  int* flag = reinterpret_cast<int*>(smem + L.seg);
+  const double* S2 = s_acc;
+  const double* BY = s_acc + Q * (Q + 1) / 2;
+  const double* CD = s_acc + NA1PAD;
+  const double* D1 = CD + Q;
+  const double* D2 = D1 + Q;
+#define BW(b) s_bucket[(b)*BV + 0]
+#define BWY(b) s_bucket[(b)*BV + 1]
+#define BC(b) s_bucket[(b)*BV + 2]
+#define BD(b, q) s_bucket[(b)*BV + 3 + (q)]
+  if (tid < 32) {
+    double sw = 0, capall = 0, bc = 0;
+    for (int b = lane; b < NB; b += 32) { sw += BW(b); capall += BC(b); bc += BWY(b); }
+    sw = warp_sum(sw); capall = warp_sum(capall); bc = warp_sum(bc);
+    const double dn = (double)n_rows;
+    double sigma = 1.0;
+    if (Q > 0) {
+      if (lane < Q) {
+        s_mp[lane] = CD[lane] / capall;
+        double sd = 0;
+        for (int b = 0; b < NB; ++b) sd += BD(b, lane);
+        SD[lane] = sd;
+      }
+      const double v = lane < Q ? D1[lane] + dn * s_piv[lane] : 0.0;
+      const double mu = warp_sum(v) / (dn * Q);
+      double t2 = 0.0;
+      if (lane < Q) {
+        const double dq = s_piv[lane] - mu;
+        t2 = D2[lane] + 2.0 * dq * D1[lane] + dn * dq * dq;
+      }
+      sigma = sqrt(warp_sum(t2) / (dn * Q));
+    }
+    if (lane == 0) { s_misc[2] = sigma; s_misc[3] = sw; s_misc[4] = bc; }
+  }
+  __syncthreads();
+  const double sigma = s_misc[2], sw = s_misc[3], bc = s_misc[4];
+  const double is = 1.0 / sigma;
+  for (int e = tid; e < K * K; e += nt) {
+    int i = e / K, j = e - i * K;
+    if (i > j) { const int tt = i; i = j; j = tt; }
+    double v;
+    if (i == 0) {
+      if (j == 0) v = sw;
+      else if (j <= P) v = BW(j - 1);
+      else { const int q = j - 1 - P; v = (SD[q] - s_mp[q] * sw) * is; }
+    } else if (i <= P) {
+      if (j <= P) v = (i == j) ? BW(i - 1) : 0.0;
+      else { const int q = j - 1 - P; v = (BD(i - 1, q) - s_mp[q] * BW(i - 1)) * is; }
+    } else {
+      const int q = i - 1 - P, r = j - 1 - P;   // q <= r
+      v = (S2[r * (r + 1) / 2 + q] - s_mp[q] * SD[r] - s_mp[r] * SD[q] + s_mp[q] * s_mp[r] * sw) * is * is;
+    }
+    const int ii = e / K, jj = e - ii * K;
+    G[ii * ld + jj] = v;
+    G0[ii * ld + jj] = v;
+  }
+  for (int k = tid; k < K; k += nt) {
+    double v;
+    if (k == 0) v = bc;
+    else if (k <= P) v = BWY(k - 1);
+    else { const int q = k - 1 - P; v = (BY[q] - s_mp[q] * bc) * is; }
+    bvec[k] = v;
+    rr[k] = (k >= 1 && k < P) ? BC(k - 1) / BC(P - 1) : 0.0;
+  }
+  __syncthreads();
+  int n = K;
+  double* A = G;
+  double* EV = V;
+  if (P > 0) {
+    n = K - 1;
+    // G R : columns 1..P-1 -= rr * column P
+    for (int e = tid; e < K * (P - 1); e += nt) {
+      const int i = e / (P - 1), c = 1 + e % (P - 1);
+      G[i * ld + c] = fma(-rr[c], G[i * ld + P], G[i * ld + c]);
+    }
+    __syncthreads();
+    // R' (G R): rows 1..P-1 -= rr * row P ; same for b
+    for (int e = tid; e < K * (P - 1); e += nt) {
+      const int j = e / (P - 1), c = 1 + e % (P - 1);
+      G[c * ld + j] = fma(-rr[c], G[P * ld + j], G[c * ld + j]);
+    }
+    if (tid >= 1 && tid < P) bvec[tid] = fma(-rr[tid], bvec[P], bvec[tid]);
+    for (int c = P + nt; c < P; c += nt) {}   // (P-1 <= 63 < blockDim)
+    __syncthreads();
+    // drop row/column P -> compact into V's storage
+    for (int e = tid; e < n * n; e += nt) {
+      const int i = e / n, j = e - i * n;
+      V[i * ld + j] = G[(i < P ? i : i + 1) * ld + (j < P ? j : j + 1)];
+    }
+    if (tid < n) xr[tid] = bvec[tid < P ? tid : tid + 1];
+    __syncthreads();
+    if (tid < n) bvec[tid] = xr[tid];
+    A = V;
+    EV = G;
+    __syncthreads();
+  }
+  // non-finite Gram: numpy's SVD raises LinAlgError
+  if (tid == 0) flag[4] = 0;
+  __syncthreads();
+  {
+    int bad = 0;
+    for (int e = tid; e < n * n; e += nt) bad |= !isfinite(A[(e / n) * ld + e % n]);
+    for (int k = tid; k < n; k += nt) bad |= !isfinite(bvec[k]);
+    if (bad) flag[4] = 1;
+  }
+  __syncthreads();
+  if (flag[4]) return BMFM_ST_NONFINITE;
+
+  jacobi_eig_cta(A, EV, n, ld, cs, flag);
+  __syncthreads();
+  // pinv: keep |lambda| > 1e-15 * max|lambda|
+  double* lam = cs;            // n  (rotation scratch is free now)
+  double* coef = rr;           // reuse after saving ratios
+  double* ratio = xr + K;      // not available -> keep ratios in registers instead
+  (void)ratio;
+  double myratio = 0.0;
+  if (tid >= 1 && tid < P) myratio = rr[tid];
+  __syncthreads();
+  if (tid < n) lam[tid] = A[tid * ld + tid];
+  __syncthreads();
+  double mx = 0.0;
+  for (int k = 0; k < n; ++k) mx = fmax(mx, fabs(lam[k]));
+  const double cutoff = 1e-15 * mx;
+  int dropped = 0;
+  for (int k = 0; k < n; ++k) dropped |= !(fabs(lam[k]) > cutoff);
+  if (tid < n) {
+    double dot = 0.0;
+    for (int j = 0; j < n; ++j) dot = fma(EV[j * ld + tid], bvec[j], dot);
+    coef[tid] = (fabs(lam[tid]) > cutoff) ? dot / lam[tid] : 0.0;
+  }
+  __syncthreads();
+  if (tid < n) {
+    double x = 0.0;
+    for (int k = 0; k < n; ++k) x = fma(EV[tid * ld + k], coef[k], x);
+    xr[tid] = x;
+  }
+  __syncthreads();
+  // f = R x
+  if (tid < K) {
+    double f;
+    if (P == 0) f = xr[tid];
+    else if (tid < P) f = xr[tid];
+    else if (tid > P) f = xr[tid - 1];
+    else f = 0.0;
+    s_f[tid] = f;
+  }
+  // the ratios were overwritten by coef: recompute the constrained entry from registers
+  if (P > 0) {
+    double part = (tid >= 1 && tid < P) ? -myratio * xr[tid] : 0.0;
+    part = warp_sum(part);
+    double* s_red = reinterpret_cast<double*>(smem + L.red);
+    if (lane == 0) s_red[tid >> 5] = part;
+    __syncthreads();
+    if (tid == 0) {
+      double s = 0.0;
+      for (int w = 0; w < (nt >> 5); ++w) s += s_red[w];
+      s_f[P] = s;
+    }
+  }
+  __syncthreads();
+
+  if (p.exposure != nullptr) {
+    // exposure = R pinv(R'GR) R' G   (CrossSection.py:104; weight normalisation cancels)
+    double* s_red = reinterpret_cast<double*>(smem + L.red);
+    (void)s_red;
+    // restore ratios
+    if (tid >= 1 && tid < P) rr[tid] = myratio;
+    if (tid == 0 || tid >= P) { if (tid < K) rr[tid] = 0.0; }
+    __syncthreads();
+    // M1 = R' G0 : rows 1..P-1 -= ratio * row P (row P then ignored)
+    if (P > 0) {
+      for (int e = tid; e < K * (P - 1); e += nt) {
+        const int j = e / (P - 1), c = 1 + e % (P - 1);
+        G0[c * ld + j] = fma(-rr[c], G0[P * ld + j], G0[c * ld + j]);
+      }
+    }
+    __syncthreads();
+    // Ginv = EV diag(inv) EV'  -> A's storage
+    for (int e = tid; e < n * n; e += nt) {
+      const int i = e / n, j = e - i * n;
+      double s = 0.0;
+      for (int k = 0; k < n; ++k) {
+        const double inv = (fabs(lam[k]) > cutoff) ? 1.0 / lam[k] : 0.0;
+        s = fma(EV[i * ld + k] * inv, EV[j * ld + k], s);
+      }
+      A[i * ld + j] = s;
+    }
+    __syncthreads();
+    // M2 = Ginv M1 (n x K) -> EV's storage
+    for (int e = tid; e < n * K; e += nt) {
+      const int i = e / K, j = e - i * K;
+      double s = 0.0;
+      for (int k = 0; k < n; ++k) s = fma(A[i * ld + k], G0[((P > 0 && k >= P) ? k + 1 : k) * ld + j], s);
+      EV[i * ld + j] = s;
+    }
+    __syncthreads();
+    double* out = p.exposure + (size_t)t * K * K;
+    for (int e = tid; e < K * K; e += nt) {
+      const int i = e / K, j = e - i * K;
+      double v;
+      if (P == 0 || i < P) v = EV[i * ld + j];
+      else if (i > P) v = EV[(i - 1) * ld + j];
+      else {
+        v = 0.0;
+        for (int c = 1; c < P; ++c) v = fma(-rr[c], EV[c * ld + j], v);
+      }
+      out[e] = v;
+    }
+    __syncthreads();
+  }
+  // coefficients for pass C
+  if (tid < Q) s_beta[tid] = s_f[1 + P + tid] * is;
+  for (int b = tid; b < NB; b += nt) s_g[b] = b < P ? s_f[1 + b] : 0.0;
+  __syncthreads();
+  if (tid == 0) {
+    double c0 = s_f[0];
+    for (int q = 0; q < Q; ++q) c0 -= s_beta[q] * s_mp[q];
+    s_misc[1] = c0;
+  }
+  int bad = 0;
+  for (int k = tid; k < K; k += nt) bad |= !isfinite(s_f[k]);
+  bad = __syncthreads_or(bad);
+#undef BW
+#undef BWY
+#undef BC
+#undef BD
+  if (bad) return BMFM_ST_NONFINITE;
+  return dropped ? BMFM_ST_PINV : BMFM_ST_OK;
+}
+
+// ---- kernels ---------------------------------------------------------------------------------
+__device__ __forceinline__ void write_nan_outputs(const RegParams& p, long long a, int n, int t) {
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = nan;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) p.spec[a + i] = nan;
+  if (threadIdx.x == 0) p.r2[t] = nan;
+}
+
+template <int Q>
+__global__ void __launch_bounds__(256) reg_fast_kernel(RegParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const RegSmem L = reg_smem_layout(p.tile_rows, p.P, Q, blockDim.x >> 5, false);
+  int* s_flag = reinterpret_cast<int*>(smem + L.seg) + 3 * (p.P + 1) + 2;
+  const double* s_f = reinterpret_cast<const double*>(smem + L.fvec);
+  for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    if (n <= 0) {
+      write_nan_outputs(p, a, 0, t);
+      if (threadIdx.x == 0) p.status[t] = BMFM_ST_NONFINITE;
+      continue;
+    }
+    int ntiles;
+    accumulate_date<Q>(p, L, smem, a, n, ntiles);
+    if (threadIdx.x < 32) {
+      const int st = solve_fast_warp0<Q>(p, L, smem, n);
+      if (threadIdx.x == 0) *s_flag = st;
+    }
+    __syncthreads();
+    const int st = *s_flag;
+    if (st == BMFM_ST_OK) {
+      for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = s_f[k];
+      residual_date<Q>(p, L, smem, a, n, ntiles, t);
+      if (threadIdx.x == 0) p.status[t] = BMFM_ST_OK;
+    } else if (st == REG_NEED_DENSE) {
+      if (threadIdx.x == 0) p.status[t] = REG_NEED_DENSE;
+    } else {
+      write_nan_outputs(p, a, n, t);
+      if (threadIdx.x == 0) p.status[t] = st;
+    }
+    __syncthreads();
+  }
+}
+
+template <int Q>
+__global__ void __launch_bounds__(256) reg_dense_kernel(RegParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const RegSmem L = reg_smem_layout(p.tile_rows, p.P, Q, blockDim.x >> 5, true);
+  const double* s_f = reinterpret_cast<const double*>(smem + L.fvec);
+  for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
+    if (!p.all_dense && p.status[t] != REG_NEED_DENSE) continue;
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    if (n <= 0) {
+      write_nan_outputs(p, a, 0, t);
+      if (threadIdx.x == 0) p.status[t] = BMFM_ST_NONFINITE;
+      continue;
+    }
+    int ntiles;
+    accumulate_date<Q>(p, L, smem, a, n, ntiles);
+    const int st = solve_dense_cta<Q>(p, L, smem, n, t);
+    if (st == BMFM_ST_NONFINITE) {
+      write_nan_outputs(p, a, n, t);
+    } else {
+      for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = s_f[k];
+      residual_date<Q>(p, L, smem, a, n, ntiles, t);
+    }
+    if (threadIdx.x == 0) p.status[t] = st;
+    __syncthreads();
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+template <int Q>
+static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
+  const int SMEM_MAX = ctx->max_smem_optin;           // 227 KB on B200
+  const int SM_TOTAL = 228 * 1024;
+  // fast kernel: size the tile so a whole date stays resident; more CTAs/SM for small dates
+  int rows = max_rows > 0 ? (max_rows + 31) / 32 * 32 : 1024;
+  int nthreads = rows <= 1536 ? 128 : 256;
+  RegSmem L = reg_smem_layout(rows, p.P, Q, nthreads / 32, false);
+  if (L.total > SMEM_MAX) {
+    // a date does not fit one CTA: stream it in tiles (pass C re-reads all but the last)
+    nthreads = 256;
+    const int fixed = reg_smem_layout(0, p.P, Q, nthreads / 32, false).total;
+    rows = (SMEM_MAX - fixed - 64) / (Q * 8 + 28) / 32 * 32;
+    L = reg_smem_layout(rows, p.P, Q, nthreads / 32, false);
+  }
+  int per_sm = SM_TOTAL / (L.total + 1024);
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  p.tile_rows = rows;
+  if (!p.all_dense) {
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_fast_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    int grid = ctx->sm_count * per_sm;
+    if (grid > p.T) grid = p.T;
+    reg_fast_kernel<Q><<<grid, nthreads, L.total, ctx->stream>>>(p);
+    ctx->launches++;
+    BMFM_CUDA(ctx, cudaGetLastError());
+  }
+  // dense kernel: flagged dates only (or all when the exposure matrix is wanted)
+  {
+    const int nthreads_d = 256;
+    const int fixed = reg_smem_layout(0, p.P, Q, nthreads_d / 32, true).total;
+    int rows_d = (SMEM_MAX - fixed - 64) / (Q * 8 + 28) / 32 * 32;
+    if (rows_d < 32) {
+      snprintf(ctx->err, sizeof(ctx->err), "K=%d too large for the dense path", p.K);
+      return BMFM_E_UNSUPPORTED;
+    }
+    if (max_rows > 0 && rows_d > (max_rows + 31) / 32 * 32) rows_d = (max_rows + 31) / 32 * 32;
+    RegSmem Ld = reg_smem_layout(rows_d, p.P, Q, nthreads_d / 32, true);
+    RegParams pd = p;
+    pd.tile_rows = rows_d;
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_dense_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, Ld.total));
+    int grid = ctx->sm_count;
+    if (grid > p.T) grid = p.T;
+    reg_dense_kernel<Q><<<grid, nthreads_d, Ld.total, ctx->stream>>>(pd);
+    ctx->launches++;
+    BMFM_CUDA(ctx, cudaGetLastError());
+  }
+  return BMFM_OK;
+}
+
+}  // namespace bmfm
+
+using namespace bmfm;
+
+extern "C" void bmfm_limits(int* max_Q, int* max_P, int* max_K) {
+  if (max_Q) *max_Q = REG_MAX_Q;
+  if (max_P) *max_P = REG_MAX_P;
+  if (max_K) *max_K = 1 + REG_MAX_P + REG_MAX_Q;
+}
+
+extern "C" int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                                const int64_t* date_off, const double* cap, const double* ret,
+                                const int32_t* ind, const double* style,
+                                double* factor_ret, double* specific_ret, double* r2,
+                                double* exposure, int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && P >= 0 && Q >= 0, "T, P, Q must be non-negative");
+  BMFM_ARG(ctx, date_off && cap && ret && ind && (style || Q == 0), "NULL input");
+  BMFM_ARG(ctx, factor_ret && specific_ret && r2 && status, "NULL output");
+  if (Q > REG_MAX_Q || P > REG_MAX_P) {
+    snprintf(ctx->err, sizeof(ctx->err), "P=%d Q=%d outside compiled limits (P<=%d, Q<=%d)", P, Q, REG_MAX_P, REG_MAX_Q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  RegParams p;
+  p.T = T; p.P = P; p.Q = Q; p.K = 1 + P + Q;
+  p.date_off = reinterpret_cast<const long long*>(date_off);
+  p.cap = cap; p.ret = ret; p.ind = ind; p.style = style;
+  p.factor_ret = factor_ret; p.spec = specific_ret; p.r2 = r2; p.exposure = exposure; p.status = status;
+  p.tile_rows = 0;
+  p.all_dense = exposure != nullptr;
+  switch (Q) {
+#define CASE(q) case q: return launch_reg<q>(ctx, p, max_rows_per_date);
+    CASE(0) CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8) CASE(9) CASE(10) CASE(11) CASE(12)
+#undef CASE
+  }
+  return BMFM_E_UNSUPPORTED;
+}

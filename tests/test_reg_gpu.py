@@ -1,0 +1,160 @@
+"""GPU parity of the regression kernel (through the C-ABI) against
+(1) outputs of the unmodified reference (tests/golden/reg.npz) and
+(2) the CPU oracle on seeded panels, plus size-independent properties."""
+import os
+
+import numpy as np
+import pytest
+
+from util import relerr
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-9   # north_star: <= 1e-9 relative, fp64
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from bmfm import ops
+    return ops
+
+
+@pytest.fixture(scope="module")
+def reg_golden(golden_dir):
+    return np.load(os.path.join(golden_dir, "reg.npz"))
+
+
+def _case(reg, case):
+    return {k.split("__", 1)[1]: reg[k] for k in reg.files if k.startswith(case + "__")}
+
+
+@pytest.mark.parametrize("case", ["small", "csi", "nostyle_scale"])
+@pytest.mark.parametrize("grouped", [True, False])
+def test_golden_reference_outputs(ops, reg_golden, case, grouped):
+    g = _case(reg_golden, case)
+    fr, spec, r2, status, _ = ops.reg_by_time(g["date_off"], g["cap"], g["ret"], g["ind"], g["style"],
+                                              int(g["P"]), group_by_industry=grouped)
+    assert relerr(fr, g["factor_ret"]) < TOL
+    assert relerr(spec, g["specific_ret"], scale=np.max(np.abs(g["ret"]))) < TOL
+    assert np.max(np.abs(r2 - g["R2"])) < TOL
+
+
+def test_golden_rank_deficient_pinv(ops, reg_golden):
+    """N < K: the reference's pinv picks the minimum-norm solution (R2 = 1)."""
+    g = _case(reg_golden, "n_lt_k")
+    fr, spec, r2, status, _ = ops.reg_by_time(g["date_off"], g["cap"], g["ret"], g["ind"], g["style"], int(g["P"]))
+    assert (status == 4).all()          # BMFM_ST_PINV: the eigen/pinv path was taken
+    assert relerr(fr, g["factor_ret"]) < 1e-6
+    assert relerr(spec, g["specific_ret"], scale=np.max(np.abs(g["ret"]))) < 1e-6
+    assert np.max(np.abs(r2 - g["R2"])) < 1e-6
+
+
+@pytest.mark.parametrize("case", ["small", "csi"])
+def test_golden_exposure(ops, reg_golden, case):
+    g = _case(reg_golden, case)
+    a, b = int(g["date_off"][0]), int(g["date_off"][1])
+    off = np.array([0, b - a], dtype=np.int64)
+    fr, spec, r2, status, expo = ops.reg_by_time(off, g["cap"][a:b], g["ret"][a:b], g["ind"][a:b],
+                                                 g["style"][a:b], int(g["P"]), want_exposure=True)
+    assert relerr(expo[0], g["exposure0"]) < 1e-8
+    assert relerr(fr[0], g["factor_ret"][0]) < TOL
+
+
+@pytest.mark.parametrize("T,N,P,Q,ragged,scale", [
+    (12, 300, 31, 10, 0.05, (-2, 2)),     # CSI300-like, un-standardised column scales
+    (6, 800, 31, 10, 0.0, (-1, 1)),       # CSI800 cross-sections (config C2)
+    (5, 97, 7, 3, 0.2, (-1, 1)),
+    (4, 64, 0, 5, 0.0, (-1, 1)),          # P = 0 branch (CrossSection.py:95-98)
+    (3, 70, 63, 12, 0.0, (0, 0)),         # compiled limits; N < K -> pinv path
+    (2, 5000, 31, 10, 0.02, (-2, 2)),     # full A-share cross-section (config C3): multi-tile path
+])
+def test_oracle_parity(ops, T, N, P, Q, ragged, scale):
+    from bmfm.synth import make_panel
+    from oracle import barra_oracle as orc
+    pan = make_panel(T, N, P, Q, seed=100 + N, ragged=ragged, scale_log10=scale)
+    csr = pan.to_csr()
+    ind = csr["ind"].copy()
+    if P > 0:
+        ind[5::37] = -1            # some rows with no industry column set
+    want_fr, want_spec, want_r2 = orc.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], ind, csr["style"], P)
+    fr, spec, r2, status, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], ind, csr["style"], P)
+    tol = 1e-6 if N < 1 + P + Q else TOL
+    assert relerr(fr, want_fr) < tol
+    assert relerr(spec, want_spec, scale=np.max(np.abs(csr["ret"]))) < tol
+    assert np.max(np.abs(r2 - want_r2)) < tol
+
+
+def test_host_buffer_entry_point(ops):
+    """bmfm_reg_by_time_host: host pointers in/out (the e2e path of bench.py)."""
+    from bmfm import _cabi
+    from bmfm.synth import make_panel
+    pan = make_panel(5, 200, 31, 10, seed=7)
+    csr = pan.to_csr()
+    T, K = pan.T, 1 + pan.P + pan.Q
+    fr = np.empty((T, K)); spec = np.empty(len(csr["cap"])); r2 = np.empty(T)
+    st = np.empty(T, dtype=np.int32)
+    ctx = _cabi.default_context()
+    ctx.reg_by_time_host(T, pan.P, pan.Q, csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"],
+                         fr, spec, r2, st)
+    fr2, spec2, r22, _, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P,
+                                            group_by_industry=False)
+    assert np.array_equal(fr, fr2) and np.array_equal(spec, spec2) and np.array_equal(r2, r22)
+
+
+def test_last_industry_empty_raises(ops):
+    """-cap/0 in the constraint row (CrossSection.py:70): numpy's pinv raises LinAlgError."""
+    from bmfm.synth import make_panel
+    pan = make_panel(2, 60, 5, 3, seed=3)
+    csr = pan.to_csr()
+    ind = csr["ind"].copy()
+    ind[ind == 4] = 0
+    with pytest.raises(np.linalg.LinAlgError):
+        ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], ind, csr["style"], pan.P)
+
+
+def test_properties_full_size(ops):
+    """Config-C3-sized cross-sections: properties that need no oracle run.
+    (a) the cap-weighted industry returns sum to zero (the constraint of CrossSection.py:66-71);
+    (b) the sqrt-cap weighted residual is orthogonal to country and every style column;
+    (c) regressing again on the residuals returns zero factor returns (idempotence)."""
+    from bmfm.synth import make_panel
+    pan = make_panel(8, 5000, 31, 10, seed=20240003, scale_log10=(-1, 1))
+    csr = pan.to_csr()
+    P, Q = pan.P, pan.Q
+    fr, spec, r2, status, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P)
+    assert (status == 0).all()
+    off = csr["date_off"]
+    for t in range(pan.T):
+        a, b = off[t], off[t + 1]
+        cap = csr["cap"][a:b]
+        indcap = np.bincount(csr["ind"][a:b], cap, P)
+        assert abs(indcap @ fr[t, 1:1 + P]) < 1e-12 * indcap.sum() * np.abs(fr[t]).max()
+        w = np.sqrt(cap)
+        e = spec[a:b]
+        scale = (w * np.abs(csr["ret"][a:b])).sum()
+        assert abs((w * e).sum()) < 1e-10 * scale
+        s = csr["style"][a:b]
+        sc = s - s.mean(0)
+        assert np.max(np.abs((w * e) @ sc) / (np.abs(sc).max(0) * scale)) < 1e-9
+    fr2, spec2, _, _, _ = ops.reg_by_time(off, csr["cap"], spec, csr["ind"], csr["style"], P)
+    assert np.max(np.abs(fr2)) < 1e-9 * np.max(np.abs(fr))
+    assert relerr(spec2, spec) < 1e-9
+
+
+def test_mfm_dropin_reg_by_time(golden_dir):
+    """The drop-in MFM class on the DataFrame demo.py builds (MFM.py:28-76)."""
+    import contextlib, io
+    from bmfm.synth import make_panel
+    from mfm.MFM import MFM
+    g = np.load(os.path.join(golden_dir, "pipeline.npz"))
+    pan = make_panel(T=90, N=48, P=4, Q=3, seed=41, ragged=0.05, scale_log10=(-1, 1))
+    df = pan.to_frame(shuffle_seed=3)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = MFM(df, pan.P, pan.Q)
+        fr, spec, r2 = model.reg_by_time()
+    assert list(fr.columns) == ['country'] + pan.industry_names + pan.style_names
+    assert relerr(fr.values, g["factor_ret"]) < TOL
+    assert relerr(np.concatenate([s.values[0] for s in spec]), g["specific_ret"]) < TOL
+    assert np.max(np.abs(r2.values[:, 0] - g["R2"])) < TOL
+    assert relerr(np.asarray(model.last_capital), g["last_capital"]) == 0.0
+    assert list(spec[0].columns) == sorted(spec[0].columns)
