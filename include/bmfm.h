@@ -97,6 +97,52 @@ int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
                           double* factor_ret, double* specific_ret, double* r2,
                           double* exposure, int32_t* status);
 
+/* ---- part 3: risk-model adjustments -------------------------------------- */
+/*
+ * Replaces MFM.Newey_West_by_time (Barra-master/mfm/MFM.py:80-101) = utils.Newey_West
+ * (Barra-master/mfm/utils.py:16-50) on every expanding window factor_ret[:t], t = 1..T.
+ *   factor_ret double [T * K];  cov double [T * K * K] (NaN-filled where status != 0)
+ *   status int32 [T]: BMFM_ST_SHORT where the reference raises (t <= q or t <= K, utils.py:29)
+ * q <= 4.  Uses bmfm_newey_west_scratch_bytes(T, K, q) bytes of context workspace.
+ */
+int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                            const double* factor_ret, double* cov, int32_t* status);
+size_t bmfm_newey_west_scratch_bytes(int T, int K, int q);
+
+/*
+ * Replaces MFM.vol_regime_adj_by_time (Barra-master/mfm/MFM.py:130-167).
+ *   cov [T*K*K] with cov_status [T] (NULL = all valid; dates with status != 0/4 are the
+ *   reference's empty DataFrames); out_cov [T*K*K] = cov * lamb^2 (NaN where invalid; may be
+ *   NULL to get lamb only); lamb [T] (the factor volatility multiplier, MFM.py:160).
+ */
+int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double tao, const double* factor_ret,
+                                const double* cov, const int32_t* cov_status, double* out_cov,
+                                double* lamb);
+
+/*
+ * Eigenfactor Monte-Carlo adjustment, utils.eigen_risk_adj (Barra-master/mfm/utils.py:55-92)
+ * for every date, MFM.eigen_risk_adj_by_time (Barra-master/mfm/MFM.py:105-126), in four steps
+ * so that simulations can be sharded across GPUs (the caller all-reduces vsum):
+ *
+ * bmfm_gauss_cov: C[j] = np.cov(z.T) of z = RandomState(m0+j+1).standard_normal((T_sim, K)),
+ *   j < nsim — the legacy stream np.random.seed(m+1) + multivariate_normal draws from
+ *   (utils.py:73-76).  C double [nsim * K * K].
+ * bmfm_eigen_decompose: D0 [T*K] (descending), U0 [T*K*K] (columns, canonical sign) of every
+ *   valid covariance (utils.py:64); status: input status passed through, BMFM_ST_NOT_PSD
+ *   where an eigenvalue is negative (utils.py:67-68), BMFM_ST_NONFINITE for NaN input.
+ * bmfm_eigen_mc_accumulate: vsum[T*K] (+)= sum over the nsim simulations in C of
+ *   diag(Um' F0 Um) / Dm in descending-eigenvalue position (utils.py:79-84).
+ * bmfm_eigen_finalize: v = c (sqrt(vsum / M) - 1) + 1; out = U0 diag(v^2 D0) U0' (utils.py:86-92),
+ *   NaN-filled where status != 0.
+ */
+int bmfm_gauss_cov(bmfm_ctx* ctx, int m0, int nsim, int T_sim, int K, double* C);
+int bmfm_eigen_decompose(bmfm_ctx* ctx, int T, int K, const double* cov, const int32_t* cov_status,
+                         double* D0, double* U0, int32_t* status);
+int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0,
+                             const int32_t* status, double* vsum, int accumulate);
+int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double scale_coef, const double* D0,
+                        const double* U0, const double* vsum, const int32_t* status, double* out);
+
 #ifdef __cplusplus
 }
 #endif

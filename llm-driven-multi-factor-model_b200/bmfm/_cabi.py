@@ -33,6 +33,13 @@ _SIGNATURES = {
     "bmfm_version": ([], C.c_char_p),
     "bmfm_reg_by_time": ([_P, _I, _I, _I, _I] + [_P] * 10, _I),
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
+    "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
+    "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
+    "bmfm_vol_regime_adj_by_time": ([_P, _I, _I, _D, _P, _P, _P, _P, _P], _I),
+    "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
+    "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
+    "bmfm_eigen_mc_accumulate": ([_P, _I, _I, _I, _P, _P, _P, _P, _I], _I),
+    "bmfm_eigen_finalize": ([_P, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
 }
 
 
@@ -132,6 +139,30 @@ class Context:
         self.check(self._L.bmfm_reg_by_time_host(self._h, T, P, Q, ptr(date_off), ptr(cap), ptr(ret),
                                                  ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
                                                  ptr(exposure), ptr(status)))
+
+
+    # ------------------------------------------------------------------ part 3
+    def newey_west_by_time(self, T, K, q, tao, fr, cov, status):
+        self.check(self._L.bmfm_newey_west_by_time(self._h, T, K, q, float(tao), ptr(fr), ptr(cov), ptr(status)))
+
+    def vol_regime_adj_by_time(self, T, K, tao, fr, cov, cov_status, out_cov, lamb):
+        self.check(self._L.bmfm_vol_regime_adj_by_time(self._h, T, K, float(tao), ptr(fr), ptr(cov),
+                                                       ptr(cov_status), ptr(out_cov), ptr(lamb)))
+
+    def gauss_cov(self, m0, nsim, T_sim, K, Cmat):
+        self.check(self._L.bmfm_gauss_cov(self._h, m0, nsim, T_sim, K, ptr(Cmat)))
+
+    def eigen_decompose(self, T, K, cov, cov_status, D0, U0, status):
+        self.check(self._L.bmfm_eigen_decompose(self._h, T, K, ptr(cov), ptr(cov_status), ptr(D0), ptr(U0),
+                                                ptr(status)))
+
+    def eigen_mc_accumulate(self, T, K, nsim, Cmat, D0, status, vsum, accumulate=False):
+        self.check(self._L.bmfm_eigen_mc_accumulate(self._h, T, K, nsim, ptr(Cmat), ptr(D0), ptr(status),
+                                                    ptr(vsum), int(bool(accumulate))))
+
+    def eigen_finalize(self, T, K, M, scale_coef, D0, U0, vsum, status, out):
+        self.check(self._L.bmfm_eigen_finalize(self._h, T, K, M, float(scale_coef), ptr(D0), ptr(U0), ptr(vsum),
+                                               ptr(status), ptr(out)))
 
 
 _default_ctx = {}

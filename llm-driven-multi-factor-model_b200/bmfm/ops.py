@@ -64,3 +64,91 @@ def reg_by_time(date_off, cap, ret, ind, style, P, want_exposure=False, group_by
     spec = spec.cpu().numpy()[pos]
     return (fr.cpu().numpy(), spec, r2.cpu().numpy(), status,
             expo.cpu().numpy() if expo is not None else None)
+
+
+# ---------------------------------------------------------------------------- part 3
+_VALID = (_cabi.ST_OK, _cabi.ST_PINV)
+
+
+def newey_west_by_time_device(ctx, d_fr, q, tao):
+    """d_fr [T,K] device -> (cov [T,K,K] device (NaN where invalid), status [T] device)."""
+    torch = _torch()
+    T, K = d_fr.shape
+    cov = torch.empty((T, K, K), dtype=torch.float64, device=d_fr.device)
+    status = torch.empty(T, dtype=torch.int32, device=d_fr.device)
+    ctx.newey_west_by_time(T, K, int(q), tao, d_fr, cov, status)
+    return cov, status
+
+
+def newey_west_by_time(factor_ret, q=2, tao=252, ctx=None):
+    """MFM.Newey_West_by_time on a [T,K] array -> (cov [T,K,K], status [T])."""
+    ctx = ctx or _cabi.default_context()
+    cov, status = newey_west_by_time_device(ctx, _dev(np.asarray(factor_ret, dtype=np.float64)), q, tao)
+    return cov.cpu().numpy(), status.cpu().numpy()
+
+
+def vol_regime_device(ctx, d_fr, d_cov, d_status, tao):
+    torch = _torch()
+    T, K = d_fr.shape
+    out = torch.empty_like(d_cov)
+    lamb = torch.empty(T, dtype=torch.float64, device=d_fr.device)
+    ctx.vol_regime_adj_by_time(T, K, tao, d_fr, d_cov, d_status, out, lamb)
+    return out, lamb
+
+
+def vol_regime_adj_by_time(factor_ret, cov, cov_status=None, tao=84, ctx=None):
+    ctx = ctx or _cabi.default_context()
+    d_st = _dev(np.asarray(cov_status, dtype=np.int32)) if cov_status is not None else None
+    out, lamb = vol_regime_device(ctx, _dev(np.asarray(factor_ret, dtype=np.float64)),
+                                  _dev(np.asarray(cov, dtype=np.float64)), d_st, tao)
+    return out.cpu().numpy(), lamb.cpu().numpy()
+
+
+_gauss_cache = {}
+
+
+def gauss_cov_device(ctx, m0, nsim, T_sim, K):
+    """cov(z_m) for simulations m0 .. m0+nsim-1 (seeds m+1), cached per device:
+    the reference re-seeds with m+1 for EVERY date (utils.py:73), so these K x K
+    sample covariances are shared by all dates."""
+    torch = _torch()
+    key = (ctx.device, m0, nsim, T_sim, K)
+    if key not in _gauss_cache:
+        if len(_gauss_cache) > 4:
+            _gauss_cache.clear()
+        Cm = torch.empty((nsim, K, K), dtype=torch.float64, device=f"cuda:{ctx.device}")
+        ctx.gauss_cov(m0, nsim, T_sim, K, Cm)
+        _gauss_cache[key] = Cm
+    return _gauss_cache[key]
+
+
+def eigen_risk_adj_device(ctx, d_cov, d_cov_status, T_sim, M, scale_coef, sim_range=None, allreduce=None):
+    """Eigenfactor adjustment of every date's covariance.
+
+    ``sim_range=(m_lo, m_hi)`` restricts this process to a shard of the M
+    simulations; ``allreduce(tensor)`` (e.g. an NCCL all-reduce) then sums the
+    per-shard accumulators before the finalisation.  Returns (out [T,K,K], status [T])."""
+    torch = _torch()
+    T, K = d_cov.shape[0], d_cov.shape[1]
+    dev = d_cov.device
+    D0 = torch.empty((T, K), dtype=torch.float64, device=dev)
+    U0 = torch.empty((T, K, K), dtype=torch.float64, device=dev)
+    status = torch.empty(T, dtype=torch.int32, device=dev)
+    ctx.eigen_decompose(T, K, d_cov, d_cov_status, D0, U0, status)
+    m_lo, m_hi = (0, M) if sim_range is None else sim_range
+    vsum = torch.zeros((T, K), dtype=torch.float64, device=dev)
+    if m_hi > m_lo:
+        Cm = gauss_cov_device(ctx, m_lo, m_hi - m_lo, T_sim, K)
+        ctx.eigen_mc_accumulate(T, K, m_hi - m_lo, Cm, D0, status, vsum, False)
+    if allreduce is not None:
+        allreduce(vsum)
+    out = torch.empty((T, K, K), dtype=torch.float64, device=dev)
+    ctx.eigen_finalize(T, K, M, scale_coef, D0, U0, vsum, status, out)
+    return out, status
+
+
+def eigen_risk_adj_by_time(cov, cov_status, T_sim, M=100, scale_coef=1.4, ctx=None):
+    ctx = ctx or _cabi.default_context()
+    d_st = _dev(np.asarray(cov_status, dtype=np.int32)) if cov_status is not None else None
+    out, status = eigen_risk_adj_device(ctx, _dev(np.asarray(cov, dtype=np.float64)), d_st, T_sim, M, scale_coef)
+    return out.cpu().numpy(), status.cpu().numpy()

@@ -1,0 +1,359 @@
+// Eigenfactor Monte-Carlo risk adjustment for every date.
+//
+// Replaces  utils.eigen_risk_adj            Barra-master/mfm/utils.py:55-92
+//           MFM.eigen_risk_adj_by_time      Barra-master/mfm/MFM.py:105-126
+//
+// Reference, per date: D0,U0 = eig(F0); for m < M: seed(m+1); bm = mvn(0, diag(D0), T).T;
+// Fm = cov(U0 bm); Dm,Um = eig(Fm); v_m = diag(Um' F0 Um) / Dm; v = sqrt(mean_m v_m);
+// v = c (v - 1) + 1; F0_hat = U0 diag(v^2 D0) U0'.
+//
+// Restructured (same numbers):
+//  * the seeds do not depend on the date, and with D0 in descending order numpy's
+//    multivariate_normal reduces to bm[k] = sqrt(D0[k]) * z[:, k] with z the seeded legacy
+//    standard-normal stream, so  C_m = cov(z_m)  (K x K) is computed ONCE per simulation
+//    (gauss_cov kernels: MT19937 + Marsaglia polar, the legacy numpy stream);
+//  * Fm = U0 (D0^1/2 C_m D0^1/2) U0' is orthogonally similar to Mm = D0^1/2 C_m D0^1/2, so
+//    with Mm = W L W':  Dm = L  and  diag(Um' F0 Um) = diag(W' D0 W).  No K^3 product is
+//    needed to build the simulated covariance, and U0 only enters the final F0_hat;
+//  * eigenvalue order is the canonical one (descending, SURVEY.md §8(c) mode (ii)); the
+//    result does not depend on eigenvector signs.
+// The hot loop is T*M symmetric K x K eigendecompositions (Jacobi in shared memory, one
+// CTA per problem slot, seven slots per SM).  Simulations shard across GPUs: each rank
+// accumulates sum_m v_m for its simulations, the host all-reduces T*K doubles.
+#include <math.h>
+#include "bmfm_common.cuh"
+#include "jacobi.cuh"
+
+namespace bmfm {
+
+// ------------------------------------------------------------------------------------------
+// legacy numpy stream: MT19937 (init_genrand), 53-bit doubles, polar gauss (second value first)
+// ------------------------------------------------------------------------------------------
+struct Mt19937 {
+  uint32_t* mt;   // 624 words (thread-private)
+  int pos;
+  __device__ void seed(uint32_t s) {
+    mt[0] = s;
+    for (int i = 1; i < 624; ++i) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (uint32_t)i;
+    pos = 624;
+  }
+  __device__ void regen() {
+    for (int kk = 0; kk < 624; ++kk) {
+      const uint32_t y = (mt[kk] & 0x80000000u) | (mt[(kk + 1) % 624] & 0x7fffffffu);
+      mt[kk] = mt[(kk + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    }
+    pos = 0;
+  }
+  __device__ uint32_t u32() {
+    if (pos == 624) regen();
+    uint32_t y = mt[pos++];
+    y ^= y >> 11;
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= y >> 18;
+    return y;
+  }
+  __device__ double dbl() {
+    const uint32_t a = u32() >> 5, b = u32() >> 6;
+    return __dmul_rn(__dadd_rn(__dmul_rn((double)a, 67108864.0), (double)b), 1.0 / 9007199254740992.0);
+  }
+};
+
+// z[m][T][K] for a batch of simulations, one thread per simulation (the stream is serial)
+__global__ void gauss_fill_kernel(int m0, int nsim, int T, int K, uint32_t* mt_scratch, double* z) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nsim) return;
+  Mt19937 g;
+  g.mt = mt_scratch + (size_t)j * 624;
+  g.seed((uint32_t)(m0 + j + 1));   // np.random.seed(m+1), utils.py:73
+  double* out = z + (size_t)j * T * K;
+  const long long n = (long long)T * K;
+  long long i = 0;
+  while (i < n) {
+    double x1, x2, r2;
+    do {
+      x1 = __dadd_rn(__dmul_rn(2.0, g.dbl()), -1.0);
+      x2 = __dadd_rn(__dmul_rn(2.0, g.dbl()), -1.0);
+      r2 = __dadd_rn(__dmul_rn(x1, x1), __dmul_rn(x2, x2));
+    } while (r2 >= 1.0 || r2 == 0.0);
+    const double f = sqrt(__ddiv_rn(__dmul_rn(-2.0, log(r2)), r2));
+    out[i++] = __dmul_rn(f, x2);              // returned first
+    if (i < n) out[i++] = __dmul_rn(f, x1);   // the cached value
+  }
+}
+
+// C[m] = cov(z_m) with ddof 1 (np.cov, utils.py:76); one CTA per simulation
+__global__ void gauss_cov_kernel(int nsim, int T, int K, const double* z, double* C) {
+  extern __shared__ double s_mean[];
+  const int j = blockIdx.x;
+  if (j >= nsim) return;
+  const double* zz = z + (size_t)j * T * K;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    double s = 0.0;
+    for (int t = 0; t < T; ++t) s += zz[(size_t)t * K + k];
+    s_mean[k] = s / T;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < K * K; e += blockDim.x) {
+    const int a = e / K, b = e - a * K;
+    if (a > b) continue;
+    const double ma = s_mean[a], mb = s_mean[b];
+    double s = 0.0;
+    for (int t = 0; t < T; ++t) s = fma(zz[(size_t)t * K + a] - ma, zz[(size_t)t * K + b] - mb, s);
+    s /= (double)(T - 1);
+    C[(size_t)j * K * K + a * K + b] = s;
+    C[(size_t)j * K * K + b * K + a] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// E1: canonical eigendecomposition of every date's covariance (utils.py:64) + PSD gate (:67)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) eig_f0_kernel(int T, int K, const double* cov, const int* cov_status,
+                                                     double* D0, double* U0, int* status) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* A = reinterpret_cast<double*>(smem);
+  double* V = A + K * ld;
+  double* cs = V + K * ld;          // K + 2
+  double* lam = cs + K + 2;         // K
+  int* rank = reinterpret_cast<int*>(lam + K);   // K
+  int* flag = rank + K;             // 8
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const int st_in = cov_status ? cov_status[t] : BMFM_ST_OK;
+    if (st_in != BMFM_ST_OK && st_in != BMFM_ST_PINV) {
+      if (tid == 0) status[t] = st_in;
+      continue;
+    }
+    const double* F = cov + (size_t)t * K * K;
+    if (tid == 0) flag[4] = 0;
+    __syncthreads();
+    for (int e = tid; e < K * K; e += nt) {
+      const int a = e / K, b = e - a * K;
+      const double v = 0.5 * (F[a * K + b] + F[b * K + a]);
+      if (!isfinite(v)) flag[4] = 1;
+      A[a * ld + b] = v;
+    }
+    __syncthreads();
+    if (flag[4]) {   // NaN input: the reference's eig raises -> empty DataFrame
+      if (tid == 0) status[t] = BMFM_ST_NONFINITE;
+      __syncthreads();
+      continue;
+    }
+    jacobi_eig_cta(A, V, K, ld, cs, flag);
+    __syncthreads();
+    if (tid < K) lam[tid] = A[tid * ld + tid];
+    __syncthreads();
+    if (tid < K) {
+      const double me = lam[tid];
+      int r = 0;
+      for (int j = 0; j < K; ++j) r += (lam[j] > me) || (lam[j] == me && j < tid);
+      rank[tid] = r;       // descending order position
+      if (me < 0.0) flag[4] = 1;
+    }
+    __syncthreads();
+    if (tid < K) {
+      // canonical sign: the largest-|.| component (first on ties) is positive
+      double best = -1.0, sgn = 1.0;
+      for (int i = 0; i < K; ++i) {
+        const double v = V[i * ld + tid];
+        if (fabs(v) > best) { best = fabs(v); sgn = v < 0.0 ? -1.0 : 1.0; }
+      }
+      const int r = rank[tid];
+      D0[(size_t)t * K + r] = lam[tid];
+      for (int i = 0; i < K; ++i) U0[((size_t)t * K + i) * K + r] = sgn * V[i * ld + tid];
+    }
+    if (tid == 0) status[t] = flag[4] ? BMFM_ST_NOT_PSD : BMFM_ST_OK;
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// E2: the Monte-Carlo loop.  CTA = (date, block of simulations); partial[t][blk][k] = sum_m v_m[k]
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int nblk, const double* C,
+                                                     const double* D0, const int* status, double* partial) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* A = reinterpret_cast<double*>(smem);
+  double* V = A + K * ld;
+  double* cs = V + K * ld;          // K + 2
+  double* d0 = cs + K + 2;          // K
+  double* sd = d0 + K;              // K sqrt(D0)
+  double* lam = sd + K;             // K
+  double* vacc = lam + K;           // K
+  int* flag = reinterpret_cast<int*>(vacc + K);   // 8
+  const int per = (nsim + nblk - 1) / nblk;
+  for (int w = blockIdx.x; w < T * nblk; w += gridDim.x) {
+    const int t = w / nblk, blk = w - t * nblk;
+    double* out = partial + ((size_t)t * nblk + blk) * K;
+    if (status[t] != BMFM_ST_OK) {
+      for (int k = tid; k < K; k += nt) out[k] = 0.0;
+      continue;
+    }
+    const int m_lo = blk * per, m_hi = min(nsim, m_lo + per);
+    if (tid < K) {
+      const double d = D0[(size_t)t * K + tid];
+      d0[tid] = d;
+      sd[tid] = sqrt(d);
+      vacc[tid] = 0.0;
+    }
+    __syncthreads();
+    for (int m = m_lo; m < m_hi; ++m) {
+      const double* Cm = C + (size_t)m * K * K;
+      for (int e = tid; e < K * K; e += nt) {
+        const int a = e / K, b = e - a * K;
+        A[a * ld + b] = sd[a] * Cm[e] * sd[b];
+      }
+      __syncthreads();
+      jacobi_eig_cta(A, V, K, ld, cs, flag);
+      __syncthreads();
+      if (tid < K) lam[tid] = A[tid * ld + tid];
+      __syncthreads();
+      if (tid < K) {
+        const double me = lam[tid];
+        int r = 0;
+        for (int j = 0; j < K; ++j) r += (lam[j] > me) || (lam[j] == me && j < tid);
+        double num = 0.0;
+        for (int i = 0; i < K; ++i) {
+          const double v = V[i * ld + tid];
+          num = fma(d0[i] * v, v, num);
+        }
+        // position r of v_m (np.diagonal(Dm_hat) / Dm, utils.py:84); distinct r per thread
+        vacc[r] += num / me;
+      }
+      __syncthreads();
+    }
+    if (tid < K) out[tid] = vacc[tid];
+    __syncthreads();
+  }
+}
+
+__global__ void eig_partial_reduce_kernel(int T, int K, int nblk, const double* partial, double* vsum, int accumulate) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= T * K) return;
+  const int t = e / K, k = e - t * K;
+  double s = accumulate ? vsum[e] : 0.0;
+  for (int b = 0; b < nblk; ++b) s += partial[((size_t)t * nblk + b) * K + k];
+  vsum[e] = s;
+}
+
+// E3: v = c (sqrt(vsum / M) - 1) + 1;  F0_hat = U0 diag(v^2 D0) U0'   (utils.py:86-92)
+__global__ void __launch_bounds__(256) eig_finalize_kernel(int T, int K, int M, double scale, const double* D0,
+                                                           const double* U0, const double* vsum,
+                                                           const int* status, double* out) {
+  extern __shared__ double sm[];
+  double* U = sm;           // K*K
+  double* g = U + K * K;    // K
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    double* o = out + (size_t)t * K * K;
+    if (status[t] != BMFM_ST_OK) {
+      for (int e = threadIdx.x; e < K * K; e += blockDim.x) o[e] = nan;
+      continue;
+    }
+    for (int e = threadIdx.x; e < K * K; e += blockDim.x) U[e] = U0[(size_t)t * K * K + e];
+    if (threadIdx.x < K) {
+      double v = sqrt(vsum[(size_t)t * K + threadIdx.x] / (double)M);
+      v = scale * (v - 1.0) + 1.0;
+      g[threadIdx.x] = v * v * D0[(size_t)t * K + threadIdx.x];
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < K * K; e += blockDim.x) {
+      const int a = e / K, b = e - a * K;
+      double s = 0.0;
+      for (int k = 0; k < K; ++k) s = fma(U[a * K + k] * g[k], U[b * K + k], s);
+      o[e] = s;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace bmfm
+
+using namespace bmfm;
+
+extern "C" int bmfm_gauss_cov(bmfm_ctx* ctx, int m0, int nsim, int T_sim, int K, double* C) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, m0 >= 0 && nsim >= 0 && T_sim >= 2 && K > 0 && C, "bad arguments");
+  if (nsim == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  // batch the simulations so the z scratch stays below ~1 GiB
+  const size_t per_sim = (size_t)T_sim * K * 8;
+  size_t batch_sz = ((size_t)1 << 30) / per_sim;
+  if (batch_sz < 1) batch_sz = 1;
+  if (batch_sz > (size_t)nsim) batch_sz = (size_t)nsim;
+  const int batch = (int)batch_sz;
+  const size_t zbytes = bmfm_align_up((size_t)batch * per_sim, 256);
+  int rc = bmfm_ws_reserve(ctx, zbytes + (size_t)batch * 624 * 4);
+  if (rc) return rc;
+  double* z = (double*)ctx->ws;
+  uint32_t* mt = (uint32_t*)((char*)ctx->ws + zbytes);
+  for (int s = 0; s < nsim; s += batch) {
+    const int nb = nsim - s < batch ? nsim - s : batch;
+    gauss_fill_kernel<<<(nb + 31) / 32, 32, 0, ctx->stream>>>(m0 + s, nb, T_sim, K, mt, z);
+    ctx->launches++;
+    gauss_cov_kernel<<<nb, 256, K * sizeof(double), ctx->stream>>>(nb, T_sim, K, z, C + (size_t)s * K * K);
+    ctx->launches++;
+  }
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+static size_t eig_smem_bytes(int K) { return ((size_t)2 * K * (K | 1) + 6 * K + 16) * 8 + 64; }
+
+extern "C" int bmfm_eigen_decompose(bmfm_ctx* ctx, int T, int K, const double* cov, const int32_t* cov_status,
+                                    double* D0, double* U0, int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && cov && D0 && U0 && status, "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t smem = eig_smem_bytes(K);
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_f0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = T < ctx->sm_count * 4 ? T : ctx->sm_count * 4;
+  eig_f0_kernel<<<grid, 256, smem, ctx->stream>>>(T, K, cov, cov_status, D0, U0, status);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// vsum[T][K] (+)= sum over the nsim simulations whose cov(z) is in C
+extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0,
+                                        const int32_t* status, double* vsum, int accumulate) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && nsim >= 0 && D0 && status && vsum && (C || nsim == 0), "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t smem = eig_smem_bytes(K);
+  const int slots = ctx->sm_count * (int)((228 * 1024) / (smem + 1024));
+  int nblk = (4 * slots + T - 1) / T;
+  if (nblk > nsim) nblk = nsim;
+  if (nblk < 1) nblk = 1;
+  int rc = bmfm_ws_reserve(ctx, (size_t)T * nblk * K * 8);
+  if (rc) return rc;
+  double* partial = (double*)ctx->ws;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long work = (long long)T * nblk;
+  int grid = work < slots ? (int)work : slots;
+  eig_mc_kernel<<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+  ctx->launches++;
+  eig_partial_reduce_kernel<<<(T * K + 255) / 256, 256, 0, ctx->stream>>>(T, K, nblk, partial, vsum, accumulate);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double scale_coef, const double* D0,
+                                   const double* U0, const double* vsum, const int32_t* status, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && M > 0 && D0 && U0 && vsum && status && out, "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t smem = ((size_t)K * K + K) * 8;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  eig_finalize_kernel<<<grid, 256, smem, ctx->stream>>>(T, K, M, scale_coef, D0, U0, vsum, status, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}

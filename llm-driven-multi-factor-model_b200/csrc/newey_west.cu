@@ -1,0 +1,253 @@
+// Expanding-window exponentially weighted Newey-West factor covariance for every date.
+//
+// Replaces  MFM.Newey_West_by_time   Barra-master/mfm/MFM.py:80-101
+//           utils.Newey_West         Barra-master/mfm/utils.py:16-50
+//
+// The reference recomputes the whole weighted covariance from scratch for each of the T
+// expanding windows (O(T^2 K^2 (q+1)) python-level outer products).  With decay
+// lam = 0.5^(1/tao) every moment it needs obeys a first-order recurrence in the window
+// length L:
+//     A0_L   = lam A0_{L-1}   + x_{L-1} x_{L-1}'          (lag-0 raw second moment)
+//     B_i,L  = lam B_i,{L-1}  + x_{L-1-i} x_{L-1}'        (lag-i raw cross moment, weight of the later row)
+//     S_L    = lam S_{L-1}    + x_{L-1},  Z_L = lam Z_{L-1} + 1
+//     R_i,L  = lam R_i,{L-1}  + x_{L-1} [L-1 >= i],  Zi_L likewise      (sums over rows r >= i)
+//     P_i,L  = lam P_i,{L-1}  + x_{L-1-i}                 (= S_{L-i}, the partner-row sum)
+// and with m = S_L / Z_L (the EW mean, utils.py:36-37)
+//     Gamma_0 = A0/Z - m m'
+//     Gamma_i = ( B_i - P_i m' - m R_i' + m m' Zi ) / Z              (utils.py:46)
+//     V = Gamma_0 + sum_i (1 - i/(1+q)) (Gamma_i + Gamma_i')             (utils.py:48)
+// O(T K^2 (q+1)) work.  Time is cut into chunks so all SMs work: kernel 1 reduces each
+// chunk from a zero start, kernel 2 scans the chunk totals (tiny), kernel 3 replays each
+// chunk from its true start state and streams out K x K matrices, one coalesced row-major
+// write per element.  Scratch: nchunks * ((1+q)(K^2+1) + (1+2q)K) doubles.
+#include <math.h>
+#include "bmfm_common.cuh"
+
+namespace bmfm {
+
+constexpr int NW_MAX_Q = 4;
+
+struct NwParams {
+  int T, K, q, C, nchunks;
+  double lam;
+  const double* fr;   // [T][K]
+  double* cov;        // [T][K][K]
+  int* status;        // [T]
+  double* state;      // [nchunks][nstate]   chunk totals, then chunk start states
+};
+
+__host__ __device__ inline int nw_nstate(int K, int q) { return (1 + q) * (K * K + 1) + (1 + 2 * q) * K; }
+// layout of one state record:
+//   mats[(1+q)][K][K] | vecs[(1+2q)][K] (S, R_1..R_q, P_1..P_q) | scal[(1+q)] (Z, Z_1..Z_q)
+__device__ __forceinline__ double nw_vec_term(const double* fr, int K, int q, int v, int r, int k) {
+  // the value row r adds to vector v
+  if (v == 0) return fr[(size_t)r * K + k];
+  if (v <= q) return r >= v ? fr[(size_t)r * K + k] : 0.0;
+  const int i = v - q;
+  return r - i >= 0 ? fr[(size_t)(r - i) * K + k] : 0.0;
+}
+
+// kernel 1: chunk totals from a zero start
+__global__ void nw_chunk_local(NwParams p) {
+  const int c = blockIdx.x, K = p.K, q = p.q;
+  const int r0 = c * p.C, r1 = min(p.T, r0 + p.C);
+  double* st = p.state + (size_t)c * nw_nstate(K, q);
+  const int nm = (1 + q) * K * K;
+  for (int e = threadIdx.x; e < nm; e += blockDim.x) {
+    const int i = e / (K * K), ab = e - i * K * K, a = ab / K, b = ab - a * K;
+    double s = 0.0;
+    for (int r = r0; r < r1; ++r) {
+      s *= p.lam;
+      if (r - i >= 0) s = fma(p.fr[(size_t)(r - i) * K + a], p.fr[(size_t)r * K + b], s);
+    }
+    st[e] = s;
+  }
+  const int nv = (1 + 2 * q) * K;
+  for (int e = threadIdx.x; e < nv; e += blockDim.x) {
+    const int v = e / K, k = e - v * K;
+    double s = 0.0;
+    for (int r = r0; r < r1; ++r) s = fma(s, p.lam, nw_vec_term(p.fr, K, q, v, r, k));
+    st[nm + e] = s;
+  }
+  if (threadIdx.x <= q) {
+    const int i = threadIdx.x;
+    double s = 0.0;
+    for (int r = r0; r < r1; ++r) {
+      s *= p.lam;
+      if (r >= i) s += 1.0;
+    }
+    st[nm + nv + i] = s;
+  }
+}
+
+// kernel 2: exclusive scan over chunks, one thread per state element
+__global__ void nw_chunk_scan(NwParams p) {
+  const int ns = nw_nstate(p.K, p.q);
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= ns) return;
+  double run = 0.0;
+  for (int c = 0; c < p.nchunks; ++c) {
+    const int len = min(p.T, (c + 1) * p.C) - c * p.C;
+    double* cell = p.state + (size_t)c * ns + e;
+    const double loc = *cell;
+    *cell = run;
+    run = fma(run, pow(p.lam, (double)len), loc);
+  }
+}
+
+// kernel 3: replay the chunk from its start state and emit V for every date in it
+__global__ void __launch_bounds__(256) nw_emit(NwParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int c = blockIdx.x, K = p.K, q = p.q, C = p.C;
+  const int r0 = c * C, r1 = min(p.T, r0 + C), len = r1 - r0;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int nm = (1 + q) * K * K;
+  const double* st = p.state + (size_t)c * nw_nstate(K, q);
+  const int NV = 1 + 2 * q, nv = NV * K;
+  double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K]  rows r0-q .. r1-1 (zeros before row 0)
+  double* sv = sx + (C + q) * K;                       // [C][NV][K]  vectors after row r0+j
+  double* sz = sv + C * nv;                            // [C][(1+q)]
+  const double lam = p.lam;
+  for (int e = tid; e < (len + q) * K; e += nt) {
+    const int j = e / K, k = e - j * K;
+    const int r = r0 - q + j;
+    sx[e] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
+  }
+  __syncthreads();
+  for (int e = tid; e < nv; e += nt) {
+    const int v = e / K, k = e - v * K;
+    double s = st[nm + e];
+    for (int j = 0; j < len; ++j) {
+      const int r = r0 + j;
+      double add;
+      if (v == 0) add = sx[(q + j) * K + k];
+      else if (v <= q) add = r >= v ? sx[(q + j) * K + k] : 0.0;
+      else add = sx[(q + j - (v - q)) * K + k];      // zero-filled before row 0
+      s = fma(s, lam, add);
+      sv[(size_t)j * nv + e] = s;
+    }
+  }
+  if (tid <= q) {
+    const int i = tid;
+    double s = st[nm + nv + i];
+    for (int j = 0; j < len; ++j) {
+      const int r = r0 + j;
+      s *= lam;
+      if (r >= i) s += 1.0;
+      sz[j * (1 + q) + i] = s;
+    }
+  }
+  __syncthreads();
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int e = tid; e < K * K; e += nt) {
+    const int a = e / K, b = e - a * K;
+    double a0 = st[e];
+    double bab[NW_MAX_Q], bba[NW_MAX_Q];
+#pragma unroll
+    for (int i = 0; i < NW_MAX_Q; ++i) {
+      bab[i] = i < q ? st[(1 + i) * K * K + a * K + b] : 0.0;
+      bba[i] = i < q ? st[(1 + i) * K * K + b * K + a] : 0.0;
+    }
+    for (int j = 0; j < len; ++j) {
+      const int r = r0 + j;       // date index; window length L = r + 1
+      const double* xr = sx + (q + j) * K;
+      const double xa = xr[a], xb = xr[b];
+      a0 = fma(a0, lam, xa * xb);
+#pragma unroll
+      for (int i = 0; i < NW_MAX_Q; ++i) {
+        if (i < q) {
+          bab[i] *= lam;
+          bba[i] *= lam;
+          if (r - (i + 1) >= 0) {
+            const double* xl = sx + (q + j - (i + 1)) * K;
+            bab[i] = fma(xl[a], xb, bab[i]);
+            bba[i] = fma(xl[b], xa, bba[i]);
+          }
+        }
+      }
+      const int L = r + 1;
+      double out;
+      if (L <= q || L <= K) {
+        out = nan;
+      } else {
+        const double* vec = sv + (size_t)j * nv;
+        const double Z = sz[j * (1 + q)];
+        const double iz = 1.0 / Z;
+        const double ma = vec[a] * iz, mb = vec[b] * iz;
+        out = a0 * iz - ma * mb;
+#pragma unroll
+        for (int i = 0; i < NW_MAX_Q; ++i) {
+          if (i < q) {
+            const int lag = i + 1;
+            const double Pa = vec[(q + lag) * K + a], Pb = vec[(q + lag) * K + b];
+            const double Ra = vec[lag * K + a], Rb = vec[lag * K + b];
+            const double Zi = sz[j * (1 + q) + lag];
+            const double gab = (bab[i] - Pa * mb - ma * Rb + ma * mb * Zi) * iz;
+            const double gba = (bba[i] - Pb * ma - mb * Ra + ma * mb * Zi) * iz;
+            out = fma(1.0 - (double)lag / (1.0 + q), gab + gba, out);
+          }
+        }
+      }
+      st_stream(p.cov + ((size_t)r * K + a) * K + b, out);
+    }
+  }
+  for (int j = tid; j < len; j += nt) {
+    const int L = r0 + j + 1;
+    p.status[r0 + j] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
+  }
+}
+
+}  // namespace bmfm
+
+using namespace bmfm;
+
+// Scratch (device) bytes bmfm_newey_west_by_time needs for given sizes.
+extern "C" size_t bmfm_newey_west_scratch_bytes(int T, int K, int q) {
+  if (T <= 0) return 0;
+  int C = (T + 295) / 296;
+  if (C < 8) C = 8;
+  const int nchunks = (T + C - 1) / C;
+  return (size_t)nchunks * nw_nstate(K, q) * sizeof(double);
+}
+
+static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const double* fr, double* cov,
+                     int32_t* status, double* scratch) {
+  NwParams p;
+  p.T = T; p.K = K; p.q = q;
+  p.C = (T + 295) / 296;
+  if (p.C < 8) p.C = 8;
+  p.nchunks = (T + p.C - 1) / p.C;
+  p.lam = pow(0.5, 1.0 / tao);
+  p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
+  nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
+  ctx->launches++;
+  const int ns = nw_nstate(K, q);
+  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
+  ctx->launches++;
+  const size_t smem = ((size_t)(p.C + q) * K + (size_t)p.C * (1 + 2 * q) * K + (size_t)p.C * (1 + q)) * 8;
+  if (smem > (size_t)ctx->max_smem_optin) {
+    snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  nw_emit<<<p.nchunks, 256, smem, ctx->stream>>>(p);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                                       const double* factor_ret, double* cov, int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && q >= 0 && tao > 0, "bad sizes");
+  BMFM_ARG(ctx, factor_ret && cov && status, "NULL pointer");
+  if (q > NW_MAX_Q) {
+    snprintf(ctx->err, sizeof(ctx->err), "q=%d exceeds compiled limit %d", q, NW_MAX_Q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
+  if (rc) return rc;
+  return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws);
+}

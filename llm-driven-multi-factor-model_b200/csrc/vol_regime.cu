@@ -1,0 +1,119 @@
+// Volatility-regime adjustment of the factor covariance series.
+//
+// Replaces  MFM.vol_regime_adj_by_time   Barra-master/mfm/MFM.py:130-167
+//
+//   var_t   = diag(cov_t), a NaN row where the date has no covariance (MFM.py:142-148)
+//   B_t^2   = mean_k f_tk^2 / var_tk            (pandas mean: NaN entries skipped, :149)
+//   w_s     = 0.5^((T-1-s)/tao)
+//   lamb_t  = sqrt( sum_{s<=t, var_s valid} w_s B_s^2 / sum_{s<=t, var_s valid} w_s ), 0 when no valid row
+//   out_t   = cov_t * lamb_t^2
+// The reference's O(T^2) python loop is two prefix sums.  Three launches: per-date bias
+// statistic, one-CTA scan over dates, then a streaming scale of T*K*K doubles (HBM-bound:
+// 16 B per matrix element).
+#include <math.h>
+#include "bmfm_common.cuh"
+
+namespace bmfm {
+
+// one warp per date
+__global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const double* cov,
+                               const int* cov_status, double* wb, double* wv) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= T) return;
+  const int t = warp;
+  const bool have = cov_status == nullptr || cov_status[t] == BMFM_ST_OK || cov_status[t] == BMFM_ST_PINV;
+  double sum = 0.0;
+  int cnt = 0, nanvar = 0;
+  if (have) {
+    for (int k = lane; k < K; k += 32) {
+      const double v = cov[((size_t)t * K + k) * K + k];
+      const double f = fr[(size_t)t * K + k];
+      if (isnan(v)) nanvar = 1;
+      const double r = f * f / v;
+      if (!isnan(r)) { sum += r; cnt++; }
+    }
+  } else {
+    nanvar = 1;
+  }
+  sum = warp_sum(sum);
+  cnt = __reduce_add_sync(0xffffffffu, cnt);
+  nanvar = __any_sync(0xffffffffu, nanvar);
+  if (lane == 0) {
+    const double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);   // B_t^2
+    const double w = pow(0.5, (double)(T - 1 - t) / tao);
+    // rows whose variance vector holds a NaN are excluded from both sums (MFM.py:158)
+    wb[t] = nanvar ? 0.0 : w * b2;
+    wv[t] = nanvar ? 0.0 : w;
+  }
+}
+
+// single CTA inclusive scan of (wb, wv) -> lamb
+__global__ void __launch_bounds__(1024) vr_scan_kernel(int T, const double* wb, const double* wv, double* lamb) {
+  __shared__ double s_b[1024], s_v[1024];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int per = (T + nt - 1) / nt;
+  const int lo = min(T, tid * per), hi = min(T, lo + per);
+  double pb = 0.0, pv = 0.0;
+  for (int t = lo; t < hi; ++t) { pb += wb[t]; pv += wv[t]; }
+  s_b[tid] = pb;
+  s_v[tid] = pv;
+  __syncthreads();
+  for (int off = 1; off < nt; off <<= 1) {
+    double ab = 0.0, av = 0.0;
+    if (tid >= off) { ab = s_b[tid - off]; av = s_v[tid - off]; }
+    __syncthreads();
+    s_b[tid] += ab;
+    s_v[tid] += av;
+    __syncthreads();
+  }
+  double rb = s_b[tid] - pb, rv = s_v[tid] - pv;   // exclusive prefix of this thread's range
+  for (int t = lo; t < hi; ++t) {
+    rb += wb[t];
+    rv += wv[t];
+    lamb[t] = rv > 0.0 ? sqrt(rb / rv) : 0.0;
+  }
+}
+
+__global__ void vr_scale_kernel(int T, int KK, const double* cov, const int* cov_status, const double* lamb,
+                                double* out) {
+  const size_t total = (size_t)T * KK;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(e / KK);
+    const bool have = cov_status == nullptr || cov_status[t] == BMFM_ST_OK || cov_status[t] == BMFM_ST_PINV;
+    const double l = lamb[t];
+    st_stream(out + e, have ? cov[e] * (l * l) : nan);
+  }
+}
+
+}  // namespace bmfm
+
+using namespace bmfm;
+
+extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double tao, const double* factor_ret,
+                                           const double* cov, const int32_t* cov_status, double* out_cov,
+                                           double* lamb) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && tao > 0, "bad sizes");
+  BMFM_ARG(ctx, factor_ret && cov && lamb, "NULL pointer");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = bmfm_ws_reserve(ctx, (size_t)2 * T * sizeof(double));
+  if (rc) return rc;
+  double* wb = (double*)ctx->ws;
+  double* wv = wb + T;
+  vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv);
+  ctx->launches++;
+  vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T, wb, wv, lamb);
+  ctx->launches++;
+  if (out_cov) {
+    const size_t total = (size_t)T * K * K;
+    int grid = (int)((total + 255) / 256);
+    const int cap = ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    vr_scale_kernel<<<grid, 256, 0, ctx->stream>>>(T, K * K, cov, cov_status, lamb, out_cov);
+    ctx->launches++;
+  }
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}

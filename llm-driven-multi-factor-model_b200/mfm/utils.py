@@ -1,0 +1,106 @@
+# -*- coding: utf-8 -*-
+"""Drop-in for Barra-master/mfm/utils.py: same function names, arguments and
+return types; Newey-West and the eigenfactor adjustment run on the GPU.
+
+Eigen-order note: the reference calls the GENERAL eigensolver
+``np.linalg.eig`` and averages simulated biases by output POSITION, so its
+literal output depends on LAPACK's deflation order.  This implementation uses
+the canonical convention (eigenvalues descending) and matches the reference
+source run with ``np.linalg.eig`` patched to that convention to <= 1e-9.
+"""
+import math
+
+import numpy as np
+import pandas as pd
+
+from bmfm import ops as _ops
+from bmfm import _cabi
+
+
+def Newey_West(ret, q=2, tao=252):
+    '''
+    Newey_West方差调整 (utils.py:16-50): ret DataFrame (rows time, cols factors) -> K x K DataFrame
+    '''
+    T = ret.shape[0]
+    K = ret.shape[1]
+    if T <= q or T <= K:
+        raise Exception("T <= q or T <= K")
+    names = ret.columns
+    cov, status = _ops.newey_west_by_time(np.ascontiguousarray(ret.values, dtype=np.float64), q, tao)
+    return (pd.DataFrame(cov[-1], columns=names, index=names))
+
+
+def eigen_risk_adj(covmat, T=1000, M=100, scale_coef=1.4):
+    '''
+    Eigenfactor Risk Adjustment (utils.py:55-92)
+    T: 序列长度   M: 模拟次数   scale_coef: scale coefficient for bias
+    '''
+    vals = np.ascontiguousarray(np.asarray(covmat, dtype=np.float64))
+    out, status = _ops.eigen_risk_adj_by_time(vals[None], None, int(T), int(M), scale_coef)
+    if status[0] == _cabi.ST_NOT_PSD:
+        # the reference does raise('...') of a str, i.e. a TypeError (utils.py:67-68)
+        raise TypeError('exceptions must derive from BaseException')
+    if status[0] != _cabi.ST_OK:
+        raise np.linalg.LinAlgError("Array must not contain infs or NaNs")
+    cols = covmat.columns if hasattr(covmat, "columns") else None
+    return (pd.DataFrame(out[0], columns=cols, index=cols))
+
+
+def eigenfactor_bias_stat(cov, ret, predlen=1):
+    '''
+    计算特征因子组合的bias统计量 (utils.py:97-117); host-side diagnostic, canonical eigen order
+    '''
+    b = []
+    for i in range(len(cov) - predlen):
+        try:
+            c = np.asarray(cov[i], dtype=float)
+            w, v = np.linalg.eigh(0.5 * (c + c.T))
+            order = np.argsort(-w, kind="stable")
+            U = v[:, order]
+            idx = np.argmax(np.abs(U), axis=0)
+            sgn = np.sign(U[idx, np.arange(U.shape[1])])
+            sgn[sgn == 0] = 1.0
+            U = U * sgn[None, :]
+            U = U / np.sum(U, axis=0)
+            sigma = np.sqrt(predlen * np.diag(U.T @ c @ U))
+            retlen = (ret.values[(i + 1):(i + predlen + 1)] + 1).prod(axis=0) - 1
+            r = U.T @ retlen
+            b.append(r / sigma)
+        except Exception:
+            pass
+    b = np.array(b)
+    bias_stat = np.std(b, axis=0)
+    try:
+        import matplotlib.pyplot as plt
+        plt.plot(bias_stat)
+    except Exception:
+        pass
+    return (bias_stat)
+
+
+def progressbar(cur, total, txt):
+    '''
+    显示进度条 (utils.py:123-128)
+    '''
+    percent = '{:.2%}'.format(cur / total)
+    print("\r[%-50s] %s" % ('=' * int(math.floor(cur * 50 / total)), percent) + txt, end='')
+
+
+def group_mean_std(x):
+    '''
+    计算一组的加权平均和波动率 (utils.py:133-139)
+    '''
+    m = sum(x.volatility * x.capital) / sum(x.capital)
+    s = np.sqrt(np.mean((x.volatility - m) ** 2))
+    return ([m, s])
+
+
+def shrink(x, group_weight_mean, q):
+    '''
+    计算shrink估计量 (utils.py:142-150)
+    '''
+    a = q * np.abs(x['volatility'] - group_weight_mean[x['group']][0])
+    b = group_weight_mean[x['group']][1]
+    v = a / (a + b)
+    SH_est = v * group_weight_mean[x['group']][0] + (1 - v) * np.abs(x['volatility'])
+    return (SH_est)
