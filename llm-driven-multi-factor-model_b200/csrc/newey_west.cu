@@ -80,18 +80,26 @@ __global__ void nw_chunk_local(NwParams p) {
   }
 }
 
-// kernel 2: exclusive scan over chunks, one thread per state element
+// kernel 2: exclusive scan over chunks, one thread per state element.  Every chunk but the
+// last has length C (the total after the last chunk is never used), so the carry factor is
+// the constant lam^C; loads are issued eight chunks at a time to overlap their latency.
 __global__ void nw_chunk_scan(NwParams p) {
   const int ns = nw_nstate(p.K, p.q);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= ns) return;
+  const double fC = pow(p.lam, (double)p.C);
   double run = 0.0;
-  for (int c = 0; c < p.nchunks; ++c) {
-    const int len = min(p.T, (c + 1) * p.C) - c * p.C;
-    double* cell = p.state + (size_t)c * ns + e;
-    const double loc = *cell;
-    *cell = run;
-    run = fma(run, pow(p.lam, (double)len), loc);
+  for (int c0 = 0; c0 < p.nchunks; c0 += 8) {
+    double loc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) loc[j] = (c0 + j < p.nchunks) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (c0 + j < p.nchunks) {
+        p.state[(size_t)(c0 + j) * ns + e] = run;
+        run = fma(run, fC, loc[j]);
+      }
+    }
   }
 }
 

@@ -24,6 +24,7 @@
 //            (eigen-decomposition, cutoff 1e-15 * max) — CrossSection.py:69-76;
 //   pass C   specific returns + R2 from the rows still resident in shared memory.
 // Dates larger than the tile are streamed tile by tile (pass C re-reads them).
+#include <stdlib.h>
 #include "bmfm_common.cuh"
 #include "jacobi.cuh"
 
@@ -243,18 +244,33 @@ __device__ void accumulate_date(const RegParams& p, const RegSmem& L, unsigned c
         for (int b = grp; b < NB; b += ngrp) {
           if (seg_runs[b] == 0) continue;
           const int lo = seg_start[b], hi = seg_end[b];
-          double sum = 0.0;
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+          int i = lo;
           if (v == 0) {
-            for (int i = lo; i < hi; ++i) sum += s_w[i];
+            for (; i + 3 < hi; i += 4) { s0 += s_w[i]; s1 += s_w[i + 1]; s2 += s_w[i + 2]; s3 += s_w[i + 3]; }
+            for (; i < hi; ++i) s0 += s_w[i];
           } else if (v == 1) {
-            for (int i = lo; i < hi; ++i) sum = fma(s_w[i], s_ret[i], sum);
+            for (; i + 3 < hi; i += 4) {
+              s0 = fma(s_w[i], s_ret[i], s0); s1 = fma(s_w[i + 1], s_ret[i + 1], s1);
+              s2 = fma(s_w[i + 2], s_ret[i + 2], s2); s3 = fma(s_w[i + 3], s_ret[i + 3], s3);
+            }
+            for (; i < hi; ++i) s0 = fma(s_w[i], s_ret[i], s0);
           } else if (v == 2) {
-            for (int i = lo; i < hi; ++i) sum += s_cap[i];
+            for (; i + 3 < hi; i += 4) { s0 += s_cap[i]; s1 += s_cap[i + 1]; s2 += s_cap[i + 2]; s3 += s_cap[i + 3]; }
+            for (; i < hi; ++i) s0 += s_cap[i];
           } else {
             const int q = v - 3;
             const double pv = s_piv[q];
-            for (int i = lo; i < hi; ++i) sum = fma(s_w[i], s_style[(size_t)i * Q + q] - pv, sum);
+            const double* col = s_style + q;
+            for (; i + 3 < hi; i += 4) {
+              s0 = fma(s_w[i], col[(size_t)i * Q] - pv, s0);
+              s1 = fma(s_w[i + 1], col[(size_t)(i + 1) * Q] - pv, s1);
+              s2 = fma(s_w[i + 2], col[(size_t)(i + 2) * Q] - pv, s2);
+              s3 = fma(s_w[i + 3], col[(size_t)(i + 3) * Q] - pv, s3);
+            }
+            for (; i < hi; ++i) s0 = fma(s_w[i], col[(size_t)i * Q] - pv, s0);
           }
+          const double sum = (s0 + s1) + (s2 + s3);
           s_bucket[b * BV + v] += sum;
         }
       }
@@ -296,16 +312,27 @@ __device__ void accumulate_date(const RegParams& p, const RegSmem& L, unsigned c
   (void)NA1; (void)NA2;
 }
 
-// ---- fast solve: block elimination of the diagonal industry block (warp 0) -----------------
+// ---- fast solve: block elimination of the diagonal industry block -------------------------
 // Minimise sum_i w_i (y_i - f_c - g_{p(i)} - beta . x_i)^2  s.t.  sum_p c_p g_p = 0,
 // x_i = d_i - m' (the sigma of style_factor_norm only rescales beta).  Eliminating g_p through
 // the diagonal block leaves  [w0 gs0' C; gs0 St t; C t' -D] (f_c, beta, mu') = (b0, bt, cy).
 // Equivalent to R pinv(R'GR) R'b of CrossSection.py:69-76 whenever R'GR is non-singular;
 // empty non-last industries (zero row/column of R'GR, pinv -> 0) are skipped the same way.
-// Returns 0 ok, REG_NEED_DENSE if a pivot is not safely positive, BMFM_ST_NONFINITE.
-template <int Q>
-__device__ int solve_fast_warp0(const RegParams& p, const RegSmem& L, unsigned char* smem, int n) {
+// The reduced matrices are formed by all threads; the Q x (Q+3) Gauss-Jordan elimination runs
+// in the registers of warp 0 (lane = row, pivot rows broadcast by shuffle, no pivoting: St is
+// SPD).  Returns 0, REG_NEED_DENSE if a pivot is not safely positive, or BMFM_ST_NONFINITE.
+template <bool WARP>
+__device__ __forceinline__ void group_sync() {
+  if (WARP) __syncwarp(); else __syncthreads();
+}
+
+// WARP = true: the calling warp owns `smem` (per-warp layout) and solves on its own;
+// WARP = false: the whole CTA cooperates (barriers are __syncthreads).
+template <int Q, bool WARP>
+__device__ int solve_fast_cta(const RegParams& p, const RegSmem& L, unsigned char* smem, int n) {
+  constexpr int QQ = Q > 0 ? Q : 1;
   const int lane = threadIdx.x & 31;
+  const int tid = WARP ? lane : (int)threadIdx.x, nt = WARP ? 32 : (int)blockDim.x;
   const int P = p.P, NB = P + 1, BV = 3 + Q, K = p.K;
   constexpr int NA1PAD = na1pad_of(Q);
   const double* s_bucket = reinterpret_cast<const double*>(smem + L.bucket);
@@ -316,11 +343,10 @@ __device__ int solve_fast_warp0(const RegParams& p, const RegSmem& L, unsigned c
   double* s_g = s_beta + Q;
   double* s_misc = s_g + NB;
   double* s_f = reinterpret_cast<double*>(smem + L.fvec);
-  double* St = reinterpret_cast<double*>(smem + L.solve);   // Q*Q
-  double* rhs = St + Q * Q;                                 // 3*Q solved in place
-  double* org = rhs + 3 * Q;                                // 3*Q originals
-  double* diag0 = org + 3 * Q;                              // Q
-  double* winv = diag0 + Q;                                 // NB
+  double* St = reinterpret_cast<double*>(smem + L.solve);   // Q*Q (lower triangle used)
+  double* rhs = St + Q * Q;                                 // gs0[Q] t[Q] bt[Q]
+  double* winv = rhs + 3 * Q;                               // NB
+  int* s_flag = reinterpret_cast<int*>(smem + L.seg) + 3 * NB + 2;
   const double* S2 = s_acc;
   const double* BY = s_acc + Q * (Q + 1) / 2;
   const double* CD = s_acc + NA1PAD;
@@ -330,164 +356,164 @@ __device__ int solve_fast_warp0(const RegParams& p, const RegSmem& L, unsigned c
 #define BWY(b) s_bucket[(b)*BV + 1]
 #define BC(b) s_bucket[(b)*BV + 2]
 #define BD(b, q) s_bucket[(b)*BV + 3 + (q)]
-  // industry sums
-  double sC = 0.0, Dm = 0.0, cy = 0.0;
-  for (int b = lane; b < P; b += 32) {
+  // S1: reciprocal industry weights (all threads); scalar sums, style means, sigma (warp 0)
+  for (int b = tid; b < P; b += nt) {
     const double wv = BW(b);
-    const double wi = wv > 0.0 ? 1.0 / wv : 0.0;
-    winv[b] = wi;
-    const double c = wv > 0.0 ? BC(b) : 0.0;
-    sC += c;
-    Dm = fma(c * c, wi, Dm);
-    cy = fma(c * wi, BWY(b), cy);
+    winv[b] = wv > 0.0 ? 1.0 / wv : 0.0;
   }
-  sC = warp_sum(sC);
-  Dm = warp_sum(Dm);
-  cy = warp_sum(cy);
-  const double W0 = BW(P), b0 = BWY(P);
-  double capall = 0.0;
-  for (int b = lane; b < NB; b += 32) capall += BC(b);
-  capall = warp_sum(capall);
-  if (lane < Q) s_mp[lane] = CD[lane] / capall;
-  // scalar std of style_factor_norm: one mean and one variance over all n*Q entries
-  const double dn = (double)n;
-  double sigma = 1.0;
-  if (Q > 0) {
-    double v = lane < Q ? D1[lane] + dn * s_piv[lane] : 0.0;
-    const double mu = warp_sum(v) / (dn * Q);
-    double t2 = 0.0;
-    if (lane < Q) {
-      const double dq = s_piv[lane] - mu;
-      t2 = D2[lane] + 2.0 * dq * D1[lane] + dn * dq * dq;
+  if (tid < 32) {
+    double sC = 0.0, Dm = 0.0, cy = 0.0, capall = 0.0;
+    for (int b = lane; b < NB; b += 32) {
+      const double wv = BW(b), cb = BC(b);
+      capall += cb;
+      if (b < P && wv > 0.0) {
+        const double wi = 1.0 / wv;
+        sC += cb;
+        Dm = fma(cb * cb, wi, Dm);
+        cy = fma(cb * wi, BWY(b), cy);
+      }
     }
-    sigma = sqrt(warp_sum(t2) / (dn * Q));
-  }
-  __syncwarp();
-  int fail = 0;
-  if (P > 0 && !(BC(P - 1) != 0.0)) fail = BMFM_ST_NONFINITE;   // -cap/0 in R (CrossSection.py:70)
-  // reduced matrices in d-units
-  for (int e = lane; e < Q * Q; e += 32) {
-    const int q = e / Q, r = e - q * Q;
-    const int hi = q > r ? q : r, lo = q > r ? r : q;
-    double a = S2[hi * (hi + 1) / 2 + lo];
-    for (int b = 0; b < P; ++b) a = fma(-BD(b, q) * winv[b], BD(b, r), a);
-    a += -s_mp[q] * BD(P, r) - s_mp[r] * BD(P, q) + s_mp[q] * s_mp[r] * W0;
-    St[e] = a;
-    if (q == r) diag0[q] = a;
-  }
-  if (lane < Q) {
-    const int q = lane;
-    double t = 0.0, bt = BY[q];
-    for (int b = 0; b < P; ++b) {
-      const double eb = BD(b, q) * winv[b];
-      if (winv[b] > 0.0) t = fma(eb - s_mp[q], BC(b), t);
-      bt = fma(-eb, BWY(b), bt);
+    sC = warp_sum(sC); Dm = warp_sum(Dm); cy = warp_sum(cy); capall = warp_sum(capall);
+    const double dn = (double)n;
+    double sigma = 1.0;
+    if (Q > 0) {
+      if (lane < Q) s_mp[lane] = CD[lane] / capall;
+      const double v = lane < Q ? D1[lane] + dn * s_piv[lane] : 0.0;
+      const double mu = warp_sum(v) / (dn * Q);
+      double t2 = 0.0;
+      if (lane < Q) {
+        const double dq = s_piv[lane] - mu;
+        t2 = D2[lane] + 2.0 * dq * D1[lane] + dn * dq * dq;
+      }
+      sigma = sqrt(warp_sum(t2) / (dn * Q));
     }
-    bt -= s_mp[q] * b0;
-    const double gs0 = BD(P, q) - s_mp[q] * W0;
-    rhs[q] = org[q] = gs0;
-    rhs[Q + q] = org[Q + q] = t;
-    rhs[2 * Q + q] = org[2 * Q + q] = bt;
-  }
-  __syncwarp();
-  // Cholesky St = L L' (lower, in place), pivots checked against the original diagonal
-  for (int k = 0; k < Q; ++k) {
-    const double dk = St[k * Q + k];
-    if (!(dk > 1e-11 * diag0[k]) || !(diag0[k] > 0.0)) { if (!fail) fail = REG_NEED_DENSE; break; }
-    const double lkk = sqrt(dk);
-    __syncwarp();
-    if (lane == k) St[k * Q + k] = lkk;
-    if (lane > k && lane < Q) St[lane * Q + k] /= lkk;
-    __syncwarp();
-    const int mtr = Q - k - 1;
-    for (int e = lane; e < mtr * mtr; e += 32) {
-      const int i = k + 1 + e / mtr, j = k + 1 + e % mtr;
-      if (j <= i) St[i * Q + j] = fma(-St[i * Q + k], St[j * Q + k], St[i * Q + j]);
+    if (lane == 0) {
+      s_misc[2] = sigma; s_misc[5] = sC; s_misc[6] = Dm; s_misc[7] = cy;
+      *s_flag = (P > 0 && !(BC(P - 1) != 0.0)) ? BMFM_ST_NONFINITE : 0;   // -cap/0 in R (CrossSection.py:70)
     }
-    __syncwarp();
   }
-  if (!fail) {
-    // three right-hand sides, lanes over (rhs, row)
+  group_sync<WARP>();
+  // S2: reduced matrices in d-units, one task per thread: St lower triangle, then t, bt, gs0
+  {
+    const double W0 = BW(P), b0 = BWY(P);
+    constexpr int NTRI = Q * (Q + 1) / 2;
+    for (int e = tid; e < NTRI + 2 * Q; e += nt) {
+      if (e < NTRI) {
+        int q = 0;
+        while ((q + 1) * (q + 2) / 2 <= e) ++q;
+        const int r = e - q * (q + 1) / 2;    // r <= q
+        double a0 = S2[e], a1 = 0.0;
+        int b = 0;
+        for (; b + 1 < P; b += 2) {
+          a0 = fma(-BD(b, q) * winv[b], BD(b, r), a0);
+          a1 = fma(-BD(b + 1, q) * winv[b + 1], BD(b + 1, r), a1);
+        }
+        if (b < P) a0 = fma(-BD(b, q) * winv[b], BD(b, r), a0);
+        const double mq = s_mp[q], mr = s_mp[r];
+        St[q * Q + r] = a0 + a1 - mq * BD(P, r) - mr * BD(P, q) + mq * mr * W0;
+      } else if (e < NTRI + Q) {
+        const int q = e - NTRI;
+        const double mq = s_mp[q];
+        double t = 0.0;
+        for (int b = 0; b < P; ++b)
+          if (winv[b] > 0.0) t = fma(BD(b, q) * winv[b] - mq, BC(b), t);
+        rhs[Q + q] = t;
+        rhs[q] = BD(P, q) - mq * W0;
+      } else {
+        const int q = e - NTRI - Q;
+        double bt = BY[q];
+        for (int b = 0; b < P; ++b) bt = fma(-BD(b, q) * winv[b], BWY(b), bt);
+        rhs[2 * Q + q] = bt - s_mp[q] * b0;
+      }
+    }
+  }
+  group_sync<WARP>();
+  // S3: warp 0 — Gauss-Jordan in registers, 2x2 Schur system, coefficients
+  if (tid < 32) {
+    int fail = *s_flag;
+    const double sigma = s_misc[2], sC = s_misc[5], Dm = s_misc[6], cy = s_misc[7];
+    const double W0 = BW(P), b0 = BWY(P);
+    double a[QQ + 3];
+    double og0 = 0.0, ot = 0.0, d0 = 1.0;
+    const int row = lane < Q ? lane : 0;
+#pragma unroll
+    for (int j = 0; j < Q; ++j) a[j] = (j <= row) ? St[row * Q + j] : St[j * Q + row];
+    if (Q > 0) {
+      a[Q] = rhs[row]; a[Q + 1] = rhs[Q + row]; a[Q + 2] = rhs[2 * Q + row];
+      og0 = a[Q]; ot = a[Q + 1];
+#pragma unroll
+      for (int j = 0; j < Q; ++j) if (j == row) d0 = a[j];
+    }
+#pragma unroll
     for (int k = 0; k < Q; ++k) {
-      const double lkk = St[k * Q + k];
-      if (lane < 3) rhs[lane * Q + k] /= lkk;
-      __syncwarp();
-      for (int e = lane; e < 3 * Q; e += 32) {
-        const int r = e / Q, i = e - r * Q;
-        if (i > k) rhs[e] = fma(-St[i * Q + k], rhs[r * Q + k], rhs[e]);
+      const double piv = __shfl_sync(0xffffffffu, a[k], k);
+      const double dk0 = __shfl_sync(0xffffffffu, d0, k);
+      if (!(piv > 1e-11 * dk0) || !(dk0 > 0.0)) { if (!fail) fail = REG_NEED_DENSE; }
+      const double inv = 1.0 / piv;
+      const double f = (lane == k) ? 0.0 : a[k] * inv;
+#pragma unroll
+      for (int j = k + 1; j < Q + 3; ++j) {
+        const double pr = __shfl_sync(0xffffffffu, a[j], k);
+        a[j] = (lane == k) ? pr * inv : fma(-f, pr, a[j]);
       }
-      __syncwarp();
     }
-    for (int k = Q - 1; k >= 0; --k) {
-      const double lkk = St[k * Q + k];
-      if (lane < 3) rhs[lane * Q + k] /= lkk;
-      __syncwarp();
-      for (int e = lane; e < 3 * Q; e += 32) {
-        const int r = e / Q, i = e - r * Q;
-        if (i < k) rhs[e] = fma(-St[k * Q + i], rhs[r * Q + k], rhs[e]);
-      }
-      __syncwarp();
-    }
-    // 2x2 Schur system for (f_c, mu')
-    double g0x0 = 0, g0x1 = 0, g0x2 = 0, tx1 = 0, tx2 = 0;
-    if (lane < Q) {
-      g0x0 = org[lane] * rhs[lane];
-      g0x1 = org[lane] * rhs[Q + lane];
-      g0x2 = org[lane] * rhs[2 * Q + lane];
-      tx1 = org[Q + lane] * rhs[Q + lane];
-      tx2 = org[Q + lane] * rhs[2 * Q + lane];
-    }
-    g0x0 = warp_sum(g0x0); g0x1 = warp_sum(g0x1); g0x2 = warp_sum(g0x2);
-    tx1 = warp_sum(tx1); tx2 = warp_sum(tx2);
+    // a[Q + r] on lane i is now x_r[i] = (St^-1 rhs_r)[i]
+    double x0 = 0.0, x1 = 0.0, x2 = 0.0;
+    if (Q > 0 && lane < Q) { x0 = a[Q]; x1 = a[Q + 1]; x2 = a[Q + 2]; } else { og0 = 0.0; ot = 0.0; }
+    const double g0x0 = warp_sum(og0 * x0), g0x1 = warp_sum(og0 * x1), g0x2 = warp_sum(og0 * x2);
+    const double tx1 = warp_sum(ot * x1), tx2 = warp_sum(ot * x2);
     const double M00 = W0 - g0x0, M01 = sC - g0x1, M11 = -Dm - tx1;
     const double r0 = b0 - g0x2, r1 = cy - tx2;
     double fc, mu;
     if (P > 0) {
       const double det = M00 * M11 - M01 * M01;
-      if (!(fabs(det) > 1e-12 * (fabs(M00 * M11) + M01 * M01))) fail = REG_NEED_DENSE;
+      if (!(fabs(det) > 1e-12 * (fabs(M00 * M11) + M01 * M01)) && !fail) fail = REG_NEED_DENSE;
       fc = (r0 * M11 - M01 * r1) / det;
       mu = (M00 * r1 - M01 * r0) / det;
     } else {
-      if (!(M00 > 1e-12 * W0)) fail = REG_NEED_DENSE;
+      if (!(M00 > 1e-12 * W0) && !fail) fail = REG_NEED_DENSE;
       fc = r0 / M00;
       mu = 0.0;
     }
     double bsum = 0.0;
     if (lane < Q) {
-      const double be = rhs[2 * Q + lane] - rhs[lane] * fc - rhs[Q + lane] * mu;
+      const double be = x2 - x0 * fc - x1 * mu;
       s_beta[lane] = be;
       s_f[1 + P + lane] = be * sigma;
       bsum = be * s_mp[lane];
     }
     bsum = warp_sum(bsum);
     __syncwarp();
+    int bad = 0;
     for (int b = lane; b < NB; b += 32) {
       double g = 0.0;
       if (b < P && winv[b] > 0.0) {
         double eb = 0.0;
+#pragma unroll
         for (int q = 0; q < Q; ++q) eb = fma(BD(b, q) * winv[b] - s_mp[q], s_beta[q], eb);
         g = BWY(b) * winv[b] - eb + mu * BC(b) * winv[b] - fc;
       }
       s_g[b] = g;
       if (b < P) s_f[1 + b] = g;
+      bad |= !isfinite(g);
     }
+    if (lane < Q) bad |= !isfinite(s_beta[lane] * sigma);
+    bad |= !isfinite(fc);
+    bad = __any_sync(0xffffffffu, bad);
     if (lane == 0) {
       s_f[0] = fc;
       s_misc[1] = fc - bsum;   // c0: intercept on the pivot-shifted styles
-      s_misc[2] = sigma;
+      if (bad && fail != REG_NEED_DENSE) fail = BMFM_ST_NONFINITE;
+      *s_flag = fail;
     }
-    __syncwarp();
-    // any non-finite coefficient -> numpy would have raised / produced NaN
-    int bad = 0;
-    for (int k = lane; k < K; k += 32) bad |= !isfinite(s_f[k]);
-    bad = __any_sync(0xffffffffu, bad);
-    if (bad && fail != REG_NEED_DENSE) fail = BMFM_ST_NONFINITE;
   }
 #undef BW
 #undef BWY
 #undef BC
 #undef BD
-  return __shfl_sync(0xffffffffu, fail, 0);
+  group_sync<WARP>();
+  (void)K;
+  return *s_flag;
 }
 
 // ---- pass C: specific returns and R2 from coefficients in shared memory -------------------
@@ -819,7 +845,6 @@ template <int Q>
 __global__ void __launch_bounds__(256) reg_fast_kernel(RegParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const RegSmem L = reg_smem_layout(p.tile_rows, p.P, Q, blockDim.x >> 5, false);
-  int* s_flag = reinterpret_cast<int*>(smem + L.seg) + 3 * (p.P + 1) + 2;
   const double* s_f = reinterpret_cast<const double*>(smem + L.fvec);
   for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
     const long long a = p.date_off[t];
@@ -831,12 +856,7 @@ __global__ void __launch_bounds__(256) reg_fast_kernel(RegParams p) {
     }
     int ntiles;
     accumulate_date<Q>(p, L, smem, a, n, ntiles);
-    if (threadIdx.x < 32) {
-      const int st = solve_fast_warp0<Q>(p, L, smem, n);
-      if (threadIdx.x == 0) *s_flag = st;
-    }
-    __syncthreads();
-    const int st = *s_flag;
+    const int st = solve_fast_cta<Q, false>(p, L, smem, n);
     if (st == BMFM_ST_OK) {
       for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = s_f[k];
       residual_date<Q>(p, L, smem, a, n, ntiles, t);
@@ -879,6 +899,229 @@ __global__ void __launch_bounds__(256) reg_dense_kernel(RegParams p) {
   }
 }
 
+// ---- streaming kernel: one WARP per date (small cross-sections) ---------------------------------
+// For N of a few hundred to ~2000 stocks a CTA per date spends most of its time in barriers around
+// short serial phases.  Here every warp owns a date end to end and never meets a CTA barrier: rows
+// flow through a per-warp cp.async ring (32-row chunks, 4 stages), pass A accumulates in registers
+// (25 rows per lane at N = 800, one warp reduction per date), the per-industry sums are a running
+// walk (lane = value column, flush on industry change), the solve is the same block elimination,
+// and pass C replays the date through the ring — the second read is served by the 126 MB L2 (the
+// in-flight footprint of 8 warps x 148 SMs x 80 KB is below it), so HBM still sees ~one read.
+constexpr int RS_STAGES = 4;
+
+template <int Q>
+__host__ __device__ constexpr int rs_stage_bytes() { return 32 * (Q * 8 + 8 + 8 + 4); }
+
+template <int Q>
+__device__ __forceinline__ void rs_issue_chunk(const RegParams& p, long long row0, int m, bool with_cap,
+                                               unsigned char* stage, int lane) {
+  double* st_style = reinterpret_cast<double*>(stage);
+  double* st_cap = st_style + 32 * Q;
+  double* st_ret = st_cap + 32;
+  int* st_ind = reinterpret_cast<int*>(st_ret + 32);
+  if (lane < m) {
+    if (with_cap) cp_async_8(&st_cap[lane], p.cap + row0 + lane);
+    cp_async_8(&st_ret[lane], p.ret + row0 + lane);
+    cp_async_4(&st_ind[lane], p.ind + row0 + lane);
+  }
+  if (Q > 0) {
+    const double* src = p.style + row0 * Q;
+    const int tot = m * Q;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+      const int n16 = tot >> 1;
+      for (int e = lane; e < n16; e += 32) cp_async_16(&st_style[2 * e], src + 2 * e);
+      if ((tot & 1) && lane == 0) cp_async_8(&st_style[tot - 1], src + tot - 1);
+    } else {
+      for (int e = lane; e < tot; e += 32) cp_async_8(&st_style[e], src + e);
+    }
+  }
+  asm volatile("cp.async.commit_group;\n" ::: "memory");
+}
+
+template <int Q>
+__global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  constexpr int NA1PAD = na1pad_of(Q), NA2PAD = na2pad_of(Q);
+  constexpr int QQ = Q > 0 ? Q : 1;
+  constexpr int SB = rs_stage_bytes<Q>();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int P = p.P, NB = P + 1, BV = 3 + Q, K = p.K;
+  const RegSmem L = reg_smem_layout(0, P, Q, 1, false);
+  const int per_warp = align16(L.total + RS_STAGES * SB + 32 * 8 + 16);
+  unsigned char* wsm = smem + (size_t)warp * per_warp;
+  unsigned char* ring = wsm + L.total;
+  double* s_w = reinterpret_cast<double*>(ring + RS_STAGES * SB);
+  double* s_one = s_w + 32;
+  double* s_bucket = reinterpret_cast<double*>(wsm + L.bucket);
+  double* s_acc = reinterpret_cast<double*>(wsm + L.acc);
+  double* s_piv = reinterpret_cast<double*>(wsm + L.coef);
+  double* s_beta = s_piv + 2 * Q;
+  double* s_g = s_beta + Q;
+  double* s_misc = s_g + NB;
+  const double* s_f = reinterpret_cast<const double*>(wsm + L.fvec);
+  if (lane == 0) *s_one = 1.0;
+  const int gw = blockIdx.x * nwarps + warp, tw = gridDim.x * nwarps;
+  // lane roles of the per-industry walk: two row streams x 16 value columns
+  const int h = lane >> 4, v = lane & 15;
+  const bool vact = v < BV;
+
+  for (int t = gw; t < p.T; t += tw) {
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    if (n <= 0) {
+      for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = nan;
+      if (lane == 0) { p.r2[t] = nan; p.status[t] = BMFM_ST_NONFINITE; }
+      continue;
+    }
+    const int nchunks = (n + 31) >> 5;
+    for (int e = lane; e < NB * BV; e += 32) s_bucket[e] = 0.0;
+    if (lane < Q) s_piv[lane] = p.style[a * Q + lane];
+    if (lane == 0) s_misc[0] = p.ret[a];
+    // prologue of the ring
+#pragma unroll
+    for (int c = 0; c < RS_STAGES - 1; ++c) {
+      if (c < nchunks) rs_issue_chunk<Q>(p, a + 32 * c, min(32, n - 32 * c), true, ring + c * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    __syncwarp();
+    const double ypiv = s_misc[0];
+    double acc1[NA1PAD];
+    double acc2[NA2PAD];
+#pragma unroll
+    for (int i = 0; i < NA1PAD; ++i) acc1[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < NA2PAD; ++i) acc2[i] = 0.0;
+    int curb = -1;
+    double bacc = 0.0;
+    const double pv = (v >= 3 && vact) ? s_piv[v - 3] : 0.0;
+
+    for (int c = 0; c < nchunks; ++c) {
+      const int cn = c + RS_STAGES - 1;
+      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), true, ring + (cn % RS_STAGES) * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(RS_STAGES - 1) : "memory");
+      __syncwarp();
+      unsigned char* stage = ring + (c % RS_STAGES) * SB;
+      const double* st_style = reinterpret_cast<const double*>(stage);
+      const double* st_cap = st_style + 32 * Q;
+      const double* st_ret = st_cap + 32;
+      const int* st_ind = reinterpret_cast<const int*>(st_ret + 32);
+      const int m = min(32, n - 32 * c);
+      if (lane < m) {
+        const double cap = st_cap[lane];
+        const double w = sqrt(cap);
+        s_w[lane] = w;
+        const double y = st_ret[lane];
+        const double u = y - ypiv;
+        acc2[3 * Q] += u;
+        acc2[3 * Q + 1] = fma(u, u, acc2[3 * Q + 1]);
+        if (Q > 0) {
+          double d[QQ];
+          load_row_styles<Q>(st_style, lane, s_piv, d);
+#pragma unroll
+          for (int q = 0; q < Q; ++q) {
+            const double wd = w * d[q];
+#pragma unroll
+            for (int r = 0; r <= q; ++r) acc1[q * (q + 1) / 2 + r] = fma(wd, d[r], acc1[q * (q + 1) / 2 + r]);
+            acc1[Q * (Q + 1) / 2 + q] = fma(wd, y, acc1[Q * (Q + 1) / 2 + q]);
+            acc2[q] = fma(cap, d[q], acc2[q]);
+            acc2[Q + q] += d[q];
+            acc2[2 * Q + q] = fma(d[q], d[q], acc2[2 * Q + q]);
+          }
+        }
+      }
+      __syncwarp();
+      // per-industry running sums: lane = value column, flush when the industry changes
+      {
+        const double* Ap = (v == 2) ? st_cap : s_w;
+        const double* Bp = (v == 1) ? st_ret : (v >= 3 ? st_style + (v - 3) : s_one);
+        const int sB = (v == 1) ? 1 : (v >= 3 ? Q : 0);
+        const int rlo = h * 16, rhi = min(m, rlo + 16);
+        for (int r = rlo; r < rhi; ++r) {
+          const int b = bucket_of(st_ind[r], P);
+          if (b != curb) {
+            if (curb >= 0 && vact) atomicAdd(&s_bucket[curb * BV + v], bacc);
+            bacc = 0.0;
+            curb = b;
+          }
+          if (vact) bacc = fma(Ap[r], Bp[r * sB] - pv, bacc);
+        }
+      }
+      __syncwarp();   // the stage may be refilled by the next iteration's loads
+    }
+    if (curb >= 0 && vact) atomicAdd(&s_bucket[curb * BV + v], bacc);
+    // start refilling the ring for pass C while the solve runs (served by L2)
+#pragma unroll
+    for (int c = 0; c < RS_STAGES - 1; ++c) {
+      if (c < nchunks) rs_issue_chunk<Q>(p, a + 32 * c, min(32, n - 32 * c), false, ring + c * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    warp_reduce_scatter<NA1PAD>(acc1, lane);
+#pragma unroll
+    for (int i = 0; i < NA1PAD / 32; ++i) s_acc[reduce_scatter_index<NA1PAD>(i, lane)] = acc1[i];
+    warp_reduce_scatter<NA2PAD>(acc2, lane);
+#pragma unroll
+    for (int i = 0; i < NA2PAD / 32; ++i) s_acc[NA1PAD + reduce_scatter_index<NA2PAD>(i, lane)] = acc2[i];
+    __syncwarp();
+    const int st = solve_fast_cta<Q, true>(p, L, wsm, n);
+    if (st != BMFM_ST_OK) {
+      // drain the prefetched ring before leaving the date
+      asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+      __syncwarp();
+      if (st == REG_NEED_DENSE) {
+        if (lane == 0) p.status[t] = REG_NEED_DENSE;
+      } else {
+        for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = nan;
+        for (int i = lane; i < n; i += 32) p.spec[a + i] = nan;
+        if (lane == 0) { p.r2[t] = nan; p.status[t] = st; }
+      }
+      continue;
+    }
+    for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = s_f[k];
+    // pass C
+    const double c0 = s_misc[1];
+    double se = 0.0, see = 0.0;
+    for (int c = 0; c < nchunks; ++c) {
+      const int cn = c + RS_STAGES - 1;
+      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), false, ring + (cn % RS_STAGES) * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(RS_STAGES - 1) : "memory");
+      __syncwarp();
+      unsigned char* stage = ring + (c % RS_STAGES) * SB;
+      const double* st_style = reinterpret_cast<const double*>(stage);
+      const double* st_ret = st_style + 32 * Q + 32;
+      const int* st_ind = reinterpret_cast<const int*>(st_ret + 32);
+      const int m = min(32, n - 32 * c);
+      if (lane < m) {
+        double e = st_ret[lane] - c0 - s_g[bucket_of(st_ind[lane], P)];
+        if (Q > 0) {
+          double d[QQ];
+          load_row_styles<Q>(st_style, lane, s_piv, d);
+#pragma unroll
+          for (int q = 0; q < Q; ++q) e = fma(-s_beta[q], d[q], e);
+        }
+        st_stream(p.spec + a + 32 * c + lane, e);
+        se += e;
+        see = fma(e, e, see);
+      }
+      __syncwarp();
+    }
+    se = warp_sum(se);
+    see = warp_sum(see);
+    if (lane == 0) {
+      const double dn = (double)n;
+      const double me = se / dn;
+      const double var_e = see / dn - me * me;
+      const double my = s_acc[NA1PAD + 3 * Q] / dn;
+      const double var_y = s_acc[NA1PAD + 3 * Q + 1] / dn - my * my;
+      p.r2[t] = 1.0 - var_e / var_y;
+      p.status[t] = BMFM_ST_OK;
+    }
+    __syncwarp();
+  }
+}
+
 // ---- host side ---------------------------------------------------------------------------------
 template <int Q>
 static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
@@ -899,7 +1142,21 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
   p.tile_rows = rows;
-  if (!p.all_dense) {
+  // small cross-sections: warp-per-date streaming kernel (BMFM_REG_MODE=1 forces the CTA kernel, 2 the stream kernel)
+  int mode = 0;
+  if (const char* ev = getenv("BMFM_REG_MODE")) mode = atoi(ev);
+  const bool use_stream = mode == 2 || (mode == 0 && max_rows > 0 && max_rows <= 2048);
+  if (!p.all_dense && use_stream) {
+    const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);
+    const int per_warp = align16(Lw.total + RS_STAGES * rs_stage_bytes<Q>() + 32 * 8 + 16);
+    const int smem_s = 4 * per_warp;
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_stream_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
+    int grid = ctx->sm_count * 2;
+    if (grid * 4 > p.T) grid = (p.T + 3) / 4;
+    reg_stream_kernel<Q><<<grid, 128, smem_s, ctx->stream>>>(p);
+    ctx->launches++;
+    BMFM_CUDA(ctx, cudaGetLastError());
+  } else if (!p.all_dense) {
     BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_fast_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
     int grid = ctx->sm_count * per_sm;
     if (grid > p.T) grid = p.T;

@@ -30,7 +30,9 @@ def _case(reg, case):
 
 @pytest.mark.parametrize("case", ["small", "csi", "nostyle_scale"])
 @pytest.mark.parametrize("grouped", [True, False])
-def test_golden_reference_outputs(ops, reg_golden, case, grouped):
+@pytest.mark.parametrize("mode", ["1", "2"])     # 1: CTA-per-date kernel, 2: warp-per-date streaming kernel
+def test_golden_reference_outputs(ops, reg_golden, case, grouped, mode, monkeypatch):
+    monkeypatch.setenv("BMFM_REG_MODE", mode)
     g = _case(reg_golden, case)
     fr, spec, r2, status, _ = ops.reg_by_time(g["date_off"], g["cap"], g["ret"], g["ind"], g["style"],
                                               int(g["P"]), group_by_industry=grouped)
@@ -68,7 +70,9 @@ def test_golden_exposure(ops, reg_golden, case):
     (3, 70, 63, 12, 0.0, (0, 0)),         # compiled limits; N < K -> pinv path
     (2, 5000, 31, 10, 0.02, (-2, 2)),     # full A-share cross-section (config C3): multi-tile path
 ])
-def test_oracle_parity(ops, T, N, P, Q, ragged, scale):
+@pytest.mark.parametrize("mode", ["0", "1", "2"])   # auto / CTA-per-date / warp-per-date streaming
+def test_oracle_parity(ops, T, N, P, Q, ragged, scale, mode, monkeypatch):
+    monkeypatch.setenv("BMFM_REG_MODE", mode)
     from bmfm.synth import make_panel
     from oracle import barra_oracle as orc
     pan = make_panel(T, N, P, Q, seed=100 + N, ragged=ragged, scale_log10=scale)
@@ -98,7 +102,8 @@ def test_host_buffer_entry_point(ops):
                          fr, spec, r2, st)
     fr2, spec2, r22, _, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P,
                                             group_by_industry=False)
-    assert np.array_equal(fr, fr2) and np.array_equal(spec, spec2) and np.array_equal(r2, r22)
+    # same kernels, same order of rows; the ungrouped path sums with shared-memory atomics, so compare to rounding
+    assert relerr(fr, fr2) < 1e-12 and relerr(spec, spec2) < 1e-12 and np.max(np.abs(r2 - r22)) < 1e-12
 
 
 def test_last_industry_empty_raises(ops):
