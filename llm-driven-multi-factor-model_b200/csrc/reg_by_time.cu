@@ -911,6 +911,13 @@ constexpr int RS_STAGES = 4;
 
 template <int Q>
 __host__ __device__ constexpr int rs_stage_bytes() { return 32 * (Q * 8 + 8 + 8 + 4); }
+// per-row staging of the 3+Q per-industry terms; odd stride (in doubles) keeps the row-per-lane
+// stores and the column-per-lane loads free of bank conflicts
+constexpr int RS_ZS = 17;
+template <int Q>
+__host__ __device__ inline int rs_per_warp_bytes(int fixed) {
+  return align16(fixed + RS_STAGES * rs_stage_bytes<Q>() + 32 * RS_ZS * 8 + 16);
+}
 
 template <int Q>
 __device__ __forceinline__ void rs_issue_chunk(const RegParams& p, long long row0, int m, bool with_cap,
@@ -928,9 +935,18 @@ __device__ __forceinline__ void rs_issue_chunk(const RegParams& p, long long row
     const double* src = p.style + row0 * Q;
     const int tot = m * Q;
     if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-      const int n16 = tot >> 1;
-      for (int e = lane; e < n16; e += 32) cp_async_16(&st_style[2 * e], src + 2 * e);
-      if ((tot & 1) && lane == 0) cp_async_8(&st_style[tot - 1], src + tot - 1);
+      if (m == 32) {
+        // full chunk: 16*Q pieces of 16 B, a compile-time trip count per lane
+#pragma unroll
+        for (int j = 0; j < (16 * Q + 31) / 32; ++j) {
+          const int e = lane + 32 * j;
+          if (e < 16 * Q) cp_async_16(&st_style[2 * e], src + 2 * e);
+        }
+      } else {
+        const int n16 = tot >> 1;
+        for (int e = lane; e < n16; e += 32) cp_async_16(&st_style[2 * e], src + 2 * e);
+        if ((tot & 1) && lane == 0) cp_async_8(&st_style[tot - 1], src + tot - 1);
+      }
     } else {
       for (int e = lane; e < tot; e += 32) cp_async_8(&st_style[e], src + e);
     }
@@ -947,11 +963,10 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int P = p.P, NB = P + 1, BV = 3 + Q, K = p.K;
   const RegSmem L = reg_smem_layout(0, P, Q, 1, false);
-  const int per_warp = align16(L.total + RS_STAGES * SB + 32 * 8 + 16);
+  const int per_warp = rs_per_warp_bytes<Q>(L.total);
   unsigned char* wsm = smem + (size_t)warp * per_warp;
   unsigned char* ring = wsm + L.total;
-  double* s_w = reinterpret_cast<double*>(ring + RS_STAGES * SB);
-  double* s_one = s_w + 32;
+  double* s_z = reinterpret_cast<double*>(ring + RS_STAGES * SB);   // [32][RS_ZS] per-row bucket terms
   double* s_bucket = reinterpret_cast<double*>(wsm + L.bucket);
   double* s_acc = reinterpret_cast<double*>(wsm + L.acc);
   double* s_piv = reinterpret_cast<double*>(wsm + L.coef);
@@ -959,7 +974,6 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
   double* s_g = s_beta + Q;
   double* s_misc = s_g + NB;
   const double* s_f = reinterpret_cast<const double*>(wsm + L.fvec);
-  if (lane == 0) *s_one = 1.0;
   const int gw = blockIdx.x * nwarps + warp, tw = gridDim.x * nwarps;
   // lane roles of the per-industry walk: two row streams x 16 value columns
   const int h = lane >> 4, v = lane & 15;
@@ -976,13 +990,19 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
     }
     const int nchunks = (n + 31) >> 5;
     for (int e = lane; e < NB * BV; e += 32) s_bucket[e] = 0.0;
-    if (lane < Q) s_piv[lane] = p.style[a * Q + lane];
-    if (lane == 0) s_misc[0] = p.ret[a];
     // prologue of the ring
 #pragma unroll
     for (int c = 0; c < RS_STAGES - 1; ++c) {
       if (c < nchunks) rs_issue_chunk<Q>(p, a + 32 * c, min(32, n - 32 * c), true, ring + c * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    // the pivot shift is the date's first row: take it from chunk 0 once it has landed
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(RS_STAGES - 2) : "memory");
+    __syncwarp();
+    {
+      const double* st0 = reinterpret_cast<const double*>(ring);
+      if (lane < Q) s_piv[lane] = st0[lane];
+      if (lane == 0) s_misc[0] = st0[32 * Q + 32];
     }
     __syncwarp();
     const double ypiv = s_misc[0];
@@ -994,7 +1014,6 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
     for (int i = 0; i < NA2PAD; ++i) acc2[i] = 0.0;
     int curb = -1;
     double bacc = 0.0;
-    const double pv = (v >= 3 && vact) ? s_piv[v - 3] : 0.0;
 
     for (int c = 0; c < nchunks; ++c) {
       const int cn = c + RS_STAGES - 1;
@@ -1011,8 +1030,11 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
       if (lane < m) {
         const double cap = st_cap[lane];
         const double w = sqrt(cap);
-        s_w[lane] = w;
         const double y = st_ret[lane];
+        double* zr = s_z + lane * RS_ZS;
+        zr[0] = w;
+        zr[1] = w * y;
+        zr[2] = cap;
         const double u = y - ypiv;
         acc2[3 * Q] += u;
         acc2[3 * Q + 1] = fma(u, u, acc2[3 * Q + 1]);
@@ -1022,6 +1044,7 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
 #pragma unroll
           for (int q = 0; q < Q; ++q) {
             const double wd = w * d[q];
+            zr[3 + q] = wd;
 #pragma unroll
             for (int r = 0; r <= q; ++r) acc1[q * (q + 1) / 2 + r] = fma(wd, d[r], acc1[q * (q + 1) / 2 + r]);
             acc1[Q * (Q + 1) / 2 + q] = fma(wd, y, acc1[Q * (Q + 1) / 2 + q]);
@@ -1032,38 +1055,63 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
         }
       }
       __syncwarp();
-      // per-industry running sums: lane = value column, flush when the industry changes
+      // per-industry running sums: lane = value column (two row streams of 16), flush when the
+      // industry changes.  Run starts come from one ballot; the terms were staged by pass A.
       {
-        const double* Ap = (v == 2) ? st_cap : s_w;
-        const double* Bp = (v == 1) ? st_ret : (v >= 3 ? st_style + (v - 3) : s_one);
-        const int sB = (v == 1) ? 1 : (v >= 3 ? Q : 0);
+        const int myb = lane < m ? bucket_of(st_ind[lane], P) : -2;
+        const int prevb = __shfl_up_sync(0xffffffffu, myb, 1);
+        const unsigned runstart = __ballot_sync(0xffffffffu, lane > 0 && lane < m && myb != prevb);
         const int rlo = h * 16, rhi = min(m, rlo + 16);
-        for (int r = rlo; r < rhi; ++r) {
-          const int b = bucket_of(st_ind[r], P);
-          if (b != curb) {
-            if (curb >= 0 && vact) atomicAdd(&s_bucket[curb * BV + v], bacc);
-            bacc = 0.0;
-            curb = b;
+        const int bfirst = __shfl_sync(0xffffffffu, myb, rlo);
+        if (rlo < rhi) {
+          unsigned flush = (runstart >> rlo) & 0xffffu;
+          flush = (flush & ~1u) | (bfirst != curb ? 1u : 0u);
+          const double* zc = s_z + rlo * RS_ZS + v;
+          for (int r = 0; r < rhi - rlo; ++r) {
+            if ((flush >> r) & 1u) {
+              if (curb >= 0 && vact) atomicAdd(&s_bucket[curb * BV + v], bacc);
+              bacc = 0.0;
+              curb = bucket_of(st_ind[rlo + r], P);
+            }
+            if (vact) bacc += zc[r * RS_ZS];
           }
-          if (vact) bacc = fma(Ap[r], Bp[r * sB] - pv, bacc);
         }
       }
       __syncwarp();   // the stage may be refilled by the next iteration's loads
     }
     if (curb >= 0 && vact) atomicAdd(&s_bucket[curb * BV + v], bacc);
+    // warp reduction of the register accumulators through the (now idle) ring: every lane stores
+    // its values as a column, then each lane sums one row — no shuffles, ~1/7 of the instructions
+    {
+      constexpr int NA1 = na1_of(Q), NA2 = na2_of(Q), NTOT = NA1 + NA2;
+      constexpr int RWX = (RS_STAGES * SB) / (33 * 8), RW = RWX < 48 ? RWX : 48;   // rows of 33 doubles that fit the ring
+      static_assert(RW >= 1, "ring too small for the reduction buffer");
+      double* red = reinterpret_cast<double*>(ring);
+#pragma unroll
+      for (int r0 = 0; r0 < NTOT; r0 += RW) {
+#pragma unroll
+        for (int j = 0; j < RW; ++j) {
+          const int i = r0 + j;
+          if (i < NTOT) red[j * 33 + lane] = (i < NA1) ? acc1[i < NA1 ? i : 0] : acc2[i >= NA1 ? i - NA1 : 0];
+        }
+        __syncwarp();
+        for (int j = lane; j < RW && r0 + j < NTOT; j += 32) {
+          const double* row = red + j * 33;
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+          for (int l = 0; l < 32; l += 4) { s0 += row[l]; s1 += row[l + 1]; s2 += row[l + 2]; s3 += row[l + 3]; }
+          const int i = r0 + j;
+          s_acc[i < NA1 ? i : NA1PAD + (i - NA1)] = (s0 + s1) + (s2 + s3);
+        }
+        __syncwarp();
+      }
+    }
     // start refilling the ring for pass C while the solve runs (served by L2)
 #pragma unroll
     for (int c = 0; c < RS_STAGES - 1; ++c) {
       if (c < nchunks) rs_issue_chunk<Q>(p, a + 32 * c, min(32, n - 32 * c), false, ring + c * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
-    warp_reduce_scatter<NA1PAD>(acc1, lane);
-#pragma unroll
-    for (int i = 0; i < NA1PAD / 32; ++i) s_acc[reduce_scatter_index<NA1PAD>(i, lane)] = acc1[i];
-    warp_reduce_scatter<NA2PAD>(acc2, lane);
-#pragma unroll
-    for (int i = 0; i < NA2PAD / 32; ++i) s_acc[NA1PAD + reduce_scatter_index<NA2PAD>(i, lane)] = acc2[i];
-    __syncwarp();
     const int st = solve_fast_cta<Q, true>(p, L, wsm, n);
     if (st != BMFM_ST_OK) {
       // drain the prefetched ring before leaving the date
@@ -1148,7 +1196,7 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   const bool use_stream = mode == 2 || (mode == 0 && max_rows > 0 && max_rows <= 2048);
   if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);
-    const int per_warp = align16(Lw.total + RS_STAGES * rs_stage_bytes<Q>() + 32 * 8 + 16);
+    const int per_warp = rs_per_warp_bytes<Q>(Lw.total);
     const int smem_s = 4 * per_warp;
     BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_stream_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
     int grid = ctx->sm_count * 2;
