@@ -47,7 +47,8 @@ enum {
   BMFM_ST_SHORT = 1,     /* t <= q or t <= K: the reference raises, caller stores an empty DataFrame (utils.py:29, MFM.py:95-96) */
   BMFM_ST_NOT_PSD = 2,   /* eigen_risk_adj PSD gate failed (utils.py:67-68) -> empty DataFrame */
   BMFM_ST_NONFINITE = 3, /* non-finite Gram (e.g. last industry empty, CrossSection.py:70) -> numpy raises LinAlgError */
-  BMFM_ST_PINV = 4       /* informational: rank-deficient Gram, eigen-based pinv path was used (CrossSection.py:76) */
+  BMFM_ST_PINV = 4,      /* informational: rank-deficient Gram, eigen-based pinv path was used (CrossSection.py:76) */
+  BMFM_ST_DUP_EDGES = 5  /* bayes_shrink: duplicate decile edges, pd.qcut raises ValueError (utils.py:161) */
 };
 
 /* ---- context ------------------------------------------------------------ */
@@ -142,6 +143,59 @@ int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, const double
                              const int32_t* status, double* vsum, int accumulate);
 int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double scale_coef, const double* D0,
                         const double* U0, const double* vsum, const int32_t* status, double* out);
+
+/*
+ * Replaces utils.bayes_shrink with group_mean_std / shrink (Barra-master/mfm/utils.py:133-168),
+ * batched over dates.  The reference defines no caller; inputs are whatever
+ * specific-volatility and capital vectors the caller has, grouped by date like the regression.
+ *   volatility, capital, out  double [rows];  status int32 [T]: BMFM_ST_DUP_EDGES where pd.qcut
+ *   would raise "Bin edges must be unique".  ngroup <= 64; at most 16384 rows per date.
+ * Decile codes are bit-exact with pd.qcut(capital, ngroup).codes.
+ */
+int bmfm_bayes_shrink(bmfm_ctx* ctx, int T, int max_rows_per_date, const int64_t* date_off,
+                      const double* volatility, const double* capital, int ngroup, double q,
+                      double* out, int32_t* status);
+
+/* ---- part 2: descriptors -------------------------------------------------- */
+/*
+ * Dense [L][S] panels in row-index-major order: element (r, s) = the r-th row of stock s (its own
+ * rows in date order, what groupby('ts_code').rolling walks), NaN = missing / padding.
+ *
+ * bmfm_prepare_returns: ret = close / close.shift(1) - 1, log_ret = log(close) - log(close.shift(1))
+ *   per stock (Barra_factor_cal/factor_calculator.py:50-51); either output may be NULL.
+ * bmfm_beta_hsigma: FactorCalculator.compute_beta_hsigma (factor_calculator.py:79-125): rolling
+ *   `window` rows, rows with NaN in ret or mkt dropped, >= min_periods valid, weights
+ *   0.5^(rank/half_life) by rank among valid rows; BETA = WLS slope of ret on mkt (with intercept),
+ *   HSIGMA = sqrt(sum w e^2 / (n - 2)).  mkt is the per-row market return [L*S].
+ * bmfm_dastd: compute_dastd (factor_calculator.py:155-196): same windows on ret - mkt, normalised
+ *   weights, weighted standard deviation.
+ * bmfm_cmra: compute_cmra (factor_calculator.py:199-234): all `window` (<= 256) rows present,
+ *   ln(1 + max Z) - ln(1 + min Z) with Z = exp(cumsum(log_ret)) - 1.
+ */
+int bmfm_prepare_returns(bmfm_ctx* ctx, int L, int S, const double* close, double* ret, double* log_ret);
+int bmfm_beta_hsigma(bmfm_ctx* ctx, int L, int S, const double* ret, const double* mkt, int window,
+                     double half_life, int min_periods, double* beta, double* hsigma);
+int bmfm_dastd(bmfm_ctx* ctx, int L, int S, const double* ret, const double* mkt, int window,
+               double half_life, int min_periods, double* out);
+int bmfm_cmra(bmfm_ctx* ctx, int L, int S, const double* log_ret, int window, double* out);
+
+/*
+ * Per-date post-processing on the long table grouped by date (date_off int64 [T+1], one fp64 array
+ * per column, NaN = missing):
+ * bmfm_winsorize: winsorize_factors (Barra_factor_cal/post_processing.py:7-24) for one column:
+ *   clip to mean +- n_std * std, pandas semantics (NaN skipped, ddof 1).
+ * bmfm_composite: calculate_composite_factors (post_processing.py:26-45):
+ *   sum_i w_i x_i(NaN->0) / sum_i w_i notna(x_i).  components / weights are HOST arrays (of device
+ *   pointers / doubles), ncomp <= 8.
+ * bmfm_orthogonalize: orthogonalize_factors (post_processing.py:47-70) for one dependent column:
+ *   OLS residual of y ~ 1 + X on complete-case rows, NaN elsewhere, all-NaN when fewer than k + 2
+ *   complete rows.  X is a HOST array of k <= 6 device pointers.
+ */
+int bmfm_winsorize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, double n_std, double* out);
+int bmfm_composite(bmfm_ctx* ctx, int64_t rows, int ncomp, const double* const* components,
+                   const double* weights, double* out);
+int bmfm_orthogonalize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* y, int k,
+                       const double* const* X, double* out);
 
 #ifdef __cplusplus
 }

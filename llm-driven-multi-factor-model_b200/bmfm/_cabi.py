@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbmfm.so")
 
 # status codes (include/bmfm.h)
-ST_OK, ST_SHORT, ST_NOT_PSD, ST_NONFINITE, ST_PINV = 0, 1, 2, 3, 4
+ST_OK, ST_SHORT, ST_NOT_PSD, ST_NONFINITE, ST_PINV, ST_DUP_EDGES = 0, 1, 2, 3, 4, 5
 
 _lib = None
 _lock = threading.Lock()
@@ -40,6 +40,14 @@ _SIGNATURES = {
     "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_eigen_mc_accumulate": ([_P, _I, _I, _I, _P, _P, _P, _P, _I], _I),
     "bmfm_eigen_finalize": ([_P, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
+    "bmfm_bayes_shrink": ([_P, _I, _I, _P, _P, _P, _I, _D, _P, _P], _I),
+    "bmfm_prepare_returns": ([_P, _I, _I, _P, _P, _P], _I),
+    "bmfm_beta_hsigma": ([_P, _I, _I, _P, _P, _I, _D, _I, _P, _P], _I),
+    "bmfm_dastd": ([_P, _I, _I, _P, _P, _I, _D, _I, _P], _I),
+    "bmfm_cmra": ([_P, _I, _I, _P, _I, _P], _I),
+    "bmfm_winsorize": ([_P, _I, _P, _P, _D, _P], _I),
+    "bmfm_composite": ([_P, C.c_int64, _I, _P, _P, _P], _I),
+    "bmfm_orthogonalize": ([_P, _I, _P, _P, _I, _P, _P], _I),
 }
 
 
@@ -163,6 +171,40 @@ class Context:
     def eigen_finalize(self, T, K, M, scale_coef, D0, U0, vsum, status, out):
         self.check(self._L.bmfm_eigen_finalize(self._h, T, K, M, float(scale_coef), ptr(D0), ptr(U0), ptr(vsum),
                                                ptr(status), ptr(out)))
+
+
+    def bayes_shrink(self, T, max_rows, date_off, vol, cap, ngroup, q, out, status):
+        self.check(self._L.bmfm_bayes_shrink(self._h, T, max_rows, ptr(date_off), ptr(vol), ptr(cap), int(ngroup),
+                                             float(q), ptr(out), ptr(status)))
+
+    # ------------------------------------------------------------------ part 2
+    def prepare_returns(self, L, S, close, ret, log_ret):
+        self.check(self._L.bmfm_prepare_returns(self._h, L, S, ptr(close), ptr(ret), ptr(log_ret)))
+
+    def beta_hsigma(self, L, S, ret, mkt, window, half_life, min_periods, beta, hsigma):
+        self.check(self._L.bmfm_beta_hsigma(self._h, L, S, ptr(ret), ptr(mkt), int(window), float(half_life),
+                                            int(min_periods), ptr(beta), ptr(hsigma)))
+
+    def dastd(self, L, S, ret, mkt, window, half_life, min_periods, out):
+        self.check(self._L.bmfm_dastd(self._h, L, S, ptr(ret), ptr(mkt), int(window), float(half_life),
+                                      int(min_periods), ptr(out)))
+
+    def cmra(self, L, S, log_ret, window, out):
+        self.check(self._L.bmfm_cmra(self._h, L, S, ptr(log_ret), int(window), ptr(out)))
+
+    def winsorize(self, T, date_off, x, n_std, out):
+        self.check(self._L.bmfm_winsorize(self._h, T, ptr(date_off), ptr(x), float(n_std), ptr(out)))
+
+    def composite(self, rows, comps, weights, out):
+        n = len(comps)
+        arr = (C.c_void_p * n)(*[t.data_ptr() for t in comps])
+        w = (C.c_double * n)(*[float(x) for x in weights])
+        self.check(self._L.bmfm_composite(self._h, rows, n, arr, w, ptr(out)))
+
+    def orthogonalize(self, T, date_off, y, Xs, out):
+        k = len(Xs)
+        arr = (C.c_void_p * k)(*[t.data_ptr() for t in Xs])
+        self.check(self._L.bmfm_orthogonalize(self._h, T, ptr(date_off), ptr(y), k, arr, ptr(out)))
 
 
 _default_ctx = {}

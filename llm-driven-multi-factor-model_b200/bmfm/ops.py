@@ -152,3 +152,97 @@ def eigen_risk_adj_by_time(cov, cov_status, T_sim, M=100, scale_coef=1.4, ctx=No
     d_st = _dev(np.asarray(cov_status, dtype=np.int32)) if cov_status is not None else None
     out, status = eigen_risk_adj_device(ctx, _dev(np.asarray(cov, dtype=np.float64)), d_st, T_sim, M, scale_coef)
     return out.cpu().numpy(), status.cpu().numpy()
+
+
+def bayes_shrink_by_time(date_off, volatility, capital, ngroup=10, q=1, ctx=None):
+    """utils.bayes_shrink on every date of a date-major table -> (out [rows], status [T])."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    date_off = np.asarray(date_off, dtype=np.int64)
+    T = len(date_off) - 1
+    vol = _dev(np.asarray(volatility, dtype=np.float64))
+    cap = _dev(np.asarray(capital, dtype=np.float64))
+    out = torch.empty_like(vol)
+    status = torch.empty(T, dtype=torch.int32, device=vol.device)
+    max_rows = int(np.diff(date_off).max()) if T else 0
+    ctx.bayes_shrink(T, max_rows, _dev(date_off), vol, cap, ngroup, q, out, status)
+    return out.cpu().numpy(), status.cpu().numpy()
+
+
+# ---------------------------------------------------------------------------- part 2
+def prepare_returns(close, ctx=None):
+    """close [L, S] (row-index-major per stock, NaN = missing) -> (ret, log_ret)."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    c = _dev(np.asarray(close, dtype=np.float64))
+    L, S = c.shape
+    ret = torch.empty_like(c)
+    lr = torch.empty_like(c)
+    ctx.prepare_returns(L, S, c, ret, lr)
+    return ret.cpu().numpy(), lr.cpu().numpy()
+
+
+def beta_hsigma(ret, mkt, window=252, half_life=63, min_periods=42, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    r = _dev(np.asarray(ret, dtype=np.float64))
+    m = _dev(np.ascontiguousarray(np.broadcast_to(np.asarray(mkt, dtype=np.float64), r.shape)))
+    L, S = r.shape
+    b = torch.empty_like(r)
+    h = torch.empty_like(r)
+    ctx.beta_hsigma(L, S, r, m, window, half_life, min_periods, b, h)
+    return b.cpu().numpy(), h.cpu().numpy()
+
+
+def dastd(ret, mkt, window=252, half_life=42, min_periods=42, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    r = _dev(np.asarray(ret, dtype=np.float64))
+    m = _dev(np.ascontiguousarray(np.broadcast_to(np.asarray(mkt, dtype=np.float64), r.shape)))
+    L, S = r.shape
+    o = torch.empty_like(r)
+    ctx.dastd(L, S, r, m, window, half_life, min_periods, o)
+    return o.cpu().numpy()
+
+
+def cmra(log_ret, window=252, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    r = _dev(np.asarray(log_ret, dtype=np.float64))
+    L, S = r.shape
+    o = torch.empty_like(r)
+    ctx.cmra(L, S, r, window, o)
+    return o.cpu().numpy()
+
+
+def winsorize(date_off, x, n_std=2.5, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    date_off = np.asarray(date_off, dtype=np.int64)
+    xd = _dev(np.asarray(x, dtype=np.float64))
+    out = torch.empty_like(xd)
+    ctx.winsorize(len(date_off) - 1, _dev(date_off), xd, n_std, out)
+    return out.cpu().numpy()
+
+
+def composite(components, weights, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    comps = [_dev(np.asarray(c, dtype=np.float64)) for c in components]
+    out = torch.empty_like(comps[0])
+    ctx.composite(comps[0].numel(), comps, weights, out)
+    return out.cpu().numpy()
+
+
+def orthogonalize(date_off, y, X, ctx=None):
+    """X: list of columns (or [rows, k] array)."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    date_off = np.asarray(date_off, dtype=np.int64)
+    X = np.asarray(X, dtype=np.float64)
+    cols = [X] if X.ndim == 1 else [np.ascontiguousarray(X[:, j]) for j in range(X.shape[1])]
+    yd = _dev(np.asarray(y, dtype=np.float64))
+    Xd = [_dev(c) for c in cols]
+    out = torch.empty_like(yd)
+    ctx.orthogonalize(len(date_off) - 1, _dev(date_off), yd, Xd, out)
+    return out.cpu().numpy()

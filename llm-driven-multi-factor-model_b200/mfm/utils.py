@@ -104,3 +104,16 @@ def shrink(x, group_weight_mean, q):
     v = a / (a + b)
     SH_est = v * group_weight_mean[x['group']][0] + (1 - v) * np.abs(x['volatility'])
     return (SH_est)
+
+
+def bayes_shrink(volatility, capital, ngroup=10, q=1):
+    '''
+    使用市值对特异性收益率波动率进行贝叶斯收缩 (utils.py:153-168); one cross-section on the GPU
+    '''
+    vol = np.asarray(volatility, dtype=np.float64)
+    cap = np.asarray(capital, dtype=np.float64)
+    out, status = _ops.bayes_shrink_by_time(np.array([0, len(vol)], dtype=np.int64), vol, cap, ngroup, q)
+    if status[0] == _cabi.ST_DUP_EDGES:
+        raise ValueError("Bin edges must be unique: duplicate quantile edges of capital "
+                         "(pd.qcut raises the same, utils.py:161)")
+    return (out)

@@ -255,7 +255,8 @@ def qcut_codes(x, ngroup):
     quantiles, bins right-closed with the lowest edge included, duplicate edges
     raise ValueError."""
     x = np.asarray(x, dtype=np.float64)
-    edges = np.quantile(x, np.linspace(0, 1, ngroup + 1))
+    # pandas: Series.quantile(linspace) -> np.percentile(values, qs * 100.0) (method 'linear')
+    edges = np.percentile(x, np.linspace(0, 1, ngroup + 1) * 100.0)
     if len(np.unique(edges)) < len(edges):
         raise ValueError("Bin edges must be unique")
     codes = np.searchsorted(edges, x, side="left") - 1
