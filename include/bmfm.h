@@ -111,6 +111,21 @@ int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, double tao,
 size_t bmfm_newey_west_scratch_bytes(int T, int K, int q);
 
 /*
+ * No counterpart in the reference: an addition for hosts that must not allocate device memory
+ * at call time (GPU memory handed out in full at start-up to pools the library does not own;
+ * loops that cannot absorb the device-wide stall of cudaMalloc/cudaFree).
+ * Same arguments and results as bmfm_newey_west_by_time, but the chunk-state scratch is a fixed
+ * 16 MiB array inside the library image (held by every GPU that loads the library, until exit)
+ * and no path through the call allocates.  Sizes whose state does not fit are refused with
+ * BMFM_E_UNSUPPORTED (K = 42, q = 2 fits for any T up to about 35 000).  The first call on a
+ * device looks up the array's device address — make it before any stream capture.  Calls on one
+ * device share the array: nothing in it needs clearing between calls, but calls that overlap on
+ * the GPU race on it, so serialise them.
+ */
+int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                                    const double* factor_ret, double* cov, int32_t* status);
+
+/*
  * Replaces MFM.vol_regime_adj_by_time (Barra-master/mfm/MFM.py:130-167).
  *   cov [T*K*K] with cov_status [T] (NULL = all valid; dates with status != 0/4 are the
  *   reference's empty DataFrames); out_cov [T*K*K] = cov * lamb^2 (NaN where invalid; may be

@@ -35,6 +35,7 @@ _SIGNATURES = {
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
+    "bmfm_newey_west_by_time_noalloc": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_vol_regime_adj_by_time": ([_P, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
     "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
@@ -152,6 +153,12 @@ class Context:
     # ------------------------------------------------------------------ part 3
     def newey_west_by_time(self, T, K, q, tao, fr, cov, status):
         self.check(self._L.bmfm_newey_west_by_time(self._h, T, K, q, float(tao), ptr(fr), ptr(cov), ptr(status)))
+
+    def newey_west_by_time_noalloc(self, T, K, q, tao, fr, cov, status):
+        """Newey-West with the library's built-in fixed scratch: for callers that may not allocate
+        device memory at call time.  Refuses sizes beyond the fixed array (BmfmError)."""
+        self.check(self._L.bmfm_newey_west_by_time_noalloc(self._h, T, K, q, float(tao), ptr(fr), ptr(cov),
+                                                           ptr(status)))
 
     def vol_regime_adj_by_time(self, T, K, tao, fr, cov, cov_status, out_cov, lamb):
         self.check(self._L.bmfm_vol_regime_adj_by_time(self._h, T, K, float(tao), ptr(fr), ptr(cov),

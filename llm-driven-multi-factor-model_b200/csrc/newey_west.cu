@@ -259,3 +259,90 @@ extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, doubl
   if (rc) return rc;
   return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Newey-West without any allocation
+// ---------------------------------------------------------------------------------------------
+// Some hosts of this library are not allowed to allocate device memory when they call it: a risk
+// service whose GPU memory was carved up at start-up (every byte belongs to a pool it does not
+// own, so a cudaMalloc from inside a library can fail or push another tenant over its budget), or
+// a latency-bound loop that cannot tolerate the device-wide synchronisation a cudaMalloc/cudaFree
+// implies.  bmfm_newey_west_by_time() grows the context workspace with cudaMalloc on first use;
+// the entry point below never does.  Its chunk-state scratch is this fixed array, which lives in
+// the library image: every GPU that loads libbmfm.so holds these 16 MiB until the process exits.
+constexpr size_t NW_STATIC_DOUBLES = (size_t)1 << 21;   // 2 Mi doubles = 16 MiB
+static __device__ __align__(256) double nw_static_scratch[NW_STATIC_DOUBLES];
+
+// In host code `nw_static_scratch` is only a handle for the runtime, not a device address, so the
+// address is looked up once per device (with that device current) and cached here.
+constexpr int NW_MAX_DEVICES = 64;
+static double* nw_static_ptr[NW_MAX_DEVICES];
+
+// chunk length that keeps nchunks * nstate inside the static array (0 if impossible)
+static int nw_static_chunk(int T, int K, int q) {
+  const size_t ns = (size_t)nw_nstate(K, q);
+  const size_t max_chunks = NW_STATIC_DOUBLES / ns;
+  if (max_chunks == 0) return 0;
+  int C = (T + 295) / 296;
+  if (C < 8) C = 8;
+  const size_t need = ((size_t)T + max_chunks - 1) / max_chunks;   // smallest C with ceil(T/C) <= max_chunks
+  if ((size_t)C < need) C = (int)need;
+  return C;
+}
+
+// Same computation and results as bmfm_newey_west_by_time, with no cudaMalloc, cudaFree or other
+// allocating call on any path.
+//   * Limits: q <= 4, and (1+q)(K^2+1) + (1+2q)K doubles of state per chunk must fit the 16 MiB
+//     array with chunks short enough for shared memory (K = 42, q = 2: any T up to ~35 000);
+//     larger problems are rejected with BMFM_E_UNSUPPORTED and a message, nothing is launched.
+//   * The first call on a device resolves the array's device address (cudaGetSymbolAddress);
+//     make that first call before starting any stream capture.
+//   * All calls on a device share the one array and it keeps whatever the previous call left.
+//     Nothing in it has to start at zero — the first kernel of a call writes every cell that the
+//     later kernels read — but two calls whose kernels overlap on the GPU (different streams or
+//     contexts, same device) race on it; serialise them.
+extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                                               const double* factor_ret, double* cov, int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && q >= 0 && tao > 0, "bad sizes");
+  BMFM_ARG(ctx, factor_ret && cov && status, "NULL pointer");
+  if (q > NW_MAX_Q) {
+    snprintf(ctx->err, sizeof(ctx->err), "q=%d exceeds compiled limit %d", q, NW_MAX_Q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  if (T == 0) return BMFM_OK;
+  if (ctx->device < 0 || ctx->device >= NW_MAX_DEVICES) {
+    snprintf(ctx->err, sizeof(ctx->err), "device %d outside the no-alloc table (%d devices)", ctx->device, NW_MAX_DEVICES);
+    return BMFM_E_UNSUPPORTED;
+  }
+  NwParams p;
+  p.T = T; p.K = K; p.q = q;
+  p.C = nw_static_chunk(T, K, q);
+  const size_t smem = p.C > 0 ? ((size_t)(p.C + q) * K + (size_t)p.C * (1 + 2 * q) * K + (size_t)p.C * (1 + q)) * 8 : 0;
+  if (p.C == 0 || smem > (size_t)ctx->max_smem_optin) {
+    snprintf(ctx->err, sizeof(ctx->err),
+             "newey_west noalloc: T=%d K=%d q=%d needs more than the fixed %zu-byte scratch; "
+             "use bmfm_newey_west_by_time", T, K, q, NW_STATIC_DOUBLES * sizeof(double));
+    return BMFM_E_UNSUPPORTED;
+  }
+  p.nchunks = (T + p.C - 1) / p.C;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (nw_static_ptr[ctx->device] == nullptr) {
+    double* dptr = nullptr;
+    BMFM_CUDA(ctx, cudaGetSymbolAddress((void**)&dptr, nw_static_scratch));
+    nw_static_ptr[ctx->device] = dptr;
+  }
+  p.lam = pow(0.5, 1.0 / tao);
+  p.fr = factor_ret; p.cov = cov; p.status = status;
+  p.state = nw_static_ptr[ctx->device];
+  nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
+  ctx->launches++;
+  const int ns = nw_nstate(K, q);
+  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  nw_emit<<<p.nchunks, 256, smem, ctx->stream>>>(p);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}

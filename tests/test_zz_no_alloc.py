@@ -1,0 +1,56 @@
+"""The allocation-free Newey-West entry point (bmfm_newey_west_by_time_noalloc).
+
+Who needs it: a host process whose GPU memory was divided up front among pools this library
+does not own (a library-side cudaMalloc could fail there, or eat someone else's share), and
+loops that cannot afford the device-wide stall that cudaMalloc / cudaFree cause.  The regular
+entry point grows a workspace on first use; this one keeps its chunk states in a fixed array
+inside the library and must give the same covariances.
+
+The file name sorts last on purpose: a run that stops at the first failure has then already
+been through every other test.  It passes on its own in a fresh process as well (the first call
+on a device does the one-time address look-up).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(ctx, fn, fr, q, tao):
+    import torch
+    T, K = fr.shape
+    d_fr = torch.from_numpy(fr).cuda()
+    cov = torch.empty((T, K, K), dtype=torch.float64, device="cuda")
+    st = torch.empty(T, dtype=torch.int32, device="cuda")
+    fn(T, K, q, tao, d_fr, cov, st)
+    torch.cuda.synchronize()
+    return cov.cpu().numpy(), st.cpu().numpy()
+
+
+def test_noalloc_matches_regular_entry_twice_in_a_row():
+    from bmfm import _cabi
+    from bmfm.synth import make_factor_returns
+    ctx = _cabi.default_context()
+    # two calls in a row with different sizes: the second one finds the first one's leftovers in
+    # the shared array and must not be affected by them
+    for (T, K, q, tao, seed) in [(900, 42, 2, 252.0, 1), (300, 17, 3, 40.0, 2)]:
+        fr = make_factor_returns(T, K, seed=seed) + 0.002
+        got, got_st = _run(ctx, ctx.newey_west_by_time_noalloc, fr, q, tao)
+        want, want_st = _run(ctx, ctx.newey_west_by_time, fr, q, tao)
+        assert np.array_equal(got_st, want_st)
+        ok = want_st == 0
+        assert ok.any() and np.isnan(got[~ok]).all()
+        scale = np.abs(want[ok]).max()
+        assert np.abs(got[ok] - want[ok]).max() <= 1e-11 * scale     # same tolerance as test_risk_gpu.py
+
+
+def test_noalloc_rejects_oversized_problems():
+    import torch
+    from bmfm import _cabi
+    ctx = _cabi.default_context()
+    K, T = 400, 500      # (1+q)(K^2+1) doubles per chunk: too many chunks of shared-memory size for 16 MiB
+    fr = torch.zeros((T, K), dtype=torch.float64, device="cuda")
+    cov = torch.empty((1,), dtype=torch.float64, device="cuda")
+    st = torch.empty(T, dtype=torch.int32, device="cuda")
+    with pytest.raises(_cabi.BmfmError, match="fixed"):
+        ctx.newey_west_by_time_noalloc(T, K, 2, 252.0, fr, cov, st)
