@@ -66,55 +66,63 @@ def load_traffic():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons sampled DURING the timed region (NVML, every ~5 ms; the
+    nvidia-smi loop of B200_PROFILING.md is too coarse for a region of tens of milliseconds)."""
 
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index):
         self.gpu = gpu_index
-        self.rows = []
-        self.proc = None
+        self.sm, self.reasons = [], set()
+        self.sm_max = None
+        self._stop = threading.Event()
+        self.thread = None
+        self.err = None
+
+    def _loop(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES; map through the UUID when it is set
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.gpu
+            if vis:
+                ent = vis.split(",")[self.gpu].strip()
+                if ent.isdigit():
+                    idx = int(ent)
+                    h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+                else:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(ent.encode() if hasattr(ent, "encode") else ent)
+            else:
+                h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            while not self._stop.is_set():
+                self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.004)
+        except Exception as e:      # noqa: BLE001
+            self.err = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
-                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            parts = [x.strip() for x in line.split(",")]
-            if len(parts) >= 8:
-                self.rows.append(parts)
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
+        time.sleep(0.02)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-            except ValueError:
-                continue
-            for n, v in zip(names, r[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        self._stop.set()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        out = {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+               "samples": len(self.sm), "reasons": sorted(self.reasons)}
+        if self.err:
+            out["error"] = self.err
+        return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -222,6 +230,7 @@ def run_gpu(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ["NCCL_DEBUG"] = os.environ.get("BENCH_NCCL_DEBUG", "WARN")   # keep NCCL's banner off stdout
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -245,10 +254,16 @@ def run_gpu(args):
     spec = torch.empty(rows, dtype=torch.float64, device=dev)
     r2 = torch.empty(T, dtype=torch.float64, device=dev)
     st = torch.empty(T, dtype=torch.int32, device=dev)
-    nw = torch.empty((T_all, K, K), dtype=torch.float64, device=dev)
-    nw_st = torch.empty(T_all, dtype=torch.int32, device=dev)
-    vr = torch.empty((T_all, K, K), dtype=torch.float64, device=dev)
+    # every rank keeps the covariance matrices of ITS dates only
+    nw = torch.empty((T, K, K), dtype=torch.float64, device=dev)
+    nw_st = torch.empty(T, dtype=torch.int32, device=dev)
+    vr = torch.empty((T, K, K), dtype=torch.float64, device=dev)
     lamb = torch.empty(T_all, dtype=torch.float64, device=dev)
+    # vol-regime terms of this rank's dates, packed [wb | wv] so that one all-gather moves both
+    wbv = torch.empty((2, T), dtype=torch.float64, device=dev)
+    wbv_all = torch.empty((world, 2, T), dtype=torch.float64, device=dev)
+    wb_all = torch.empty(T_all, dtype=torch.float64, device=dev)
+    wv_all = torch.empty(T_all, dtype=torch.float64, device=dev)
     out_host = {"fr": torch.empty((T, K), dtype=torch.float64).pin_memory(),
                 "spec": torch.empty(rows, dtype=torch.float64).pin_memory(),
                 "r2": torch.empty(T, dtype=torch.float64).pin_memory(),
@@ -265,12 +280,21 @@ def run_gpu(args):
         e[1].record()
         if world > 1:
             dist.all_gather_into_tensor(fr_all, fr)
-        # every rank needs the decayed moments of all earlier dates: the recurrence is replayed over the
-        # gathered series (cheap: T_all*K doubles in, this rank's dates' matrices are the ones it keeps)
-        ctx.newey_west_by_time(T_all, K, NW_Q, NW_TAO, fr_all, nw, nw_st)
+        # the recurrence reads the whole gathered series (T_all*K doubles) and emits this rank's dates only
+        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
         e[2].record()
-        ctx.vol_regime_adj_by_time(T_all, K, VR_TAO, fr_all, nw, nw_st, vr, lamb)
+        vol_regime()
         e[3].record()
+
+    def vol_regime():
+        if world == 1:
+            ctx.vol_regime_adj_by_time(T, K, VR_TAO, fr, nw, nw_st, vr, lamb)
+        else:
+            ctx.vol_regime_bias(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wbv[0], wbv[1])
+            dist.all_gather_into_tensor(wbv_all, wbv)
+            wb_all.view(world, T).copy_(wbv_all[:, 0])
+            wv_all.view(world, T).copy_(wbv_all[:, 1])
+            ctx.vol_regime_scale(T_all, lo, T, K, wb_all, wv_all, nw, nw_st, vr, lamb)
 
     def barrier():
         if world > 1:
@@ -318,12 +342,12 @@ def run_gpu(args):
         ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
         if world > 1:
             dist.all_gather_into_tensor(fr_all, fr)
-        ctx.newey_west_by_time(T_all, K, NW_Q, NW_TAO, fr_all, nw, nw_st)
-        ctx.vol_regime_adj_by_time(T_all, K, VR_TAO, fr_all, nw, nw_st, vr, lamb)
+        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
+        vol_regime()
         out_host["fr"].copy_(fr, non_blocking=True)
         out_host["spec"].copy_(spec, non_blocking=True)
         out_host["r2"].copy_(r2, non_blocking=True)
-        out_host["vr"].copy_(vr[lo:lo + T], non_blocking=True)
+        out_host["vr"].copy_(vr, non_blocking=True)
         out_host["lamb"].copy_(lamb[lo:lo + T], non_blocking=True)
 
     for _ in range(max(1, args.warmup // 2)):
@@ -344,8 +368,11 @@ def run_gpu(args):
     from bmfm import ops
     sims_per_rank = EIG_SIMS // world
     m_lo = rank * sims_per_rank
-    covs = nw[T_all - EIG_DATES:].contiguous()
-    csts = nw_st[T_all - EIG_DATES:].contiguous()
+    covs = nw[T - EIG_DATES:].contiguous()      # the same rank-local dates on every rank: only the sims are sharded
+    csts = nw_st[T - EIG_DATES:].contiguous()
+    if world > 1:
+        dist.broadcast(covs, 0)
+        dist.broadcast(csts, 0)
     D0 = torch.empty((EIG_DATES, K), dtype=torch.float64, device=dev)
     U0 = torch.empty((EIG_DATES, K, K), dtype=torch.float64, device=dev)
     est = torch.empty(EIG_DATES, dtype=torch.int32, device=dev)
@@ -389,7 +416,7 @@ def run_gpu(args):
             "config": {"workload": f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES} per GPU, P={P}, Q={Q}: reg_by_time + "
                                    f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})",
                        "parallelism": f"dates sharded over {world} GPU(s); all-gather of factor returns" if world > 1 else "1 GPU",
-                       "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T_all * K * K * 8 / 1e6:.0f} MB of covariance output per step vs 126 MB L2",
+                       "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
                        "all_status_ok": status_ok},
             "roofline": {"kernel": "reg_fast_kernel<10> (per-date Gram + constrained solve + residuals)",

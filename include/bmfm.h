@@ -109,6 +109,11 @@ int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
 int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, double tao,
                             const double* factor_ret, double* cov, int32_t* status);
 size_t bmfm_newey_west_scratch_bytes(int T, int K, int q);
+/* Same for the dates [t0, t1) only (date-sharded runs): factor_ret is still the WHOLE series
+ * [T * K]; cov [(t1-t0) * K * K] and status [t1-t0] hold this block. */
+int bmfm_newey_west_by_time_range(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                                  const double* factor_ret, int t0, int t1, double* cov,
+                                  int32_t* status);
 
 /*
  * No counterpart in the reference: an addition for hosts that must not allocate device memory
@@ -134,6 +139,16 @@ int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int q, double t
 int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double tao, const double* factor_ret,
                                 const double* cov, const int32_t* cov_status, double* out_cov,
                                 double* lamb);
+/* The same pass split for date-sharded runs (MFM.py:149-163): _bias gives this rank's block
+ * (n dates from global date t0 of T_total) of weighted bias terms wb = w_t B_t^2, wv = w_t; the
+ * caller gathers them over ranks in date order; _scale turns the gathered terms into lamb_all
+ * [T_total] and scales this rank's block (out_cov_block may be NULL). */
+int bmfm_vol_regime_bias(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                         const double* factor_ret_block, const double* cov_block,
+                         const int32_t* cov_status_block, double* wb, double* wv);
+int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, int K, const double* wb_all,
+                          const double* wv_all, const double* cov_block,
+                          const int32_t* cov_status_block, double* out_cov_block, double* lamb_all);
 
 /*
  * Eigenfactor Monte-Carlo adjustment, utils.eigen_risk_adj (Barra-master/mfm/utils.py:55-92)

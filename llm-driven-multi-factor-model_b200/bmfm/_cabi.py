@@ -35,6 +35,9 @@ _SIGNATURES = {
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
+    "bmfm_newey_west_by_time_range": ([_P, _I, _I, _I, _D, _P, _I, _I, _P, _P], _I),
+    "bmfm_vol_regime_bias": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
+    "bmfm_vol_regime_scale": ([_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P], _I),
     "bmfm_newey_west_by_time_noalloc": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_vol_regime_adj_by_time": ([_P, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
@@ -153,6 +156,18 @@ class Context:
     # ------------------------------------------------------------------ part 3
     def newey_west_by_time(self, T, K, q, tao, fr, cov, status):
         self.check(self._L.bmfm_newey_west_by_time(self._h, T, K, q, float(tao), ptr(fr), ptr(cov), ptr(status)))
+
+    def newey_west_by_time_range(self, T, K, q, tao, fr, t0, t1, cov, status):
+        self.check(self._L.bmfm_newey_west_by_time_range(self._h, T, K, q, float(tao), ptr(fr), t0, t1, ptr(cov),
+                                                         ptr(status)))
+
+    def vol_regime_bias(self, T_total, t0, n, K, tao, fr_block, cov_block, status_block, wb, wv):
+        self.check(self._L.bmfm_vol_regime_bias(self._h, T_total, t0, n, K, float(tao), ptr(fr_block),
+                                                ptr(cov_block), ptr(status_block), ptr(wb), ptr(wv)))
+
+    def vol_regime_scale(self, T_total, t0, n, K, wb_all, wv_all, cov_block, status_block, out_block, lamb_all):
+        self.check(self._L.bmfm_vol_regime_scale(self._h, T_total, t0, n, K, ptr(wb_all), ptr(wv_all),
+                                                 ptr(cov_block), ptr(status_block), ptr(out_block), ptr(lamb_all)))
 
     def newey_west_by_time_noalloc(self, T, K, q, tao, fr, cov, status):
         """Newey-West with the library's built-in fixed scratch: for callers that may not allocate

@@ -1,0 +1,133 @@
+"""Multi-GPU plumbing for the risk-model path: one process per GPU,
+``torch.distributed`` (NCCL on GPUs, gloo in the CPU tests) for the few small
+exchanges the path has:
+
+* dates shard for the regression — no exchange;
+* factor returns are all-gathered (T x K doubles) so that every rank's
+  expanding Newey-West windows see the earlier ranks' dates;
+* the vol-regime sums need every date's weighted bias term: all-gather of
+  2 x T doubles;
+* the eigenfactor simulations can shard instead of the dates: all-reduce of
+  the T x K bias accumulators.
+
+``RiskPipeline`` holds only this orchestration; the arithmetic comes from a
+backend object (``GpuBackend`` = the C-ABI kernels).  The CPU tests run the same
+orchestration over gloo with an oracle-backed backend to check the exchange
+logic without a GPU.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_range(n, rank, world):
+    """Contiguous balanced block [lo, hi) of n items for `rank` of `world`."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_counts(n, world):
+    return [shard_range(n, r, world)[1] - shard_range(n, r, world)[0] for r in range(world)]
+
+
+def all_gather_rows(x, counts, group=None):
+    """Concatenate per-rank row blocks (rank r contributes counts[r] rows) in rank order."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return x
+    world = dist.get_world_size(group)
+    mx = max(counts)
+    pad = torch.zeros((mx,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    pad[: x.shape[0]] = x
+    outs = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(outs, pad, group=group)
+    return torch.cat([outs[r][: counts[r]] for r in range(world)], dim=0)
+
+
+def all_reduce_sum(x, group=None):
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(x, group=group)
+    return x
+
+
+class GpuBackend:
+    """The arithmetic of the pipeline on this process's GPU (C-ABI kernels)."""
+
+    def __init__(self, ctx=None):
+        from . import _cabi
+        self.ctx = ctx or _cabi.default_context()
+
+    def reg(self, T, P, Q, max_rows, off, cap, ret, ind, style):
+        from .ops import reg_by_time_device
+        fr, spec, r2, status, _ = reg_by_time_device(self.ctx, T, P, Q, max_rows, off, cap, ret, ind, style)
+        return fr, spec, r2, status
+
+    def newey_west_range(self, fr_all, t0, t1, q, tao):
+        import torch
+        T, K = fr_all.shape
+        cov = torch.empty((t1 - t0, K, K), dtype=torch.float64, device=fr_all.device)
+        st = torch.empty(t1 - t0, dtype=torch.int32, device=fr_all.device)
+        self.ctx.newey_west_by_time_range(T, K, q, tao, fr_all, t0, t1, cov, st)
+        return cov, st
+
+    def eigen(self, cov, status, T_sim, M, scale, sim_range=None, allreduce=None):
+        from .ops import eigen_risk_adj_device
+        return eigen_risk_adj_device(self.ctx, cov, status, T_sim, M, scale, sim_range, allreduce)
+
+    def vr_bias(self, T_total, t0, fr_block, cov_block, status_block, tao):
+        import torch
+        n, K = fr_block.shape
+        wb = torch.empty(n, dtype=torch.float64, device=fr_block.device)
+        wv = torch.empty(n, dtype=torch.float64, device=fr_block.device)
+        self.ctx.vol_regime_bias(T_total, t0, n, K, tao, fr_block, cov_block, status_block, wb, wv)
+        return wb, wv
+
+    def vr_scale(self, T_total, t0, wb_all, wv_all, cov_block, status_block):
+        import torch
+        n, K = cov_block.shape[0], cov_block.shape[1]
+        out = torch.empty_like(cov_block)
+        lamb = torch.empty(T_total, dtype=torch.float64, device=cov_block.device)
+        self.ctx.vol_regime_scale(T_total, t0, n, K, wb_all, wv_all, cov_block, status_block, out, lamb)
+        return out, lamb
+
+
+class RiskPipeline:
+    """reg_by_time -> Newey_West_by_time -> [eigen_risk_adj_by_time] -> vol_regime_adj_by_time with the
+    dates of the panel sharded over the ranks of `group` (demo.py:38-42, MFM.py:48-167)."""
+
+    def __init__(self, backend, rank=0, world=1, group=None):
+        self.b = backend
+        self.rank, self.world, self.group = rank, world, group
+
+    def run(self, counts, P, Q, max_rows, off, cap, ret, ind, style, q=2, tao_nw=252, tao_vr=84,
+            eigen=None):
+        """`counts[r]` = number of dates owned by rank r (date order = rank order); the panel arrays are
+        this rank's block.  `eigen` = None (vol-regime directly on the Newey-West covariances, BASELINE
+        config 2) or dict(T_sim=, M=, scale_coef=).  Returns a dict of this rank's blocks + lamb_all."""
+        T_total = int(sum(counts))
+        t0 = int(sum(counts[: self.rank]))
+        n = int(counts[self.rank])
+        fr, spec, r2, status = self.b.reg(n, P, Q, max_rows, off, cap, ret, ind, style)
+        fr_all = all_gather_rows(fr, counts, self.group)
+        nw, nw_st = self.b.newey_west_range(fr_all, t0, t0 + n, q, tao_nw)
+        cov, cov_st = nw, nw_st
+        if eigen is not None:
+            cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])
+        wb, wv = self.b.vr_bias(T_total, t0, fr, cov, cov_st, tao_vr)
+        wb_all = all_gather_rows(wb, counts, self.group)
+        wv_all = all_gather_rows(wv, counts, self.group)
+        vr, lamb_all = self.b.vr_scale(T_total, t0, wb_all, wv_all, cov, cov_st)
+        return {"factor_ret": fr, "factor_ret_all": fr_all, "specific_ret": spec, "R2": r2, "status": status,
+                "nw": nw, "nw_status": nw_st, "cov": cov, "cov_status": cov_st, "vr": vr,
+                "lamb_all": lamb_all, "t0": t0, "n": n}
+
+
+def eigen_sharded_by_sims(backend, cov_all, status_all, T_sim, M, scale_coef, rank, world, group=None):
+    """BASELINE config 4: every rank holds all dates' covariances and runs M/world simulations;
+    one all-reduce of the T x K accumulators, then every rank finalises (utils.py:71-92)."""
+    m_lo, m_hi = shard_range(M, rank, world)
+    return backend.eigen(cov_all, status_all, T_sim, M, scale_coef, sim_range=(m_lo, m_hi),
+                         allreduce=lambda t: all_reduce_sum(t, group))

@@ -29,6 +29,7 @@ constexpr int NW_MAX_Q = 4;
 
 struct NwParams {
   int T, K, q, C, nchunks;
+  int t0, t1, c_first;   // emit only dates [t0, t1) (chunks from c_first on), written at row t - t0
   double lam;
   const double* fr;   // [T][K]
   double* cov;        // [T][K][K]
@@ -106,7 +107,7 @@ __global__ void nw_chunk_scan(NwParams p) {
 // kernel 3: replay the chunk from its start state and emit V for every date in it
 __global__ void __launch_bounds__(256) nw_emit(NwParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int c = blockIdx.x, K = p.K, q = p.q, C = p.C;
+  const int c = p.c_first + blockIdx.x, K = p.K, q = p.q, C = p.C;
   const int r0 = c * C, r1 = min(p.T, r0 + C), len = r1 - r0;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int nm = (1 + q) * K * K;
@@ -196,12 +197,12 @@ __global__ void __launch_bounds__(256) nw_emit(NwParams p) {
           }
         }
       }
-      st_stream(p.cov + ((size_t)r * K + a) * K + b, out);
+      if (r >= p.t0 && r < p.t1) st_stream(p.cov + ((size_t)(r - p.t0) * K + a) * K + b, out);
     }
   }
   for (int j = tid; j < len; j += nt) {
-    const int L = r0 + j + 1;
-    p.status[r0 + j] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
+    const int r = r0 + j, L = r + 1;
+    if (r >= p.t0 && r < p.t1) p.status[r - p.t0] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
   }
 }
 
@@ -219,7 +220,7 @@ extern "C" size_t bmfm_newey_west_scratch_bytes(int T, int K, int q) {
 }
 
 static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const double* fr, double* cov,
-                     int32_t* status, double* scratch) {
+                     int32_t* status, double* scratch, int t0, int t1) {
   NwParams p;
   p.T = T; p.K = K; p.q = q;
   p.C = (T + 295) / 296;
@@ -227,6 +228,11 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
+  if (t0 < 0) t0 = 0;
+  if (t1 > T) t1 = T;
+  p.t0 = t0; p.t1 = t1;
+  p.c_first = t0 / p.C;
+  const int c_last = t1 > t0 ? (t1 - 1) / p.C : p.c_first - 1;
   nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
   ctx->launches++;
   const int ns = nw_nstate(K, q);
@@ -238,10 +244,32 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
     return BMFM_E_UNSUPPORTED;
   }
   BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  nw_emit<<<p.nchunks, 256, smem, ctx->stream>>>(p);
-  ctx->launches++;
+  if (c_last >= p.c_first) {
+    nw_emit<<<c_last - p.c_first + 1, 256, smem, ctx->stream>>>(p);
+    ctx->launches++;
+  }
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
+}
+
+// dates [t0, t1) only: cov [(t1-t0)*K*K], status [t1-t0].  The decayed moments of ALL earlier dates are
+// still accumulated (chunk totals + scan read the whole series, T*K doubles), so a rank that owns a block
+// of dates gets exactly the expanding-window result without any exchange beyond the factor returns.
+extern "C" int bmfm_newey_west_by_time_range(bmfm_ctx* ctx, int T, int K, int q, double tao,
+                                             const double* factor_ret, int t0, int t1, double* cov,
+                                             int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && q >= 0 && tao > 0 && t0 >= 0 && t1 >= t0 && t1 <= T, "bad sizes");
+  BMFM_ARG(ctx, factor_ret && (t1 == t0 || (cov && status)), "NULL pointer");
+  if (q > NW_MAX_Q) {
+    snprintf(ctx->err, sizeof(ctx->err), "q=%d exceeds compiled limit %d", q, NW_MAX_Q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  if (T == 0 || t1 == t0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
+  if (rc) return rc;
+  return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws, t0, t1);
 }
 
 extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, double tao,
@@ -257,7 +285,7 @@ extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, doubl
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
   if (rc) return rc;
-  return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws);
+  return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws, 0, T);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -334,6 +362,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   }
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;
+  p.t0 = 0; p.t1 = T; p.c_first = 0;
   p.state = nw_static_ptr[ctx->device];
   nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
   ctx->launches++;

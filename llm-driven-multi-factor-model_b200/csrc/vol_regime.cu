@@ -17,7 +17,7 @@ namespace bmfm {
 
 // one warp per date
 __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const double* cov,
-                               const int* cov_status, double* wb, double* wv) {
+                               const int* cov_status, double* wb, double* wv, int t_off, int T_total) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= T) return;
   const int t = warp;
@@ -40,7 +40,7 @@ __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const
   nanvar = __any_sync(0xffffffffu, nanvar);
   if (lane == 0) {
     const double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);   // B_t^2
-    const double w = pow(0.5, (double)(T - 1 - t) / tao);
+    const double w = pow(0.5, (double)(T_total - 1 - (t_off + t)) / tao);
     // rows whose variance vector holds a NaN are excluded from both sums (MFM.py:158)
     wb[t] = nanvar ? 0.0 : w * b2;
     wv[t] = nanvar ? 0.0 : w;
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(1024) vr_scan_kernel(int T, const double* wb, 
 }
 
 __global__ void vr_scale_kernel(int T, int KK, const double* cov, const int* cov_status, const double* lamb,
-                                double* out) {
+                                double* out) {   // lamb already offset to this block of dates
   const size_t total = (size_t)T * KK;
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
@@ -102,7 +102,7 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
   if (rc) return rc;
   double* wb = (double*)ctx->ws;
   double* wv = wb + T;
-  vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv);
+  vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv, 0, T);
   ctx->launches++;
   vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T, wb, wv, lamb);
   ctx->launches++;
@@ -112,6 +112,49 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
     const int cap = ctx->sm_count * 16;
     if (grid > cap) grid = cap;
     vr_scale_kernel<<<grid, 256, 0, ctx->stream>>>(T, K * K, cov, cov_status, lamb, out_cov);
+    ctx->launches++;
+  }
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// ---- the same pass split for date-sharded runs -------------------------------------------------
+// bmfm_vol_regime_bias: per-date weighted bias terms of this rank's block of n dates that starts at
+//   global date t0 of T_total:  wb[i] = w_t B_t^2, wv[i] = w_t (0 where the variance row is invalid).
+// The caller gathers wb / wv of all ranks in date order and calls
+// bmfm_vol_regime_scale: lamb over ALL T_total dates from the gathered terms, then this rank's
+//   block scaled by its own lamb values.  lamb_all [T_total]; out_cov [n*K*K] may be NULL.
+extern "C" int bmfm_vol_regime_bias(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                                    const double* factor_ret_block, const double* cov_block,
+                                    const int32_t* cov_status_block, double* wb, double* wv) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && t0 >= 0 && n >= 0 && t0 + n <= T_total && K > 0 && tao > 0, "bad sizes");
+  BMFM_ARG(ctx, n == 0 || (factor_ret_block && cov_block && wb && wv), "NULL pointer");
+  if (n == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  vr_bias_kernel<<<(n * 32 + 255) / 256, 256, 0, ctx->stream>>>(n, K, tao, factor_ret_block, cov_block,
+                                                              cov_status_block, wb, wv, t0, T_total);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, int K, const double* wb_all,
+                                     const double* wv_all, const double* cov_block,
+                                     const int32_t* cov_status_block, double* out_cov_block, double* lamb_all) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && t0 >= 0 && n >= 0 && t0 + n <= T_total && K > 0, "bad sizes");
+  BMFM_ARG(ctx, wb_all && wv_all && lamb_all, "NULL pointer");
+  if (T_total == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T_total, wb_all, wv_all, lamb_all);
+  ctx->launches++;
+  if (out_cov_block && n > 0) {
+    const size_t total = (size_t)n * K * K;
+    int grid = (int)((total + 255) / 256);
+    const int cap = ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    vr_scale_kernel<<<grid, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_all + t0, out_cov_block);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());

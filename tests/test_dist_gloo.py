@@ -1,0 +1,177 @@
+"""World-size-2 `gloo` tests (CPU) of the multi-GPU orchestration in bmfm/dist.py: the exchange logic
+(all-gather of factor returns and vol-regime terms, all-reduce of the eigen accumulators) is run with
+an oracle-backed backend and must reproduce the single-process oracle."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from bmfm import dist as bd
+from bmfm.synth import make_panel
+from oracle import barra_oracle as orc
+
+
+class OracleBackend:
+    """Same interface as bmfm.dist.GpuBackend, arithmetic from the CPU oracle (test only)."""
+
+    def reg(self, T, P, Q, max_rows, off, cap, ret, ind, style):
+        fr, spec, r2 = orc.reg_by_time(off.numpy(), cap.numpy(), ret.numpy(), ind.numpy(), style.numpy(), P)
+        return torch.from_numpy(fr), torch.from_numpy(spec), torch.from_numpy(r2), torch.zeros(T, dtype=torch.int32)
+
+    def newey_west_range(self, fr_all, t0, t1, q, tao):
+        fr = fr_all.numpy()
+        K = fr.shape[1]
+        cov = np.full((t1 - t0, K, K), np.nan)
+        st = np.ones(t1 - t0, dtype=np.int32)
+        for t in range(t0, t1):
+            try:
+                cov[t - t0] = orc.newey_west(fr[:t + 1], q, tao)
+                st[t - t0] = 0
+            except Exception:
+                pass
+        return torch.from_numpy(cov), torch.from_numpy(st)
+
+    def eigen(self, cov, status, T_sim, M, scale, sim_range=None, allreduce=None):
+        cov, status = cov.numpy(), status.numpy()
+        T, K = cov.shape[0], cov.shape[1]
+        m_lo, m_hi = (0, M) if sim_range is None else sim_range
+        vsum = np.zeros((T, K))
+        eig = {}
+        for t in range(T):
+            if status[t] != 0:
+                continue
+            D0, U0 = orc.canonical_eig(cov[t])
+            eig[t] = (D0, U0)
+            _, _, sims = orc.eigen_risk_adj(cov[t], T_sim, m_hi, scale, return_sims=True)
+            for (Dm, dg) in sims[m_lo:m_hi]:
+                vsum[t] += dg / Dm
+        vs = torch.from_numpy(vsum)
+        if allreduce is not None:
+            allreduce(vs)
+        out = np.full_like(cov, np.nan)
+        for t, (D0, U0) in eig.items():
+            v = scale * (np.sqrt(vs.numpy()[t] / M) - 1) + 1
+            out[t] = U0 @ np.diag(v ** 2 * D0) @ U0.T
+        return torch.from_numpy(out), torch.from_numpy(status.copy())
+
+    def vr_bias(self, T_total, t0, fr_block, cov_block, status_block, tao):
+        fr, cov, st = fr_block.numpy(), cov_block.numpy(), status_block.numpy()
+        n = len(fr)
+        wb, wv = np.zeros(n), np.zeros(n)
+        for i in range(n):
+            if st[i] != 0:
+                continue
+            var = np.diag(cov[i])
+            b2 = np.mean(fr[i] ** 2 / var)
+            w = 0.5 ** ((T_total - 1 - (t0 + i)) / tao)
+            wb[i], wv[i] = w * b2, w
+        return torch.from_numpy(wb), torch.from_numpy(wv)
+
+    def vr_scale(self, T_total, t0, wb_all, wv_all, cov_block, status_block):
+        nb, nv = np.cumsum(wb_all.numpy()), np.cumsum(wv_all.numpy())
+        with np.errstate(invalid="ignore", divide="ignore"):
+            lamb = np.where(nv > 0, np.sqrt(nb / np.where(nv > 0, nv, 1)), 0.0)
+        cov = cov_block.numpy()
+        n = cov.shape[0]
+        out = cov * (lamb[t0:t0 + n] ** 2)[:, None, None]
+        return torch.from_numpy(out), torch.from_numpy(lamb)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _panel():
+    return make_panel(T=40, N=30, P=3, Q=2, seed=77, ragged=0.1)
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pan = _panel()
+        csr = pan.to_csr()
+        T = pan.T
+        counts = bd.shard_counts(T, world)
+        lo, hi = bd.shard_range(T, rank, world)
+        a, b = int(csr["date_off"][lo]), int(csr["date_off"][hi])
+        off = torch.from_numpy(csr["date_off"][lo:hi + 1] - csr["date_off"][lo])
+        tt = lambda x: torch.from_numpy(np.ascontiguousarray(x))
+        pipe = bd.RiskPipeline(OracleBackend(), rank, world)
+        res = pipe.run(counts, pan.P, pan.Q, pan.N, off, tt(csr["cap"][a:b]), tt(csr["ret"][a:b]),
+                       tt(csr["ind"][a:b]), tt(csr["style"][a:b]), q=2, tao_nw=15, tao_vr=8,
+                       eigen=dict(T_sim=30, M=4, scale_coef=1.4))
+        # config-4 style: all dates on every rank, simulations sharded
+        fr_all = res["factor_ret_all"]
+        nw_all, st_all = OracleBackend().newey_west_range(fr_all, 0, T, 2, 15)
+        er_sims, _ = bd.eigen_sharded_by_sims(OracleBackend(), nw_all, st_all, 30, 4, 1.4, rank, world)
+        q.put((rank, {k: (v.numpy() if torch.is_tensor(v) else v) for k, v in res.items()}, er_sims.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_range_partitions():
+    for n in (0, 1, 7, 2500, 3750):
+        for world in (1, 2, 3, 8):
+            edges = [bd.shard_range(n, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == n
+            assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in edges]
+            assert max(sizes) - min(sizes) <= 1 and sizes == bd.shard_counts(n, world)
+
+
+@pytest.mark.timeout(300)
+def test_sharded_pipeline_matches_single_process():
+    world = 2
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        rank, res, er_sims = q.get(timeout=240)
+        got[rank] = (res, er_sims)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+
+    pan = _panel()
+    csr = pan.to_csr()
+    fr, spec, r2 = orc.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P)
+    nw = orc.newey_west_by_time(fr, 2, 15)
+    er = orc.eigen_risk_adj_by_time(nw, 30, 4, 1.4)
+    vr, lamb = orc.vol_regime_adj_by_time(fr, er, 8)
+
+    def close(a, b, tol=1e-11):
+        a, b = np.asarray(a), np.asarray(b)
+        assert np.array_equal(np.isnan(a), np.isnan(b))
+        return np.nanmax(np.abs(a - b)) <= tol * max(np.nanmax(np.abs(b)), 1e-300)
+
+    for rank in range(world):
+        res, er_sims = got[rank]
+        t0, n = res["t0"], res["n"]
+        assert close(res["factor_ret"], fr[t0:t0 + n])
+        assert close(res["factor_ret_all"], fr)
+        assert close(res["lamb_all"], np.array(lamb), 1e-10)
+        for i in range(n):
+            t = t0 + i
+            assert (res["nw_status"][i] == 0) == (nw[t] is not None)
+            if nw[t] is not None:
+                assert close(res["nw"][i], nw[t])
+            if er[t] is not None:
+                assert close(res["cov"][i], er[t], 1e-10)
+                assert close(res["vr"][i], vr[t], 1e-10)
+        for t in range(pan.T):       # simulations sharded, all-reduced
+            if er[t] is not None:
+                assert close(er_sims[t], er[t], 1e-10)

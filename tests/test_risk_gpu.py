@@ -144,3 +144,54 @@ def test_mfm_dropin_full_pipeline(pipe):
             assert relerr(vr[t].values, pipe["vr"][t]) < TOL
     assert relerr(np.array(lamb), pipe["lamb"]) < TOL
     assert isinstance(lamb, list) and isinstance(lamb[0], float)
+
+
+def test_date_sharded_entry_points_match_full(ops):
+    """bmfm_newey_west_by_time_range and the split vol-regime pass, run shard by shard on one GPU
+    (three 'ranks' of dates), must reproduce the un-sharded calls."""
+    import torch
+    from bmfm import _cabi, dist as bd
+    from bmfm.synth import make_factor_returns
+    ctx = _cabi.default_context()
+    T, K, q, tao, tao_vr = 500, 17, 2, 60.0, 21.0
+    fr = make_factor_returns(T, K, seed=11)
+    cov_full, st_full = ops.newey_west_by_time(fr, q, tao)
+    vr_full, lamb_full = ops.vol_regime_adj_by_time(fr, np.nan_to_num(cov_full), st_full, tao_vr)
+    d_fr = torch.from_numpy(fr).cuda()
+    be = bd.GpuBackend(ctx)
+    world = 3
+    counts = bd.shard_counts(T, world)
+    blocks, wbs, wvs = [], [], []
+    for r in range(world):
+        lo, hi = bd.shard_range(T, r, world)
+        cov, st = be.newey_west_range(d_fr, lo, hi, q, tao)
+        assert np.array_equal(st.cpu().numpy(), st_full[lo:hi])
+        got = cov.cpu().numpy()
+        ok = st_full[lo:hi] == 0
+        assert np.array_equal(got[ok], cov_full[lo:hi][ok])       # same kernels, same chunks: bit-identical
+        wb, wv = be.vr_bias(T, lo, d_fr[lo:hi].contiguous(), cov, st, tao_vr)
+        blocks.append((lo, hi, cov, st))
+        wbs.append(wb)
+        wvs.append(wv)
+    wb_all, wv_all = torch.cat(wbs), torch.cat(wvs)
+    for (lo, hi, cov, st) in blocks:
+        out, lamb = be.vr_scale(T, lo, wb_all, wv_all, cov, st)
+        assert relerr(lamb.cpu().numpy(), lamb_full) < 1e-14
+        assert relerr(out.cpu().numpy(), vr_full[lo:hi]) < 1e-14
+    # the orchestration class with world = 1
+    from bmfm.synth import make_panel
+    from bmfm.panel import pack_arrays
+    pan = make_panel(T=60, N=50, P=4, Q=3, seed=5)
+    csr = pan.to_csr()
+    (cap, ret, ind, style), pos = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P)
+    dv = lambda a: torch.from_numpy(a).cuda()
+    res = bd.RiskPipeline(be).run([pan.T], pan.P, pan.Q, pan.N, dv(csr["date_off"]), dv(cap), dv(ret), dv(ind),
+                                  dv(style), q=2, tao_nw=20, tao_vr=10, eigen=dict(T_sim=60, M=3, scale_coef=1.4))
+    from oracle import barra_oracle as orc
+    wfr, _, _ = orc.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P)
+    nw = orc.newey_west_by_time(wfr, 2, 20)
+    er = orc.eigen_risk_adj_by_time(nw, 60, 3, 1.4)
+    vr, lamb = orc.vol_regime_adj_by_time(wfr, er, 10)
+    assert relerr(res["factor_ret"].cpu().numpy(), wfr) < TOL
+    assert relerr(res["lamb_all"].cpu().numpy(), np.array(lamb)) < TOL
+    assert relerr(res["vr"].cpu().numpy()[-1], vr[-1]) < TOL
