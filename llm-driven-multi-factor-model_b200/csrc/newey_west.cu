@@ -26,6 +26,7 @@
 namespace bmfm {
 
 constexpr int NW_MAX_Q = 4;
+constexpr int NW_EMIT_SPLIT = 4;   // CTAs per chunk in the emit kernel (the K*K elements are split)
 
 struct NwParams {
   int T, K, q, C, nchunks;
@@ -48,33 +49,47 @@ __device__ __forceinline__ double nw_vec_term(const double* fr, int K, int q, in
   return r - i >= 0 ? fr[(size_t)(r - i) * K + k] : 0.0;
 }
 
-// kernel 1: chunk totals from a zero start
-__global__ void nw_chunk_local(NwParams p) {
+// kernel 1: chunk totals from a zero start.  The chunk's rows (plus q rows of history for the lagged
+// products) are staged in shared memory once.
+__global__ void __launch_bounds__(256) nw_chunk_local(NwParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K], rows r0-q .. r1-1, zeros before row 0
   const int c = blockIdx.x, K = p.K, q = p.q;
-  const int r0 = c * p.C, r1 = min(p.T, r0 + p.C);
+  const int r0 = c * p.C, r1 = min(p.T, r0 + p.C), len = r1 - r0;
   double* st = p.state + (size_t)c * nw_nstate(K, q);
+  for (int e = threadIdx.x; e < (len + q) * K; e += blockDim.x) {
+    const int j = e / K, k = e - j * K;
+    const int r = r0 - q + j;
+    sx[e] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
+  }
+  __syncthreads();
+  const double lam = p.lam;
   const int nm = (1 + q) * K * K;
   for (int e = threadIdx.x; e < nm; e += blockDim.x) {
     const int i = e / (K * K), ab = e - i * K * K, a = ab / K, b = ab - a * K;
     double s = 0.0;
-    for (int r = r0; r < r1; ++r) {
-      s *= p.lam;
-      if (r - i >= 0) s = fma(p.fr[(size_t)(r - i) * K + a], p.fr[(size_t)r * K + b], s);
-    }
+    for (int j = 0; j < len; ++j) s = fma(s, lam, sx[(q + j - i) * K + a] * sx[(q + j) * K + b]);   // zero rows before row 0
     st[e] = s;
   }
   const int nv = (1 + 2 * q) * K;
   for (int e = threadIdx.x; e < nv; e += blockDim.x) {
     const int v = e / K, k = e - v * K;
     double s = 0.0;
-    for (int r = r0; r < r1; ++r) s = fma(s, p.lam, nw_vec_term(p.fr, K, q, v, r, k));
+    for (int j = 0; j < len; ++j) {
+      const int r = r0 + j;
+      double add;
+      if (v == 0) add = sx[(q + j) * K + k];
+      else if (v <= q) add = r >= v ? sx[(q + j) * K + k] : 0.0;
+      else add = sx[(q + j - (v - q)) * K + k];
+      s = fma(s, lam, add);
+    }
     st[nm + e] = s;
   }
   if (threadIdx.x <= q) {
     const int i = threadIdx.x;
     double s = 0.0;
     for (int r = r0; r < r1; ++r) {
-      s *= p.lam;
+      s *= lam;
       if (r >= i) s += 1.0;
     }
     st[nm + nv + i] = s;
@@ -83,19 +98,19 @@ __global__ void nw_chunk_local(NwParams p) {
 
 // kernel 2: exclusive scan over chunks, one thread per state element.  Every chunk but the
 // last has length C (the total after the last chunk is never used), so the carry factor is
-// the constant lam^C; loads are issued eight chunks at a time to overlap their latency.
+// the constant lam^C; loads are issued 32 chunks at a time to overlap their latency.
 __global__ void nw_chunk_scan(NwParams p) {
   const int ns = nw_nstate(p.K, p.q);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= ns) return;
   const double fC = pow(p.lam, (double)p.C);
   double run = 0.0;
-  for (int c0 = 0; c0 < p.nchunks; c0 += 8) {
-    double loc[8];
+  for (int c0 = 0; c0 < p.nchunks; c0 += 32) {
+    double loc[32];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) loc[j] = (c0 + j < p.nchunks) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
+    for (int j = 0; j < 32; ++j) loc[j] = (c0 + j < p.nchunks) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < 32; ++j) {
       if (c0 + j < p.nchunks) {
         p.state[(size_t)(c0 + j) * ns + e] = run;
         run = fma(run, fC, loc[j]);
@@ -148,7 +163,7 @@ __global__ void __launch_bounds__(256) nw_emit(NwParams p) {
   }
   __syncthreads();
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  for (int e = tid; e < K * K; e += nt) {
+  for (int e = blockIdx.y * nt + tid; e < K * K; e += gridDim.y * nt) {
     const int a = e / K, b = e - a * K;
     double a0 = st[e];
     double bab[NW_MAX_Q], bba[NW_MAX_Q];
@@ -200,6 +215,7 @@ __global__ void __launch_bounds__(256) nw_emit(NwParams p) {
       if (r >= p.t0 && r < p.t1) st_stream(p.cov + ((size_t)(r - p.t0) * K + a) * K + b, out);
     }
   }
+  if (blockIdx.y == 0)
   for (int j = tid; j < len; j += nt) {
     const int r = r0 + j, L = r + 1;
     if (r >= p.t0 && r < p.t1) p.status[r - p.t0] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
@@ -233,7 +249,16 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.t0 = t0; p.t1 = t1;
   p.c_first = t0 / p.C;
   const int c_last = t1 > t0 ? (t1 - 1) / p.C : p.c_first - 1;
-  nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
+  {
+    const size_t smem_local = (size_t)(p.C + q) * K * 8;
+    if (smem_local > (size_t)ctx->max_smem_optin) {
+      snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
+      return BMFM_E_UNSUPPORTED;
+    }
+    if (smem_local > 48 * 1024)
+      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
+    nw_chunk_local<<<p.nchunks, 256, smem_local, ctx->stream>>>(p);
+  }
   ctx->launches++;
   const int ns = nw_nstate(K, q);
   nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
@@ -245,7 +270,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   }
   BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (c_last >= p.c_first) {
-    nw_emit<<<c_last - p.c_first + 1, 256, smem, ctx->stream>>>(p);
+    nw_emit<<<dim3(c_last - p.c_first + 1, NW_EMIT_SPLIT), 256, smem, ctx->stream>>>(p);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());
@@ -364,13 +389,22 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   p.fr = factor_ret; p.cov = cov; p.status = status;
   p.t0 = 0; p.t1 = T; p.c_first = 0;
   p.state = nw_static_ptr[ctx->device];
-  nw_chunk_local<<<p.nchunks, 256, 0, ctx->stream>>>(p);
+  {
+    const size_t smem_local = (size_t)(p.C + q) * K * 8;
+    if (smem_local > (size_t)ctx->max_smem_optin) {
+      snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
+      return BMFM_E_UNSUPPORTED;
+    }
+    if (smem_local > 48 * 1024)
+      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
+    nw_chunk_local<<<p.nchunks, 256, smem_local, ctx->stream>>>(p);
+  }
   ctx->launches++;
   const int ns = nw_nstate(K, q);
   nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  nw_emit<<<p.nchunks, 256, smem, ctx->stream>>>(p);
+  nw_emit<<<dim3(p.nchunks, NW_EMIT_SPLIT), 256, smem, ctx->stream>>>(p);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
