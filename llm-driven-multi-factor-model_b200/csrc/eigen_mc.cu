@@ -21,8 +21,10 @@
 // CTA per problem slot, seven slots per SM).  Simulations shard across GPUs: each rank
 // accumulates sum_m v_m for its simulations, the host all-reduces T*K doubles.
 #include <math.h>
+#include <stdlib.h>
 #include "bmfm_common.cuh"
 #include "jacobi.cuh"
+#include "tridiag_ql.cuh"
 
 namespace bmfm {
 
@@ -171,6 +173,7 @@ __global__ void __launch_bounds__(256) eig_f0_kernel(int T, int K, const double*
 // ------------------------------------------------------------------------------------------
 // E2: the Monte-Carlo loop.  CTA = (date, block of simulations); partial[t][blk][k] = sum_m v_m[k]
 // ------------------------------------------------------------------------------------------
+template <int N>
 __global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int nblk, const double* C,
                                                      const double* D0, const int* status, double* partial) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -183,6 +186,11 @@ __global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int
   double* lam = sd + K;             // K
   double* vacc = lam + K;           // K
   int* flag = reinterpret_cast<int*>(vacc + K);   // 8
+  JacobiTables tb;
+  tb.pair = reinterpret_cast<unsigned short*>(flag + 8);          // (K-1) * K/2
+  tb.blk = tb.pair + (K - 1) * (K >> 1);                           // K/2 (K/2 - 1) / 2
+  const bool even = (K & 1) == 0;
+  if (even) jacobi_build_tables(K, tb);
   const int per = (nsim + nblk - 1) / nblk;
   for (int w = blockIdx.x; w < T * nblk; w += gridDim.x) {
     const int t = w / nblk, blk = w - t * nblk;
@@ -206,7 +214,8 @@ __global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int
         A[a * ld + b] = sd[a] * Cm[e] * sd[b];
       }
       __syncthreads();
-      jacobi_eig_cta(A, V, K, ld, cs, flag);
+      if (even) jacobi_eig_blocks<N>(A, V, K, ld, cs, tb);
+      else jacobi_eig_cta(A, V, K, ld, cs, flag);
       __syncthreads();
       if (tid < K) lam[tid] = A[tid * ld + tid];
       __syncthreads();
@@ -226,6 +235,63 @@ __global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int
     }
     if (tid < K) out[tid] = vacc[tid];
     __syncthreads();
+  }
+}
+
+// E2 (default): same loop with the two-stage solver (tridiag_ql.cuh); CTA = 64 threads = one problem slot
+__global__ void __launch_bounds__(64) eig_mc_tql_kernel(int T, int K, int nsim, int nblk, const double* C,
+                                                        const double* D0, const int* status, double* partial) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* Z = reinterpret_cast<double*>(smem);
+  double* d = Z + K * ld;      // K eigenvalues
+  double* e = d + K;           // K
+  double* cs = e + K;          // 2K
+  double* red = cs + 2 * K;    // 4
+  double* d0 = red + 4;        // K
+  double* sd = d0 + K;         // K
+  double* vacc = sd + K;       // K
+  const int per = (nsim + nblk - 1) / nblk;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int w = blockIdx.x; w < T * nblk; w += gridDim.x) {
+    const int t = w / nblk, blk = w - t * nblk;
+    double* out = partial + ((size_t)t * nblk + blk) * K;
+    if (status[t] != BMFM_ST_OK) {
+      for (int k = tid; k < K; k += nt) out[k] = 0.0;
+      continue;
+    }
+    const int m_lo = blk * per, m_hi = min(nsim, m_lo + per);
+    __syncthreads();
+    if (tid < K) {
+      const double dv = D0[(size_t)t * K + tid];
+      d0[tid] = dv;
+      sd[tid] = sqrt(dv);
+      vacc[tid] = 0.0;
+    }
+    __syncthreads();
+    for (int m = m_lo; m < m_hi; ++m) {
+      const double* Cm = C + (size_t)m * K * K;
+      for (int a = 0; a < K; ++a) {
+        const double sa = sd[a];
+        for (int b = tid; b < K; b += nt) Z[a * ld + b] = sa * Cm[a * K + b] * sd[b];
+      }
+      __syncthreads();
+      const int fail = tridiag_ql_cta(Z, d, e, cs, red, K, ld);
+      __syncthreads();
+      if (tid < K) {
+        const double me = d[tid];
+        int r = 0;
+        for (int j = 0; j < K; ++j) r += (d[j] > me) || (d[j] == me && j < tid);
+        double num = 0.0;
+        for (int i = 0; i < K; ++i) {
+          const double v = Z[i * ld + tid];
+          num = fma(d0[i] * v, v, num);
+        }
+        vacc[r] += fail ? nan : num / me;
+      }
+      __syncthreads();
+    }
+    if (tid < K) out[tid] = vacc[tid];
   }
 }
 
@@ -300,7 +366,10 @@ extern "C" int bmfm_gauss_cov(bmfm_ctx* ctx, int m0, int nsim, int T_sim, int K,
   return BMFM_OK;
 }
 
-static size_t eig_smem_bytes(int K) { return ((size_t)2 * K * (K | 1) + 6 * K + 16) * 8 + 64; }
+static size_t eig_smem_bytes(int K) {
+  const size_t tables = ((size_t)(K - 1) * (K / 2) + (size_t)(K / 2) * (K / 2) / 2 + 8) * 2;
+  return ((size_t)2 * K * (K | 1) + 6 * K + 16) * 8 + 64 + tables;
+}
 
 extern "C" int bmfm_eigen_decompose(bmfm_ctx* ctx, int T, int K, const double* cov, const int32_t* cov_status,
                                     double* D0, double* U0, int32_t* status) {
@@ -324,18 +393,32 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
   BMFM_ARG(ctx, T >= 0 && K > 0 && nsim >= 0 && D0 && status && vsum && (C || nsim == 0), "bad arguments");
   if (T == 0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  const size_t smem = eig_smem_bytes(K);
-  const int slots = ctx->sm_count * (int)((228 * 1024) / (smem + 1024));
+  // solver choice: tridiagonal QL (default, K <= 64) or block Jacobi (BMFM_EIG_MODE=1, any K)
+  int mode = 0;
+  if (const char* ev = getenv("BMFM_EIG_MODE")) mode = atoi(ev);
+  const bool use_ql = mode != 1 && K <= 64;
+  const size_t smem = use_ql ? ((size_t)K * (K | 1) + 7 * K + 8) * 8 : eig_smem_bytes(K);
+  int per_sm = (int)((228 * 1024) / (smem + 1024));
+  if (per_sm > 16) per_sm = 16;
+  const int slots = ctx->sm_count * per_sm;
   int nblk = (4 * slots + T - 1) / T;
   if (nblk > nsim) nblk = nsim;
   if (nblk < 1) nblk = 1;
   int rc = bmfm_ws_reserve(ctx, (size_t)T * nblk * K * 8);
   if (rc) return rc;
   double* partial = (double*)ctx->ws;
-  BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long work = (long long)T * nblk;
   int grid = work < slots ? (int)work : slots;
-  eig_mc_kernel<<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+  if (use_ql) {
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_tql_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    eig_mc_tql_kernel<<<grid, 64, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+  } else if (K == 42) {   // the flagship factor count (31 industries + 10 styles + country): compile-time loops
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel<42>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    eig_mc_kernel<42><<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+  } else {
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    eig_mc_kernel<0><<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+  }
   ctx->launches++;
   eig_partial_reduce_kernel<<<(T * K + 255) / 256, 256, 0, ctx->stream>>>(T, K, nblk, partial, vsum, accumulate);
   ctx->launches++;

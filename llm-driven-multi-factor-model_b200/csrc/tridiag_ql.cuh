@@ -1,0 +1,182 @@
+// CTA-cooperative symmetric eigensolver: Householder tridiagonalisation + implicit QL.
+//
+// The Monte-Carlo loop of the eigenfactor adjustment (utils.py:71-84) needs T*M full
+// eigendecompositions of K x K matrices.  Jacobi in shared memory makes ~330 read-modify-write
+// passes over the matrix and its eigenvectors and is bound by shared-memory bandwidth
+// (profiles/: 217 k wavefronts per 42 x 42 problem); the classic two-stage method touches the
+// matrix ~40 times during the reduction and then only two columns of Z per QL rotation, about
+// an eighth of the shared-memory traffic and a fifth of the instructions.
+//   stage 1  tred2: A -> Q T Q', Q accumulated in place (A becomes Q)
+//   stage 2  tql2 : per QL sweep one thread runs the (serial, Z-independent) chain of rotation
+//            parameters, then every thread applies the whole sweep to its own row of Z with no
+//            barrier in between (row k only ever touches Z[k][*]).
+// Many problems per SM hide the serial chain: one CTA = 64 threads = one problem, ~16 KB.
+#pragma once
+#include "bmfm_common.cuh"
+
+namespace bmfm {
+
+__device__ __forceinline__ double block_sum64(double v, double* red) {
+  // blockDim.x == 64 (two warps)
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  return red[0] + red[1];
+}
+
+// Z: n x n (row stride ld, odd) holding the symmetric matrix (both triangles) on entry and the
+// eigenvectors (columns) on exit; d: eigenvalues (unsorted); e, cs (2n), red (4): scratch.
+// Returns 0, or 1 if a QL iteration did not converge in 60 sweeps (caller falls back).
+__device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs, double* red, int n, int ld) {
+  const int tid = threadIdx.x;
+  // ---- stage 1: Householder reduction (EISPACK tred2, lower triangle), parallel over j ----
+  for (int i = n - 1; i >= 1; --i) {
+    const int l = i - 1;
+    double h = 0.0;
+    if (l > 0) {
+      const double scale = block_sum64(tid <= l ? fabs(Z[i * ld + tid]) : 0.0, red);
+      if (scale == 0.0) {
+        if (tid == 0) e[i] = Z[i * ld + l];
+      } else {
+        double v = 0.0;
+        if (tid <= l) {
+          v = Z[i * ld + tid] / scale;
+          Z[i * ld + tid] = v;
+        }
+        h = block_sum64(v * v, red);
+        const double f0 = Z[i * ld + l];
+        const double g0 = f0 >= 0.0 ? -sqrt(h) : sqrt(h);
+        h -= f0 * g0;
+        __syncthreads();
+        if (tid == 0) {
+          e[i] = scale * g0;
+          Z[i * ld + l] = f0 - g0;
+        }
+        __syncthreads();
+        // p = A u / h  (thread j: row j up to the diagonal, column j below it)
+        double fj = 0.0, ej = 0.0;
+        if (tid <= l) {
+          const int j = tid;
+          const double uj = Z[i * ld + j];
+          Z[j * ld + i] = uj / h;
+          double g = 0.0;
+          for (int k = 0; k <= j; ++k) g = fma(Z[j * ld + k], Z[i * ld + k], g);
+          for (int k = j + 1; k <= l; ++k) g = fma(Z[k * ld + j], Z[i * ld + k], g);
+          ej = g / h;
+          fj = ej * uj;
+        }
+        const double f = block_sum64(fj, red);
+        const double hh = f / (h + h);
+        if (tid <= l) e[tid] = ej - hh * Z[i * ld + tid];
+        __syncthreads();
+        // rank-2 update of the leading lower triangle
+        if (tid <= l) {
+          const int j = tid;
+          const double fu = Z[i * ld + j], gq = e[j];
+          for (int k = 0; k <= j; ++k) Z[j * ld + k] -= fu * e[k] + gq * Z[i * ld + k];
+        }
+        __syncthreads();
+      }
+    } else {
+      if (tid == 0) e[i] = Z[i * ld + l];
+    }
+    if (tid == 0) d[i] = h;
+    __syncthreads();
+  }
+  if (tid == 0) { d[0] = 0.0; e[0] = 0.0; }
+  __syncthreads();
+  // accumulate the transformation: Z <- Q
+  for (int i = 0; i < n; ++i) {
+    const int l = i - 1;
+    if (d[i] != 0.0 && tid <= l) {
+      const int j = tid;
+      double g = 0.0;
+      for (int k = 0; k <= l; ++k) g = fma(Z[i * ld + k], Z[k * ld + j], g);
+      for (int k = 0; k <= l; ++k) Z[k * ld + j] -= g * Z[k * ld + i];
+    }
+    __syncthreads();
+    if (tid == 0) { d[i] = Z[i * ld + i]; Z[i * ld + i] = 1.0; }
+    if (tid <= l) { Z[tid * ld + i] = 0.0; Z[i * ld + tid] = 0.0; }
+    __syncthreads();
+  }
+  // ---- stage 2: implicit QL on (d, e) with the rotations of each sweep applied row-wise ----
+  if (tid == 0) {
+    for (int i = 1; i < n; ++i) e[i - 1] = e[i];
+    e[n - 1] = 0.0;
+  }
+  __syncthreads();
+  int* ictl = reinterpret_cast<int*>(red + 2);   // [0] = m, [1] = lowest rotation index applied, [2] = fail
+  if (tid == 0) ictl[2] = 0;
+  for (int l = 0; l < n; ++l) {
+    for (int iter = 0;; ++iter) {
+      if (tid == 0) {
+        int m = l;
+        for (; m < n - 1; ++m) {
+          const double dd = fabs(d[m]) + fabs(d[m + 1]);
+          if (fabs(e[m]) <= 2.220446049250313e-16 * dd) break;
+        }
+        int ilo = m;          // no rotation
+        if (m != l) {
+          if (iter >= 60) ictl[2] = 1;
+          double g = (d[l + 1] - d[l]) / (2.0 * e[l]);
+          double r = sqrt(g * g + 1.0);
+          g = d[m] - d[l] + e[l] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
+          double s = 1.0, c = 1.0, p = 0.0;
+          int i = m - 1;
+          bool brk = false;
+          for (; i >= l; --i) {
+            double f = s * e[i];
+            const double b = c * e[i];
+            const double h2 = f * f + g * g;
+            const double ir = rsqrt(h2);     // one reciprocal square root instead of a sqrt and two divisions
+            r = h2 * ir;
+            e[i + 1] = h2 > 0.0 ? r : 0.0;
+            if (!(h2 > 0.0)) {
+              d[i + 1] -= p;
+              e[m] = 0.0;
+              brk = true;
+              break;
+            }
+            s = f * ir;
+            c = g * ir;
+            g = d[i + 1] - p;
+            r = (d[i] - g) * s + 2.0 * c * b;
+            p = s * r;
+            d[i + 1] = g + p;
+            g = c * r - b;
+            cs[2 * i] = c;
+            cs[2 * i + 1] = s;
+          }
+          ilo = brk ? i + 1 : l;
+          if (!brk) {
+            d[l] -= p;
+            e[l] = g;
+            e[m] = 0.0;
+          }
+        }
+        ictl[0] = m;
+        ictl[1] = ilo;
+      }
+      __syncthreads();
+      const int m = ictl[0], ilo = ictl[1], fail = ictl[2];
+      if (m != l && tid < n && ilo < m) {
+        double* zr = Z + tid * ld;
+        double z1 = zr[m];
+        for (int i = m - 1; i >= ilo; --i) {
+          const double c = cs[2 * i], s = cs[2 * i + 1];
+          const double zi = zr[i];
+          zr[i + 1] = fma(s, zi, c * z1);
+          z1 = fma(c, zi, -s * z1);
+        }
+        zr[ilo] = z1;
+      }
+      __syncthreads();
+      if (m == l || fail) break;
+    }
+    if (ictl[2]) return 1;
+  }
+  return 0;
+}
+
+}  // namespace bmfm

@@ -81,7 +81,9 @@ def test_gauss_cov_legacy_stream(ops):
 
 
 @pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
-def test_eigen_risk_adj_golden_canonical(ops, risk, T, M):
+@pytest.mark.parametrize("solver", ["0", "1"])     # 0: tridiagonal QL (default), 1: block Jacobi
+def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, monkeypatch):
+    monkeypatch.setenv("BMFM_EIG_MODE", solver)
     cov = risk["eig_cov_in"]
     out, status = ops.eigen_risk_adj_by_time(cov[None], None, T, M, 1.4)
     assert status[0] == 0
@@ -92,8 +94,10 @@ def test_eigen_risk_adj_golden_canonical(ops, risk, T, M):
     print(f"literal-vs-canonical gap T={T} M={M}: {gap:.3e}")
 
 
-def test_eigen_by_time_oracle(ops):
+@pytest.mark.parametrize("solver", ["0", "1"])
+def test_eigen_by_time_oracle(ops, solver, monkeypatch):
     """K = 42 factor covariances from an expanding Newey-West run, simulation length 252."""
+    monkeypatch.setenv("BMFM_EIG_MODE", solver)
     from bmfm.synth import make_factor_returns
     from oracle import barra_oracle as orc
     K, T = 42, 140
