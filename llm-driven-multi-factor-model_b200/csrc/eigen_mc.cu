@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(128) eig_mc_kernel(int T, int K, int nsim, int
 
 // E2 (default): same loop with the two-stage solver (tridiag_ql.cuh); CTA = 64 threads = one problem slot
 __global__ void __launch_bounds__(64) eig_mc_tql_kernel(int T, int K, int nsim, int nblk, const double* C,
-                                                        const double* D0, const int* status, double* partial) {
+                                                        const double* D0, const int* status, double* partial, int dbg) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
   double* Z = reinterpret_cast<double*>(smem);
@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(64) eig_mc_tql_kernel(int T, int K, int nsim, 
         for (int b = tid; b < K; b += nt) Z[a * ld + b] = sa * Cm[a * K + b] * sd[b];
       }
       __syncthreads();
-      const int fail = tridiag_ql_cta(Z, d, e, cs, red, K, ld);
+      const int fail = tridiag_ql_cta(Z, d, e, cs, red, K, ld, dbg);
       __syncthreads();
       if (tid < K) {
         const double me = d[tid];
@@ -291,6 +291,151 @@ __global__ void __launch_bounds__(64) eig_mc_tql_kernel(int T, int K, int nsim, 
       }
       __syncthreads();
     }
+    if (tid < K) out[tid] = vacc[tid];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// E2 (default), split form.  In the fused kernel above 62% of the time is the serial QL rotation
+// chain, run by one lane while shared memory limits an SM to 13 problems in flight.  The chain
+// needs only the tridiagonal (d, e), so it is split off:
+//   A  eig_split_tred_kernel   CTA per problem: build D0^1/2 C_m D0^1/2, Householder-reduce, write
+//                              Q (K x K) and (d, e) to scratch
+//   B  eig_split_chain_kernel  THREAD per problem (32 chains per warp, thousands per SM): QL on
+//                              private (d, e); records every sweep's rotations + the eigenvalues
+//   C  eig_split_apply_kernel  CTA per (date, block of sims): replays the recorded rotations on
+//                              the rows of Q (thread = row, no barriers), then v_m = diag(W'D0W)/lambda
+// Scratch per problem: Q 8K^2 + rotations 16 * 2K^2 + headers 4 * 8K + 24K bytes (~72 KB at K = 42).
+// ------------------------------------------------------------------------------------------
+struct EigSplit {
+  int K, nsim, P;          // P = problems in this batch = dates_in_batch * nsim
+  int t0;                  // first date of the batch
+  int rmax, smax;
+  double* Qs;              // [P][K*K]
+  double* de;              // [2K][P]   d then e, problem-minor (coalesced for the chain kernel)
+  double* lam;             // [K][P]
+  double2* cs;             // [P][rmax]
+  int* hdr;                // [P][smax]
+  int* nsw;                // [P]  sweeps recorded, -1 = failed
+};
+
+__global__ void __launch_bounds__(64) eig_split_tred_kernel(EigSplit sp, const double* C, const double* D0,
+                                                            const int* status) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int K = sp.K, ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* Z = reinterpret_cast<double*>(smem);
+  double* d = Z + K * ld;
+  double* e = d + K;
+  double* red = e + K;      // 4
+  double* sd = red + 4;     // K
+  for (int p = blockIdx.x; p < sp.P; p += gridDim.x) {
+    const int t = sp.t0 + p / sp.nsim, m = p % sp.nsim;
+    if (status[t] != BMFM_ST_OK) continue;
+    __syncthreads();
+    if (tid < K) sd[tid] = sqrt(D0[(size_t)t * K + tid]);
+    __syncthreads();
+    const double* Cm = C + (size_t)m * K * K;
+    for (int a = 0; a < K; ++a) {
+      const double sa = sd[a];
+      for (int b = tid; b < K; b += nt) Z[a * ld + b] = sa * Cm[a * K + b] * sd[b];
+    }
+    __syncthreads();
+    tred2_cta(Z, d, e, red, K, ld);
+    double* Q = sp.Qs + (size_t)p * K * K;
+    for (int a = 0; a < K; ++a)
+      for (int b = tid; b < K; b += nt) Q[a * K + b] = Z[a * ld + b];
+    if (tid < K) {
+      sp.de[(size_t)tid * sp.P + p] = d[tid];
+      sp.de[(size_t)(K + tid) * sp.P + p] = e[tid];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) eig_split_chain_kernel(EigSplit sp, const int* status) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= sp.P) return;
+  const int K = sp.K;
+  const int t = sp.t0 + p / sp.nsim;
+  if (status[t] != BMFM_ST_OK) { sp.nsw[p] = 0; return; }
+  double d[64], e[64];
+  for (int k = 0; k < K; ++k) {
+    d[k] = sp.de[(size_t)k * sp.P + p];
+    e[k] = sp.de[(size_t)(K + k) * sp.P + p];
+  }
+  int nrot = 0;
+  const int nsw = ql_chain_record(d, e, K, sp.cs + (size_t)p * sp.rmax, sp.rmax, sp.hdr + (size_t)p * sp.smax,
+                                  sp.smax, &nrot);
+  sp.nsw[p] = nsw;
+  for (int k = 0; k < K; ++k) sp.lam[(size_t)k * sp.P + p] = d[k];
+}
+
+__global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nblk, const double* D0,
+                                                             const int* status, double* partial) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int K = sp.K, ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* Z = reinterpret_cast<double*>(smem);
+  double* lamv = Z + K * ld;    // K
+  double* d0 = lamv + K;        // K
+  double* vacc = d0 + K;        // K
+  const int per = (sp.nsim + nblk - 1) / nblk;
+  const int nd = sp.P / sp.nsim;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int w = blockIdx.x; w < nd * nblk; w += gridDim.x) {
+    const int tl = w / nblk, blk = w - tl * nblk, t = sp.t0 + tl;
+    double* out = partial + ((size_t)t * nblk + blk) * K;
+    if (status[t] != BMFM_ST_OK) {
+      for (int k = tid; k < K; k += nt) out[k] = 0.0;
+      continue;
+    }
+    __syncthreads();
+    if (tid < K) { d0[tid] = D0[(size_t)t * K + tid]; vacc[tid] = 0.0; }
+    const int m_lo = blk * per, m_hi = min(sp.nsim, m_lo + per);
+    for (int m = m_lo; m < m_hi; ++m) {
+      const int p = tl * sp.nsim + m;
+      const double* Q = sp.Qs + (size_t)p * K * K;
+      __syncthreads();
+      for (int a = 0; a < K; ++a)
+        for (int b = tid; b < K; b += nt) Z[a * ld + b] = Q[a * K + b];
+      if (tid < K) lamv[tid] = sp.lam[(size_t)tid * sp.P + p];
+      __syncthreads();
+      const int nsw = sp.nsw[p];
+      if (tid < K && nsw > 0) {
+        const double2* cs = sp.cs + (size_t)p * sp.rmax;
+        const int* hdr = sp.hdr + (size_t)p * sp.smax;
+        double* zr = Z + tid * ld;
+        int pos = 0;
+        for (int sw = 0; sw < nsw; ++sw) {
+          const int h = hdr[sw];
+          const int mm = h & 0xff, ilo = h >> 8;
+          if (ilo < mm) {
+            double z1 = zr[mm];
+            const double2* c2 = cs + pos + (mm - 1);
+#pragma unroll 4
+            for (int i = mm - 1; i >= ilo; --i) {
+              const double2 r = c2[-i];          // rotation of index i is stored at pos + (mm-1-i)
+              const double zi = zr[i];
+              zr[i + 1] = fma(r.y, zi, r.x * z1);
+              z1 = fma(r.x, zi, -r.y * z1);
+            }
+            zr[ilo] = z1;
+            pos += mm - ilo;
+          }
+        }
+      }
+      __syncthreads();
+      if (tid < K) {
+        const double me = lamv[tid];
+        int r = 0;
+        for (int j = 0; j < K; ++j) r += (lamv[j] > me) || (lamv[j] == me && j < tid);
+        double num = 0.0;
+        for (int i = 0; i < K; ++i) {
+          const double v = Z[i * ld + tid];
+          num = fma(d0[i] * v, v, num);
+        }
+        vacc[r] += nsw < 0 ? nan : num / me;
+      }
+    }
+    __syncthreads();
     if (tid < K) out[tid] = vacc[tid];
   }
 }
@@ -393,33 +538,76 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
   BMFM_ARG(ctx, T >= 0 && K > 0 && nsim >= 0 && D0 && status && vsum && (C || nsim == 0), "bad arguments");
   if (T == 0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  // solver choice: tridiagonal QL (default, K <= 64) or block Jacobi (BMFM_EIG_MODE=1, any K)
+  // solver choice (BMFM_EIG_MODE): 0 split tridiagonal QL (default, K <= 64), 2 fused tridiagonal QL,
+  // 1 block Jacobi (any K)
   int mode = 0;
   if (const char* ev = getenv("BMFM_EIG_MODE")) mode = atoi(ev);
-  const bool use_ql = mode != 1 && K <= 64;
-  const size_t smem = use_ql ? ((size_t)K * (K | 1) + 7 * K + 8) * 8 : eig_smem_bytes(K);
+  const size_t budget = (size_t)3 << 29;   // 1.5 GiB of scratch for the split form
+  const int rmax = 2 * K * K, smax = 8 * K;
+  const size_t per_problem = (size_t)K * K * 8 + (size_t)3 * K * 8 + (size_t)rmax * 16 + (size_t)smax * 4 + 4;
+  bool use_split = mode == 0 && K <= 64 && (size_t)nsim * per_problem <= budget && nsim > 0;
+  const bool use_ql = (mode == 2 || (mode == 0 && !use_split)) && K <= 64;
+  const size_t smem = (use_split || use_ql) ? ((size_t)K * (K | 1) + 7 * K + 8) * 8 : eig_smem_bytes(K);
   int per_sm = (int)((228 * 1024) / (smem + 1024));
   if (per_sm > 16) per_sm = 16;
   const int slots = ctx->sm_count * per_sm;
   int nblk = (4 * slots + T - 1) / T;
   if (nblk > nsim) nblk = nsim;
   if (nblk < 1) nblk = 1;
-  int rc = bmfm_ws_reserve(ctx, (size_t)T * nblk * K * 8);
+  const size_t partial_bytes = bmfm_align_up((size_t)T * nblk * K * 8, 256);
+  int nd_batch = 0;
+  if (use_split) {
+    nd_batch = (int)(budget / ((size_t)nsim * per_problem));
+    if (nd_batch > T) nd_batch = T;
+    if (nd_batch < 1) nd_batch = 1;
+  }
+  const size_t Pb = (size_t)nd_batch * nsim;
+  const size_t off_Q = partial_bytes;
+  const size_t off_de = off_Q + bmfm_align_up(Pb * K * K * 8, 256);
+  const size_t off_lam = off_de + bmfm_align_up(Pb * 2 * K * 8, 256);
+  const size_t off_cs = off_lam + bmfm_align_up(Pb * K * 8, 256);
+  const size_t off_hdr = off_cs + bmfm_align_up(Pb * rmax * 16, 256);
+  const size_t off_nsw = off_hdr + bmfm_align_up(Pb * smax * 4, 256);
+  const size_t total_ws = use_split ? off_nsw + bmfm_align_up(Pb * 4, 256) : partial_bytes;
+  int rc = bmfm_ws_reserve(ctx, total_ws);
   if (rc) return rc;
   double* partial = (double*)ctx->ws;
   long long work = (long long)T * nblk;
   int grid = work < slots ? (int)work : slots;
-  if (use_ql) {
+  if (use_split) {
+    char* base = (char*)ctx->ws;
+    EigSplit sp;
+    sp.K = K; sp.nsim = nsim; sp.rmax = rmax; sp.smax = smax;
+    sp.Qs = (double*)(base + off_Q); sp.de = (double*)(base + off_de); sp.lam = (double*)(base + off_lam);
+    sp.cs = (double2*)(base + off_cs); sp.hdr = (int*)(base + off_hdr); sp.nsw = (int*)(base + off_nsw);
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_tred_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (int t0 = 0; t0 < T; t0 += nd_batch) {
+      const int nd = T - t0 < nd_batch ? T - t0 : nd_batch;
+      sp.t0 = t0;
+      sp.P = nd * nsim;
+      const int gA = sp.P < slots ? sp.P : slots;
+      eig_split_tred_kernel<<<gA, 64, smem, ctx->stream>>>(sp, C, D0, status);
+      eig_split_chain_kernel<<<(sp.P + 127) / 128, 128, 0, ctx->stream>>>(sp, status);
+      const long long wC = (long long)nd * nblk;
+      eig_split_apply_kernel<<<(int)(wC < slots ? wC : slots), 64, smem, ctx->stream>>>(sp, nblk, D0, status, partial);
+      ctx->launches += 3;
+    }
+  } else if (use_ql) {
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_tql_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    eig_mc_tql_kernel<<<grid, 64, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+    int dbg = 0;
+    if (const char* ev = getenv("BMFM_EIG_DEBUG_STAGE")) dbg = atoi(ev);   // timing experiments only
+    eig_mc_tql_kernel<<<grid, 64, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial, dbg);
+    ctx->launches++;
   } else if (K == 42) {   // the flagship factor count (31 industries + 10 styles + country): compile-time loops
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel<42>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     eig_mc_kernel<42><<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+    ctx->launches++;
   } else {
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     eig_mc_kernel<0><<<grid, 128, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial);
+    ctx->launches++;
   }
-  ctx->launches++;
   eig_partial_reduce_kernel<<<(T * K + 255) / 256, 256, 0, ctx->stream>>>(T, K, nblk, partial, vsum, accumulate);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());

@@ -28,7 +28,9 @@ __device__ __forceinline__ double block_sum64(double v, double* red) {
 // Z: n x n (row stride ld, odd) holding the symmetric matrix (both triangles) on entry and the
 // eigenvectors (columns) on exit; d: eigenvalues (unsorted); e, cs (2n), red (4): scratch.
 // Returns 0, or 1 if a QL iteration did not converge in 60 sweeps (caller falls back).
-__device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs, double* red, int n, int ld) {
+// stage 1 only: on exit Z = Q (accumulated Householder transform), d = diagonal, e[0..n-2] =
+// sub-diagonal (already shifted for the QL stage), e[n-1] = 0.
+__device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, int n, int ld) {
   const int tid = threadIdx.x;
   // ---- stage 1: Householder reduction (EISPACK tred2, lower triangle), parallel over j ----
   for (int i = n - 1; i >= 1; --i) {
@@ -100,12 +102,18 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
     if (tid <= l) { Z[tid * ld + i] = 0.0; Z[i * ld + tid] = 0.0; }
     __syncthreads();
   }
-  // ---- stage 2: implicit QL on (d, e) with the rotations of each sweep applied row-wise ----
   if (tid == 0) {
     for (int i = 1; i < n; ++i) e[i - 1] = e[i];
     e[n - 1] = 0.0;
   }
   __syncthreads();
+}
+
+__device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs, double* red, int n, int ld, int dbg = 0) {
+  const int tid = threadIdx.x;
+  tred2_cta(Z, d, e, red, n, ld);
+  if (dbg == 1) return 0;
+  // ---- stage 2: implicit QL on (d, e) with the rotations of each sweep applied row-wise ----
   int* ictl = reinterpret_cast<int*>(red + 2);   // [0] = m, [1] = lowest rotation index applied, [2] = fail
   if (tid == 0) ictl[2] = 0;
   for (int l = 0; l < n; ++l) {
@@ -125,32 +133,39 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
           double s = 1.0, c = 1.0, p = 0.0;
           int i = m - 1;
           bool brk = false;
+          // the chain is one long dependency; the operands of the NEXT step are fetched a step
+          // ahead and d[i+1] is carried in a register so no shared-memory latency sits on it
+          double e_i = e[i], d_i = d[i], d_ip1 = d[i + 1];
           for (; i >= l; --i) {
-            double f = s * e[i];
-            const double b = c * e[i];
+            const double e_nx = i > l ? e[i - 1] : 0.0, d_nx = i > l ? d[i - 1] : 0.0;
+            const double f = s * e_i;
+            const double b = c * e_i;
             const double h2 = f * f + g * g;
             const double ir = rsqrt(h2);     // one reciprocal square root instead of a sqrt and two divisions
             r = h2 * ir;
             e[i + 1] = h2 > 0.0 ? r : 0.0;
             if (!(h2 > 0.0)) {
-              d[i + 1] -= p;
+              d[i + 1] = d_ip1 - p;
               e[m] = 0.0;
               brk = true;
               break;
             }
             s = f * ir;
             c = g * ir;
-            g = d[i + 1] - p;
-            r = (d[i] - g) * s + 2.0 * c * b;
+            g = d_ip1 - p;
+            r = (d_i - g) * s + 2.0 * c * b;
             p = s * r;
             d[i + 1] = g + p;
             g = c * r - b;
             cs[2 * i] = c;
             cs[2 * i + 1] = s;
+            d_ip1 = d_i;
+            d_i = d_nx;
+            e_i = e_nx;
           }
           ilo = brk ? i + 1 : l;
           if (!brk) {
-            d[l] -= p;
+            d[l] = d_ip1 - p;     // d_ip1 now holds the untouched d[l]
             e[l] = g;
             e[m] = 0.0;
           }
@@ -160,7 +175,7 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
       }
       __syncthreads();
       const int m = ictl[0], ilo = ictl[1], fail = ictl[2];
-      if (m != l && tid < n && ilo < m) {
+      if (dbg != 2 && m != l && tid < n && ilo < m) {
         double* zr = Z + tid * ld;
         double z1 = zr[m];
         for (int i = m - 1; i >= ilo; --i) {
@@ -177,6 +192,66 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
     if (ictl[2]) return 1;
   }
   return 0;
+}
+
+
+// ---- stage 2, split form: one THREAD runs the whole QL iteration of one problem on private
+// copies of (d, e) and records every sweep — header (m | ilo << 8) and the (c, s) of its rotations
+// in application order — so that the eigenvector update can be replayed later by a CTA.  The
+// rotation chain is serial per problem but independent across problems: 32 problems per warp.
+// Returns the number of sweeps, or -1 on overflow / non-convergence.
+__device__ inline int ql_chain_record(double* d, double* e, int n, double2* cs_out, int cs_cap, int* hdr_out,
+                                      int hdr_cap, int* n_rot_out) {
+  int nrot = 0, nsw = 0;
+  for (int l = 0; l < n; ++l) {
+    for (int iter = 0;; ++iter) {
+      int m = l;
+      for (; m < n - 1; ++m) {
+        const double dd = fabs(d[m]) + fabs(d[m + 1]);
+        if (fabs(e[m]) <= 2.220446049250313e-16 * dd) break;
+      }
+      if (m == l) break;
+      if (iter >= 60) return -1;
+      double g = (d[l + 1] - d[l]) / (2.0 * e[l]);
+      double r = sqrt(g * g + 1.0);
+      g = d[m] - d[l] + e[l] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
+      double s = 1.0, c = 1.0, p = 0.0;
+      int i = m - 1;
+      bool brk = false;
+      if (nrot + (m - l) > cs_cap || nsw >= hdr_cap) return -1;
+      for (; i >= l; --i) {
+        const double f = s * e[i];
+        const double b = c * e[i];
+        const double h2 = f * f + g * g;
+        const double ir = rsqrt(h2);
+        r = h2 * ir;
+        e[i + 1] = h2 > 0.0 ? r : 0.0;
+        if (!(h2 > 0.0)) {
+          d[i + 1] -= p;
+          e[m] = 0.0;
+          brk = true;
+          break;
+        }
+        s = f * ir;
+        c = g * ir;
+        g = d[i + 1] - p;
+        r = (d[i] - g) * s + 2.0 * c * b;
+        p = s * r;
+        d[i + 1] = g + p;
+        g = c * r - b;
+        cs_out[nrot++] = make_double2(c, s);
+      }
+      const int ilo = brk ? i + 1 : l;
+      if (!brk) {
+        d[l] -= p;
+        e[l] = g;
+        e[m] = 0.0;
+      }
+      hdr_out[nsw++] = m | (ilo << 8);
+    }
+  }
+  *n_rot_out = nrot;
+  return nsw;
 }
 
 }  // namespace bmfm

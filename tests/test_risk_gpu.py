@@ -81,7 +81,7 @@ def test_gauss_cov_legacy_stream(ops):
 
 
 @pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
-@pytest.mark.parametrize("solver", ["0", "1"])     # 0: tridiagonal QL (default), 1: block Jacobi
+@pytest.mark.parametrize("solver", ["0", "1", "2"])     # 0: split tridiagonal QL (default), 1: block Jacobi, 2: fused QL
 def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, monkeypatch):
     monkeypatch.setenv("BMFM_EIG_MODE", solver)
     cov = risk["eig_cov_in"]
@@ -94,7 +94,7 @@ def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, monkeypatch):
     print(f"literal-vs-canonical gap T={T} M={M}: {gap:.3e}")
 
 
-@pytest.mark.parametrize("solver", ["0", "1"])
+@pytest.mark.parametrize("solver", ["0", "1", "2"])
 def test_eigen_by_time_oracle(ops, solver, monkeypatch):
     """K = 42 factor covariances from an expanding Newey-West run, simulation length 252."""
     monkeypatch.setenv("BMFM_EIG_MODE", solver)
