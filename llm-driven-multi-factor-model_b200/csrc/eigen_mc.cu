@@ -307,6 +307,8 @@ __global__ void __launch_bounds__(64) eig_mc_tql_kernel(int T, int K, int nsim, 
 //                              the rows of Q (thread = row, no barriers), then v_m = diag(W'D0W)/lambda
 // Scratch per problem: Q 8K^2 + rotations 16 * 2K^2 + headers 4 * 8K + 24K bytes (~72 KB at K = 42).
 // ------------------------------------------------------------------------------------------
+constexpr int EIG_WIN = 256;   // rotations per staged window in the apply kernel
+
 struct EigSplit {
   int K, nsim, P;          // P = problems in this batch = dates_in_batch * nsim
   int t0;                  // first date of the batch
@@ -377,6 +379,8 @@ __global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nb
   double* lamv = Z + K * ld;    // K
   double* d0 = lamv + K;        // K
   double* vacc = d0 + K;        // K
+  double2* s_win = reinterpret_cast<double2*>(vacc + K + (K & 1));   // EIG_WIN rotations
+  int* s_hdr = reinterpret_cast<int*>(s_win + EIG_WIN);              // smax sweep headers
   const int per = (sp.nsim + nblk - 1) / nblk;
   const int nd = sp.P / sp.nsim;
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
@@ -399,17 +403,29 @@ __global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nb
       if (tid < K) lamv[tid] = sp.lam[(size_t)tid * sp.P + p];
       __syncthreads();
       const int nsw = sp.nsw[p];
-      if (tid < K && nsw > 0) {
+      if (nsw > 0) {
+        // headers and rotations are staged through shared memory by the whole CTA (coalesced
+        // 16-byte loads); a sweep has at most K-1 rotations, so it always fits one window
         const double2* cs = sp.cs + (size_t)p * sp.rmax;
         const int* hdr = sp.hdr + (size_t)p * sp.smax;
-        double* zr = Z + tid * ld;
-        int pos = 0;
+        for (int i = tid; i < nsw; i += nt) s_hdr[i] = hdr[i];
+        int win_base = 0, win_end = 0, pos = 0;
+        double* zr = Z + (tid < K ? tid : 0) * ld;
+        __syncthreads();
         for (int sw = 0; sw < nsw; ++sw) {
-          const int h = hdr[sw];
-          const int mm = h & 0xff, ilo = h >> 8;
-          if (ilo < mm) {
+          const int h = s_hdr[sw];
+          const int mm = h & 0xff, ilo = h >> 8, len = mm - ilo;
+          if (len <= 0) continue;
+          if (pos + len > win_end) {          // uniform across the CTA
+            __syncthreads();
+            win_base = pos;
+            win_end = min(pos + EIG_WIN, sp.rmax);
+            for (int i = tid; i < win_end - win_base; i += nt) s_win[i] = cs[win_base + i];
+            __syncthreads();
+          }
+          if (tid < K) {
             double z1 = zr[mm];
-            const double2* c2 = cs + pos + (mm - 1);
+            const double2* c2 = s_win + (pos - win_base) + (mm - 1);
 #pragma unroll 4
             for (int i = mm - 1; i >= ilo; --i) {
               const double2 r = c2[-i];          // rotation of index i is stored at pos + (mm-1-i)
@@ -418,8 +434,8 @@ __global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nb
               z1 = fma(r.x, zi, -r.y * z1);
             }
             zr[ilo] = z1;
-            pos += mm - ilo;
           }
+          pos += len;
         }
       }
       __syncthreads();
@@ -581,7 +597,8 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
     sp.Qs = (double*)(base + off_Q); sp.de = (double*)(base + off_de); sp.lam = (double*)(base + off_lam);
     sp.cs = (double2*)(base + off_cs); sp.hdr = (int*)(base + off_hdr); sp.nsw = (int*)(base + off_nsw);
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_tred_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem_apply = ((size_t)K * (K | 1) + 3 * K + 2) * 8 + (size_t)EIG_WIN * 16 + (size_t)smax * 4 + 16;
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_apply));
     for (int t0 = 0; t0 < T; t0 += nd_batch) {
       const int nd = T - t0 < nd_batch ? T - t0 : nd_batch;
       sp.t0 = t0;
@@ -590,7 +607,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
       eig_split_tred_kernel<<<gA, 64, smem, ctx->stream>>>(sp, C, D0, status);
       eig_split_chain_kernel<<<(sp.P + 127) / 128, 128, 0, ctx->stream>>>(sp, status);
       const long long wC = (long long)nd * nblk;
-      eig_split_apply_kernel<<<(int)(wC < slots ? wC : slots), 64, smem, ctx->stream>>>(sp, nblk, D0, status, partial);
+      eig_split_apply_kernel<<<(int)(wC < slots ? wC : slots), 64, smem_apply, ctx->stream>>>(sp, nblk, D0, status, partial);
       ctx->launches += 3;
     }
   } else if (use_ql) {

@@ -62,9 +62,23 @@ __device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, i
           const int j = tid;
           const double uj = Z[i * ld + j];
           Z[j * ld + i] = uj / h;
-          double g = 0.0;
-          for (int k = 0; k <= j; ++k) g = fma(Z[j * ld + k], Z[i * ld + k], g);
-          for (int k = j + 1; k <= l; ++k) g = fma(Z[k * ld + j], Z[i * ld + k], g);
+          // four independent partial sums: the loop is otherwise one LDS -> FMA dependency chain
+          double g0 = 0.0, g1 = 0.0, g2 = 0.0, g3 = 0.0;
+          const double* zj = Z + j * ld;
+          const double* zi = Z + i * ld;
+          int k = 0;
+          for (; k + 3 <= j; k += 4) {
+            g0 = fma(zj[k], zi[k], g0); g1 = fma(zj[k + 1], zi[k + 1], g1);
+            g2 = fma(zj[k + 2], zi[k + 2], g2); g3 = fma(zj[k + 3], zi[k + 3], g3);
+          }
+          for (; k <= j; ++k) g0 = fma(zj[k], zi[k], g0);
+          k = j + 1;
+          for (; k + 3 <= l; k += 4) {
+            g0 = fma(Z[k * ld + j], zi[k], g0); g1 = fma(Z[(k + 1) * ld + j], zi[k + 1], g1);
+            g2 = fma(Z[(k + 2) * ld + j], zi[k + 2], g2); g3 = fma(Z[(k + 3) * ld + j], zi[k + 3], g3);
+          }
+          for (; k <= l; ++k) g0 = fma(Z[k * ld + j], zi[k], g0);
+          const double g = (g0 + g1) + (g2 + g3);
           ej = g / h;
           fj = ej * uj;
         }
@@ -76,7 +90,16 @@ __device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, i
         if (tid <= l) {
           const int j = tid;
           const double fu = Z[i * ld + j], gq = e[j];
-          for (int k = 0; k <= j; ++k) Z[j * ld + k] -= fu * e[k] + gq * Z[i * ld + k];
+          double* zj = Z + j * ld;
+          const double* zi = Z + i * ld;
+          int k = 0;
+          for (; k + 3 <= j; k += 4) {
+            const double a0 = zj[k], a1 = zj[k + 1], a2 = zj[k + 2], a3 = zj[k + 3];
+            const double b0 = fma(fu, e[k], gq * zi[k]), b1 = fma(fu, e[k + 1], gq * zi[k + 1]);
+            const double b2 = fma(fu, e[k + 2], gq * zi[k + 2]), b3 = fma(fu, e[k + 3], gq * zi[k + 3]);
+            zj[k] = a0 - b0; zj[k + 1] = a1 - b1; zj[k + 2] = a2 - b2; zj[k + 3] = a3 - b3;
+          }
+          for (; k <= j; ++k) zj[k] -= fu * e[k] + gq * zi[k];
         }
         __syncthreads();
       }
@@ -93,9 +116,23 @@ __device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, i
     const int l = i - 1;
     if (d[i] != 0.0 && tid <= l) {
       const int j = tid;
-      double g = 0.0;
-      for (int k = 0; k <= l; ++k) g = fma(Z[i * ld + k], Z[k * ld + j], g);
-      for (int k = 0; k <= l; ++k) Z[k * ld + j] -= g * Z[k * ld + i];
+      double g0 = 0.0, g1 = 0.0, g2 = 0.0, g3 = 0.0;
+      const double* zi = Z + i * ld;
+      int k = 0;
+      for (; k + 3 <= l; k += 4) {
+        g0 = fma(zi[k], Z[k * ld + j], g0); g1 = fma(zi[k + 1], Z[(k + 1) * ld + j], g1);
+        g2 = fma(zi[k + 2], Z[(k + 2) * ld + j], g2); g3 = fma(zi[k + 3], Z[(k + 3) * ld + j], g3);
+      }
+      for (; k <= l; ++k) g0 = fma(zi[k], Z[k * ld + j], g0);
+      const double g = (g0 + g1) + (g2 + g3);
+      k = 0;
+      for (; k + 3 <= l; k += 4) {
+        const double a0 = Z[k * ld + j], a1 = Z[(k + 1) * ld + j], a2 = Z[(k + 2) * ld + j], a3 = Z[(k + 3) * ld + j];
+        const double u0 = Z[k * ld + i], u1 = Z[(k + 1) * ld + i], u2 = Z[(k + 2) * ld + i], u3 = Z[(k + 3) * ld + i];
+        Z[k * ld + j] = fma(-g, u0, a0); Z[(k + 1) * ld + j] = fma(-g, u1, a1);
+        Z[(k + 2) * ld + j] = fma(-g, u2, a2); Z[(k + 3) * ld + j] = fma(-g, u3, a3);
+      }
+      for (; k <= l; ++k) Z[k * ld + j] -= g * Z[k * ld + i];
     }
     __syncthreads();
     if (tid == 0) { d[i] = Z[i * ld + i]; Z[i * ld + i] = 1.0; }
