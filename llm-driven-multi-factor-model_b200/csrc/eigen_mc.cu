@@ -354,21 +354,23 @@ __global__ void __launch_bounds__(64) eig_split_tred_kernel(EigSplit sp, const d
 }
 
 __global__ void __launch_bounds__(128) eig_split_chain_kernel(EigSplit sp, const int* status) {
+  extern __shared__ __align__(16) unsigned char smem[];
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= sp.P) return;
-  const int K = sp.K;
+  const int K = sp.K, st = blockDim.x;
   const int t = sp.t0 + p / sp.nsim;
   if (status[t] != BMFM_ST_OK) { sp.nsw[p] = 0; return; }
-  double d[64], e[64];
+  double* d = reinterpret_cast<double*>(smem) + threadIdx.x;      // [k][thread]
+  double* e = d + (size_t)K * st;
   for (int k = 0; k < K; ++k) {
-    d[k] = sp.de[(size_t)k * sp.P + p];
-    e[k] = sp.de[(size_t)(K + k) * sp.P + p];
+    d[k * st] = sp.de[(size_t)k * sp.P + p];
+    e[k * st] = sp.de[(size_t)(K + k) * sp.P + p];
   }
   int nrot = 0;
-  const int nsw = ql_chain_record(d, e, K, sp.cs + (size_t)p * sp.rmax, sp.rmax, sp.hdr + (size_t)p * sp.smax,
+  const int nsw = ql_chain_record(d, e, st, K, sp.cs + (size_t)p * sp.rmax, sp.rmax, sp.hdr + (size_t)p * sp.smax,
                                   sp.smax, &nrot);
   sp.nsw[p] = nsw;
-  for (int k = 0; k < K; ++k) sp.lam[(size_t)k * sp.P + p] = d[k];
+  for (int k = 0; k < K; ++k) sp.lam[(size_t)k * sp.P + p] = d[k * st];
 }
 
 __global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nblk, const double* D0,
@@ -597,6 +599,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
     sp.Qs = (double*)(base + off_Q); sp.de = (double*)(base + off_de); sp.lam = (double*)(base + off_lam);
     sp.cs = (double2*)(base + off_cs); sp.hdr = (int*)(base + off_hdr); sp.nsw = (int*)(base + off_nsw);
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_tred_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * K * 64 * 8));
     const size_t smem_apply = ((size_t)K * (K | 1) + 3 * K + 2) * 8 + (size_t)EIG_WIN * 16 + (size_t)smax * 4 + 16;
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_split_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_apply));
     for (int t0 = 0; t0 < T; t0 += nd_batch) {
@@ -605,7 +608,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
       sp.P = nd * nsim;
       const int gA = sp.P < slots ? sp.P : slots;
       eig_split_tred_kernel<<<gA, 64, smem, ctx->stream>>>(sp, C, D0, status);
-      eig_split_chain_kernel<<<(sp.P + 127) / 128, 128, 0, ctx->stream>>>(sp, status);
+      eig_split_chain_kernel<<<(sp.P + 63) / 64, 64, (size_t)2 * K * 64 * 8, ctx->stream>>>(sp, status);
       const long long wC = (long long)nd * nblk;
       eig_split_apply_kernel<<<(int)(wC < slots ? wC : slots), 64, smem_apply, ctx->stream>>>(sp, nblk, D0, status, partial);
       ctx->launches += 3;

@@ -237,52 +237,60 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
 // in application order — so that the eigenvector update can be replayed later by a CTA.  The
 // rotation chain is serial per problem but independent across problems: 32 problems per warp.
 // Returns the number of sweeps, or -1 on overflow / non-convergence.
-__device__ inline int ql_chain_record(double* d, double* e, int n, double2* cs_out, int cs_cap, int* hdr_out,
-                                      int hdr_cap, int* n_rot_out) {
+// d, e: private copies with element stride `st` (shared memory laid out [k][thread], so the lanes of
+// a warp touch consecutive banks).
+__device__ inline int ql_chain_record(double* d, double* e, int st, int n, double2* cs_out, int cs_cap,
+                                      int* hdr_out, int hdr_cap, int* n_rot_out) {
   int nrot = 0, nsw = 0;
   for (int l = 0; l < n; ++l) {
     for (int iter = 0;; ++iter) {
       int m = l;
       for (; m < n - 1; ++m) {
-        const double dd = fabs(d[m]) + fabs(d[m + 1]);
-        if (fabs(e[m]) <= 2.220446049250313e-16 * dd) break;
+        const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
+        if (fabs(e[m * st]) <= 2.220446049250313e-16 * dd) break;
       }
       if (m == l) break;
       if (iter >= 60) return -1;
-      double g = (d[l + 1] - d[l]) / (2.0 * e[l]);
+      double g = (d[(l + 1) * st] - d[l * st]) / (2.0 * e[l * st]);
       double r = sqrt(g * g + 1.0);
-      g = d[m] - d[l] + e[l] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
+      g = d[m * st] - d[l * st] + e[l * st] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
       double s = 1.0, c = 1.0, p = 0.0;
       int i = m - 1;
       bool brk = false;
       if (nrot + (m - l) > cs_cap || nsw >= hdr_cap) return -1;
+      // operands of the next step are fetched one step ahead; d[i+1] is carried in a register
+      double e_i = e[i * st], d_i = d[i * st], d_ip1 = d[(i + 1) * st];
       for (; i >= l; --i) {
-        const double f = s * e[i];
-        const double b = c * e[i];
+        const double e_nx = i > l ? e[(i - 1) * st] : 0.0, d_nx = i > l ? d[(i - 1) * st] : 0.0;
+        const double f = s * e_i;
+        const double b = c * e_i;
         const double h2 = f * f + g * g;
         const double ir = rsqrt(h2);
         r = h2 * ir;
-        e[i + 1] = h2 > 0.0 ? r : 0.0;
+        e[(i + 1) * st] = h2 > 0.0 ? r : 0.0;
         if (!(h2 > 0.0)) {
-          d[i + 1] -= p;
-          e[m] = 0.0;
+          d[(i + 1) * st] = d_ip1 - p;
+          e[m * st] = 0.0;
           brk = true;
           break;
         }
         s = f * ir;
         c = g * ir;
-        g = d[i + 1] - p;
-        r = (d[i] - g) * s + 2.0 * c * b;
+        g = d_ip1 - p;
+        r = (d_i - g) * s + 2.0 * c * b;
         p = s * r;
-        d[i + 1] = g + p;
+        d[(i + 1) * st] = g + p;
         g = c * r - b;
         cs_out[nrot++] = make_double2(c, s);
+        d_ip1 = d_i;
+        d_i = d_nx;
+        e_i = e_nx;
       }
       const int ilo = brk ? i + 1 : l;
       if (!brk) {
-        d[l] -= p;
-        e[l] = g;
-        e[m] = 0.0;
+        d[l * st] = d_ip1 - p;
+        e[l * st] = g;
+        e[m * st] = 0.0;
       }
       hdr_out[nsw++] = m | (ilo << 8);
     }
