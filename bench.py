@@ -128,10 +128,12 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU port (oracle) — the reference arm and the cpu_baseline leg
 # ------------------------------------------------------------------------------------------------
-def cpu_sample(panel_csr, n_dates_sample=24, seed=0):
+def cpu_sample(panel_csr, n_dates_sample=24, vr_dates=None):
     """Time the numpy restatement of the reference on a bounded sample of the C2 step and
     return (dates_per_sec, description).  One 'date' of the step costs: its cross-sectional
-    regression + its expanding-window Newey-West + its share of the vol-regime loop."""
+    regression + its expanding-window Newey-West + its share of the vol-regime loop.
+    `vr_dates`: run the O(T^2) vol-regime loop on that many dates only and scale its per-date
+    cost linearly to the full T (None = the full loop)."""
     from oracle import barra_oracle as orc
     from bmfm.synth import make_factor_returns
     off = panel_csr["date_off"]
@@ -150,15 +152,17 @@ def cpu_sample(panel_csr, n_dates_sample=24, seed=0):
     for t in pick:
         covs[t] = orc.newey_west(fr[:t + 1], NW_Q, NW_TAO)
     t_nw = (time.perf_counter() - t0) / len(pick)
-    # vol-regime: the O(T^2) loop over all dates on a covariance series that repeats the sampled ones
-    cov_list = [covs[pick[min(np.searchsorted(pick, t), len(pick) - 1)]] for t in range(T)]
+    # vol-regime: the reference's O(T^2) loop on a covariance series that repeats the sampled ones
+    Tv = T if vr_dates is None else min(T, int(vr_dates))
+    cov_list = [covs[pick[min(np.searchsorted(pick, t), len(pick) - 1)]] for t in range(Tv)]
     t0 = time.perf_counter()
-    orc.vol_regime_adj_by_time(fr, cov_list, VR_TAO)
-    t_vr = (time.perf_counter() - t0) / T
+    orc.vol_regime_adj_by_time(fr[:Tv], cov_list, VR_TAO)
+    t_vr = (time.perf_counter() - t0) / Tv * (T / Tv)      # per-date cost grows linearly with T
     per_date = t_reg + t_nw + t_vr
+    vr_txt = "full vol-regime loop" if Tv == T else f"vol-regime loop on {Tv} dates scaled x{T / Tv:.1f} to T={T}"
     desc = (f"numpy port of the reference (oracle/barra_oracle.py; vectorised Newey-West, no N x N diag(W)): "
             f"{len(pick)} evenly spaced dates of the {N_STOCKS}x{T} panel for reg ({t_reg*1e3:.2f} ms/date) and "
-            f"expanding Newey-West ({t_nw*1e3:.2f} ms/date), full vol-regime loop ({t_vr*1e3:.3f} ms/date); "
+            f"expanding Newey-West ({t_nw*1e3:.2f} ms/date), {vr_txt} ({t_vr*1e3:.3f} ms/date); "
             f"dates/s = 1 / sum")
     return 1.0 / per_date, desc
 
@@ -190,12 +194,16 @@ def run_reference(args):
     pan = make_panel(N_DATES, N_STOCKS, P, Q, seed=20240002, scale_log10=(-2, 2))
     csr = pan.to_csr()
     vals = []
+    # every step is a bounded sample; the sample shrinks with the step count so that the whole
+    # --steps K --warmup W run stays within a few minutes
+    n_dates = int(max(8, min(600, 12000 // max(1, args.steps + args.warmup))))
+    vr_dates = None if args.steps + args.warmup <= 8 else 400
     for i in range(args.warmup):
-        cpu_sample(csr, 4)
+        cpu_sample(csr, n_dates, vr_dates)
     t0 = time.perf_counter()
     desc = ""
     for i in range(args.steps):
-        v, desc = cpu_sample(csr, 600)
+        v, desc = cpu_sample(csr, n_dates, vr_dates)
         vals.append(v)
     dt = time.perf_counter() - t0
     value = float(np.mean(vals))

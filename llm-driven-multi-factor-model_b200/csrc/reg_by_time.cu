@@ -217,7 +217,7 @@ __device__ void accumulate_date(const RegParams& p, const RegSmem& L, unsigned c
         for (int q = 0; q < Q; ++q) {
           acc2[q] = fma(cap, d[q], acc2[q]);
           acc2[Q + q] += d[q];
-          acc2[2 * Q + q] = fma(d[q], d[q], acc2[2 * Q + q]);
+          acc2[2 * Q] = fma(d[q], d[q], acc2[2 * Q]);   // only the total over q enters the scalar std
         }
       }
     }
@@ -908,6 +908,8 @@ __global__ void __launch_bounds__(256) reg_dense_kernel(RegParams p) {
 // and pass C replays the date through the ring — the second read is served by the 126 MB L2 (the
 // in-flight footprint of 8 warps x 148 SMs x 80 KB is below it), so HBM still sees ~one read.
 constexpr int RS_STAGES = 4;
+constexpr int RS_WARPS = 4;   // warps per CTA of the streaming kernel
+constexpr int RS_CTAS = 2;    // CTAs per SM
 
 template <int Q>
 __host__ __device__ constexpr int rs_stage_bytes() { return 32 * (Q * 8 + 8 + 8 + 4); }
@@ -955,7 +957,9 @@ __device__ __forceinline__ void rs_issue_chunk(const RegParams& p, long long row
 }
 
 template <int Q>
-__global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
+// 128 threads x 2 CTAs = 8 warps per SM at 255 registers (97 fp64 accumulators); 9 warps at 224 registers
+// was tried and is 1.9x slower (spills inside the accumulation loop)
+__global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int NA1PAD = na1pad_of(Q), NA2PAD = na2pad_of(Q);
   constexpr int QQ = Q > 0 ? Q : 1;
@@ -1050,7 +1054,7 @@ __global__ void __launch_bounds__(128, 2) reg_stream_kernel(RegParams p) {
             acc1[Q * (Q + 1) / 2 + q] = fma(wd, y, acc1[Q * (Q + 1) / 2 + q]);
             acc2[q] = fma(cap, d[q], acc2[q]);
             acc2[Q + q] += d[q];
-            acc2[2 * Q + q] = fma(d[q], d[q], acc2[2 * Q + q]);
+            acc2[2 * Q] = fma(d[q], d[q], acc2[2 * Q]);   // only the total over q enters the scalar std
           }
         }
       }
@@ -1197,11 +1201,11 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);
     const int per_warp = rs_per_warp_bytes<Q>(Lw.total);
-    const int smem_s = 4 * per_warp;
+    const int smem_s = RS_WARPS * per_warp;
     BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_stream_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
-    int grid = ctx->sm_count * 2;
-    if (grid * 4 > p.T) grid = (p.T + 3) / 4;
-    reg_stream_kernel<Q><<<grid, 128, smem_s, ctx->stream>>>(p);
+    int grid = ctx->sm_count * RS_CTAS;
+    if (grid * RS_WARPS > p.T) grid = (p.T + RS_WARPS - 1) / RS_WARPS;
+    reg_stream_kernel<Q><<<grid, RS_WARPS * 32, smem_s, ctx->stream>>>(p);
     ctx->launches++;
     BMFM_CUDA(ctx, cudaGetLastError());
   } else if (!p.all_dense) {

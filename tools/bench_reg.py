@@ -1,0 +1,46 @@
+#!/usr/bin/env python
+"""Time the regression entry point alone on a synthetic panel of a given shape (CUDA events).
+
+    python tools/bench_reg.py N T [mode]        mode: BMFM_REG_MODE (0 auto, 1 CTA kernel, 2 stream kernel)
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "llm-driven-multi-factor-model_b200"))
+from bmfm import _cabi            # noqa: E402
+from bmfm.panel import pack_arrays  # noqa: E402
+from bmfm.synth import make_panel   # noqa: E402
+
+N, T = int(sys.argv[1]), int(sys.argv[2])
+if len(sys.argv) > 3:
+    os.environ["BMFM_REG_MODE"] = sys.argv[3]
+P, Q = 31, 10
+K = 1 + P + Q
+pan = make_panel(T, N, P, Q, seed=3, scale_log10=(-2, 2))
+csr = pan.to_csr()
+(cap, ret, ind, style), pos = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P)
+d = lambda a: torch.from_numpy(a).cuda()
+off, cap, ret, ind, style = d(csr["date_off"]), d(cap), d(ret), d(ind), d(style)
+rows = int(csr["date_off"][-1])
+fr = torch.empty((T, K), dtype=torch.float64, device="cuda")
+spec = torch.empty(rows, dtype=torch.float64, device="cuda")
+r2 = torch.empty(T, dtype=torch.float64, device="cuda")
+st = torch.empty(T, dtype=torch.int32, device="cuda")
+ctx = _cabi.default_context()
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+times = []
+for i in range(8):
+    flush.fill_(i)        # evict the panel from L2 between iterations
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ctx.reg_by_time(T, P, Q, N, off, cap, ret, ind, style, fr, spec, r2, st)
+    e1.record()
+    torch.cuda.synchronize()
+    times.append(e0.elapsed_time(e1))
+ms = float(np.median(times[3:]))
+print(f"N={N} T={T} mode={os.environ.get('BMFM_REG_MODE', '0')}: {ms:.3f} ms, {rows * 108 / ms / 1e6:.0f} GB/s "
+      f"({rows * 108 / ms / 1e6 / 6538:.3f} of measured HBM), {T / ms * 1e3:.0f} dates/s, status ok={bool((st == 0).all())}")
