@@ -66,7 +66,7 @@ def load_traffic():
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region (NVML, every ~5 ms; the
+    """SM clock and throttle reasons sampled DURING the timed region (NVML, every ~50 ms — faster polling was seen to slow the GPU being polled; the
     nvidia-smi loop of B200_PROFILING.md is too coarse for a region of tens of milliseconds)."""
 
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
@@ -105,7 +105,7 @@ class ClockSampler:
                 for bit, name in self.REASONS.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.004)
+                time.sleep(0.05)
         except Exception as e:      # noqa: BLE001
             self.err = repr(e)
 
@@ -238,12 +238,17 @@ def run_gpu(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    os.environ["NCCL_DEBUG"] = os.environ.get("BENCH_NCCL_DEBUG", "WARN")   # keep NCCL's banner off stdout
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep NCCL's version banner off stdout (one JSON line)
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
-    ctx = _cabi.Context(local_rank)
+    # everything runs on one side stream, so that the multi-GPU step can be captured in a CUDA graph
+    gs = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(gs)
+    ctx = _cabi.Context(local_rank, stream=gs.cuda_stream)
+    nocoll = os.environ.get("BENCH_NO_COLL") == "1"     # timing experiment only (results are wrong)
+    use_graph = os.environ.get("BENCH_GRAPH", "1" if world > 1 else "0") == "1"
 
     # this rank's block of dates (weak scaling: 2500 dates per rank)
     pan = make_panel(N_DATES, N_STOCKS, P, Q, seed=20240002 + rank, scale_log10=(-2, 2))
@@ -294,12 +299,20 @@ def run_gpu(args):
         vol_regime()
         e[3].record()
 
+    def step_body():      # the same step without timing events (graph capture)
+        ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
+        if world > 1 and not nocoll:
+            dist.all_gather_into_tensor(fr_all, fr)
+        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
+        vol_regime()
+
     def vol_regime():
         if world == 1:
             ctx.vol_regime_adj_by_time(T, K, VR_TAO, fr, nw, nw_st, vr, lamb)
         else:
             ctx.vol_regime_bias(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wbv[0], wbv[1])
-            dist.all_gather_into_tensor(wbv_all, wbv)
+            if not nocoll:
+                dist.all_gather_into_tensor(wbv_all, wbv)
             wb_all.view(world, T).copy_(wbv_all[:, 0])
             wv_all.view(world, T).copy_(wbv_all[:, 1])
             ctx.vol_regime_scale(T_all, lo, T, K, wb_all, wv_all, nw, nw_st, vr, lamb)
@@ -309,22 +322,44 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    l0 = ctx.launches
     for i in range(args.warmup):
         step(i)
+    launches_per_step = (ctx.launches - l0) // max(1, args.warmup)
     barrier()
+    graph = None
+    if use_graph:
+        # one step (kernels + NCCL collectives) captured once and replayed: removes the host-side launch and
+        # collective-enqueue gaps that dominate a sub-millisecond multi-GPU step
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=gs):
+                step_body()
+            graph.replay()
+            barrier()
+        except Exception as e:      # noqa: BLE001
+            log(f"CUDA graph capture failed ({e!r}); timing eager steps")
+            graph = None
+            torch.cuda.set_stream(gs)
     sampler = ClockSampler(local_rank)
-    if rank == 0:
+    if rank == 0 and os.environ.get("BENCH_NO_SAMPLER") != "1":
         sampler.start()
     launches0 = ctx.launches
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
     t_start.record()
-    for i in range(args.warmup, args.warmup + args.steps):
-        step(i)
+    if graph is not None:
+        for i in range(args.steps):
+            graph.replay()
+    else:
+        for i in range(args.warmup, args.warmup + args.steps):
+            step(i)
     t_end.record()
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if (rank == 0 and sampler.thread is not None) else None
     launches = ctx.launches - launches0
+    if graph is not None:
+        launches = launches_per_step * args.steps      # replays do not go through the C-ABI counters
     ms_total = t_start.elapsed_time(t_end)
     tm = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
@@ -332,13 +367,20 @@ def run_gpu(args):
     ms_total = float(tm.item())
     ms_step = ms_total / args.steps
     value = T_all / (ms_step * 1e-3)
-    timed = ev[args.warmup:]
+    # per-phase times: from the timed steps (eager) or, in graph mode, from the eager warm-up steps
+    timed = ev[args.warmup:] if graph is None else ev[max(0, args.warmup - 3):args.warmup]
     ms_reg = float(np.mean([e[0].elapsed_time(e[1]) for e in timed]))
     ms_nw = float(np.mean([e[1].elapsed_time(e[2]) for e in timed]))
     ms_vr = float(np.mean([e[2].elapsed_time(e[3]) for e in timed]))
 
     # parity spot-check of what was timed (not a substitute for tests/)
     status_ok = bool((st == 0).all().item())
+    log(f"rank {rank}: phases ms reg {ms_reg:.3f} nw {ms_nw:.3f} vr {ms_vr:.3f}; step {ms_step:.3f}; "
+        f"status!=0 on {int((st != 0).sum().item())} dates")
+    if world > 1:
+        ok_t = torch.tensor([1 if status_ok else 0], device=dev)
+        dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+        status_ok = bool(ok_t.item())
 
     # ---- end to end: pinned host buffers -> device -> results back in pinned host buffers ----
     h2d = sum(v.numel() * v.element_size() for v in host.values())
@@ -348,7 +390,7 @@ def run_gpu(args):
         for k in host:
             d[k].copy_(host[k], non_blocking=True)
         ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
-        if world > 1:
+        if world > 1 and not nocoll:
             dist.all_gather_into_tensor(fr_all, fr)
         ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
         vol_regime()
@@ -423,7 +465,8 @@ def run_gpu(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES} per GPU, P={P}, Q={Q}: reg_by_time + "
                                    f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})",
-                       "parallelism": f"dates sharded over {world} GPU(s); all-gather of factor returns" if world > 1 else "1 GPU",
+                       "parallelism": f"dates sharded over {world} GPU(s); all-gather of factor returns and vol-regime terms" if world > 1 else "1 GPU",
+                       "timed_as": "CUDA graph replays of one captured step (phase_ms from the eager warm-up steps)" if graph is not None else "eager launches",
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
                        "all_status_ok": status_ok},
@@ -443,7 +486,13 @@ def run_gpu(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # leave without tearing NCCL down: destroying the process group while a captured graph still holds
+        # NCCL work was seen to hang at exit; everything is flushed and the numbers are out
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
