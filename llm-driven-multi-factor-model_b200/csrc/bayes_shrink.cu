@@ -19,6 +19,14 @@ namespace bmfm {
 
 constexpr int BS_MAX_GROUPS = 64;
 constexpr int BS_ST_DUP_EDGES = 5;
+constexpr int BS_BIN_BITS = 11, BS_BINS = 1 << BS_BIN_BITS;   // histogram of the multi-select
+constexpr int BS_COLL_MAX = 2048;                              // members of needed bins ranked by counting
+
+// order-preserving map double -> uint64
+__device__ __forceinline__ unsigned long long bs_key(double x) {
+  const unsigned long long u = (unsigned long long)__double_as_longlong(x);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
 
 struct BsParams {
   int T, ngroup;
@@ -38,41 +46,165 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
   double* s_edges = s_sort + p.npad;                  // ngroup + 1
   double* s_gsum = s_edges + BS_MAX_GROUPS + 1;       // [ngroup][4]: sum vol*cap, sum cap, count, sum (vol-m)^2
   int* s_flag = reinterpret_cast<int*>(s_gsum + 4 * BS_MAX_GROUPS);
+  // per-warp private copies of the group sums: the ~10 groups are hit by every row, one shared table
+  // would serialise thousands of shared-memory atomics on a handful of addresses
+  double* s_wsum = reinterpret_cast<double*>(s_flag + 4);   // [nwarps][ngroup][4]
+  const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  double* my = s_wsum + (size_t)warp * p.ngroup * 4;
+  // multi-select scratch
+  double* s_rval = s_wsum + (size_t)nwarps * p.ngroup * 4;            // [2 (G+1)] values at the wanted ranks
+  unsigned long long* s_k = reinterpret_cast<unsigned long long*>(s_rval + 2 * BS_MAX_GROUPS + 2);   // key min / max
+  int* s_hist = reinterpret_cast<int*>(s_k + 2);                      // [BS_BINS + 1] counts, then exclusive prefix
+  int* s_need = s_hist + BS_BINS + 1;                                 // [BS_BINS] slot of a needed bin, -1 otherwise
+  int* s_rank = s_need + BS_BINS;                                     // [2 (G+1)] wanted ranks
+  int* s_rbin = s_rank + 2 * BS_MAX_GROUPS + 2;
+  int* s_slotbin = s_rbin + 2 * BS_MAX_GROUPS + 2;
+  int* s_slotoff = s_slotbin + 2 * BS_MAX_GROUPS + 2;                 // [+1]
+  int* s_fill = s_slotoff + 2 * BS_MAX_GROUPS + 3;
+  int* s_ctl = s_fill + 2 * BS_MAX_GROUPS + 2;                        // nslots, ncoll, spare
   const int tid = threadIdx.x, nt = blockDim.x, G = p.ngroup;
   for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
     const long long a = p.date_off[t];
     const int n = (int)(p.date_off[t + 1] - a);
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    for (int i = tid; i < p.npad; i += nt) s_sort[i] = i < n ? p.cap[a + i] : inf;
     for (int i = tid; i < 4 * G; i += nt) s_gsum[i] = 0.0;
-    if (tid == 0) *s_flag = 0;
+    for (int i = tid; i < nwarps * 4 * G; i += nt) s_wsum[i] = 0.0;
+    if (tid == 0) { *s_flag = 0; s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; s_k[0] = ~0ull; s_k[1] = 0ull; }
+    for (int i = tid; i < BS_BINS + 1; i += nt) { s_hist[i] = 0; if (i < BS_BINS) s_need[i] = -1; }
+    // the order statistics the quantile edges need: ranks ip / in of every edge (numpy 'linear')
+    if (tid <= G && n > 0) {
+      const double virt = __dmul_rn((double)(n - 1), p.quant[tid]);
+      int ip = (int)floor(virt), in = ip + 1;
+      if (virt >= (double)(n - 1)) ip = in = n - 1;
+      if (virt < 0.0) ip = in = 0;
+      s_rank[2 * tid] = ip;
+      s_rank[2 * tid + 1] = in;
+    }
+    // ---- multi-select instead of a full sort: 2048-bin histogram on the leading bits in which the
+    // ---- keys differ, then only the few bins that hold a wanted rank are collected and ranked
+    unsigned long long kmin = ~0ull, kmax = 0ull;
+    for (int i = tid; i < n; i += nt) {
+      const unsigned long long u = bs_key(p.cap[a + i]);
+      kmin = u < kmin ? u : kmin;
+      kmax = u > kmax ? u : kmax;
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, kmin, off), o2 = __shfl_xor_sync(0xffffffffu, kmax, off);
+      kmin = o1 < kmin ? o1 : kmin;
+      kmax = o2 > kmax ? o2 : kmax;
+    }
     __syncthreads();
-    // bitonic sort ascending
-    for (int k = 2; k <= p.npad; k <<= 1) {
-      for (int j = k >> 1; j > 0; j >>= 1) {
-        for (int i = tid; i < p.npad; i += nt) {
-          const int ixj = i ^ j;
-          if (ixj > i) {
-            const double x = s_sort[i], y = s_sort[ixj];
-            const bool up = (i & k) == 0;
-            if ((x > y) == up) { s_sort[i] = y; s_sort[ixj] = x; }
-          }
-        }
-        __syncthreads();
+    if ((tid & 31) == 0) { atomicMin(&s_k[0], kmin); atomicMax(&s_k[1], kmax); }
+    __syncthreads();
+    kmin = s_k[0]; kmax = s_k[1];
+    const unsigned long long diff = kmin ^ kmax;
+    const int hb = diff ? 63 - __clzll((long long)diff) : 0;
+    const int shift = hb + 1 > BS_BIN_BITS ? hb + 1 - BS_BIN_BITS : 0;
+    const unsigned long long base = kmin >> shift;
+    for (int i = tid; i < n; i += nt) atomicAdd(&s_hist[(int)((bs_key(p.cap[a + i]) >> shift) - base)], 1);
+    __syncthreads();
+    // exclusive prefix over the bins (warp 0: 64 bins per lane, then a shuffle scan)
+    if (tid < 32) {
+      constexpr int PER = BS_BINS / 32;
+      int loc = 0;
+      for (int j = 0; j < PER; ++j) loc += s_hist[tid * PER + j];
+      int inc = loc;
+      for (int off = 1; off < 32; off <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, inc, off);
+        if (tid >= off) inc += o;
       }
+      int run = inc - loc;
+      for (int j = 0; j < PER; ++j) {
+        const int h = s_hist[tid * PER + j];
+        s_hist[tid * PER + j] = run;
+        run += h;
+      }
+      if (tid == 31) s_hist[BS_BINS] = run;
+    }
+    __syncthreads();
+    // bins that contain a wanted rank get a slot; their sizes decide whether the short path applies
+    if (tid < 2 * (G + 1) && n > 0) {
+      const int r = s_rank[tid];
+      int lo = 0, hi = BS_BINS;             // largest b with prefix[b] <= r
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_hist[mid] <= r) lo = mid; else hi = mid;
+      }
+      s_rbin[tid] = lo;
+      if (atomicCAS(&s_need[lo], -1, -2) == -1) {
+        const int slot = atomicAdd(&s_ctl[0], 1);
+        s_need[lo] = slot;
+        s_slotbin[slot] = lo;
+      }
+    }
+    __syncthreads();
+    const int nslots = s_ctl[0];
+    if (tid == 0) {
+      int tot = 0;
+      for (int sl = 0; sl < nslots; ++sl) {
+        const int bn = s_slotbin[sl];
+        s_slotoff[sl] = tot;
+        tot += s_hist[bn + 1] - s_hist[bn];
+      }
+      s_slotoff[nslots] = tot;
+      s_ctl[1] = tot;
+    }
+    for (int i = tid; i < 2 * BS_MAX_GROUPS + 2; i += nt) s_fill[i] = 0;
+    __syncthreads();
+    const int ncoll = s_ctl[1];
+    if (ncoll <= BS_COLL_MAX && ncoll <= p.npad) {
+      // collect the members of the needed bins into s_sort (grouped by slot), rank them in place
+      for (int i = tid; i < n; i += nt) {
+        const double c = p.cap[a + i];
+        const int bn = (int)((bs_key(c) >> shift) - base);
+        const int sl = s_need[bn];
+        if (sl >= 0) s_sort[s_slotoff[sl] + atomicAdd(&s_fill[sl], 1)] = c;
+      }
+      __syncthreads();
+      for (int e = tid; e < ncoll; e += nt) {
+        int sl = 0;
+        while (s_slotoff[sl + 1] <= e) ++sl;
+        const int lo = s_slotoff[sl], hi = s_slotoff[sl + 1];
+        const double x = s_sort[e];
+        int rk = 0;
+        for (int i = lo; i < hi; ++i) {
+          const double y = s_sort[i];
+          rk += (y < x) || (y == x && i < e);
+        }
+        const int grank = s_hist[s_slotbin[sl]] + rk;      // position in the fully sorted order
+        for (int q2 = 0; q2 < 2 * (G + 1); ++q2)
+          if (s_rank[q2] == grank) s_rval[q2] = x;
+      }
+      __syncthreads();
+    } else {
+      // degenerate key distribution: full bitonic sort (ascending) of the date's caps
+      for (int i = tid; i < p.npad; i += nt) s_sort[i] = i < n ? p.cap[a + i] : inf;
+      __syncthreads();
+      for (int k = 2; k <= p.npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int i = tid; i < p.npad; i += nt) {
+            const int ixj = i ^ j;
+            if (ixj > i) {
+              const double x = s_sort[i], y = s_sort[ixj];
+              const bool up = (i & k) == 0;
+              if ((x > y) == up) { s_sort[i] = y; s_sort[ixj] = x; }
+            }
+          }
+          __syncthreads();
+        }
+      }
+      if (tid < 2 * (G + 1) && n > 0) s_rval[tid] = s_sort[s_rank[tid]];
+      __syncthreads();
     }
     // quantile edges (numpy 'linear' method, _lerp with the t >= 0.5 branch)
     if (tid <= G && n > 0) {
       const double virt = __dmul_rn((double)(n - 1), p.quant[tid]);
-      double prev = floor(virt);
+      const double prev = floor(virt);
       const double gamma = __dsub_rn(virt, prev);
-      int ip = (int)prev, in = ip + 1;
-      if (virt >= (double)(n - 1)) ip = in = n - 1;
-      if (virt < 0.0) ip = in = 0;
-      const double lo = s_sort[ip], hi = s_sort[in];
-      const double diff = __dsub_rn(hi, lo);
-      double e = __dadd_rn(lo, __dmul_rn(diff, gamma));
-      if (gamma >= 0.5) e = __dsub_rn(hi, __dmul_rn(diff, __dsub_rn(1.0, gamma)));
+      const double lo = s_rval[2 * tid], hi = s_rval[2 * tid + 1];
+      const double diffv = __dsub_rn(hi, lo);
+      double e = __dadd_rn(lo, __dmul_rn(diffv, gamma));
+      if (gamma >= 0.5) e = __dsub_rn(hi, __dmul_rn(diffv, __dsub_rn(1.0, gamma)));
       s_edges[tid] = e;
     }
     __syncthreads();
@@ -94,10 +226,17 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
       int g = cnt - 1;
       if (c == e0) g = 0;
       if (g >= 0 && g < G) {
-        atomicAdd(&s_gsum[4 * g + 0], v * c);
-        atomicAdd(&s_gsum[4 * g + 1], c);
-        atomicAdd(&s_gsum[4 * g + 2], 1.0);
+        atomicAdd(&my[4 * g + 0], v * c);
+        atomicAdd(&my[4 * g + 1], c);
+        atomicAdd(&my[4 * g + 2], 1.0);
       }
+    }
+    __syncthreads();
+    for (int e = tid; e < 4 * G; e += nt) {
+      if ((e & 3) == 3) continue;
+      double acc = 0.0;
+      for (int w = 0; w < nwarps; ++w) acc += s_wsum[(size_t)w * G * 4 + e];
+      s_gsum[e] = acc;
     }
     __syncthreads();
     // pass 2: dispersion about the group mean
@@ -110,8 +249,14 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
       if (g >= 0 && g < G) {
         const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
         const double d = v - m;
-        atomicAdd(&s_gsum[4 * g + 3], d * d);
+        atomicAdd(&my[4 * g + 3], d * d);
       }
+    }
+    __syncthreads();
+    for (int g = tid; g < G; g += nt) {
+      double acc = 0.0;
+      for (int w = 0; w < nwarps; ++w) acc += s_wsum[(size_t)w * G * 4 + 4 * g + 3];
+      s_gsum[4 * g + 3] = acc;
     }
     __syncthreads();
     for (int i = tid; i < n; i += nt) {
@@ -165,14 +310,15 @@ extern "C" int bmfm_bayes_shrink(bmfm_ctx* ctx, int T, int max_rows_per_date, co
     volatile double pct = y * 100.0;
     p.quant[k] = pct / 100.0;
   }
-  const size_t smem = ((size_t)npad + BS_MAX_GROUPS + 1 + 4 * BS_MAX_GROUPS) * 8 + 16;
+  int nthreads = npad >= 2048 ? 1024 : (npad >= 512 ? 256 : 128);
+  const size_t smem = ((size_t)npad + BS_MAX_GROUPS + 1 + 4 * BS_MAX_GROUPS) * 8 + 16 + (size_t)(nthreads / 32) * ngroup * 4 * 8 +
+                      (size_t)(2 * BS_MAX_GROUPS + 2 + 2) * 8 + (size_t)(2 * BS_BINS + 1 + 6 * (2 * BS_MAX_GROUPS + 3) + 8) * 4;
   if (smem > (size_t)ctx->max_smem_optin) {
     snprintf(ctx->err, sizeof(ctx->err), "bayes_shrink: %d rows per date exceed the shared-memory sort (max 16384)",
              max_rows_per_date);
     return BMFM_E_UNSUPPORTED;
   }
   BMFM_CUDA(ctx, cudaFuncSetAttribute(bayes_shrink_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int nthreads = npad >= 2048 ? 1024 : (npad >= 512 ? 256 : 128);
   int per_sm = (int)((228 * 1024) / (smem + 1024));
   if (per_sm < 1) per_sm = 1;
   if (per_sm * nthreads > 2048) per_sm = 2048 / nthreads;

@@ -57,11 +57,22 @@ __global__ void __launch_bounds__(128) ew_window_kernel(int L, int S, int W, int
   const int s0 = max(0, r0 - W);        // warm-up start: the window of row r0-1 is rows [s0, r0)
   double Sw = 0, Sx = 0, Sy = 0, Sxx = 0, Sxy = 0, Syy = 0;
   int n = 0;
+  // the four values of a step (arriving row, leaving row) do not depend on the running sums: they are
+  // fetched one step ahead so that their latency overlaps the arithmetic of the current step
+  const double qn = qnan();
+  double y_nx = ret[(size_t)s0 * S + s], x_nx = mkt[(size_t)s0 * S + s], yl_nx = qn, xl_nx = qn;
   for (int r = s0; r < r1; ++r) {
+    const double y = y_nx, x = x_nx, yl = yl_nx, xl = xl_nx;
+    if (r + 1 < r1) {
+      y_nx = ret[(size_t)(r + 1) * S + s];
+      x_nx = mkt[(size_t)(r + 1) * S + s];
+      const int rn = r + 1 - W;
+      yl_nx = rn >= s0 ? ret[(size_t)rn * S + s] : qn;
+      xl_nx = rn >= s0 ? mkt[(size_t)rn * S + s] : qn;
+    }
     const int rl = r - W;
     if (rl >= s0) {
       // the oldest row of the previous window leaves; among n valid rows it had rank n-1
-      const double yl = ret[(size_t)rl * S + s], xl = mkt[(size_t)rl * S + s];
       if (!isnan(yl) && !isnan(xl)) {
         const double wg = pw[n - 1];
         if (MODE == 0) {
@@ -74,7 +85,6 @@ __global__ void __launch_bounds__(128) ew_window_kernel(int L, int S, int W, int
         n -= 1;
       }
     }
-    const double y = ret[(size_t)r * S + s], x = mkt[(size_t)r * S + s];
     if (!isnan(y) && !isnan(x)) {
       if (MODE == 0) {
         Sw = fma(Sw, lam, 1.0); Sx = fma(Sx, lam, x); Sy = fma(Sy, lam, y);
