@@ -321,7 +321,7 @@ struct EigSplit {
   int* nsw;                // [P]  sweeps recorded, -1 = failed
 };
 
-__global__ void __launch_bounds__(64) eig_split_tred_kernel(EigSplit sp, const double* C, const double* D0,
+__global__ void __launch_bounds__(32) eig_split_tred_kernel(EigSplit sp, const double* C, const double* D0,
                                                             const int* status) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int K = sp.K, ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(64) eig_split_tred_kernel(EigSplit sp, const d
     const int t = sp.t0 + p / sp.nsim, m = p % sp.nsim;
     if (status[t] != BMFM_ST_OK) continue;
     __syncthreads();
-    if (tid < K) sd[tid] = sqrt(D0[(size_t)t * K + tid]);
+    for (int k = tid; k < K; k += nt) sd[k] = sqrt(D0[(size_t)t * K + k]);
     __syncthreads();
     const double* Cm = C + (size_t)m * K * K;
     for (int a = 0; a < K; ++a) {
@@ -346,9 +346,9 @@ __global__ void __launch_bounds__(64) eig_split_tred_kernel(EigSplit sp, const d
     double* Q = sp.Qs + (size_t)p * K * K;
     for (int a = 0; a < K; ++a)
       for (int b = tid; b < K; b += nt) Q[a * K + b] = Z[a * ld + b];
-    if (tid < K) {
-      sp.de[(size_t)tid * sp.P + p] = d[tid];
-      sp.de[(size_t)(K + tid) * sp.P + p] = e[tid];
+    for (int k = tid; k < K; k += nt) {
+      sp.de[(size_t)k * sp.P + p] = d[k];
+      sp.de[(size_t)(K + k) * sp.P + p] = e[k];
     }
   }
 }
@@ -607,7 +607,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
       sp.t0 = t0;
       sp.P = nd * nsim;
       const int gA = sp.P < slots ? sp.P : slots;
-      eig_split_tred_kernel<<<gA, 64, smem, ctx->stream>>>(sp, C, D0, status);
+      eig_split_tred_kernel<<<gA, 32, smem, ctx->stream>>>(sp, C, D0, status);
       eig_split_chain_kernel<<<(sp.P + 63) / 64, 64, (size_t)2 * K * 64 * 8, ctx->stream>>>(sp, status);
       const long long wC = (long long)nd * nblk;
       eig_split_apply_kernel<<<(int)(wC < slots ? wC : slots), 64, smem_apply, ctx->stream>>>(sp, nblk, D0, status, partial);

@@ -16,38 +16,44 @@
 
 namespace bmfm {
 
+// sum over the CTA (one or two warps; with one warp no shared memory or barrier is needed)
 __device__ __forceinline__ double block_sum64(double v, double* red) {
-  // blockDim.x == 64 (two warps)
   v = warp_sum(v);
+  if (blockDim.x <= 32) return v;
   __syncthreads();
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
   __syncthreads();
   return red[0] + red[1];
 }
 
-// Z: n x n (row stride ld, odd) holding the symmetric matrix (both triangles) on entry and the
-// eigenvectors (columns) on exit; d: eigenvalues (unsorted); e, cs (2n), red (4): scratch.
-// Returns 0, or 1 if a QL iteration did not converge in 60 sweeps (caller falls back).
 // stage 1 only: on exit Z = Q (accumulated Householder transform), d = diagonal, e[0..n-2] =
 // sub-diagonal (already shifted for the QL stage), e[n-1] = 0.
+// Works for blockDim.x = 32 or 64 (n <= 64): thread t owns rows t, t + blockDim.x.  One warp per
+// problem is the efficient shape: with two warps the second one carries n - 32 live lanes through
+// every loop, and every step pays CTA barriers instead of warp barriers.
 __device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, int n, int ld) {
-  const int tid = threadIdx.x;
-  // ---- stage 1: Householder reduction (EISPACK tred2, lower triangle), parallel over j ----
+  const int tid = threadIdx.x, nt = blockDim.x;
+  // ---- stage 1: Householder reduction (EISPACK tred2, lower triangle), parallel over rows j ----
   for (int i = n - 1; i >= 1; --i) {
     const int l = i - 1;
     double h = 0.0;
+    const double* zi = Z + i * ld;
     if (l > 0) {
-      const double scale = block_sum64(tid <= l ? fabs(Z[i * ld + tid]) : 0.0, red);
+      double sc = 0.0;
+      for (int k = tid; k <= l; k += nt) sc += fabs(zi[k]);
+      const double scale = block_sum64(sc, red);
       if (scale == 0.0) {
-        if (tid == 0) e[i] = Z[i * ld + l];
+        if (tid == 0) e[i] = zi[l];
       } else {
-        double v = 0.0;
-        if (tid <= l) {
-          v = Z[i * ld + tid] / scale;
-          Z[i * ld + tid] = v;
+        double hs = 0.0;
+        for (int k = tid; k <= l; k += nt) {
+          const double v = zi[k] / scale;
+          Z[i * ld + k] = v;
+          hs = fma(v, v, hs);
         }
-        h = block_sum64(v * v, red);
-        const double f0 = Z[i * ld + l];
+        h = block_sum64(hs, red);      // (its barriers also publish the scaled row)
+        if (nt <= 32) __syncwarp();
+        const double f0 = zi[l];
         const double g0 = f0 >= 0.0 ? -sqrt(h) : sqrt(h);
         h -= f0 * g0;
         __syncthreads();
@@ -56,87 +62,63 @@ __device__ inline void tred2_cta(double* Z, double* d, double* e, double* red, i
           Z[i * ld + l] = f0 - g0;
         }
         __syncthreads();
-        // p = A u / h  (thread j: row j up to the diagonal, column j below it)
-        double fj = 0.0, ej = 0.0;
-        if (tid <= l) {
-          const int j = tid;
-          const double uj = Z[i * ld + j];
+        // p = A u / h  (row j up to the diagonal, column j below it)
+        double fsum = 0.0;
+        double ejv[2] = {0.0, 0.0};
+        int jj = 0;
+        for (int j = tid; j <= l; j += nt, ++jj) {
+          const double uj = zi[j];
           Z[j * ld + i] = uj / h;
-          // four independent partial sums: the loop is otherwise one LDS -> FMA dependency chain
-          double g0 = 0.0, g1 = 0.0, g2 = 0.0, g3 = 0.0;
+          double g0a = 0.0, g1a = 0.0;
           const double* zj = Z + j * ld;
-          const double* zi = Z + i * ld;
           int k = 0;
-          for (; k + 3 <= j; k += 4) {
-            g0 = fma(zj[k], zi[k], g0); g1 = fma(zj[k + 1], zi[k + 1], g1);
-            g2 = fma(zj[k + 2], zi[k + 2], g2); g3 = fma(zj[k + 3], zi[k + 3], g3);
-          }
-          for (; k <= j; ++k) g0 = fma(zj[k], zi[k], g0);
+          for (; k + 1 <= j; k += 2) { g0a = fma(zj[k], zi[k], g0a); g1a = fma(zj[k + 1], zi[k + 1], g1a); }
+          for (; k <= j; ++k) g0a = fma(zj[k], zi[k], g0a);
           k = j + 1;
-          for (; k + 3 <= l; k += 4) {
-            g0 = fma(Z[k * ld + j], zi[k], g0); g1 = fma(Z[(k + 1) * ld + j], zi[k + 1], g1);
-            g2 = fma(Z[(k + 2) * ld + j], zi[k + 2], g2); g3 = fma(Z[(k + 3) * ld + j], zi[k + 3], g3);
-          }
-          for (; k <= l; ++k) g0 = fma(Z[k * ld + j], zi[k], g0);
-          const double g = (g0 + g1) + (g2 + g3);
-          ej = g / h;
-          fj = ej * uj;
+          for (; k + 1 <= l; k += 2) { g0a = fma(Z[k * ld + j], zi[k], g0a); g1a = fma(Z[(k + 1) * ld + j], zi[k + 1], g1a); }
+          for (; k <= l; ++k) g0a = fma(Z[k * ld + j], zi[k], g0a);
+          const double ej = (g0a + g1a) / h;
+          ejv[jj] = ej;
+          fsum = fma(ej, uj, fsum);
         }
-        const double f = block_sum64(fj, red);
+        const double f = block_sum64(fsum, red);
         const double hh = f / (h + h);
-        if (tid <= l) e[tid] = ej - hh * Z[i * ld + tid];
+        jj = 0;
+        for (int j = tid; j <= l; j += nt, ++jj) e[j] = ejv[jj] - hh * zi[j];
         __syncthreads();
         // rank-2 update of the leading lower triangle
-        if (tid <= l) {
-          const int j = tid;
-          const double fu = Z[i * ld + j], gq = e[j];
+        for (int j = tid; j <= l; j += nt) {
+          const double fu = zi[j], gq = e[j];
           double* zj = Z + j * ld;
-          const double* zi = Z + i * ld;
-          int k = 0;
-          for (; k + 3 <= j; k += 4) {
-            const double a0 = zj[k], a1 = zj[k + 1], a2 = zj[k + 2], a3 = zj[k + 3];
-            const double b0 = fma(fu, e[k], gq * zi[k]), b1 = fma(fu, e[k + 1], gq * zi[k + 1]);
-            const double b2 = fma(fu, e[k + 2], gq * zi[k + 2]), b3 = fma(fu, e[k + 3], gq * zi[k + 3]);
-            zj[k] = a0 - b0; zj[k + 1] = a1 - b1; zj[k + 2] = a2 - b2; zj[k + 3] = a3 - b3;
-          }
-          for (; k <= j; ++k) zj[k] -= fu * e[k] + gq * zi[k];
+          for (int k = 0; k <= j; ++k) zj[k] -= fma(fu, e[k], gq * zi[k]);
         }
         __syncthreads();
       }
     } else {
-      if (tid == 0) e[i] = Z[i * ld + l];
+      if (tid == 0) e[i] = zi[l];
     }
     if (tid == 0) d[i] = h;
     __syncthreads();
   }
   if (tid == 0) { d[0] = 0.0; e[0] = 0.0; }
   __syncthreads();
-  // accumulate the transformation: Z <- Q
+  // accumulate the transformation: Z <- Q (thread = column j)
   for (int i = 0; i < n; ++i) {
     const int l = i - 1;
-    if (d[i] != 0.0 && tid <= l) {
-      const int j = tid;
-      double g0 = 0.0, g1 = 0.0, g2 = 0.0, g3 = 0.0;
+    if (d[i] != 0.0) {
       const double* zi = Z + i * ld;
-      int k = 0;
-      for (; k + 3 <= l; k += 4) {
-        g0 = fma(zi[k], Z[k * ld + j], g0); g1 = fma(zi[k + 1], Z[(k + 1) * ld + j], g1);
-        g2 = fma(zi[k + 2], Z[(k + 2) * ld + j], g2); g3 = fma(zi[k + 3], Z[(k + 3) * ld + j], g3);
+      for (int j = tid; j <= l; j += nt) {
+        double g0a = 0.0, g1a = 0.0;
+        int k = 0;
+        for (; k + 1 <= l; k += 2) { g0a = fma(zi[k], Z[k * ld + j], g0a); g1a = fma(zi[k + 1], Z[(k + 1) * ld + j], g1a); }
+        for (; k <= l; ++k) g0a = fma(zi[k], Z[k * ld + j], g0a);
+        const double g = g0a + g1a;
+        for (k = 0; k <= l; ++k) Z[k * ld + j] = fma(-g, Z[k * ld + i], Z[k * ld + j]);
       }
-      for (; k <= l; ++k) g0 = fma(zi[k], Z[k * ld + j], g0);
-      const double g = (g0 + g1) + (g2 + g3);
-      k = 0;
-      for (; k + 3 <= l; k += 4) {
-        const double a0 = Z[k * ld + j], a1 = Z[(k + 1) * ld + j], a2 = Z[(k + 2) * ld + j], a3 = Z[(k + 3) * ld + j];
-        const double u0 = Z[k * ld + i], u1 = Z[(k + 1) * ld + i], u2 = Z[(k + 2) * ld + i], u3 = Z[(k + 3) * ld + i];
-        Z[k * ld + j] = fma(-g, u0, a0); Z[(k + 1) * ld + j] = fma(-g, u1, a1);
-        Z[(k + 2) * ld + j] = fma(-g, u2, a2); Z[(k + 3) * ld + j] = fma(-g, u3, a3);
-      }
-      for (; k <= l; ++k) Z[k * ld + j] -= g * Z[k * ld + i];
     }
     __syncthreads();
     if (tid == 0) { d[i] = Z[i * ld + i]; Z[i * ld + i] = 1.0; }
-    if (tid <= l) { Z[tid * ld + i] = 0.0; Z[i * ld + tid] = 0.0; }
+    for (int j = tid; j <= l; j += nt) { Z[j * ld + i] = 0.0; Z[i * ld + j] = 0.0; }
     __syncthreads();
   }
   if (tid == 0) {
@@ -212,16 +194,18 @@ __device__ inline int tridiag_ql_cta(double* Z, double* d, double* e, double* cs
       }
       __syncthreads();
       const int m = ictl[0], ilo = ictl[1], fail = ictl[2];
-      if (dbg != 2 && m != l && tid < n && ilo < m) {
-        double* zr = Z + tid * ld;
-        double z1 = zr[m];
-        for (int i = m - 1; i >= ilo; --i) {
-          const double c = cs[2 * i], s = cs[2 * i + 1];
-          const double zi = zr[i];
-          zr[i + 1] = fma(s, zi, c * z1);
-          z1 = fma(c, zi, -s * z1);
+      if (dbg != 2 && m != l && ilo < m) {
+        for (int row = tid; row < n; row += blockDim.x) {
+          double* zr = Z + row * ld;
+          double z1 = zr[m];
+          for (int i = m - 1; i >= ilo; --i) {
+            const double c = cs[2 * i], s = cs[2 * i + 1];
+            const double zi = zr[i];
+            zr[i + 1] = fma(s, zi, c * z1);
+            z1 = fma(c, zi, -s * z1);
+          }
+          zr[ilo] = z1;
         }
-        zr[ilo] = z1;
       }
       __syncthreads();
       if (m == l || fail) break;
