@@ -66,8 +66,10 @@ def load_traffic():
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region (NVML, every ~50 ms — faster polling was seen to slow the GPU being polled; the
-    nvidia-smi loop of B200_PROFILING.md is too coarse for a region of tens of milliseconds)."""
+    """SM clock and throttle reasons sampled DURING the timed region through NVML.  Each NVML query was
+    seen to stall the polled GPU for milliseconds, so the region is sampled sparsely: one query right after
+    the timed launches are enqueued (the GPU is then in the middle of them) and one every 250 ms after that
+    (the recipe's nvidia-smi loop uses 200 ms)."""
 
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
@@ -78,41 +80,42 @@ class ClockSampler:
         self._stop = threading.Event()
         self.thread = None
         self.err = None
-
-    def _loop(self):
+        self.h = None
         try:
             import pynvml
+            self.nv = pynvml
             pynvml.nvmlInit()
-            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES; map through the UUID when it is set
             vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            idx = self.gpu
-            if vis:
-                ent = vis.split(",")[self.gpu].strip()
-                if ent.isdigit():
-                    idx = int(ent)
-                    h = pynvml.nvmlDeviceGetHandleByIndex(idx)
-                else:
-                    h = pynvml.nvmlDeviceGetHandleByUUID(ent.encode() if hasattr(ent, "encode") else ent)
-            else:
-                h = pynvml.nvmlDeviceGetHandleByIndex(idx)
-            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
-            while not self._stop.is_set():
-                self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
-                try:
-                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
-                except Exception:
-                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in self.REASONS.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                time.sleep(0.05)
+            ent = vis.split(",")[gpu_index].strip() if vis else str(gpu_index)
+            self.h = (pynvml.nvmlDeviceGetHandleByIndex(int(ent)) if ent.isdigit()
+                      else pynvml.nvmlDeviceGetHandleByUUID(ent.encode()))
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         except Exception as e:      # noqa: BLE001
             self.err = repr(e)
+
+    def sample(self):
+        if self.h is None:
+            return
+        try:
+            nv = self.nv
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+            try:
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for bit, name in self.REASONS.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception as e:      # noqa: BLE001
+            self.err = repr(e)
+
+    def _loop(self):
+        while not self._stop.wait(0.25):
+            self.sample()
 
     def start(self):
         self.thread = threading.Thread(target=self._loop, daemon=True)
         self.thread.start()
-        time.sleep(0.02)
 
     def stop(self):
         self._stop.set()
@@ -263,7 +266,25 @@ def run_gpu(args):
             "style": torch.from_numpy(style).pin_memory()}
     d = {k: v.to(dev) for k, v in host.items()}
     fr = torch.empty((T, K), dtype=torch.float64, device=dev)
-    fr_all = torch.empty((T_all, K), dtype=torch.float64, device=dev) if world > 1 else fr
+    # multi-GPU: the gathered factor returns and vol-regime terms live in symmetric (peer-mapped) memory and
+    # are filled by the producing kernels themselves over NVLink (fused all-gather); NCCL is the fallback
+    fused = world > 1 and os.environ.get("BENCH_FUSED", "1") == "1"
+    h_fr = h_wbv = None
+    if fused:
+        try:
+            import torch.distributed._symmetric_memory as symm
+            fr_all = symm.empty((T_all, K), dtype=torch.float64, device=dev)
+            h_fr = symm.rendezvous(fr_all, group=dist.group.WORLD)
+            wbv_sym = symm.empty((2, T_all), dtype=torch.float64, device=dev)
+            h_wbv = symm.rendezvous(wbv_sym, group=dist.group.WORLD)
+            fr_peers = [int(x) for x in h_fr.buffer_ptrs]
+            wb_peers = [int(x) for x in h_wbv.buffer_ptrs]
+            wv_peers = [int(x) + T_all * 8 for x in h_wbv.buffer_ptrs]
+        except Exception as e:      # noqa: BLE001
+            log(f"symmetric memory unavailable ({e!r}); using NCCL all-gathers")
+            fused = False
+    if not fused:
+        fr_all = torch.empty((T_all, K), dtype=torch.float64, device=dev) if world > 1 else fr
     spec = torch.empty(rows, dtype=torch.float64, device=dev)
     r2 = torch.empty(T, dtype=torch.float64, device=dev)
     st = torch.empty(T, dtype=torch.int32, device=dev)
@@ -275,8 +296,11 @@ def run_gpu(args):
     # vol-regime terms of this rank's dates, packed [wb | wv] so that one all-gather moves both
     wbv = torch.empty((2, T), dtype=torch.float64, device=dev)
     wbv_all = torch.empty((world, 2, T), dtype=torch.float64, device=dev)
-    wb_all = torch.empty(T_all, dtype=torch.float64, device=dev)
-    wv_all = torch.empty(T_all, dtype=torch.float64, device=dev)
+    if fused:
+        wb_all, wv_all = wbv_sym[0], wbv_sym[1]
+    else:
+        wb_all = torch.empty(T_all, dtype=torch.float64, device=dev)
+        wv_all = torch.empty(T_all, dtype=torch.float64, device=dev)
     out_host = {"fr": torch.empty((T, K), dtype=torch.float64).pin_memory(),
                 "spec": torch.empty(rows, dtype=torch.float64).pin_memory(),
                 "r2": torch.empty(T, dtype=torch.float64).pin_memory(),
@@ -289,26 +313,41 @@ def run_gpu(args):
     def step(i):
         e = ev[i]
         e[0].record()
-        ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
+        regress()
         e[1].record()
-        if world > 1:
-            dist.all_gather_into_tensor(fr_all, fr)
+        gather_fr()
         # the recurrence reads the whole gathered series (T_all*K doubles) and emits this rank's dates only
         ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
         e[2].record()
         vol_regime()
         e[3].record()
 
-    def step_body():      # the same step without timing events (graph capture)
-        ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
-        if world > 1 and not nocoll:
+    def regress():
+        if fused:
+            ctx.reg_by_time_gather(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2,
+                                   st, fr_peers, lo)
+        else:
+            ctx.reg_by_time(T, P, Q, N_STOCKS, d["off"], d["cap"], d["ret"], d["ind"], d["style"], fr, spec, r2, st)
+
+    def gather_fr():
+        if fused:
+            h_fr.barrier()            # the factor returns were stored into every rank's buffer by the kernel
+        elif world > 1 and not nocoll:
             dist.all_gather_into_tensor(fr_all, fr)
+
+    def step_body():      # the same step without timing events (graph capture)
+        regress()
+        gather_fr()
         ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
         vol_regime()
 
     def vol_regime():
         if world == 1:
             ctx.vol_regime_adj_by_time(T, K, VR_TAO, fr, nw, nw_st, vr, lamb)
+        elif fused:
+            ctx.vol_regime_bias_gather(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wb_peers, wv_peers)
+            h_wbv.barrier()
+            ctx.vol_regime_scale(T_all, lo, T, K, wb_all, wv_all, nw, nw_st, vr, lamb)
         else:
             ctx.vol_regime_bias(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wbv[0], wbv[1])
             if not nocoll:
@@ -328,7 +367,11 @@ def run_gpu(args):
     launches_per_step = (ctx.launches - l0) // max(1, args.warmup)
     barrier()
     graph = None
+    n_phase = min(3, args.steps)
     if use_graph:
+        for i in range(args.warmup, args.warmup + n_phase):    # eager steps that only feed phase_ms / the roofline
+            step(i)
+        barrier()
         # one step (kernels + NCCL collectives) captured once and replayed: removes the host-side launch and
         # collective-enqueue gaps that dominate a sub-millisecond multi-GPU step
         try:
@@ -355,6 +398,8 @@ def run_gpu(args):
         for i in range(args.warmup, args.warmup + args.steps):
             step(i)
     t_end.record()
+    if rank == 0 and sampler.thread is not None:
+        sampler.sample()          # the launches above are asynchronous: the GPU is inside the timed region now
     barrier()
     clocks = sampler.stop() if (rank == 0 and sampler.thread is not None) else None
     launches = ctx.launches - launches0
@@ -368,7 +413,7 @@ def run_gpu(args):
     ms_step = ms_total / args.steps
     value = T_all / (ms_step * 1e-3)
     # per-phase times: from the timed steps (eager) or, in graph mode, from the eager warm-up steps
-    timed = ev[args.warmup:] if graph is None else ev[max(0, args.warmup - 3):args.warmup]
+    timed = ev[args.warmup:] if graph is None else ev[args.warmup:args.warmup + n_phase]
     ms_reg = float(np.mean([e[0].elapsed_time(e[1]) for e in timed]))
     ms_nw = float(np.mean([e[1].elapsed_time(e[2]) for e in timed]))
     ms_vr = float(np.mean([e[2].elapsed_time(e[3]) for e in timed]))
@@ -381,6 +426,23 @@ def run_gpu(args):
         ok_t = torch.tensor([1 if status_ok else 0], device=dev)
         dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
         status_ok = bool(ok_t.item())
+
+    # multi-GPU: the fused (peer-memory) gather must give what the NCCL all-gather gives
+    gather_check = None
+    if fused:
+        lamb_fused = lamb.clone()
+        fr_all_fused = fr_all.clone()
+        ref_all = torch.empty((T_all, K), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(ref_all, fr)
+        w2 = torch.stack([wb_all[lo:lo + T], wv_all[lo:lo + T]]).contiguous()
+        w2_all = torch.empty((world, 2, T), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(w2_all, w2)
+        ok = bool(torch.equal(ref_all, fr_all_fused)) and bool(torch.equal(w2_all[:, 0].reshape(-1), wb_all)) \
+            and bool(torch.equal(w2_all[:, 1].reshape(-1), wv_all))
+        ok_t = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+        gather_check = "peer-memory gather == NCCL all-gather (bit-identical on every rank)" if ok_t.item() else "MISMATCH"
+        del lamb_fused
 
     # ---- end to end: pinned host buffers -> device -> results back in pinned host buffers ----
     h2d = sum(v.numel() * v.element_size() for v in host.values())
@@ -465,11 +527,13 @@ def run_gpu(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES} per GPU, P={P}, Q={Q}: reg_by_time + "
                                    f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})",
-                       "parallelism": f"dates sharded over {world} GPU(s); all-gather of factor returns and vol-regime terms" if world > 1 else "1 GPU",
-                       "timed_as": "CUDA graph replays of one captured step (phase_ms from the eager warm-up steps)" if graph is not None else "eager launches",
+                       "parallelism": (f"dates sharded over {world} GPU(s); factor returns and vol-regime terms gathered "
+                                       + ("by the producing kernels over peer memory (symmetric memory + device barrier)" if fused
+                                          else "with NCCL all-gather")) if world > 1 else "1 GPU",
+                       "timed_as": "CUDA graph replays of one captured step (phase_ms from 3 extra eager steps after the warm-up)" if graph is not None else "eager launches",
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
-                       "all_status_ok": status_ok},
+                       "all_status_ok": status_ok, "gather_check": gather_check},
             "roofline": {"kernel": "reg_stream_kernel<10> (per-date Gram + constrained solve + residuals, one warp per date)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": load_traffic(), "traffic_source": "ncu --set full capture of one launch, profiles/roofline_traffic.json",

@@ -91,6 +91,17 @@ int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
                      double* factor_ret, double* specific_ret, double* r2,
                      double* exposure, int32_t* status);
 
+/* Same regression with the all-gather of the factor returns fused into the kernel (multi-GPU, dates
+ * sharded): every date's K factor returns are also stored into each rank's gathered series over peer
+ * memory — peer_bufs is a HOST array of n_peer (<= 8) device pointers to [T_total * K] buffers mapped
+ * for peer access (e.g. torch symmetric memory), written at row peer_row0 + t.  Replaces the
+ * all-gather after MFM.reg_by_time in a sharded run; the caller issues one cross-rank barrier. */
+int bmfm_reg_by_time_gather(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                            const int64_t* date_off, const double* cap, const double* ret,
+                            const int32_t* ind, const double* style,
+                            double* factor_ret, double* specific_ret, double* r2, int32_t* status,
+                            int n_peer, double* const* peer_bufs, int64_t peer_row0);
+
 /* Same, HOST pointers; copies inputs to the device, runs, copies results back. */
 int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
                           const int64_t* date_off, const double* cap, const double* ret,
@@ -146,6 +157,12 @@ int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double tao, const d
 int bmfm_vol_regime_bias(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
                          const double* factor_ret_block, const double* cov_block,
                          const int32_t* cov_status_block, double* wb, double* wv);
+/* _bias with the gather fused in: terms are stored into every rank's wb_all / wv_all [T_total] (HOST
+ * arrays of n_peer peer-mapped device pointers) at offset t0. */
+int bmfm_vol_regime_bias_gather(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                                const double* factor_ret_block, const double* cov_block,
+                                const int32_t* cov_status_block, int n_peer, double* const* peer_wb,
+                                double* const* peer_wv);
 int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, int K, const double* wb_all,
                           const double* wv_all, const double* cov_block,
                           const int32_t* cov_status_block, double* out_cov_block, double* lamb_all);

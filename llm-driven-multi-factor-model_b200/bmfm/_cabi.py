@@ -32,6 +32,8 @@ _SIGNATURES = {
     "bmfm_limits": ([C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)], None),
     "bmfm_version": ([], C.c_char_p),
     "bmfm_reg_by_time": ([_P, _I, _I, _I, _I] + [_P] * 10, _I),
+    "bmfm_reg_by_time_gather": ([_P, _I, _I, _I, _I] + [_P] * 9 + [_I, _P, C.c_int64], _I),
+    "bmfm_vol_regime_bias_gather": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _I, _P, _P], _I),
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
@@ -145,6 +147,21 @@ class Context:
         self.check(self._L.bmfm_reg_by_time(self._h, T, P, Q, max_rows, ptr(date_off), ptr(cap), ptr(ret),
                                             ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
                                             ptr(exposure), ptr(status)))
+
+    def reg_by_time_gather(self, T, P, Q, max_rows, date_off, cap, ret, ind, style, factor_ret, spec, r2, status,
+                           peer_ptrs, row0):
+        """Regression + fused all-gather: `peer_ptrs` = device addresses (ints) of every rank's gathered
+        [T_total, K] buffer (peer-mapped, e.g. symmetric memory), written at row row0 + t."""
+        arr = (C.c_void_p * len(peer_ptrs))(*[int(x) for x in peer_ptrs])
+        self.check(self._L.bmfm_reg_by_time_gather(self._h, T, P, Q, max_rows, ptr(date_off), ptr(cap), ptr(ret),
+                                                   ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
+                                                   ptr(status), len(peer_ptrs), arr, int(row0)))
+
+    def vol_regime_bias_gather(self, T_total, t0, n, K, tao, fr_block, cov_block, status_block, peer_wb, peer_wv):
+        a = (C.c_void_p * len(peer_wb))(*[int(x) for x in peer_wb])
+        b = (C.c_void_p * len(peer_wv))(*[int(x) for x in peer_wv])
+        self.check(self._L.bmfm_vol_regime_bias_gather(self._h, T_total, t0, n, K, float(tao), ptr(fr_block),
+                                                       ptr(cov_block), ptr(status_block), len(peer_wb), a, b))
 
     def reg_by_time_host(self, T, P, Q, date_off, cap, ret, ind, style,
                          factor_ret, spec, r2, status, exposure=None):

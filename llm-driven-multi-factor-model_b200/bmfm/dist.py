@@ -53,6 +53,26 @@ def all_reduce_sum(x, group=None):
     return x
 
 
+class SymmetricGather:
+    """Gathered series in symmetric (peer-mapped) memory: the producing kernels store each rank's block
+    straight into every rank's copy over NVLink (bmfm_reg_by_time_gather, bmfm_vol_regime_bias_gather) and
+    a device-side barrier replaces the all-gather.  Needs torch symmetric memory on an NVLink/NVSwitch box;
+    RiskPipeline falls back to NCCL all-gathers when it is not given one of these."""
+
+    def __init__(self, T_total, K, device, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        g = group or dist.group.WORLD
+        self.fr_all = symm.empty((T_total, K), dtype=torch.float64, device=device)
+        self.h_fr = symm.rendezvous(self.fr_all, group=g)
+        self.wbv = symm.empty((2, T_total), dtype=torch.float64, device=device)
+        self.h_wbv = symm.rendezvous(self.wbv, group=g)
+        self.fr_peers = [int(x) for x in self.h_fr.buffer_ptrs]
+        self.wb_peers = [int(x) for x in self.h_wbv.buffer_ptrs]
+        self.wv_peers = [int(x) + T_total * 8 for x in self.h_wbv.buffer_ptrs]
+
+
 class GpuBackend:
     """The arithmetic of the pipeline on this process's GPU (C-ABI kernels)."""
 
@@ -103,13 +123,16 @@ class RiskPipeline:
         self.rank, self.world, self.group = rank, world, group
 
     def run(self, counts, P, Q, max_rows, off, cap, ret, ind, style, q=2, tao_nw=252, tao_vr=84,
-            eigen=None):
+            eigen=None, symmetric=None):
         """`counts[r]` = number of dates owned by rank r (date order = rank order); the panel arrays are
         this rank's block.  `eigen` = None (vol-regime directly on the Newey-West covariances, BASELINE
         config 2) or dict(T_sim=, M=, scale_coef=).  Returns a dict of this rank's blocks + lamb_all."""
         T_total = int(sum(counts))
         t0 = int(sum(counts[: self.rank]))
         n = int(counts[self.rank])
+        if symmetric is not None:
+            return self._run_fused(symmetric, T_total, t0, n, P, Q, max_rows, off, cap, ret, ind, style, q, tao_nw,
+                                   tao_vr, eigen)
         fr, spec, r2, status = self.b.reg(n, P, Q, max_rows, off, cap, ret, ind, style)
         fr_all = all_gather_rows(fr, counts, self.group)
         nw, nw_st = self.b.newey_west_range(fr_all, t0, t0 + n, q, tao_nw)
@@ -121,6 +144,30 @@ class RiskPipeline:
         wv_all = all_gather_rows(wv, counts, self.group)
         vr, lamb_all = self.b.vr_scale(T_total, t0, wb_all, wv_all, cov, cov_st)
         return {"factor_ret": fr, "factor_ret_all": fr_all, "specific_ret": spec, "R2": r2, "status": status,
+                "nw": nw, "nw_status": nw_st, "cov": cov, "cov_status": cov_st, "vr": vr,
+                "lamb_all": lamb_all, "t0": t0, "n": n}
+
+
+    def _run_fused(self, sg, T_total, t0, n, P, Q, max_rows, off, cap, ret, ind, style, q, tao_nw, tao_vr, eigen):
+        """Same pipeline with both gathers done by the kernels over peer memory (GpuBackend only)."""
+        import torch
+        ctx = self.b.ctx
+        K = 1 + P + Q
+        dev = cap.device
+        fr = torch.empty((n, K), dtype=torch.float64, device=dev)
+        spec = torch.empty(cap.shape[0], dtype=torch.float64, device=dev)
+        r2 = torch.empty(n, dtype=torch.float64, device=dev)
+        status = torch.empty(n, dtype=torch.int32, device=dev)
+        ctx.reg_by_time_gather(n, P, Q, max_rows, off, cap, ret, ind, style, fr, spec, r2, status, sg.fr_peers, t0)
+        sg.h_fr.barrier()
+        nw, nw_st = self.b.newey_west_range(sg.fr_all, t0, t0 + n, q, tao_nw)
+        cov, cov_st = nw, nw_st
+        if eigen is not None:
+            cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])
+        ctx.vol_regime_bias_gather(T_total, t0, n, K, tao_vr, fr, cov, cov_st, sg.wb_peers, sg.wv_peers)
+        sg.h_wbv.barrier()
+        vr, lamb_all = self.b.vr_scale(T_total, t0, sg.wbv[0], sg.wbv[1], cov, cov_st)
+        return {"factor_ret": fr, "factor_ret_all": sg.fr_all, "specific_ret": spec, "R2": r2, "status": status,
                 "nw": nw, "nw_status": nw_st, "cov": cov, "cov_status": cov_st, "vr": vr,
                 "lamb_all": lamb_all, "t0": t0, "n": n}
 

@@ -33,6 +33,7 @@ namespace bmfm {
 constexpr int REG_MAX_Q = 12;       // register-accumulator template range
 constexpr int REG_MAX_P = 63;       // P + 1 buckets <= 64
 constexpr int REG_NEED_DENSE = 100; // internal status: redo this date in the dense kernel
+constexpr int REG_MAX_PEERS = 8;    // GPUs of one NVSwitch box
 
 struct RegParams {
   int T, P, Q, K;
@@ -48,7 +49,17 @@ struct RegParams {
   int* status;
   int tile_rows;
   int all_dense;  // dense kernel: process every date (exposure requested)
+  // fused all-gather: every date's factor returns are also stored straight into each rank's gathered
+  // series (peer memory over NVLink), at row peer_row0 + t; n_peer = 0 disables it
+  int n_peer;
+  long long peer_row0;
+  double* peer_fr[REG_MAX_PEERS];
 };
+
+__device__ __forceinline__ void store_factor_ret(const RegParams& p, int t, int k, double v) {
+  p.factor_ret[(size_t)t * p.K + k] = v;
+  for (int r = 0; r < p.n_peer; ++r) p.peer_fr[r][(size_t)(p.peer_row0 + t) * p.K + k] = v;
+}
 
 __host__ __device__ constexpr int round_up32(int x) { return (x + 31) / 32 * 32; }
 __host__ __device__ constexpr int na1_of(int Q) { return Q * (Q + 1) / 2 + Q; }
@@ -836,7 +847,7 @@ __device__ int solve_dense_cta(const RegParams& p, const RegSmem& L, unsigned ch
 // ---- kernels ---------------------------------------------------------------------------------
 __device__ __forceinline__ void write_nan_outputs(const RegParams& p, long long a, int n, int t) {
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = nan;
+  for (int k = threadIdx.x; k < p.K; k += blockDim.x) store_factor_ret(p, t, k, nan);
   for (int i = threadIdx.x; i < n; i += blockDim.x) p.spec[a + i] = nan;
   if (threadIdx.x == 0) p.r2[t] = nan;
 }
@@ -858,7 +869,7 @@ __global__ void __launch_bounds__(256) reg_fast_kernel(RegParams p) {
     accumulate_date<Q>(p, L, smem, a, n, ntiles);
     const int st = solve_fast_cta<Q, false>(p, L, smem, n);
     if (st == BMFM_ST_OK) {
-      for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = s_f[k];
+      for (int k = threadIdx.x; k < p.K; k += blockDim.x) store_factor_ret(p, t, k, s_f[k]);
       residual_date<Q>(p, L, smem, a, n, ntiles, t);
       if (threadIdx.x == 0) p.status[t] = BMFM_ST_OK;
     } else if (st == REG_NEED_DENSE) {
@@ -891,7 +902,7 @@ __global__ void __launch_bounds__(256) reg_dense_kernel(RegParams p) {
     if (st == BMFM_ST_NONFINITE) {
       write_nan_outputs(p, a, n, t);
     } else {
-      for (int k = threadIdx.x; k < p.K; k += blockDim.x) p.factor_ret[(size_t)t * p.K + k] = s_f[k];
+      for (int k = threadIdx.x; k < p.K; k += blockDim.x) store_factor_ret(p, t, k, s_f[k]);
       residual_date<Q>(p, L, smem, a, n, ntiles, t);
     }
     if (threadIdx.x == 0) p.status[t] = st;
@@ -988,7 +999,7 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
     const int n = (int)(p.date_off[t + 1] - a);
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     if (n <= 0) {
-      for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = nan;
+      for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
       if (lane == 0) { p.r2[t] = nan; p.status[t] = BMFM_ST_NONFINITE; }
       continue;
     }
@@ -1124,13 +1135,13 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
       if (st == REG_NEED_DENSE) {
         if (lane == 0) p.status[t] = REG_NEED_DENSE;
       } else {
-        for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = nan;
+        for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
         for (int i = lane; i < n; i += 32) p.spec[a + i] = nan;
         if (lane == 0) { p.r2[t] = nan; p.status[t] = st; }
       }
       continue;
     }
-    for (int k = lane; k < K; k += 32) p.factor_ret[(size_t)t * K + k] = s_f[k];
+    for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, s_f[k]);
     // pass C
     const double c0 = s_misc[1];
     double se = 0.0, see = 0.0;
@@ -1249,15 +1260,17 @@ extern "C" void bmfm_limits(int* max_Q, int* max_P, int* max_K) {
   if (max_K) *max_K = 1 + REG_MAX_P + REG_MAX_Q;
 }
 
-extern "C" int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
-                                const int64_t* date_off, const double* cap, const double* ret,
-                                const int32_t* ind, const double* style,
-                                double* factor_ret, double* specific_ret, double* r2,
-                                double* exposure, int32_t* status) {
+static int reg_by_time_impl(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                            const int64_t* date_off, const double* cap, const double* ret,
+                            const int32_t* ind, const double* style,
+                            double* factor_ret, double* specific_ret, double* r2,
+                            double* exposure, int32_t* status, int n_peer, double* const* peer_bufs,
+                            int64_t peer_row0) {
   if (!ctx) return BMFM_E_ARG;
   BMFM_ARG(ctx, T >= 0 && P >= 0 && Q >= 0, "T, P, Q must be non-negative");
   BMFM_ARG(ctx, date_off && cap && ret && ind && (style || Q == 0), "NULL input");
   BMFM_ARG(ctx, factor_ret && specific_ret && r2 && status, "NULL output");
+  BMFM_ARG(ctx, n_peer >= 0 && n_peer <= REG_MAX_PEERS && (n_peer == 0 || peer_bufs) && peer_row0 >= 0, "bad peer list");
   if (Q > REG_MAX_Q || P > REG_MAX_P) {
     snprintf(ctx->err, sizeof(ctx->err), "P=%d Q=%d outside compiled limits (P<=%d, Q<=%d)", P, Q, REG_MAX_P, REG_MAX_Q);
     return BMFM_E_UNSUPPORTED;
@@ -1271,10 +1284,35 @@ extern "C" int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows
   p.factor_ret = factor_ret; p.spec = specific_ret; p.r2 = r2; p.exposure = exposure; p.status = status;
   p.tile_rows = 0;
   p.all_dense = exposure != nullptr;
+  p.n_peer = n_peer;
+  p.peer_row0 = peer_row0;
+  for (int r = 0; r < REG_MAX_PEERS; ++r) p.peer_fr[r] = r < n_peer ? peer_bufs[r] : nullptr;
   switch (Q) {
 #define CASE(q) case q: return launch_reg<q>(ctx, p, max_rows_per_date);
     CASE(0) CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8) CASE(9) CASE(10) CASE(11) CASE(12)
 #undef CASE
   }
   return BMFM_E_UNSUPPORTED;
+}
+
+extern "C" int bmfm_reg_by_time(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                                const int64_t* date_off, const double* cap, const double* ret,
+                                const int32_t* ind, const double* style,
+                                double* factor_ret, double* specific_ret, double* r2,
+                                double* exposure, int32_t* status) {
+  return reg_by_time_impl(ctx, T, P, Q, max_rows_per_date, date_off, cap, ret, ind, style, factor_ret, specific_ret,
+                          r2, exposure, status, 0, nullptr, 0);
+}
+
+// The same regression with the all-gather of the factor returns fused in: each date's K factor returns
+// are stored by the regression kernel itself into the gathered series of every rank (`peer_bufs`: HOST
+// array of n_peer device pointers to [T_total * K] buffers mapped for peer access, e.g. symmetric
+// memory), at row peer_row0 + t.  The caller only needs a cross-rank barrier afterwards.
+extern "C" int bmfm_reg_by_time_gather(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per_date,
+                                       const int64_t* date_off, const double* cap, const double* ret,
+                                       const int32_t* ind, const double* style,
+                                       double* factor_ret, double* specific_ret, double* r2, int32_t* status,
+                                       int n_peer, double* const* peer_bufs, int64_t peer_row0) {
+  return reg_by_time_impl(ctx, T, P, Q, max_rows_per_date, date_off, cap, ret, ind, style, factor_ret, specific_ret,
+                          r2, nullptr, status, n_peer, peer_bufs, peer_row0);
 }

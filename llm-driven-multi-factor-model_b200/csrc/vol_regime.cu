@@ -16,8 +16,15 @@
 namespace bmfm {
 
 // one warp per date
+struct VrPeers {
+  int n;
+  double* wb[8];
+  double* wv[8];
+};
+
 __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const double* cov,
-                               const int* cov_status, double* wb, double* wv, int t_off, int T_total) {
+                               const int* cov_status, double* wb, double* wv, int t_off, int T_total,
+                               VrPeers peers) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= T) return;
   const int t = warp;
@@ -42,8 +49,12 @@ __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const
     const double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);   // B_t^2
     const double w = pow(0.5, (double)(T_total - 1 - (t_off + t)) / tao);
     // rows whose variance vector holds a NaN are excluded from both sums (MFM.py:158)
-    wb[t] = nanvar ? 0.0 : w * b2;
-    wv[t] = nanvar ? 0.0 : w;
+    const double ob = nanvar ? 0.0 : w * b2, ov = nanvar ? 0.0 : w;
+    if (wb) { wb[t] = ob; wv[t] = ov; }
+    for (int r = 0; r < peers.n; ++r) {     // fused all-gather: straight into every rank's full-length arrays
+      peers.wb[r][t_off + t] = ob;
+      peers.wv[r][t_off + t] = ov;
+    }
   }
 }
 
@@ -102,7 +113,9 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
   if (rc) return rc;
   double* wb = (double*)ctx->ws;
   double* wv = wb + T;
-  vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv, 0, T);
+  VrPeers nopeers;
+  nopeers.n = 0;
+  vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv, 0, T, nopeers);
   ctx->launches++;
   vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T, wb, wv, lamb);
   ctx->launches++;
@@ -132,8 +145,32 @@ extern "C" int bmfm_vol_regime_bias(bmfm_ctx* ctx, int T_total, int t0, int n, i
   BMFM_ARG(ctx, n == 0 || (factor_ret_block && cov_block && wb && wv), "NULL pointer");
   if (n == 0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  VrPeers nopeers;
+  nopeers.n = 0;
   vr_bias_kernel<<<(n * 32 + 255) / 256, 256, 0, ctx->stream>>>(n, K, tao, factor_ret_block, cov_block,
-                                                              cov_status_block, wb, wv, t0, T_total);
+                                                              cov_status_block, wb, wv, t0, T_total, nopeers);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// bmfm_vol_regime_bias with the all-gather fused in: the terms of this rank's block are stored into every
+// rank's full-length wb_all / wv_all (HOST arrays of n_peer device pointers, peer-mapped) at offset t0.
+extern "C" int bmfm_vol_regime_bias_gather(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                                           const double* factor_ret_block, const double* cov_block,
+                                           const int32_t* cov_status_block, int n_peer, double* const* peer_wb,
+                                           double* const* peer_wv) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && t0 >= 0 && n >= 0 && t0 + n <= T_total && K > 0 && tao > 0, "bad sizes");
+  BMFM_ARG(ctx, n_peer >= 1 && n_peer <= 8 && peer_wb && peer_wv, "bad peer list");
+  BMFM_ARG(ctx, n == 0 || (factor_ret_block && cov_block), "NULL pointer");
+  if (n == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  VrPeers peers;
+  peers.n = n_peer;
+  for (int r = 0; r < 8; ++r) { peers.wb[r] = r < n_peer ? peer_wb[r] : nullptr; peers.wv[r] = r < n_peer ? peer_wv[r] : nullptr; }
+  vr_bias_kernel<<<(n * 32 + 255) / 256, 256, 0, ctx->stream>>>(n, K, tao, factor_ret_block, cov_block,
+                                                              cov_status_block, nullptr, nullptr, t0, T_total, peers);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;

@@ -163,3 +163,42 @@ def test_mfm_dropin_reg_by_time(golden_dir):
     assert np.max(np.abs(r2.values[:, 0] - g["R2"])) < TOL
     assert relerr(np.asarray(model.last_capital), g["last_capital"]) == 0.0
     assert list(spec[0].columns) == sorted(spec[0].columns)
+
+
+def test_fused_gather_entry_points_single_gpu(ops):
+    """bmfm_reg_by_time_gather / bmfm_vol_regime_bias_gather with this GPU as its own (only) peer: the
+    kernels' peer stores must land in the gathered buffers at the rank offset."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.panel import pack_arrays
+    from bmfm.synth import make_panel
+    ctx = _cabi.default_context()
+    pan = make_panel(7, 120, 6, 4, seed=21)
+    csr = pan.to_csr()
+    (cap, ret, ind, style), pos = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P)
+    dv = lambda a: torch.from_numpy(a).cuda()
+    T, K, row0, T_all = pan.T, 1 + pan.P + pan.Q, 5, 20
+    off, dcap, dret, dind, dsty = dv(csr["date_off"]), dv(cap), dv(ret), dv(ind), dv(style)
+    fr = torch.empty((T, K), dtype=torch.float64, device="cuda")
+    fr2 = torch.empty_like(fr)
+    spec = torch.empty(len(cap), dtype=torch.float64, device="cuda")
+    r2 = torch.empty(T, dtype=torch.float64, device="cuda")
+    st = torch.empty(T, dtype=torch.int32, device="cuda")
+    gathered = torch.full((T_all, K), -7.0, dtype=torch.float64, device="cuda")
+    ctx.reg_by_time(T, pan.P, pan.Q, pan.N, off, dcap, dret, dind, dsty, fr, spec, r2, st)
+    ctx.reg_by_time_gather(T, pan.P, pan.Q, pan.N, off, dcap, dret, dind, dsty, fr2, spec, r2, st,
+                           [gathered.data_ptr()], row0)
+    torch.cuda.synchronize()
+    assert torch.equal(fr, fr2) and torch.equal(gathered[row0:row0 + T], fr)
+    assert (gathered[:row0] == -7.0).all() and (gathered[row0 + T:] == -7.0).all()
+    cov = torch.eye(K, dtype=torch.float64, device="cuda").repeat(T, 1, 1) * 1e-4
+    cst = torch.zeros(T, dtype=torch.int32, device="cuda")
+    wb = torch.empty(T, dtype=torch.float64, device="cuda")
+    wv = torch.empty(T, dtype=torch.float64, device="cuda")
+    ctx.vol_regime_bias(T_all, row0, T, K, 10.0, fr, cov, cst, wb, wv)
+    wba = torch.zeros(T_all, dtype=torch.float64, device="cuda")
+    wva = torch.zeros(T_all, dtype=torch.float64, device="cuda")
+    ctx.vol_regime_bias_gather(T_all, row0, T, K, 10.0, fr, cov, cst, [wba.data_ptr()], [wva.data_ptr()])
+    torch.cuda.synchronize()
+    assert torch.equal(wba[row0:row0 + T], wb) and torch.equal(wva[row0:row0 + T], wv)
+    assert wba.sum() == wb.sum()
