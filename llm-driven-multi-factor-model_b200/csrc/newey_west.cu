@@ -31,6 +31,7 @@ constexpr int NW_EMIT_SPLIT = 4;   // CTAs per chunk in the emit kernel (the K*K
 struct NwParams {
   int T, K, q, C, nchunks;
   int t0, t1, c_first;   // emit only dates [t0, t1) (chunks from c_first on), written at row t - t0
+  int c_used;            // chunks 0 .. c_used-1 are needed (those up to the last emitted one)
   double lam;
   const double* fr;   // [T][K]
   double* cov;        // [T][K][K]
@@ -105,13 +106,13 @@ __global__ void nw_chunk_scan(NwParams p) {
   if (e >= ns) return;
   const double fC = pow(p.lam, (double)p.C);
   double run = 0.0;
-  for (int c0 = 0; c0 < p.nchunks; c0 += 32) {
+  for (int c0 = 0; c0 < p.c_used; c0 += 32) {
     double loc[32];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) loc[j] = (c0 + j < p.nchunks) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
+    for (int j = 0; j < 32; ++j) loc[j] = (c0 + j < p.c_used) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-      if (c0 + j < p.nchunks) {
+      if (c0 + j < p.c_used) {
         p.state[(size_t)(c0 + j) * ns + e] = run;
         run = fma(run, fC, loc[j]);
       }
@@ -249,6 +250,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.t0 = t0; p.t1 = t1;
   p.c_first = t0 / p.C;
   const int c_last = t1 > t0 ? (t1 - 1) / p.C : p.c_first - 1;
+  p.c_used = c_last + 1;   // later chunks feed nothing this call emits
   {
     const size_t smem_local = (size_t)(p.C + q) * K * 8;
     if (smem_local > (size_t)ctx->max_smem_optin) {
@@ -257,7 +259,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
     }
     if (smem_local > 48 * 1024)
       BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-    nw_chunk_local<<<p.nchunks, 256, smem_local, ctx->stream>>>(p);
+    nw_chunk_local<<<p.c_used, 256, smem_local, ctx->stream>>>(p);
   }
   ctx->launches++;
   const int ns = nw_nstate(K, q);
@@ -387,7 +389,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   }
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;
-  p.t0 = 0; p.t1 = T; p.c_first = 0;
+  p.t0 = 0; p.t1 = T; p.c_first = 0; p.c_used = p.nchunks;
   p.state = nw_static_ptr[ctx->device];
   {
     const size_t smem_local = (size_t)(p.C + q) * K * 8;
@@ -397,7 +399,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
     }
     if (smem_local > 48 * 1024)
       BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-    nw_chunk_local<<<p.nchunks, 256, smem_local, ctx->stream>>>(p);
+    nw_chunk_local<<<p.c_used, 256, smem_local, ctx->stream>>>(p);
   }
   ctx->launches++;
   const int ns = nw_nstate(K, q);
