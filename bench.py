@@ -44,6 +44,26 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """Keep stdout to exactly one JSON line: libraries (NCCL's version banner, ...) write to fd 1 directly, so
+    fd 1 is pointed at stderr for the whole run and the result line goes to a saved copy of the real stdout."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    fd = _RESULT_FD if _RESULT_FD is not None else 1
+    while data:
+        data = data[os.write(fd, data):]
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -225,7 +245,7 @@ def run_reference(args):
         "eigen_mc": {"value": eig, "unit": "sims/s", "config": f"K={K}, T_sim={EIG_TSIM}, 24 sims of one date (numpy port)"},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -549,7 +569,7 @@ def run_gpu(args):
                          "all_status_ok": eig_ok,
                          "cpu_baseline": {"value": cpu_eig, "unit": "sims/s", "kind": "port", "sample": "16 sims of one date"}},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # leave without tearing NCCL down: destroying the process group while a captured graph still holds
         # NCCL work was seen to hang at exit; everything is flushed and the numbers are out
@@ -567,6 +587,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
+    claim_stdout()
     if args.warmup < 3 and args.impl != "reference":
         args.warmup = 3
     if args.impl == "reference":

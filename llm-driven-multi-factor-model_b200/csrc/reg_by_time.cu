@@ -1185,7 +1185,27 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
   }
 }
 
+#include "reg_mma.cuh"
+
 // ---- host side ---------------------------------------------------------------------------------
+template <int Q, int NSTAGE>
+static int launch_reg_mma(bmfm_ctx* ctx, const RegParams& p) {
+  const int per_warp = rm_layout<Q, NSTAGE>(p.P).total;
+  int warps = RM_WARPS;
+  if (const char* ev = getenv("BMFM_REG_WARPS")) warps = atoi(ev) >= 1 && atoi(ev) <= RM_WARPS ? atoi(ev) : warps;
+  const int smem_s = warps * per_warp;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_mma_kernel<Q, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
+  int per_sm = (228 * 1024) / (smem_s + 1024);
+  if (per_sm < 1) per_sm = 1;
+  if (const char* ev = getenv("BMFM_REG_CTAS")) per_sm = atoi(ev) > 0 ? atoi(ev) : per_sm;
+  int grid = ctx->sm_count * per_sm;
+  if (grid * warps > p.T) grid = (p.T + warps - 1) / warps;
+  reg_mma_kernel<Q, NSTAGE><<<grid, warps * 32, smem_s, ctx->stream>>>(p);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
 template <int Q>
 static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   const int SMEM_MAX = ctx->max_smem_optin;           // 227 KB on B200
@@ -1209,7 +1229,12 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   int mode = 0;
   if (const char* ev = getenv("BMFM_REG_MODE")) mode = atoi(ev);
   const bool use_stream = mode == 2 || (mode == 0 && max_rows > 0 && max_rows <= 2048);
-  if (!p.all_dense && use_stream) {
+  if (!p.all_dense && mode == 3) {
+    int ns = 3;
+    if (const char* ev = getenv("BMFM_REG_STAGES")) ns = atoi(ev);
+    const int rc = ns == 2 ? launch_reg_mma<Q, 2>(ctx, p) : launch_reg_mma<Q, 3>(ctx, p);
+    if (rc != BMFM_OK) return rc;
+  } else if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);
     const int per_warp = rs_per_warp_bytes<Q>(Lw.total);
     const int smem_s = RS_WARPS * per_warp;

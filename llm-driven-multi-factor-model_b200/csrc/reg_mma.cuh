@@ -1,0 +1,389 @@
+// Tensor-core streaming kernel of the per-date regression: one WARP per date, like reg_stream_kernel,
+// but the weighted Gram of pass A is formed by FP64 MMA (mma.sync m8n8k4 -> DMMA.8x8x4) instead of 97
+// register accumulators per lane.  Included by reg_by_time.cu (inside namespace bmfm).
+//
+// Per 32-row chunk of the cp.async ring:
+//   stage   lane = row: w = sqrt(cap), z = [w, w y, cap, w d_1..w d_Q] (d = style - first row) -> shared
+//   gram    8 k-steps of 4 rows.  Left vector  L = [w d_1..w d_Q, cap, 1]   (A fragments, read from z)
+//                                 right vector R = [d_1..d_Q, u, 1]         (B fragments, raw stage - shift)
+//           laid out in 8-wide tiles so that three 8x8 products (one when Q <= 6) hold every sum the solve
+//           needs: w d d' (lower triangle), w d u, w d, cap d, sum d, sum u.  Accumulators: 6 doubles a lane.
+//   buckets lane = row: rows of the chunk that share an industry are found with one match.any; the first
+//           lane of each group adds the group's z rows and updates the per-warp table — no atomics, and
+//           the summation order is fixed (deterministic results).
+// The solve and pass C are the ones of reg_stream_kernel.  ~90 registers instead of 255, so the SM holds
+// 12-16 warps instead of 8 (shared memory per warp is the limit) and each warp has far more independent
+// work in flight.
+#pragma once
+
+constexpr int RM_WARPS = 4;   // warps per CTA
+
+__host__ __device__ constexpr int rm_zs(int Q) { return (3 + Q) | 1; }   // odd row stride of the z staging
+
+struct RmSmem { int bucket, acc, coef, fvec, flag, uni, cst, ring, total; };
+
+template <int Q, int NSTAGE>
+__host__ __device__ inline RmSmem rm_layout(int P) {
+  const int NB = P + 1, BV = 3 + Q, K = 1 + P + Q;
+  RmSmem s;
+  int o = 0;
+  s.bucket = o; o = align16(o + NB * BV * 8);
+  s.acc = o;    o = align16(o + (na1pad_of(Q) + na2pad_of(Q)) * 8);
+  s.coef = o;   o = align16(o + (3 * Q + NB + 32) * 8);
+  s.fvec = o;   o = align16(o + (K + 2) * 8);
+  s.flag = o;   o += 16;
+  const int solve = (Q * Q + 7 * Q + 2 * NB + 8) * 8, zst = 32 * rm_zs(Q) * 8;
+  s.uni = o;    o = align16(o + (solve > zst ? solve : zst));   // z staging (pass A) / solve scratch
+  s.cst = o;    o = align16(o + 16 + rm_zs(Q) * 8);             // {1.0, 0.0}, then a z row of zeros
+  s.ring = o;   o = align16(o + NSTAGE * rs_stage_bytes<Q>());
+  s.total = o;
+  return s;
+}
+
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void dmma_884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// what row m of left tile i / column n of right tile j stands for
+enum { RM_NONE = -1, RM_CAP = -2, RM_ONE = -3, RM_U = -4 };   // >= 0: style index
+template <int Q>
+__device__ __forceinline__ int rm_left(int i, int m) {
+  constexpr int Q0 = Q < 6 ? Q : 6, Q1 = Q - Q0;
+  constexpr bool TWO = Q > 6;
+  if (i == 0) {
+    if (m < Q0) return m;
+    if (!TWO && m == 6) return RM_CAP;
+    if (!TWO && m == 7) return RM_ONE;
+    return RM_NONE;
+  }
+  if (m < Q1) return 6 + m;
+  if (m == Q1) return RM_CAP;
+  if (m == Q1 + 1) return RM_ONE;
+  return RM_NONE;
+}
+template <int Q>
+__device__ __forceinline__ int rm_right(int j, int n) {
+  constexpr int Q0 = Q < 6 ? Q : 6, Q1 = Q - Q0;
+  if (j == 0) {
+    if (n < Q0) return n;
+    if (n == 6) return RM_U;
+    if (n == 7) return RM_ONE;
+    return RM_NONE;
+  }
+  return n < Q1 ? 6 + n : RM_NONE;
+}
+
+// one lane's two accumulators of tile (i, j) -> the s_acc slots the solve reads
+template <int Q>
+__device__ __forceinline__ void rm_scatter(int i, int j, int lane, double c0, double c1, double ypiv, double* s_acc) {
+  constexpr int NA1PAD = na1pad_of(Q);
+  double* S2 = s_acc;
+  double* BY = s_acc + Q * (Q + 1) / 2;
+  double* CD = s_acc + NA1PAD;
+  double* D1 = CD + Q;
+  const int m = lane >> 2, n0 = 2 * (lane & 3);
+  const int lt = rm_left<Q>(i, m);
+  if (lt == RM_NONE) return;
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const int rt = rm_right<Q>(j, n0 + e);
+    const double v = e ? c1 : c0;
+    if (lt >= 0) {
+      if (rt >= 0) { if (rt <= lt) S2[lt * (lt + 1) / 2 + rt] = v; }
+      else if (rt == RM_U) BY[lt] = c0 + ypiv * c1;      // sum w d y = sum w d u + ypiv sum w d (columns 6, 7)
+    } else if (lt == RM_CAP) {
+      if (rt >= 0) CD[rt] = v;
+    } else {   // RM_ONE
+      if (rt >= 0) D1[rt] = v;
+      else if (rt == RM_U) D1[2 * Q] = v;                // Y1 = sum u, at s_acc[NA1PAD + 3Q]
+    }
+  }
+}
+
+template <int Q, int NSTAGE>
+__global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  constexpr int NA1PAD = na1pad_of(Q);
+  constexpr int QQ = Q > 0 ? Q : 1;
+  constexpr int SB = rs_stage_bytes<Q>();
+  constexpr int ZS = rm_zs(Q), BV = 3 + Q;
+  constexpr int Q0 = Q < 6 ? Q : 6, Q1 = Q - Q0;
+  constexpr bool TWO = Q > 6;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int P = p.P, NB = P + 1, K = p.K;
+  const RmSmem M = rm_layout<Q, NSTAGE>(P);
+  unsigned char* wsm = smem + (size_t)warp * M.total;
+  RegSmem L;   // the view solve_fast_cta expects
+  L.bucket = M.bucket; L.acc = M.acc; L.coef = M.coef; L.fvec = M.fvec; L.solve = M.uni;
+  L.seg = M.flag - (3 * NB + 2) * 4;
+  unsigned char* ring = wsm + M.ring;
+  double* s_z = reinterpret_cast<double*>(wsm + M.uni);
+  double* s_cst = reinterpret_cast<double*>(wsm + M.cst);
+  double* s_bucket = reinterpret_cast<double*>(wsm + M.bucket);
+  double* s_acc = reinterpret_cast<double*>(wsm + M.acc);
+  double* s_piv = reinterpret_cast<double*>(wsm + M.coef);
+  double* s_beta = s_piv + 2 * Q;
+  double* s_g = s_beta + Q;
+  double* s_misc = s_g + NB;
+  const double* s_f = reinterpret_cast<const double*>(wsm + M.fvec);
+  const int gw = blockIdx.x * nwarps + warp, tw = gridDim.x * nwarps;
+  if (lane == 0) { s_cst[0] = 1.0; s_cst[1] = 0.0; }
+  if (lane < ZS) s_cst[2 + lane] = 0.0;
+  const double* s_zero = s_cst + 2;
+
+  // fragment sources of this lane (row k = lane & 3 of a k-step, element c = lane >> 2 of a tile):
+  // byte offset relative to the stage (raw inputs) or an absolute shared address (z staging, constants)
+  const int c = lane >> 2, kq = lane & 3;
+  const unsigned z_sa = (unsigned)__cvta_generic_to_shared(s_z);
+  const unsigned one_sa = (unsigned)__cvta_generic_to_shared(s_cst), zero_sa = one_sa + 8;
+  constexpr int OFF_CAP = 32 * Q, OFF_RET = 32 * Q + 32;   // doubles inside a stage
+  (void)OFF_CAP;
+  // B tile 0
+  bool b0_st; unsigned b0_a, b0_s; int b0_sub;             // sub: -1 none, -2 one (-> 0), -3 ypiv, >= 0 piv index
+  if (c < Q0)       { b0_st = true;  b0_a = (c + kq * Q) * 8;      b0_s = 4 * Q * 8; b0_sub = c; }
+  else if (c == 6)  { b0_st = true;  b0_a = (OFF_RET + kq) * 8;    b0_s = 4 * 8;     b0_sub = -3; }
+  else if (c == 7)  { b0_st = false; b0_a = one_sa;                b0_s = 0;         b0_sub = -1; }
+  else              { b0_st = false; b0_a = one_sa;                b0_s = 0;         b0_sub = -2; }
+  // B tile 1
+  bool b1_st; unsigned b1_a, b1_s; int b1_sub;
+  if (c < Q1)       { b1_st = true;  b1_a = (6 + c + kq * Q) * 8;  b1_s = 4 * Q * 8; b1_sub = 6 + c; }
+  else              { b1_st = false; b1_a = one_sa;                b1_s = 0;         b1_sub = -2; }
+  // A tiles (absolute addresses)
+  unsigned a0_a, a0_s, a1_a, a1_s;
+  {
+    const int l0 = rm_left<Q>(0, c), l1 = rm_left<Q>(1, c);
+    if (l0 >= 0)            { a0_a = z_sa + (3 + l0 + kq * ZS) * 8; a0_s = 4 * ZS * 8; }
+    else if (l0 == RM_CAP)  { a0_a = z_sa + (2 + kq * ZS) * 8;      a0_s = 4 * ZS * 8; }
+    else if (l0 == RM_ONE)  { a0_a = one_sa;  a0_s = 0; }
+    else                    { a0_a = zero_sa; a0_s = 0; }
+    if (l1 >= 0)            { a1_a = z_sa + (3 + l1 + kq * ZS) * 8; a1_s = 4 * ZS * 8; }
+    else if (l1 == RM_CAP)  { a1_a = z_sa + (2 + kq * ZS) * 8;      a1_s = 4 * ZS * 8; }
+    else if (l1 == RM_ONE)  { a1_a = one_sa;  a1_s = 0; }
+    else                    { a1_a = zero_sa; a1_s = 0; }
+  }
+  __syncwarp();
+
+  for (int t = gw; t < p.T; t += tw) {
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    if (n <= 0) {
+      for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
+      if (lane == 0) { p.r2[t] = nan; p.status[t] = BMFM_ST_NONFINITE; }
+      continue;
+    }
+    const int nchunks = (n + 31) >> 5;
+    for (int e = lane; e < NB * BV; e += 32) s_bucket[e] = 0.0;
+#pragma unroll
+    for (int cc = 0; cc < NSTAGE - 1; ++cc) {
+      if (cc < nchunks) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), true, ring + cc * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    // the pivot shift is the date's first row: take it from chunk 0 once it has landed
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 2) : "memory");
+    __syncwarp();
+    {
+      const double* st0 = reinterpret_cast<const double*>(ring);
+      if (lane < Q) s_piv[lane] = st0[lane];
+      if (lane == 0) s_misc[0] = st0[32 * Q + 32];
+    }
+    __syncwarp();
+    const double ypiv = s_misc[0];
+    const double sub0 = b0_sub >= 0 ? s_piv[b0_sub] : (b0_sub == -3 ? ypiv : (b0_sub == -2 ? 1.0 : 0.0));
+    const double sub1 = b1_sub >= 0 ? s_piv[b1_sub] : 1.0;
+    double c00a = 0.0, c00b = 0.0, c10a = 0.0, c10b = 0.0, c11a = 0.0, c11b = 0.0, sq0 = 0.0, sq1 = 0.0;
+
+    for (int cc = 0; cc < nchunks; ++cc) {
+      const int cn = cc + NSTAGE - 1;
+      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), true, ring + (cn % NSTAGE) * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 1) : "memory");
+      __syncwarp();
+      unsigned char* stage = ring + (cc % NSTAGE) * SB;
+      double* st_style = reinterpret_cast<double*>(stage);
+      double* st_cap = st_style + 32 * Q;
+      double* st_ret = st_cap + 32;
+      const int* st_ind = reinterpret_cast<const int*>(st_ret + 32);
+      const int m = min(32, n - 32 * cc);
+      // stage: per-row terms z (lane = row); rows past the end become exact zeros in every sum
+      {
+        double* zr = s_z + lane * ZS;
+        if (lane < m) {
+          const double cap = st_cap[lane];
+          const double w = sqrt(cap);
+          const double y = st_ret[lane];
+          zr[0] = w;
+          zr[1] = w * y;
+          zr[2] = cap;
+          if (Q > 0) {
+            double d[QQ];
+            load_row_styles<Q>(st_style, lane, s_piv, d);
+#pragma unroll
+            for (int q = 0; q < Q; ++q) zr[3 + q] = w * d[q];
+          }
+        } else {
+#pragma unroll
+          for (int v = 0; v < BV; ++v) zr[v] = 0.0;
+#pragma unroll
+          for (int q = 0; q < Q; ++q) st_style[lane * Q + q] = s_piv[q];
+          st_ret[lane] = ypiv;
+        }
+      }
+      __syncwarp();
+      // gram: 8 k-steps of 4 rows
+      {
+        const unsigned st_sa = (unsigned)__cvta_generic_to_shared(stage);
+        const unsigned pb0 = b0_st ? st_sa + b0_a : b0_a;
+        const unsigned pb1 = b1_st ? st_sa + b1_a : b1_a;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const double b0 = lds_f64(pb0 + ks * b0_s) - sub0;
+          const double a0 = lds_f64(a0_a + ks * a0_s);
+          dmma_884(c00a, c00b, a0, b0);
+          sq0 = fma(b0, b0, sq0);
+          if (TWO) {
+            const double b1 = lds_f64(pb1 + ks * b1_s) - sub1;
+            const double a1 = lds_f64(a1_a + ks * a1_s);
+            dmma_884(c10a, c10b, a1, b0);
+            dmma_884(c11a, c11b, a1, b1);
+            sq1 = fma(b1, b1, sq1);
+          }
+        }
+      }
+      // per-industry sums of the chunk's z rows, no atomics (the table is this warp's own)
+      {
+        const int myb = lane < m ? bucket_of(st_ind[lane], P) : 64 + lane;
+        const int prevb = __shfl_up_sync(0xffffffffu, myb, 1);
+        const unsigned runstart = __ballot_sync(0xffffffffu, lane < m && (lane == 0 || myb != prevb));
+        const int nruns = __popc(runstart);
+        bool by_runs = nruns <= 3;
+        unsigned peers = 0u;
+        if (!by_runs) {
+          peers = __match_any_sync(0xffffffffu, myb);
+          const int maxg = __reduce_max_sync(0xffffffffu, __popc(peers));
+          by_runs = 15 * nruns + 70 <= 26 * maxg + 39;       // estimated instruction counts of the two ways
+        }
+        if (by_runs) {
+          // rows grouped by industry (what the packer produces): column sums over each run of equal
+          // industries, lane = (row parity, value column)
+          const int h = lane >> 4, v = lane & 15;
+          const bool vact = v < BV;
+          unsigned rs = runstart;
+          while (rs) {
+            const int s = __ffs(rs) - 1;
+            rs &= rs - 1;
+            const int e = rs ? __ffs(rs) - 1 : m;
+            double acc = 0.0;
+            const double* zc = s_z + (s + h) * ZS + (vact ? v : 0);
+            const int half = (e - s + 1) >> 1;
+            for (int i = 0; i < half; ++i)
+              if (s + h + 2 * i < e) acc += zc[2 * i * ZS];
+            acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+            const int b = __shfl_sync(0xffffffffu, myb, s);
+            if (h == 0 && vact) s_bucket[b * BV + v] += acc;
+          }
+        } else {
+          // arbitrary row order: the first lane of every group of equal industries adds the group's rows;
+          // warp-uniform trip count (the largest group), idle lanes add a row of zeros
+          const bool lead = lane < m && (__ffs(peers) - 1) == lane;
+          double acc[BV];
+#pragma unroll
+          for (int v = 0; v < BV; ++v) acc[v] = 0.0;
+          unsigned rest = lead ? peers : 0u;
+          while (__any_sync(0xffffffffu, rest != 0u)) {
+            const double* zj = rest ? s_z + (__ffs(rest) - 1) * ZS : s_zero;
+            rest &= rest - 1;
+#pragma unroll
+            for (int v = 0; v < BV; ++v) acc[v] += zj[v];
+          }
+          if (lead) {
+            double* tb = s_bucket + myb * BV;
+#pragma unroll
+            for (int v = 0; v < BV; ++v) tb[v] += acc[v];
+          }
+        }
+      }
+      __syncwarp();   // z and the stage may be rewritten by the next iteration
+    }
+    // accumulators -> the layout the solve reads
+    rm_scatter<Q>(0, 0, lane, c00a, c00b, ypiv, s_acc);
+    if (TWO) {
+      rm_scatter<Q>(1, 0, lane, c10a, c10b, ypiv, s_acc);
+      rm_scatter<Q>(1, 1, lane, c11a, c11b, ypiv, s_acc);
+    }
+    {
+      const double d2 = warp_sum((c < Q0 ? sq0 : 0.0) + (TWO ? sq1 : 0.0));
+      const double y2 = warp_sum(c == 6 ? sq0 : 0.0);
+      if (Q > 0 && lane < Q) s_acc[NA1PAD + 2 * Q + lane] = lane == 0 ? d2 : 0.0;
+      if (lane == 0) s_acc[NA1PAD + 3 * Q + 1] = y2;
+    }
+    __syncwarp();
+    // start refilling the ring for pass C while the solve runs (served by L2)
+#pragma unroll
+    for (int cc = 0; cc < NSTAGE - 1; ++cc) {
+      if (cc < nchunks) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), false, ring + cc * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    const int st = solve_fast_cta<Q, true>(p, L, wsm, n);
+    if (st != BMFM_ST_OK) {
+      asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+      __syncwarp();
+      if (st == REG_NEED_DENSE) {
+        if (lane == 0) p.status[t] = REG_NEED_DENSE;
+      } else {
+        for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
+        for (int i = lane; i < n; i += 32) p.spec[a + i] = nan;
+        if (lane == 0) { p.r2[t] = nan; p.status[t] = st; }
+      }
+      continue;
+    }
+    for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, s_f[k]);
+    // pass C
+    const double c0 = s_misc[1];
+    double se = 0.0, see = 0.0;
+    for (int cc = 0; cc < nchunks; ++cc) {
+      const int cn = cc + NSTAGE - 1;
+      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), false, ring + (cn % NSTAGE) * SB, lane);
+      else asm volatile("cp.async.commit_group;\n" ::: "memory");
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 1) : "memory");
+      __syncwarp();
+      unsigned char* stage = ring + (cc % NSTAGE) * SB;
+      const double* st_style = reinterpret_cast<const double*>(stage);
+      const double* st_ret = st_style + 32 * Q + 32;
+      const int* st_ind = reinterpret_cast<const int*>(st_ret + 32);
+      const int m = min(32, n - 32 * cc);
+      if (lane < m) {
+        double e = st_ret[lane] - c0 - s_g[bucket_of(st_ind[lane], P)];
+        if (Q > 0) {
+          double d[QQ];
+          load_row_styles<Q>(st_style, lane, s_piv, d);
+#pragma unroll
+          for (int q = 0; q < Q; ++q) e = fma(-s_beta[q], d[q], e);
+        }
+        st_stream(p.spec + a + 32 * cc + lane, e);
+        se += e;
+        see = fma(e, e, see);
+      }
+      __syncwarp();
+    }
+    se = warp_sum(se);
+    see = warp_sum(see);
+    if (lane == 0) {
+      const double dn = (double)n;
+      const double me = se / dn;
+      const double var_e = see / dn - me * me;
+      const double my = s_acc[NA1PAD + 3 * Q] / dn;
+      const double var_y = s_acc[NA1PAD + 3 * Q + 1] / dn - my * my;
+      p.r2[t] = 1.0 - var_e / var_y;
+      p.status[t] = BMFM_ST_OK;
+    }
+    __syncwarp();
+  }
+}

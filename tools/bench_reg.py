@@ -22,7 +22,9 @@ P, Q = 31, 10
 K = 1 + P + Q
 pan = make_panel(T, N, P, Q, seed=3, scale_log10=(-2, 2))
 csr = pan.to_csr()
-(cap, ret, ind, style), pos = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P)
+GROUPED = os.environ.get("BENCH_UNGROUPED") != "1"     # rows sorted by industry inside a date (what pack_frame does)
+(cap, ret, ind, style), pos = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P,
+                                          group_by_industry=GROUPED)
 d = lambda a: torch.from_numpy(a).cuda()
 off, cap, ret, ind, style = d(csr["date_off"]), d(cap), d(ret), d(ind), d(style)
 rows = int(csr["date_off"][-1])
@@ -42,5 +44,5 @@ for i in range(8):
     torch.cuda.synchronize()
     times.append(e0.elapsed_time(e1))
 ms = float(np.median(times[3:]))
-print(f"N={N} T={T} mode={os.environ.get('BMFM_REG_MODE', '0')}: {ms:.3f} ms, {rows * 108 / ms / 1e6:.0f} GB/s "
+print(f"{'grouped' if GROUPED else 'ungrouped'} N={N} T={T} mode={os.environ.get('BMFM_REG_MODE', '0')}: {ms:.3f} ms, {rows * 108 / ms / 1e6:.0f} GB/s "
       f"({rows * 108 / ms / 1e6 / 6538:.3f} of measured HBM), {T / ms * 1e3:.0f} dates/s, status ok={bool((st == 0).all())}")
