@@ -536,7 +536,7 @@ def run_gpu(args):
     if rank == 0:
         peak, peak_src = load_peaks()
         achieved = BYTES_PER_STOCK_DATE * rows / (ms_reg * 1e-3) / 1e9
-        dominant = max((ms_reg, "reg_by_time (reg_stream_kernel)"), (ms_nw, "newey_west (nw_emit)"), (ms_vr, "vol_regime (vr_scale_kernel)"))[1]
+        dominant = max((ms_reg, "reg_by_time (reg_mma_kernel)"), (ms_nw, "newey_west (nw_emit)"), (ms_vr, "vol_regime (vr_scale_kernel)"))[1]
         t0 = time.perf_counter()
         cpu_v, cpu_desc = cpu_sample(csr, 600)
         cpu_eig = cpu_eigen_sample(16)
@@ -554,7 +554,7 @@ def run_gpu(args):
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
                        "all_status_ok": status_ok, "gather_check": gather_check},
-            "roofline": {"kernel": "reg_stream_kernel<10> (per-date Gram + constrained solve + residuals, one warp per date)",
+            "roofline": {"kernel": "reg_mma_kernel<10,3,1> (per-date weighted Gram on FP64 MMA + constrained solve + residuals, one warp per date)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": load_traffic(), "traffic_source": "ncu --set full capture of one launch, profiles/roofline_traffic.json",
                          "peak_source": peak_src,

@@ -1188,19 +1188,20 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
 #include "reg_mma.cuh"
 
 // ---- host side ---------------------------------------------------------------------------------
-template <int Q, int NSTAGE>
+template <int Q, int NSTAGE, int WPD>
 static int launch_reg_mma(bmfm_ctx* ctx, const RegParams& p) {
-  const int per_warp = rm_layout<Q, NSTAGE>(p.P).total;
   int warps = RM_WARPS;
-  if (const char* ev = getenv("BMFM_REG_WARPS")) warps = atoi(ev) >= 1 && atoi(ev) <= RM_WARPS ? atoi(ev) : warps;
-  const int smem_s = warps * per_warp;
-  BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_mma_kernel<Q, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
+  if (WPD == 1)
+    if (const char* ev = getenv("BMFM_REG_WARPS")) warps = atoi(ev) >= 1 && atoi(ev) <= RM_WARPS ? atoi(ev) : warps;
+  const int smem_s = rm_cta_bytes<Q, NSTAGE>(p.P, WPD, warps);
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_mma_kernel<Q, NSTAGE, WPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
   int per_sm = (228 * 1024) / (smem_s + 1024);
   if (per_sm < 1) per_sm = 1;
   if (const char* ev = getenv("BMFM_REG_CTAS")) per_sm = atoi(ev) > 0 ? atoi(ev) : per_sm;
   int grid = ctx->sm_count * per_sm;
-  if (grid * warps > p.T) grid = (p.T + warps - 1) / warps;
-  reg_mma_kernel<Q, NSTAGE><<<grid, warps * 32, smem_s, ctx->stream>>>(p);
+  const int dates_per_cta = WPD > 1 ? 1 : warps;
+  if (grid * dates_per_cta > p.T) grid = (p.T + dates_per_cta - 1) / dates_per_cta;
+  reg_mma_kernel<Q, NSTAGE, WPD><<<grid, warps * 32, smem_s, ctx->stream>>>(p);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
@@ -1225,14 +1226,19 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
   p.tile_rows = rows;
-  // small cross-sections: warp-per-date streaming kernel (BMFM_REG_MODE=1 forces the CTA kernel, 2 the stream kernel)
+  // Default: the FP64-MMA kernel, one warp per date for cross-sections up to 2048 rows (mode 3), one CTA per
+  // date above (mode 4).  BMFM_REG_MODE forces a kernel: 1 = CTA kernel with the date resident in shared
+  // memory, 2 = warp-per-date kernel with register accumulators (the two earlier designs, kept for comparison).
   int mode = 0;
   if (const char* ev = getenv("BMFM_REG_MODE")) mode = atoi(ev);
-  const bool use_stream = mode == 2 || (mode == 0 && max_rows > 0 && max_rows <= 2048);
-  if (!p.all_dense && mode == 3) {
-    int ns = 3;
+  if (mode < 1 || mode > 4) mode = (max_rows > 0 && max_rows <= 2048) ? 3 : 4;
+  const bool use_stream = mode == 2;
+  if (!p.all_dense && (mode == 3 || mode == 4)) {
+    int ns = mode == 4 ? 2 : 3;
     if (const char* ev = getenv("BMFM_REG_STAGES")) ns = atoi(ev);
-    const int rc = ns == 2 ? launch_reg_mma<Q, 2>(ctx, p) : launch_reg_mma<Q, 3>(ctx, p);
+    const int wpd = mode == 4 ? RM_WARPS : 1;   // 3: one warp per date, 4: one CTA of RM_WARPS warps per date
+    const int rc = wpd > 1 ? (ns == 2 ? launch_reg_mma<Q, 2, RM_WARPS>(ctx, p) : launch_reg_mma<Q, 3, RM_WARPS>(ctx, p))
+                           : (ns == 2 ? launch_reg_mma<Q, 2, 1>(ctx, p) : launch_reg_mma<Q, 3, 1>(ctx, p));
     if (rc != BMFM_OK) return rc;
   } else if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);

@@ -16,28 +16,52 @@
 // work in flight.
 #pragma once
 
-constexpr int RM_WARPS = 4;   // warps per CTA
+constexpr int RM_WARPS = 4;   // warps per CTA (= warps per date in the CTA-per-date form)
 
 __host__ __device__ constexpr int rm_zs(int Q) { return (3 + Q) | 1; }   // odd row stride of the z staging
 
-struct RmSmem { int bucket, acc, coef, fvec, flag, uni, cst, ring, total; };
+// Shared memory: a "solve" block (accumulator vector, coefficients, factor returns, flag) and a "warp" block
+// (bucket table, z staging, constants, ring).  WPD = warps per date: with WPD == 1 every warp has both blocks and
+// the solve scratch aliases the z staging; with WPD > 1 the CTA has one solve block and WPD warp blocks.
+struct RmSolveBlk { int acc, coef, fvec, flag, solve, red, total; };
+struct RmWarpBlk { int bucket, z, cst, ring, total; };
 
-template <int Q, int NSTAGE>
-__host__ __device__ inline RmSmem rm_layout(int P) {
-  const int NB = P + 1, BV = 3 + Q, K = 1 + P + Q;
-  RmSmem s;
+template <int Q>
+__host__ __device__ inline RmSolveBlk rm_solve_blk(int P, int wpd) {
+  const int NB = P + 1, K = 1 + P + Q;
+  RmSolveBlk s;
   int o = 0;
-  s.bucket = o; o = align16(o + NB * BV * 8);
   s.acc = o;    o = align16(o + (na1pad_of(Q) + na2pad_of(Q)) * 8);
   s.coef = o;   o = align16(o + (3 * Q + NB + 32) * 8);
   s.fvec = o;   o = align16(o + (K + 2) * 8);
   s.flag = o;   o += 16;
-  const int solve = (Q * Q + 7 * Q + 2 * NB + 8) * 8, zst = 32 * rm_zs(Q) * 8;
-  s.uni = o;    o = align16(o + (solve > zst ? solve : zst));   // z staging (pass A) / solve scratch
-  s.cst = o;    o = align16(o + 16 + rm_zs(Q) * 8);             // {1.0, 0.0}, then a z row of zeros
+  s.solve = o;  if (wpd > 1) o = align16(o + (Q * Q + 7 * Q + 2 * NB + 8) * 8);
+  s.red = o;    if (wpd > 1) o = align16(o + 2 * wpd * 8);
+  if (o < (3 * NB + 2) * 4) o = align16((3 * NB + 2) * 4);   // keeps the flag's RegSmem-style offset non-negative
+  s.total = o;
+  return s;
+}
+
+template <int Q, int NSTAGE>
+__host__ __device__ inline RmWarpBlk rm_warp_blk(int P) {
+  const int NB = P + 1, BV = 3 + Q;
+  RmWarpBlk s;
+  int o = 0;
+  s.bucket = o; o = align16(o + NB * BV * 8);
+  const int solve = (Q * Q + 7 * Q + 2 * NB + 8) * 8, zst = 32 * rm_zs(Q) * 8, cf = 8 * 32 * 8;
+  int u = solve > zst ? solve : zst;
+  if (cf > u) u = cf;
+  s.z = o;      o = align16(o + u);                     // z staging; later solve scratch (WPD 1) / fragment hand-over (WPD > 1)
+  s.cst = o;    o = align16(o + 16 + rm_zs(Q) * 8);     // {1.0, 0.0}, then a z row of zeros
   s.ring = o;   o = align16(o + NSTAGE * rs_stage_bytes<Q>());
   s.total = o;
   return s;
+}
+
+template <int Q, int NSTAGE>
+__host__ __device__ inline int rm_cta_bytes(int P, int wpd, int warps) {
+  const int sb = rm_solve_blk<Q>(P, wpd).total, wb = rm_warp_blk<Q, NSTAGE>(P).total;
+  return wpd > 1 ? sb + wpd * wb : warps * (sb + wb);
 }
 
 __device__ __forceinline__ double lds_f64(unsigned addr) {
@@ -107,9 +131,11 @@ __device__ __forceinline__ void rm_scatter(int i, int j, int lane, double c0, do
   }
 }
 
-template <int Q, int NSTAGE>
+
+template <int Q, int NSTAGE, int WPD>
 __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
+  constexpr bool CTA = WPD > 1;            // WPD warps (one CTA) share a date; otherwise one warp per date
   constexpr int NA1PAD = na1pad_of(Q);
   constexpr int QQ = Q > 0 ? Q : 1;
   constexpr int SB = rs_stage_bytes<Q>();
@@ -117,23 +143,28 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
   constexpr int Q0 = Q < 6 ? Q : 6, Q1 = Q - Q0;
   constexpr bool TWO = Q > 6;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int tid = CTA ? (int)threadIdx.x : lane, nt = CTA ? (int)blockDim.x : 32;
   const int P = p.P, NB = P + 1, K = p.K;
-  const RmSmem M = rm_layout<Q, NSTAGE>(P);
-  unsigned char* wsm = smem + (size_t)warp * M.total;
-  RegSmem L;   // the view solve_fast_cta expects
-  L.bucket = M.bucket; L.acc = M.acc; L.coef = M.coef; L.fvec = M.fvec; L.solve = M.uni;
-  L.seg = M.flag - (3 * NB + 2) * 4;
-  unsigned char* ring = wsm + M.ring;
-  double* s_z = reinterpret_cast<double*>(wsm + M.uni);
-  double* s_cst = reinterpret_cast<double*>(wsm + M.cst);
-  double* s_bucket = reinterpret_cast<double*>(wsm + M.bucket);
-  double* s_acc = reinterpret_cast<double*>(wsm + M.acc);
-  double* s_piv = reinterpret_cast<double*>(wsm + M.coef);
+  const RmSolveBlk SK = rm_solve_blk<Q>(P, WPD);
+  const RmWarpBlk WK = rm_warp_blk<Q, NSTAGE>(P);
+  unsigned char* sbase = CTA ? smem : smem + (size_t)warp * (SK.total + WK.total);
+  unsigned char* wbase = CTA ? smem + SK.total + (size_t)warp * WK.total : sbase + SK.total;
+  RegSmem L;   // the view solve_fast_cta expects, offsets from sbase (bucket table: warp 0's in the CTA form)
+  L.acc = SK.acc; L.coef = SK.coef; L.fvec = SK.fvec;
+  L.seg = SK.flag - (3 * NB + 2) * 4;
+  L.bucket = SK.total + WK.bucket;
+  L.solve = CTA ? SK.solve : SK.total + WK.z;
+  unsigned char* ring = wbase + WK.ring;
+  double* s_z = reinterpret_cast<double*>(wbase + WK.z);
+  double* s_cst = reinterpret_cast<double*>(wbase + WK.cst);
+  double* s_bucket = reinterpret_cast<double*>(wbase + WK.bucket);
+  double* s_acc = reinterpret_cast<double*>(sbase + SK.acc);
+  double* s_piv = reinterpret_cast<double*>(sbase + SK.coef);
   double* s_beta = s_piv + 2 * Q;
   double* s_g = s_beta + Q;
   double* s_misc = s_g + NB;
-  const double* s_f = reinterpret_cast<const double*>(wsm + M.fvec);
-  const int gw = blockIdx.x * nwarps + warp, tw = gridDim.x * nwarps;
+  double* s_red = reinterpret_cast<double*>(sbase + SK.red);
+  const double* s_f = reinterpret_cast<const double*>(sbase + SK.fvec);
   if (lane == 0) { s_cst[0] = 1.0; s_cst[1] = 0.0; }
   if (lane < ZS) s_cst[2 + lane] = 0.0;
   const double* s_zero = s_cst + 2;
@@ -143,19 +174,15 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
   const int c = lane >> 2, kq = lane & 3;
   const unsigned z_sa = (unsigned)__cvta_generic_to_shared(s_z);
   const unsigned one_sa = (unsigned)__cvta_generic_to_shared(s_cst), zero_sa = one_sa + 8;
-  constexpr int OFF_CAP = 32 * Q, OFF_RET = 32 * Q + 32;   // doubles inside a stage
-  (void)OFF_CAP;
-  // B tile 0
+  constexpr int OFF_RET = 32 * Q + 32;   // doubles inside a stage
   bool b0_st; unsigned b0_a, b0_s; int b0_sub;             // sub: -1 none, -2 one (-> 0), -3 ypiv, >= 0 piv index
   if (c < Q0)       { b0_st = true;  b0_a = (c + kq * Q) * 8;      b0_s = 4 * Q * 8; b0_sub = c; }
   else if (c == 6)  { b0_st = true;  b0_a = (OFF_RET + kq) * 8;    b0_s = 4 * 8;     b0_sub = -3; }
   else if (c == 7)  { b0_st = false; b0_a = one_sa;                b0_s = 0;         b0_sub = -1; }
   else              { b0_st = false; b0_a = one_sa;                b0_s = 0;         b0_sub = -2; }
-  // B tile 1
   bool b1_st; unsigned b1_a, b1_s; int b1_sub;
   if (c < Q1)       { b1_st = true;  b1_a = (6 + c + kq * Q) * 8;  b1_s = 4 * Q * 8; b1_sub = 6 + c; }
   else              { b1_st = false; b1_a = one_sa;                b1_s = 0;         b1_sub = -2; }
-  // A tiles (absolute addresses)
   unsigned a0_a, a0_s, a1_a, a1_s;
   {
     const int l0 = rm_left<Q>(0, c), l1 = rm_left<Q>(1, c);
@@ -170,43 +197,55 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
   }
   __syncwarp();
 
-  for (int t = gw; t < p.T; t += tw) {
+  const int wq = CTA ? warp : 0;                       // this warp takes chunks wq, wq + WPD, ...
+  const int t_first = CTA ? (int)blockIdx.x : (int)blockIdx.x * nwarps + warp;
+  const int t_step = CTA ? (int)gridDim.x : (int)gridDim.x * nwarps;
+  for (int t = t_first; t < p.T; t += t_step) {
     const long long a = p.date_off[t];
     const int n = (int)(p.date_off[t + 1] - a);
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     if (n <= 0) {
-      for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
-      if (lane == 0) { p.r2[t] = nan; p.status[t] = BMFM_ST_NONFINITE; }
+      for (int k = tid; k < K; k += nt) store_factor_ret(p, t, k, nan);
+      if (tid == 0) { p.r2[t] = nan; p.status[t] = BMFM_ST_NONFINITE; }
       continue;
     }
     const int nchunks = (n + 31) >> 5;
+    const int myn = nchunks > wq ? (nchunks - wq + WPD - 1) / WPD : 0;   // chunks of this warp
     for (int e = lane; e < NB * BV; e += 32) s_bucket[e] = 0.0;
 #pragma unroll
-    for (int cc = 0; cc < NSTAGE - 1; ++cc) {
-      if (cc < nchunks) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), true, ring + cc * SB, lane);
+    for (int k = 0; k < NSTAGE - 1; ++k) {
+      const int cc = wq + k * WPD;
+      if (k < myn) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), true, ring + k * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
-    // the pivot shift is the date's first row: take it from chunk 0 once it has landed
-    asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 2) : "memory");
-    __syncwarp();
-    {
+    // the pivot shift is the date's first row
+    if (CTA) {
+      if (warp == 0) {
+        if (lane < Q) s_piv[lane] = p.style[a * Q + lane];
+        if (lane == 0) s_misc[0] = p.ret[a];
+      }
+      __syncthreads();
+    } else {
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 2) : "memory");
+      __syncwarp();
       const double* st0 = reinterpret_cast<const double*>(ring);
       if (lane < Q) s_piv[lane] = st0[lane];
       if (lane == 0) s_misc[0] = st0[32 * Q + 32];
+      __syncwarp();
     }
-    __syncwarp();
     const double ypiv = s_misc[0];
     const double sub0 = b0_sub >= 0 ? s_piv[b0_sub] : (b0_sub == -3 ? ypiv : (b0_sub == -2 ? 1.0 : 0.0));
     const double sub1 = b1_sub >= 0 ? s_piv[b1_sub] : 1.0;
     double c00a = 0.0, c00b = 0.0, c10a = 0.0, c10b = 0.0, c11a = 0.0, c11b = 0.0, sq0 = 0.0, sq1 = 0.0;
 
-    for (int cc = 0; cc < nchunks; ++cc) {
-      const int cn = cc + NSTAGE - 1;
-      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), true, ring + (cn % NSTAGE) * SB, lane);
+    for (int k = 0; k < myn; ++k) {
+      const int cc = wq + k * WPD;
+      const int kn = k + NSTAGE - 1, cn = wq + kn * WPD;
+      if (kn < myn) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), true, ring + (kn % NSTAGE) * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
       asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 1) : "memory");
       __syncwarp();
-      unsigned char* stage = ring + (cc % NSTAGE) * SB;
+      unsigned char* stage = ring + (k % NSTAGE) * SB;
       double* st_style = reinterpret_cast<double*>(stage);
       double* st_cap = st_style + 32 * Q;
       double* st_ret = st_cap + 32;
@@ -313,48 +352,74 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
       __syncwarp();   // z and the stage may be rewritten by the next iteration
     }
     // accumulators -> the layout the solve reads
-    rm_scatter<Q>(0, 0, lane, c00a, c00b, ypiv, s_acc);
-    if (TWO) {
-      rm_scatter<Q>(1, 0, lane, c10a, c10b, ypiv, s_acc);
-      rm_scatter<Q>(1, 1, lane, c11a, c11b, ypiv, s_acc);
+    if (CTA) {
+      // hand the fragments over through the (now idle) z staging; warp 0 adds them in warp order
+      double* cf = s_z;
+      cf[0 * 32 + lane] = c00a; cf[1 * 32 + lane] = c00b; cf[2 * 32 + lane] = c10a; cf[3 * 32 + lane] = c10b;
+      cf[4 * 32 + lane] = c11a; cf[5 * 32 + lane] = c11b; cf[6 * 32 + lane] = sq0;  cf[7 * 32 + lane] = sq1;
+      __syncthreads();
+      if (warp == 0) {
+#pragma unroll
+        for (int w = 1; w < WPD; ++w) {
+          const double* o = reinterpret_cast<const double*>(wbase + (size_t)w * WK.total + WK.z);
+          c00a += o[0 * 32 + lane]; c00b += o[1 * 32 + lane]; c10a += o[2 * 32 + lane]; c10b += o[3 * 32 + lane];
+          c11a += o[4 * 32 + lane]; c11b += o[5 * 32 + lane]; sq0 += o[6 * 32 + lane];  sq1 += o[7 * 32 + lane];
+        }
+      }
+      {
+        double* tb0 = reinterpret_cast<double*>(smem + SK.total + WK.bucket);
+        for (int e = tid; e < NB * BV; e += nt) {
+          double s = tb0[e];
+#pragma unroll
+          for (int w = 1; w < WPD; ++w) s += reinterpret_cast<const double*>(smem + SK.total + (size_t)w * WK.total + WK.bucket)[e];
+          tb0[e] = s;
+        }
+      }
     }
-    {
+    if (!CTA || warp == 0) {
+      rm_scatter<Q>(0, 0, lane, c00a, c00b, ypiv, s_acc);
+      if (TWO) {
+        rm_scatter<Q>(1, 0, lane, c10a, c10b, ypiv, s_acc);
+        rm_scatter<Q>(1, 1, lane, c11a, c11b, ypiv, s_acc);
+      }
       const double d2 = warp_sum((c < Q0 ? sq0 : 0.0) + (TWO ? sq1 : 0.0));
       const double y2 = warp_sum(c == 6 ? sq0 : 0.0);
       if (Q > 0 && lane < Q) s_acc[NA1PAD + 2 * Q + lane] = lane == 0 ? d2 : 0.0;
       if (lane == 0) s_acc[NA1PAD + 3 * Q + 1] = y2;
     }
-    __syncwarp();
+    if (CTA) __syncthreads(); else __syncwarp();
     // start refilling the ring for pass C while the solve runs (served by L2)
 #pragma unroll
-    for (int cc = 0; cc < NSTAGE - 1; ++cc) {
-      if (cc < nchunks) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), false, ring + cc * SB, lane);
+    for (int k = 0; k < NSTAGE - 1; ++k) {
+      const int cc = wq + k * WPD;
+      if (k < myn) rs_issue_chunk<Q>(p, a + 32 * cc, min(32, n - 32 * cc), false, ring + k * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
-    const int st = solve_fast_cta<Q, true>(p, L, wsm, n);
+    const int st = solve_fast_cta<Q, !CTA>(p, L, sbase, n);
     if (st != BMFM_ST_OK) {
       asm volatile("cp.async.wait_group 0;\n" ::: "memory");
       __syncwarp();
       if (st == REG_NEED_DENSE) {
-        if (lane == 0) p.status[t] = REG_NEED_DENSE;
+        if (tid == 0) p.status[t] = REG_NEED_DENSE;
       } else {
-        for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, nan);
-        for (int i = lane; i < n; i += 32) p.spec[a + i] = nan;
-        if (lane == 0) { p.r2[t] = nan; p.status[t] = st; }
+        for (int k = tid; k < K; k += nt) store_factor_ret(p, t, k, nan);
+        for (int i = tid; i < n; i += nt) p.spec[a + i] = nan;
+        if (tid == 0) { p.r2[t] = nan; p.status[t] = st; }
       }
       continue;
     }
-    for (int k = lane; k < K; k += 32) store_factor_ret(p, t, k, s_f[k]);
+    for (int k = tid; k < K; k += nt) store_factor_ret(p, t, k, s_f[k]);
     // pass C
     const double c0 = s_misc[1];
     double se = 0.0, see = 0.0;
-    for (int cc = 0; cc < nchunks; ++cc) {
-      const int cn = cc + NSTAGE - 1;
-      if (cn < nchunks) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), false, ring + (cn % NSTAGE) * SB, lane);
+    for (int k = 0; k < myn; ++k) {
+      const int cc = wq + k * WPD;
+      const int kn = k + NSTAGE - 1, cn = wq + kn * WPD;
+      if (kn < myn) rs_issue_chunk<Q>(p, a + 32 * cn, min(32, n - 32 * cn), false, ring + (kn % NSTAGE) * SB, lane);
       else asm volatile("cp.async.commit_group;\n" ::: "memory");
       asm volatile("cp.async.wait_group %0;\n" ::"n"(NSTAGE - 1) : "memory");
       __syncwarp();
-      unsigned char* stage = ring + (cc % NSTAGE) * SB;
+      unsigned char* stage = ring + (k % NSTAGE) * SB;
       const double* st_style = reinterpret_cast<const double*>(stage);
       const double* st_ret = st_style + 32 * Q + 32;
       const int* st_ind = reinterpret_cast<const int*>(st_ret + 32);
@@ -375,7 +440,16 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
     }
     se = warp_sum(se);
     see = warp_sum(see);
-    if (lane == 0) {
+    if (CTA) {
+      if (lane == 0) { s_red[2 * warp] = se; s_red[2 * warp + 1] = see; }
+      __syncthreads();
+      se = 0.0; see = 0.0;
+      if (tid == 0) {
+#pragma unroll
+        for (int w = 0; w < WPD; ++w) { se += s_red[2 * w]; see += s_red[2 * w + 1]; }
+      }
+    }
+    if (tid == 0) {
       const double dn = (double)n;
       const double me = se / dn;
       const double var_e = see / dn - me * me;
