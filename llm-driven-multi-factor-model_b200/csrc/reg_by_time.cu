@@ -54,6 +54,7 @@ struct RegParams {
   int n_peer;
   long long peer_row0;
   double* peer_fr[REG_MAX_PEERS];
+  int smma;       // per-industry sums by MMA against indicator columns (else shared-memory column sums)
 };
 
 __device__ __forceinline__ void store_factor_ret(const RegParams& p, int t, int k, double v) {
@@ -887,6 +888,13 @@ __global__ void __launch_bounds__(256) reg_dense_kernel(RegParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const RegSmem L = reg_smem_layout(p.tile_rows, p.P, Q, blockDim.x >> 5, true);
   const double* s_f = reinterpret_cast<const double*>(smem + L.fvec);
+  // one parallel look at the statuses of this CTA's dates (a serial walk costs a global-memory latency per date)
+  if (!p.all_dense) {
+    int any = 0;
+    for (int t = blockIdx.x + (int)threadIdx.x * (int)gridDim.x; t < p.T; t += (int)(blockDim.x * gridDim.x))
+      any |= p.status[t] == REG_NEED_DENSE;
+    if (!__syncthreads_or(any)) return;
+  }
   for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
     if (!p.all_dense && p.status[t] != REG_NEED_DENSE) continue;
     const long long a = p.date_off[t];
@@ -1190,7 +1198,7 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
 // ---- host side ---------------------------------------------------------------------------------
 template <int Q, int NSTAGE, int WPD>
 static int launch_reg_mma(bmfm_ctx* ctx, const RegParams& p) {
-  int warps = RM_WARPS;
+  int warps = WPD > 1 ? WPD : RM_WARPS;
   if (WPD == 1)
     if (const char* ev = getenv("BMFM_REG_WARPS")) warps = atoi(ev) >= 1 && atoi(ev) <= RM_WARPS ? atoi(ev) : warps;
   const int smem_s = rm_cta_bytes<Q, NSTAGE>(p.P, WPD, warps);
@@ -1226,19 +1234,23 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
   p.tile_rows = rows;
-  // Default: the FP64-MMA kernel, one warp per date for cross-sections up to 2048 rows (mode 3), one CTA per
-  // date above (mode 4).  BMFM_REG_MODE forces a kernel: 1 = CTA kernel with the date resident in shared
-  // memory, 2 = warp-per-date kernel with register accumulators (the two earlier designs, kept for comparison).
+  // Default: the FP64-MMA kernel with 1, 2 or 4 warps per date (modes 3, 5, 4): one warp per date is the
+  // best grain for the serial solve, more warps per date when the cross-section is long (per-date latency,
+  // L2 footprint of the dates in flight) or when there are too few dates to fill the SMs.  BMFM_REG_MODE
+  // forces a kernel: 1 = CTA kernel with the date resident in shared memory, 2 = warp-per-date kernel with
+  // register accumulators (the two earlier designs, kept for comparison).
   int mode = 0;
   if (const char* ev = getenv("BMFM_REG_MODE")) mode = atoi(ev);
-  if (mode < 1 || mode > 4) mode = (max_rows > 0 && max_rows <= 2048) ? 3 : 4;
+  if (mode < 1 || mode > 5) {
+    int wpd = (max_rows > 0 && max_rows <= 1024) ? 1 : 2;
+    const long long slots = (long long)ctx->sm_count * 12;      // warps the SMs hold with one warp per date
+    while (wpd < 4 && (long long)p.T * wpd * 2 <= slots) wpd *= 2;
+    mode = wpd == 1 ? 3 : (wpd == 2 ? 5 : 4);
+  }
   const bool use_stream = mode == 2;
-  if (!p.all_dense && (mode == 3 || mode == 4)) {
-    int ns = mode == 4 ? 2 : 3;
-    if (const char* ev = getenv("BMFM_REG_STAGES")) ns = atoi(ev);
-    const int wpd = mode == 4 ? RM_WARPS : 1;   // 3: one warp per date, 4: one CTA of RM_WARPS warps per date
-    const int rc = wpd > 1 ? (ns == 2 ? launch_reg_mma<Q, 2, RM_WARPS>(ctx, p) : launch_reg_mma<Q, 3, RM_WARPS>(ctx, p))
-                           : (ns == 2 ? launch_reg_mma<Q, 2, 1>(ctx, p) : launch_reg_mma<Q, 3, 1>(ctx, p));
+  if (!p.all_dense && mode >= 3) {
+    const int rc = mode == 3 ? launch_reg_mma<Q, 3, 1>(ctx, p)
+                 : mode == 5 ? launch_reg_mma<Q, 2, 2>(ctx, p) : launch_reg_mma<Q, 2, RM_WARPS>(ctx, p);
     if (rc != BMFM_OK) return rc;
   } else if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);
@@ -1317,6 +1329,8 @@ static int reg_by_time_impl(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per
   p.all_dense = exposure != nullptr;
   p.n_peer = n_peer;
   p.peer_row0 = peer_row0;
+  p.smma = 1;
+  if (const char* ev = getenv("BMFM_REG_SMMA")) p.smma = atoi(ev);
   for (int r = 0; r < REG_MAX_PEERS; ++r) p.peer_fr[r] = r < n_peer ? peer_bufs[r] : nullptr;
   switch (Q) {
 #define CASE(q) case q: return launch_reg<q>(ctx, p, max_rows_per_date);

@@ -52,7 +52,7 @@ __host__ __device__ inline RmWarpBlk rm_warp_blk(int P) {
   int u = solve > zst ? solve : zst;
   if (cf > u) u = cf;
   s.z = o;      o = align16(o + u);                     // z staging; later solve scratch (WPD 1) / fragment hand-over (WPD > 1)
-  s.cst = o;    o = align16(o + 16 + rm_zs(Q) * 8);     // {1.0, 0.0}, then a z row of zeros
+  s.cst = o;    o = align16(o + 16 + rm_zs(Q) * 8 + 32);     // {1.0, 0.0}, a z row of zeros, bucket of local id [8]
   s.ring = o;   o = align16(o + NSTAGE * rs_stage_bytes<Q>());
   s.total = o;
   return s;
@@ -76,7 +76,10 @@ __device__ __forceinline__ void dmma_884(double& c0, double& c1, double a, doubl
 }
 
 // what row m of left tile i / column n of right tile j stands for
-enum { RM_NONE = -1, RM_CAP = -2, RM_ONE = -3, RM_U = -4 };   // >= 0: style index
+enum { RM_NONE = -1, RM_CAP = -2, RM_ONE = -3, RM_U = -4, RM_W = -5, RM_WY = -6 };   // >= 0: style index
+// 7 <= Q <= 10: the second left tile has room for w and w y, and the per-industry sums come from two more
+// 8x8 products with the chunk's industry indicator columns (see the kernel)
+__host__ __device__ constexpr bool rm_has_s(int Q) { return Q >= 7 && Q <= 10; }
 template <int Q>
 __device__ __forceinline__ int rm_left(int i, int m) {
   constexpr int Q0 = Q < 6 ? Q : 6, Q1 = Q - Q0;
@@ -90,6 +93,8 @@ __device__ __forceinline__ int rm_left(int i, int m) {
   if (m < Q1) return 6 + m;
   if (m == Q1) return RM_CAP;
   if (m == Q1 + 1) return RM_ONE;
+  if (rm_has_s(Q) && m == Q1 + 2) return RM_W;
+  if (rm_has_s(Q) && m == Q1 + 3) return RM_WY;
   return RM_NONE;
 }
 template <int Q>
@@ -114,7 +119,7 @@ __device__ __forceinline__ void rm_scatter(int i, int j, int lane, double c0, do
   double* D1 = CD + Q;
   const int m = lane >> 2, n0 = 2 * (lane & 3);
   const int lt = rm_left<Q>(i, m);
-  if (lt == RM_NONE) return;
+  if (lt == RM_NONE || lt == RM_W || lt == RM_WY) return;
 #pragma unroll
   for (int e = 0; e < 2; ++e) {
     const int rt = rm_right<Q>(j, n0 + e);
@@ -133,7 +138,7 @@ __device__ __forceinline__ void rm_scatter(int i, int j, int lane, double c0, do
 
 
 template <int Q, int NSTAGE, int WPD>
-__global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) {
+__global__ void __launch_bounds__(RM_WARPS * 32, (NSTAGE >= 3 && WPD == 1) ? 3 : 4) reg_mma_kernel(RegParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr bool CTA = WPD > 1;            // WPD warps (one CTA) share a date; otherwise one warp per date
   constexpr int NA1PAD = na1pad_of(Q);
@@ -168,6 +173,8 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
   if (lane == 0) { s_cst[0] = 1.0; s_cst[1] = 0.0; }
   if (lane < ZS) s_cst[2 + lane] = 0.0;
   const double* s_zero = s_cst + 2;
+  int* s_runb = reinterpret_cast<int*>(s_cst + 2 + ZS);
+  constexpr bool HAS_S = rm_has_s(Q);
 
   // fragment sources of this lane (row k = lane & 3 of a k-step, element c = lane >> 2 of a tile):
   // byte offset relative to the stage (raw inputs) or an absolute shared address (z staging, constants)
@@ -192,8 +199,16 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
     else                    { a0_a = zero_sa; a0_s = 0; }
     if (l1 >= 0)            { a1_a = z_sa + (3 + l1 + kq * ZS) * 8; a1_s = 4 * ZS * 8; }
     else if (l1 == RM_CAP)  { a1_a = z_sa + (2 + kq * ZS) * 8;      a1_s = 4 * ZS * 8; }
+    else if (l1 == RM_W)    { a1_a = z_sa + (0 + kq * ZS) * 8;      a1_s = 4 * ZS * 8; }
+    else if (l1 == RM_WY)   { a1_a = z_sa + (1 + kq * ZS) * 8;      a1_s = 4 * ZS * 8; }
     else if (l1 == RM_ONE)  { a1_a = one_sa;  a1_s = 0; }
     else                    { a1_a = zero_sa; a1_s = 0; }
+  }
+  int val0 = -1, val1 = -1;
+  {
+    const int l0 = rm_left<Q>(0, c), l1 = rm_left<Q>(1, c);
+    val0 = l0 >= 0 ? 3 + l0 : -1;
+    val1 = l1 >= 0 ? 3 + l1 : (l1 == RM_CAP ? 2 : (l1 == RM_W ? 0 : (l1 == RM_WY ? 1 : -1)));
   }
   __syncwarp();
 
@@ -261,11 +276,13 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
           zr[0] = w;
           zr[1] = w * y;
           zr[2] = cap;
+          const double u = y - ypiv;
+          sq1 = fma(u, u, sq1);
           if (Q > 0) {
             double d[QQ];
             load_row_styles<Q>(st_style, lane, s_piv, d);
 #pragma unroll
-            for (int q = 0; q < Q; ++q) zr[3 + q] = w * d[q];
+            for (int q = 0; q < Q; ++q) { zr[3 + q] = w * d[q]; sq0 = fma(d[q], d[q], sq0); }
           }
         } else {
 #pragma unroll
@@ -276,7 +293,18 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
         }
       }
       __syncwarp();
-      // gram: 8 k-steps of 4 rows
+      // industries of the chunk: groups of equal industry (match.any), their number G and a local id per row
+      const int myb = lane < m ? bucket_of(st_ind[lane], P) : 64 + lane;
+      const unsigned peers = __match_any_sync(0xffffffffu, myb);
+      const int myleader = __ffs(peers) - 1;
+      const unsigned leaders = __ballot_sync(0xffffffffu, lane < m && myleader == lane);
+      const int G = __popc(leaders);
+      const bool use_s = HAS_S && p.smma && G <= 8;                // warp-uniform
+      const int lid = lane < m ? __popc(leaders & ((1u << myleader) - 1u)) : 99;
+      if (use_s && lane < m && myleader == lane) s_runb[lid] = myb;
+      // gram: 8 k-steps of 4 rows; with use_s two more products against the indicator columns of the chunk's
+      // (at most 8) industries give the per-industry sums of w d, cap, w, w y
+      double cs0a = 0.0, cs0b = 0.0, cs1a = 0.0, cs1b = 0.0;
       {
         const unsigned st_sa = (unsigned)__cvta_generic_to_shared(stage);
         const unsigned pb0 = b0_st ? st_sa + b0_a : b0_a;
@@ -286,26 +314,42 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
           const double b0 = lds_f64(pb0 + ks * b0_s) - sub0;
           const double a0 = lds_f64(a0_a + ks * a0_s);
           dmma_884(c00a, c00b, a0, b0);
-          sq0 = fma(b0, b0, sq0);
           if (TWO) {
             const double b1 = lds_f64(pb1 + ks * b1_s) - sub1;
             const double a1 = lds_f64(a1_a + ks * a1_s);
             dmma_884(c10a, c10b, a1, b0);
             dmma_884(c11a, c11b, a1, b1);
-            sq1 = fma(b1, b1, sq1);
+            if (HAS_S) {
+              const int rl = __shfl_sync(0xffffffffu, lid, 4 * ks + kq);
+              if (use_s) {
+                const double sb = rl == c ? 1.0 : 0.0;
+                dmma_884(cs0a, cs0b, a0, sb);
+                dmma_884(cs1a, cs1b, a1, sb);
+              }
+            }
           }
         }
       }
+      if (use_s) {
+        __syncwarp();
+        const int n0 = 2 * kq;
+        const int bn0 = s_runb[n0 & 7], bn1 = s_runb[(n0 + 1) & 7];
+        if (val0 >= 0) {
+          if (n0 < G) s_bucket[bn0 * BV + val0] += cs0a;
+          if (n0 + 1 < G) s_bucket[bn1 * BV + val0] += cs0b;
+        }
+        if (val1 >= 0) {
+          if (n0 < G) s_bucket[bn0 * BV + val1] += cs1a;
+          if (n0 + 1 < G) s_bucket[bn1 * BV + val1] += cs1b;
+        }
+      } else
       // per-industry sums of the chunk's z rows, no atomics (the table is this warp's own)
       {
-        const int myb = lane < m ? bucket_of(st_ind[lane], P) : 64 + lane;
         const int prevb = __shfl_up_sync(0xffffffffu, myb, 1);
         const unsigned runstart = __ballot_sync(0xffffffffu, lane < m && (lane == 0 || myb != prevb));
         const int nruns = __popc(runstart);
         bool by_runs = nruns <= 3;
-        unsigned peers = 0u;
         if (!by_runs) {
-          peers = __match_any_sync(0xffffffffu, myb);
           const int maxg = __reduce_max_sync(0xffffffffu, __popc(peers));
           by_runs = 15 * nruns + 70 <= 26 * maxg + 39;       // estimated instruction counts of the two ways
         }
@@ -382,8 +426,8 @@ __global__ void __launch_bounds__(RM_WARPS * 32, 4) reg_mma_kernel(RegParams p) 
         rm_scatter<Q>(1, 0, lane, c10a, c10b, ypiv, s_acc);
         rm_scatter<Q>(1, 1, lane, c11a, c11b, ypiv, s_acc);
       }
-      const double d2 = warp_sum((c < Q0 ? sq0 : 0.0) + (TWO ? sq1 : 0.0));
-      const double y2 = warp_sum(c == 6 ? sq0 : 0.0);
+      const double d2 = warp_sum(sq0);    // sum over rows and styles of d^2 (lane = row partial sums)
+      const double y2 = warp_sum(sq1);    // sum u^2
       if (Q > 0 && lane < Q) s_acc[NA1PAD + 2 * Q + lane] = lane == 0 ? d2 : 0.0;
       if (lane == 0) s_acc[NA1PAD + 3 * Q + 1] = y2;
     }

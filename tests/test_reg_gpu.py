@@ -30,7 +30,7 @@ def _case(reg, case):
 
 @pytest.mark.parametrize("case", ["small", "csi", "nostyle_scale"])
 @pytest.mark.parametrize("grouped", [True, False])
-@pytest.mark.parametrize("mode", ["1", "2", "3", "4"])     # 1: CTA-per-date kernel, 2: warp-per-date streaming kernel, 3: warp-per-date FP64-MMA kernel
+@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5"])     # 1: CTA-per-date kernel, 2: warp-per-date streaming kernel, 3: warp-per-date FP64-MMA kernel
 def test_golden_reference_outputs(ops, reg_golden, case, grouped, mode, monkeypatch):
     monkeypatch.setenv("BMFM_REG_MODE", mode)
     g = _case(reg_golden, case)
@@ -70,7 +70,7 @@ def test_golden_exposure(ops, reg_golden, case):
     (3, 70, 63, 12, 0.0, (0, 0)),         # compiled limits; N < K -> pinv path
     (2, 5000, 31, 10, 0.02, (-2, 2)),     # full A-share cross-section (config C3): multi-tile path
 ])
-@pytest.mark.parametrize("mode", ["0", "1", "2", "3", "4"])   # auto / CTA-per-date / warp-per-date streaming / warp-per-date FP64-MMA
+@pytest.mark.parametrize("mode", ["0", "1", "2", "3", "4", "5"])   # auto / CTA-per-date / warp-per-date streaming / warp-per-date FP64-MMA
 def test_oracle_parity(ops, T, N, P, Q, ragged, scale, mode, monkeypatch):
     monkeypatch.setenv("BMFM_REG_MODE", mode)
     from bmfm.synth import make_panel
