@@ -108,4 +108,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 __device__ __forceinline__ void st_stream(double* p, double v) {
   asm volatile("st.global.cs.f64 [%0], %1;\n" ::"l"(p), "d"(v) : "memory");
 }
+__device__ __forceinline__ void st_stream2(double* p, double v0, double v1) {   // p 16-byte aligned
+  asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};\n" ::"l"(p), "d"(v0), "d"(v1) : "memory");
+}
 #endif

@@ -26,7 +26,10 @@
 namespace bmfm {
 
 constexpr int NW_MAX_Q = 4;
-constexpr int NW_EMIT_SPLIT = 4;   // CTAs per chunk in the emit kernel (the K*K elements are split)
+constexpr int NW_LOCAL_THREADS = 512;   // chunk-total kernel: one state element per thread
+constexpr int NW_EMIT_THREADS = 128;    // emit kernel: one 2 x 2 block of the covariance per thread
+constexpr int NW_TARGET_CHUNKS = 72;    // chunks per series aimed at (state traffic ~ nchunks * 44 KB at K = 42)
+constexpr int NW_EMIT_SMEM = 56 * 1024; // shared memory the emit kernel may use (several CTAs per SM)
 
 struct NwParams {
   int T, K, q, C, nchunks;
@@ -42,39 +45,48 @@ struct NwParams {
 __host__ __device__ inline int nw_nstate(int K, int q) { return (1 + q) * (K * K + 1) + (1 + 2 * q) * K; }
 // layout of one state record:
 //   mats[(1+q)][K][K] | vecs[(1+2q)][K] (S, R_1..R_q, P_1..P_q) | scal[(1+q)] (Z, Z_1..Z_q)
-__device__ __forceinline__ double nw_vec_term(const double* fr, int K, int q, int v, int r, int k) {
-  // the value row r adds to vector v
-  if (v == 0) return fr[(size_t)r * K + k];
-  if (v <= q) return r >= v ? fr[(size_t)r * K + k] : 0.0;
-  const int i = v - q;
-  return r - i >= 0 ? fr[(size_t)(r - i) * K + k] : 0.0;
+__host__ __device__ inline size_t nw_emit_smem(int C, int K, int q) {
+  return ((size_t)(C + q) * K + 2 * (size_t)C * K + 2 * (size_t)C) * sizeof(double);
+}
+// chunk length: about NW_TARGET_CHUNKS chunks, at least 8 rows, short enough for the emit kernel's shared memory
+__host__ inline int nw_pick_chunk(int T, int K, int q) {
+  int C = (T + NW_TARGET_CHUNKS - 1) / NW_TARGET_CHUNKS;
+  if (C < 8) C = 8;
+  while (C > 1 && nw_emit_smem(C, K, q) > (size_t)NW_EMIT_SMEM) --C;
+  return C;
 }
 
-// kernel 1: chunk totals from a zero start.  The chunk's rows (plus q rows of history for the lagged
-// products) are staged in shared memory once.
-__global__ void __launch_bounds__(256) nw_chunk_local(NwParams p) {
+// stage rows r0-q .. r1-1 of the series (zeros before row 0) in shared memory
+__device__ __forceinline__ void nw_stage_rows(const NwParams& p, double* sx, int r0, int len) {
+  const int K = p.K, q = p.q;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int j = warp; j < len + q; j += nwarps) {
+    const int r = r0 - q + j;
+    for (int k = lane; k < K; k += 32) sx[j * K + k] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
+  }
+}
+
+// kernel 1: chunk totals from a zero start, one state element per thread (grid: chunks x element blocks)
+__global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K], rows r0-q .. r1-1, zeros before row 0
+  double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K]
   const int c = blockIdx.x, K = p.K, q = p.q;
   const int r0 = c * p.C, r1 = min(p.T, r0 + p.C), len = r1 - r0;
   double* st = p.state + (size_t)c * nw_nstate(K, q);
-  for (int e = threadIdx.x; e < (len + q) * K; e += blockDim.x) {
-    const int j = e / K, k = e - j * K;
-    const int r = r0 - q + j;
-    sx[e] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
-  }
+  nw_stage_rows(p, sx, r0, len);
   __syncthreads();
   const double lam = p.lam;
-  const int nm = (1 + q) * K * K;
-  for (int e = threadIdx.x; e < nm; e += blockDim.x) {
+  const int nm = (1 + q) * K * K, nv = (1 + 2 * q) * K;
+  const int e = blockIdx.y * blockDim.x + threadIdx.x;
+  if (e < nm) {
     const int i = e / (K * K), ab = e - i * K * K, a = ab / K, b = ab - a * K;
+    const double* xa = sx + (q - i) * K + a;   // row j - i (zero rows before row 0)
+    const double* xb = sx + q * K + b;         // row j
     double s = 0.0;
-    for (int j = 0; j < len; ++j) s = fma(s, lam, sx[(q + j - i) * K + a] * sx[(q + j) * K + b]);   // zero rows before row 0
+    for (int j = 0; j < len; ++j) s = fma(s, lam, xa[j * K] * xb[j * K]);
     st[e] = s;
-  }
-  const int nv = (1 + 2 * q) * K;
-  for (int e = threadIdx.x; e < nv; e += blockDim.x) {
-    const int v = e / K, k = e - v * K;
+  } else if (e < nm + nv) {
+    const int v = (e - nm) / K, k = (e - nm) - v * K;
     double s = 0.0;
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
@@ -84,16 +96,15 @@ __global__ void __launch_bounds__(256) nw_chunk_local(NwParams p) {
       else add = sx[(q + j - (v - q)) * K + k];
       s = fma(s, lam, add);
     }
-    st[nm + e] = s;
-  }
-  if (threadIdx.x <= q) {
-    const int i = threadIdx.x;
+    st[e] = s;
+  } else if (e < nm + nv + 1 + q) {
+    const int i = e - nm - nv;
     double s = 0.0;
     for (int r = r0; r < r1; ++r) {
       s *= lam;
       if (r >= i) s += 1.0;
     }
-    st[nm + nv + i] = s;
+    st[e] = s;
   }
 }
 
@@ -120,107 +131,194 @@ __global__ void nw_chunk_scan(NwParams p) {
   }
 }
 
-// kernel 3: replay the chunk from its start state and emit V for every date in it
-__global__ void __launch_bounds__(256) nw_emit(NwParams p) {
+// kernel 3: replay the chunk from its start state and emit V for every date in it.  Grid: chunks x element
+// blocks, one covariance element (a, b) per thread.  With m = S/Z, w_i = 1 - i/(1+q) and
+//   U_k = sum_i w_i (P_i,k + R_i,k) / Z,   cc = 1 - 2 sum_i w_i Z_i / Z
+// the combination of utils.py:46-48 is
+//   V_ab = [A0_ab + sum_i w_i (B_i,ab + B_i,ba)] / Z - m_a m_b cc - m_b U_a - m_a U_b,
+// so the per-date vectors m, U and scalars 1/Z, cc are prepared once per CTA and the element loop is a few
+// FMAs per date.
+template <int QL>   // QL = q, the number of lags (compile-time so that the lag loops carry no predicates)
+__global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int c = p.c_first + blockIdx.x, K = p.K, q = p.q, C = p.C;
+  constexpr int q = QL;
+  constexpr int QN = QL > 0 ? QL : 1;
+  const int c = p.c_first + blockIdx.x, K = p.K, C = p.C;
   const int r0 = c * C, r1 = min(p.T, r0 + C), len = r1 - r0;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int nm = (1 + q) * K * K;
   const double* st = p.state + (size_t)c * nw_nstate(K, q);
-  const int NV = 1 + 2 * q, nv = NV * K;
   double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K]  rows r0-q .. r1-1 (zeros before row 0)
-  double* sv = sx + (C + q) * K;                       // [C][NV][K]  vectors after row r0+j
-  double* sz = sv + C * nv;                            // [C][(1+q)]
+  double* sm = sx + (C + q) * K;                       // [C][K]  EW mean after row r0+j
+  double* su = sm + C * K;                             // [C][K]  U
+  double* siz = su + C * K;                            // [C]     1/Z
+  double* scc = siz + C;                               // [C]     cc
   const double lam = p.lam;
-  for (int e = tid; e < (len + q) * K; e += nt) {
-    const int j = e / K, k = e - j * K;
-    const int r = r0 - q + j;
-    sx[e] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
-  }
+  nw_stage_rows(p, sx, r0, len);
   __syncthreads();
-  for (int e = tid; e < nv; e += nt) {
-    const int v = e / K, k = e - v * K;
-    double s = st[nm + e];
+  for (int k = tid; k < K; k += nt) {
+    double S = st[nm + k];
+    double R[QN], Pv[QN], Z[QL + 1];
+#pragma unroll
+    for (int i = 0; i < QL; ++i) {
+      R[i] = st[nm + (1 + i) * K + k];
+      Pv[i] = st[nm + (1 + q + i) * K + k];
+    }
+#pragma unroll
+    for (int i = 0; i <= QL; ++i) Z[i] = st[nm + (1 + 2 * q) * K + i];
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
-      double add;
-      if (v == 0) add = sx[(q + j) * K + k];
-      else if (v <= q) add = r >= v ? sx[(q + j) * K + k] : 0.0;
-      else add = sx[(q + j - (v - q)) * K + k];      // zero-filled before row 0
-      s = fma(s, lam, add);
-      sv[(size_t)j * nv + e] = s;
-    }
-  }
-  if (tid <= q) {
-    const int i = tid;
-    double s = st[nm + nv + i];
-    for (int j = 0; j < len; ++j) {
-      const int r = r0 + j;
-      s *= lam;
-      if (r >= i) s += 1.0;
-      sz[j * (1 + q) + i] = s;
+      const double x = sx[(q + j) * K + k];
+      S = fma(S, lam, x);
+      Z[0] = fma(Z[0], lam, 1.0);
+      const double iz = 1.0 / Z[0];
+      double u = 0.0, zs = 0.0;
+#pragma unroll
+      for (int i = 0; i < QL; ++i) {
+        const int lag = i + 1;
+        R[i] = fma(R[i], lam, r >= lag ? x : 0.0);
+        Pv[i] = fma(Pv[i], lam, sx[(q + j - lag) * K + k]);      // zero-filled before row 0
+        Z[lag] = fma(Z[lag], lam, r >= lag ? 1.0 : 0.0);
+        const double w = 1.0 - (double)lag / (1.0 + q);
+        u = fma(w, Pv[i] + R[i], u);
+        zs = fma(w, Z[lag], zs);
+      }
+      sm[j * K + k] = S * iz;
+      su[j * K + k] = u * iz;
+      if (k == 0) { siz[j] = iz; scc[j] = 1.0 - 2.0 * zs * iz; }
     }
   }
   __syncthreads();
+  // one 2 x 2 block of V per thread: rows a, a+1 and columns b, b+1 share their loads
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  for (int e = blockIdx.y * nt + tid; e < K * K; e += gridDim.y * nt) {
-    const int a = e / K, b = e - a * K;
-    double a0 = st[e];
-    double bab[NW_MAX_Q], bba[NW_MAX_Q];
+  const int KB = (K + 1) >> 1;
+  const int e = blockIdx.y * nt + tid;
+  if (e < KB * KB) {
+    const int a = 2 * (e / KB), b = 2 * (e - (e / KB) * KB);
+    const int a1 = a + 1 < K ? a + 1 : a, b1 = b + 1 < K ? b + 1 : b;     // clamped partner (stores are guarded)
+    const bool aok = a + 1 < K, bok = b + 1 < K;
+    const bool keven = (K & 1) == 0 && (reinterpret_cast<uintptr_t>(p.cov) & 15) == 0;
+    const int ia[2] = {a, a1}, ib[2] = {b, b1};
+    double a0[2][2], bab[QN][2][2], bba[QN][2][2], wl[QN];
 #pragma unroll
-    for (int i = 0; i < NW_MAX_Q; ++i) {
-      bab[i] = i < q ? st[(1 + i) * K * K + a * K + b] : 0.0;
-      bba[i] = i < q ? st[(1 + i) * K * K + b * K + a] : 0.0;
-    }
-    for (int j = 0; j < len; ++j) {
-      const int r = r0 + j;       // date index; window length L = r + 1
+    for (int x = 0; x < 2; ++x)
+#pragma unroll
+      for (int y = 0; y < 2; ++y) {
+        a0[x][y] = st[ia[x] * K + ib[y]];
+#pragma unroll
+        for (int i = 0; i < QL; ++i) {
+          bab[i][x][y] = st[(1 + i) * K * K + ia[x] * K + ib[y]];
+          bba[i][x][y] = st[(1 + i) * K * K + ib[y] * K + ia[x]];
+        }
+      }
+#pragma unroll
+    for (int i = 0; i < QL; ++i) wl[i] = 1.0 - (double)(i + 1) / (1.0 + q);
+    const int jlo = max(0, p.t0 - r0), jhi = min(len, p.t1 - r0);   // dates of this chunk that are emitted
+    const int jnan = min(jhi, max(q, K) - r0);                      // dates with L = r + 1 <= max(q, K): NaN
+    const long long kk = (long long)K * K;
+    double* dst = p.cov + (((long long)(r0 - p.t0) * K + a) * K + b);   // date r0 (dereferenced for emitted dates only)
+    for (int j = 0; j < jhi; ++j) {
       const double* xr = sx + (q + j) * K;
-      const double xa = xr[a], xb = xr[b];
-      a0 = fma(a0, lam, xa * xb);
+      const double va[2] = {xr[a], xr[a1]}, vb[2] = {xr[b], xr[b1]};
+      double acc[2][2];
 #pragma unroll
-      for (int i = 0; i < NW_MAX_Q; ++i) {
-        if (i < q) {
-          bab[i] *= lam;
-          bba[i] *= lam;
-          if (r - (i + 1) >= 0) {
-            const double* xl = sx + (q + j - (i + 1)) * K;
-            bab[i] = fma(xl[a], xb, bab[i]);
-            bba[i] = fma(xl[b], xa, bba[i]);
+      for (int x = 0; x < 2; ++x)
+#pragma unroll
+        for (int y = 0; y < 2; ++y) {
+          a0[x][y] = fma(a0[x][y], lam, va[x] * vb[y]);
+          acc[x][y] = a0[x][y];
+        }
+#pragma unroll
+      for (int i = 0; i < QL; ++i) {
+        const double* xl = xr - (i + 1) * K;                         // zero rows before row 0
+        const double la[2] = {xl[a], xl[a1]}, lb[2] = {xl[b], xl[b1]};
+#pragma unroll
+        for (int x = 0; x < 2; ++x)
+#pragma unroll
+          for (int y = 0; y < 2; ++y) {
+            bab[i][x][y] = fma(bab[i][x][y], lam, la[x] * vb[y]);
+            bba[i][x][y] = fma(bba[i][x][y], lam, lb[y] * va[x]);
+            acc[x][y] = fma(wl[i], bab[i][x][y] + bba[i][x][y], acc[x][y]);
+          }
+      }
+      if (j >= jlo) {
+        double o00 = nan, o01 = nan, o10 = nan, o11 = nan;
+        if (j >= jnan) {
+          const double* mj = sm + j * K;
+          const double* uj = su + j * K;
+          const double iz = siz[j], cc = scc[j];
+          const double ma[2] = {mj[a], mj[a1]}, mb[2] = {mj[b], mj[b1]};
+          const double ua[2] = {uj[a], uj[a1]}, ub[2] = {uj[b], uj[b1]};
+          o00 = acc[0][0] * iz - ma[0] * mb[0] * cc - mb[0] * ua[0] - ma[0] * ub[0];
+          o01 = acc[0][1] * iz - ma[0] * mb[1] * cc - mb[1] * ua[0] - ma[0] * ub[1];
+          o10 = acc[1][0] * iz - ma[1] * mb[0] * cc - mb[0] * ua[1] - ma[1] * ub[0];
+          o11 = acc[1][1] * iz - ma[1] * mb[1] * cc - mb[1] * ua[1] - ma[1] * ub[1];
+        }
+        if (keven) {                       // b even and K even: 16-byte aligned pairs
+          st_stream2(dst, o00, o01);
+          st_stream2(dst + K, o10, o11);
+        } else {
+          st_stream(dst, o00);
+          if (bok) st_stream(dst + 1, o01);
+          if (aok) {
+            st_stream(dst + K, o10);
+            if (bok) st_stream(dst + K + 1, o11);
           }
         }
       }
-      const int L = r + 1;
-      double out;
-      if (L <= q || L <= K) {
-        out = nan;
-      } else {
-        const double* vec = sv + (size_t)j * nv;
-        const double Z = sz[j * (1 + q)];
-        const double iz = 1.0 / Z;
-        const double ma = vec[a] * iz, mb = vec[b] * iz;
-        out = a0 * iz - ma * mb;
-#pragma unroll
-        for (int i = 0; i < NW_MAX_Q; ++i) {
-          if (i < q) {
-            const int lag = i + 1;
-            const double Pa = vec[(q + lag) * K + a], Pb = vec[(q + lag) * K + b];
-            const double Ra = vec[lag * K + a], Rb = vec[lag * K + b];
-            const double Zi = sz[j * (1 + q) + lag];
-            const double gab = (bab[i] - Pa * mb - ma * Rb + ma * mb * Zi) * iz;
-            const double gba = (bba[i] - Pb * ma - mb * Ra + ma * mb * Zi) * iz;
-            out = fma(1.0 - (double)lag / (1.0 + q), gab + gba, out);
-          }
-        }
-      }
-      if (r >= p.t0 && r < p.t1) st_stream(p.cov + ((size_t)(r - p.t0) * K + a) * K + b, out);
+      dst += kk;
     }
   }
   if (blockIdx.y == 0)
-  for (int j = tid; j < len; j += nt) {
-    const int r = r0 + j, L = r + 1;
-    if (r >= p.t0 && r < p.t1) p.status[r - p.t0] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
+    for (int j = tid; j < len; j += nt) {
+      const int r = r0 + j, L = r + 1;
+      if (r >= p.t0 && r < p.t1) p.status[r - p.t0] = (L <= q || L <= K) ? BMFM_ST_SHORT : BMFM_ST_OK;
+    }
+}
+
+template <int QL>
+static int nw_launch_emit(bmfm_ctx* ctx, const NwParams& p, int nchunks_emit, size_t smem_emit) {
+  if (smem_emit > 48 * 1024)
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit<QL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_emit));
+  nw_emit<QL><<<dim3(nchunks_emit, (((p.K + 1) / 2) * ((p.K + 1) / 2) + NW_EMIT_THREADS - 1) / NW_EMIT_THREADS), NW_EMIT_THREADS, smem_emit, ctx->stream>>>(p);
+  return BMFM_OK;
+}
+
+// the three launches for a filled-in NwParams (C, nchunks, state and the date range set by the caller)
+static int nw_run(bmfm_ctx* ctx, NwParams& p) {
+  const int K = p.K, q = p.q;
+  p.c_first = p.t0 / p.C;
+  const int c_last = p.t1 > p.t0 ? (p.t1 - 1) / p.C : p.c_first - 1;
+  p.c_used = c_last + 1;   // later chunks feed nothing this call emits
+  const size_t smem_local = (size_t)(p.C + q) * K * sizeof(double);
+  const size_t smem_emit = nw_emit_smem(p.C, K, q);
+  if (smem_local > (size_t)ctx->max_smem_optin || smem_emit > (size_t)ctx->max_smem_optin) {
+    snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
+    return BMFM_E_UNSUPPORTED;
   }
+  if (c_last < p.c_first) return BMFM_OK;
+  const int ns = nw_nstate(K, q);
+  if (smem_local > 48 * 1024)
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
+  nw_chunk_local<<<dim3(p.c_used, (ns + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
+  ctx->launches++;
+  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
+  ctx->launches++;
+  {
+    const int ne = c_last - p.c_first + 1;
+    int rc = BMFM_E_UNSUPPORTED;
+    switch (q) {
+      case 0: rc = nw_launch_emit<0>(ctx, p, ne, smem_emit); break;
+      case 1: rc = nw_launch_emit<1>(ctx, p, ne, smem_emit); break;
+      case 2: rc = nw_launch_emit<2>(ctx, p, ne, smem_emit); break;
+      case 3: rc = nw_launch_emit<3>(ctx, p, ne, smem_emit); break;
+      case 4: rc = nw_launch_emit<4>(ctx, p, ne, smem_emit); break;
+    }
+    if (rc) return rc;
+  }
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
 }
 
 }  // namespace bmfm
@@ -230,8 +328,7 @@ using namespace bmfm;
 // Scratch (device) bytes bmfm_newey_west_by_time needs for given sizes.
 extern "C" size_t bmfm_newey_west_scratch_bytes(int T, int K, int q) {
   if (T <= 0) return 0;
-  int C = (T + 295) / 296;
-  if (C < 8) C = 8;
+  const int C = nw_pick_chunk(T, K, q);
   const int nchunks = (T + C - 1) / C;
   return (size_t)nchunks * nw_nstate(K, q) * sizeof(double);
 }
@@ -240,43 +337,14 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
                      int32_t* status, double* scratch, int t0, int t1) {
   NwParams p;
   p.T = T; p.K = K; p.q = q;
-  p.C = (T + 295) / 296;
-  if (p.C < 8) p.C = 8;
+  p.C = nw_pick_chunk(T, K, q);
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
   if (t0 < 0) t0 = 0;
   if (t1 > T) t1 = T;
   p.t0 = t0; p.t1 = t1;
-  p.c_first = t0 / p.C;
-  const int c_last = t1 > t0 ? (t1 - 1) / p.C : p.c_first - 1;
-  p.c_used = c_last + 1;   // later chunks feed nothing this call emits
-  {
-    const size_t smem_local = (size_t)(p.C + q) * K * 8;
-    if (smem_local > (size_t)ctx->max_smem_optin) {
-      snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
-      return BMFM_E_UNSUPPORTED;
-    }
-    if (smem_local > 48 * 1024)
-      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-    nw_chunk_local<<<p.c_used, 256, smem_local, ctx->stream>>>(p);
-  }
-  ctx->launches++;
-  const int ns = nw_nstate(K, q);
-  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
-  ctx->launches++;
-  const size_t smem = ((size_t)(p.C + q) * K + (size_t)p.C * (1 + 2 * q) * K + (size_t)p.C * (1 + q)) * 8;
-  if (smem > (size_t)ctx->max_smem_optin) {
-    snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
-    return BMFM_E_UNSUPPORTED;
-  }
-  BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  if (c_last >= p.c_first) {
-    nw_emit<<<dim3(c_last - p.c_first + 1, NW_EMIT_SPLIT), 256, smem, ctx->stream>>>(p);
-    ctx->launches++;
-  }
-  BMFM_CUDA(ctx, cudaGetLastError());
-  return BMFM_OK;
+  return nw_run(ctx, p);
 }
 
 // dates [t0, t1) only: cov [(t1-t0)*K*K], status [t1-t0].  The decayed moments of ALL earlier dates are
@@ -338,8 +406,7 @@ static int nw_static_chunk(int T, int K, int q) {
   const size_t ns = (size_t)nw_nstate(K, q);
   const size_t max_chunks = NW_STATIC_DOUBLES / ns;
   if (max_chunks == 0) return 0;
-  int C = (T + 295) / 296;
-  if (C < 8) C = 8;
+  int C = nw_pick_chunk(T, K, q);
   const size_t need = ((size_t)T + max_chunks - 1) / max_chunks;   // smallest C with ceil(T/C) <= max_chunks
   if ((size_t)C < need) C = (int)need;
   return C;
@@ -373,7 +440,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   NwParams p;
   p.T = T; p.K = K; p.q = q;
   p.C = nw_static_chunk(T, K, q);
-  const size_t smem = p.C > 0 ? ((size_t)(p.C + q) * K + (size_t)p.C * (1 + 2 * q) * K + (size_t)p.C * (1 + q)) * 8 : 0;
+  const size_t smem = p.C > 0 ? nw_emit_smem(p.C, K, q) : 0;
   if (p.C == 0 || smem > (size_t)ctx->max_smem_optin) {
     snprintf(ctx->err, sizeof(ctx->err),
              "newey_west noalloc: T=%d K=%d q=%d needs more than the fixed %zu-byte scratch; "
@@ -389,25 +456,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   }
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;
-  p.t0 = 0; p.t1 = T; p.c_first = 0; p.c_used = p.nchunks;
+  p.t0 = 0; p.t1 = T;
   p.state = nw_static_ptr[ctx->device];
-  {
-    const size_t smem_local = (size_t)(p.C + q) * K * 8;
-    if (smem_local > (size_t)ctx->max_smem_optin) {
-      snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
-      return BMFM_E_UNSUPPORTED;
-    }
-    if (smem_local > 48 * 1024)
-      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-    nw_chunk_local<<<p.c_used, 256, smem_local, ctx->stream>>>(p);
-  }
-  ctx->launches++;
-  const int ns = nw_nstate(K, q);
-  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
-  ctx->launches++;
-  BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  nw_emit<<<dim3(p.nchunks, NW_EMIT_SPLIT), 256, smem, ctx->stream>>>(p);
-  ctx->launches++;
-  BMFM_CUDA(ctx, cudaGetLastError());
-  return BMFM_OK;
+  return nw_run(ctx, p);
 }
