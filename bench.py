@@ -289,7 +289,8 @@ def run_gpu(args):
     # multi-GPU: the gathered factor returns and vol-regime terms live in symmetric (peer-mapped) memory and
     # are filled by the producing kernels themselves over NVLink (fused all-gather); NCCL is the fallback
     fused = world > 1 and os.environ.get("BENCH_FUSED", "1") == "1"
-    h_fr = h_wbv = None
+    nw_shard = os.environ.get("BENCH_NW_SHARD", "1") == "1"
+    h_fr = h_wbv = h_tot = None
     if fused:
         try:
             import torch.distributed._symmetric_memory as symm
@@ -300,6 +301,12 @@ def run_gpu(args):
             fr_peers = [int(x) for x in h_fr.buffer_ptrs]
             wb_peers = [int(x) for x in h_wbv.buffer_ptrs]
             wv_peers = [int(x) + T_all * 8 for x in h_wbv.buffer_ptrs]
+            # sharded Newey-West: one end-of-range state record per rank instead of every rank reducing all
+            # earlier dates
+            nw_ns = ctx.newey_west_state_doubles(K, NW_Q)
+            tot_sym = symm.empty((world, nw_ns), dtype=torch.float64, device=dev)
+            h_tot = symm.rendezvous(tot_sym, group=dist.group.WORLD)
+            tot_peers = [int(x) for x in h_tot.buffer_ptrs]
         except Exception as e:      # noqa: BLE001
             log(f"symmetric memory unavailable ({e!r}); using NCCL all-gathers")
             fused = False
@@ -336,8 +343,7 @@ def run_gpu(args):
         regress()
         e[1].record()
         gather_fr()
-        # the recurrence reads the whole gathered series (T_all*K doubles) and emits this rank's dates only
-        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
+        newey_west()
         e[2].record()
         vol_regime()
         e[3].record()
@@ -355,10 +361,21 @@ def run_gpu(args):
         elif world > 1 and not nocoll:
             dist.all_gather_into_tensor(fr_all, fr)
 
+    def newey_west():
+        if fused and nw_shard:
+            # every rank reduces its own dates only; the ranks exchange one 44 KB state record each
+            ctx.newey_west_shard_totals(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, rank, tot_peers)
+            h_tot.barrier()
+            ctx.newey_west_shard_emit(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, rank,
+                                      [(r + 1) * T for r in range(rank)], tot_sym, nw, nw_st)
+        else:
+            # the recurrence reads the whole gathered series (T_all*K doubles) and emits this rank's dates only
+            ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
+
     def step_body():      # the same step without timing events (graph capture)
         regress()
         gather_fr()
-        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
+        newey_west()
         vol_regime()
 
     def vol_regime():
@@ -463,6 +480,17 @@ def run_gpu(args):
         dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
         gather_check = "peer-memory gather == NCCL all-gather (bit-identical on every rank)" if ok_t.item() else "MISMATCH"
         del lamb_fused
+        if nw_shard:
+            # the sharded Newey-West against the pass that reduces the whole gathered series on every rank
+            nw_ref = torch.empty_like(nw)
+            st_ref = torch.empty_like(nw_st)
+            ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw_ref, st_ref)
+            okm = st_ref == 0
+            dmax = (nw[okm] - nw_ref[okm]).abs().max() / nw_ref[okm].abs().max()
+            same = torch.equal(st_ref, nw_st) and bool(dmax.item() < 1e-12)
+            ok_t = torch.tensor([1 if same else 0], device=dev)
+            dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+            gather_check += "; sharded Newey-West == whole-series pass (<1e-12 rel)" if ok_t.item() else "; sharded Newey-West MISMATCH"
 
     # ---- end to end: pinned host buffers -> device -> results back in pinned host buffers ----
     h2d = sum(v.numel() * v.element_size() for v in host.values())

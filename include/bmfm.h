@@ -125,6 +125,27 @@ size_t bmfm_newey_west_scratch_bytes(int T, int K, int q);
 int bmfm_newey_west_by_time_range(bmfm_ctx* ctx, int T, int K, int q, double tao,
                                   const double* factor_ret, int t0, int t1, double* cov,
                                   int32_t* status);
+/* Date-sharded form whose cost does not grow with the number of ranks (no counterpart in the
+ * reference, which is single-process; results = rows [t0, t1) of bmfm_newey_west_by_time).
+ * Every rank reduces only its own dates [t0, t1) of the gathered series from a zero state
+ * (rows t0-q .. t0-1 are read for the lagged products) and the ranks exchange one state record
+ * each, bmfm_newey_west_state_doubles(K, q) doubles (44 KB at K = 42, q = 2):
+ *   _shard_totals  stores this rank's end-of-range state into slot `rank` of every peer's totals
+ *                  buffer: peer_totals = HOST array of n_peer (<= 8) device pointers to
+ *                  [n_rank * state_doubles], mapped for peer access (e.g. symmetric memory);
+ *   (the caller runs a cross-rank barrier)
+ *   _shard_emit    builds the carry-in from `totals` (this rank's own copy) and range_ends
+ *                  (HOST int64 [rank]: one past the last date of ranks 0 .. rank-1) and writes
+ *                  cov [(t1-t0) * K * K], status [t1-t0].
+ * Both calls use the same context; its workspace keeps the chunk states in between. */
+size_t bmfm_newey_west_state_doubles(int K, int q);
+int bmfm_newey_west_shard_totals(bmfm_ctx* ctx, int T_total, int K, int q, double tao,
+                                 const double* factor_ret_all, int t0, int t1, int rank, int n_peer,
+                                 double* const* peer_totals);
+int bmfm_newey_west_shard_emit(bmfm_ctx* ctx, int T_total, int K, int q, double tao,
+                               const double* factor_ret_all, int t0, int t1, int rank,
+                               const int64_t* range_ends, const double* totals, double* cov,
+                               int32_t* status);
 
 /*
  * No counterpart in the reference: an addition for hosts that must not allocate device memory

@@ -38,6 +38,9 @@ _SIGNATURES = {
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
     "bmfm_newey_west_by_time_range": ([_P, _I, _I, _I, _D, _P, _I, _I, _P, _P], _I),
+    "bmfm_newey_west_state_doubles": ([_I, _I], C.c_size_t),
+    "bmfm_newey_west_shard_totals": ([_P, _I, _I, _I, _D, _P, _I, _I, _I, _I, _P], _I),
+    "bmfm_newey_west_shard_emit": ([_P, _I, _I, _I, _D, _P, _I, _I, _I, _P, _P, _P, _P], _I),
     "bmfm_vol_regime_bias": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_vol_regime_scale": ([_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P], _I),
     "bmfm_newey_west_by_time_noalloc": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
@@ -177,6 +180,23 @@ class Context:
     def newey_west_by_time_range(self, T, K, q, tao, fr, t0, t1, cov, status):
         self.check(self._L.bmfm_newey_west_by_time_range(self._h, T, K, q, float(tao), ptr(fr), t0, t1, ptr(cov),
                                                          ptr(status)))
+
+    def newey_west_state_doubles(self, K, q):
+        return int(self._L.bmfm_newey_west_state_doubles(K, q))
+
+    def newey_west_shard_totals(self, T_total, K, q, tao, fr_all, t0, t1, rank, peer_totals):
+        """Sharded Newey-West, step 1: reduce this rank's dates and store its end-of-range state into slot
+        `rank` of every buffer in `peer_totals` (device addresses of [n_rank, state_doubles] buffers)."""
+        arr = (C.c_void_p * len(peer_totals))(*[int(x) for x in peer_totals])
+        self.check(self._L.bmfm_newey_west_shard_totals(self._h, T_total, K, q, float(tao), ptr(fr_all), t0, t1,
+                                                        rank, len(peer_totals), arr))
+
+    def newey_west_shard_emit(self, T_total, K, q, tao, fr_all, t0, t1, rank, range_ends, totals, cov, status):
+        """Step 2 (after a cross-rank barrier): covariances of dates [t0, t1) with the earlier ranks' totals
+        as carry-in.  `range_ends[r]` = one past the last date of rank r (host ints, ranks before this one)."""
+        ends = (C.c_int64 * max(1, len(range_ends)))(*[int(x) for x in range_ends])
+        self.check(self._L.bmfm_newey_west_shard_emit(self._h, T_total, K, q, float(tao), ptr(fr_all), t0, t1, rank,
+                                                      ends, ptr(totals), ptr(cov), ptr(status)))
 
     def vol_regime_bias(self, T_total, t0, n, K, tao, fr_block, cov_block, status_block, wb, wv):
         self.check(self._L.bmfm_vol_regime_bias(self._h, T_total, t0, n, K, float(tao), ptr(fr_block),

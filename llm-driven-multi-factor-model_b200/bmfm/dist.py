@@ -59,11 +59,18 @@ class SymmetricGather:
     a device-side barrier replaces the all-gather.  Needs torch symmetric memory on an NVLink/NVSwitch box;
     RiskPipeline falls back to NCCL all-gathers when it is not given one of these."""
 
-    def __init__(self, T_total, K, device, group=None):
+    def __init__(self, T_total, K, device, group=None, nw_state_doubles=0):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
         g = group or dist.group.WORLD
+        self.world = dist.get_world_size(g)
+        # sharded Newey-West: one end-of-range state record per rank (bmfm_newey_west_shard_totals / _emit)
+        self.nw_totals = self.h_tot = None
+        if nw_state_doubles:
+            self.nw_totals = symm.empty((self.world, int(nw_state_doubles)), dtype=torch.float64, device=device)
+            self.h_tot = symm.rendezvous(self.nw_totals, group=g)
+            self.tot_peers = [int(x) for x in self.h_tot.buffer_ptrs]
         self.fr_all = symm.empty((T_total, K), dtype=torch.float64, device=device)
         self.h_fr = symm.rendezvous(self.fr_all, group=g)
         self.wbv = symm.empty((2, T_total), dtype=torch.float64, device=device)
@@ -131,6 +138,7 @@ class RiskPipeline:
         t0 = int(sum(counts[: self.rank]))
         n = int(counts[self.rank])
         if symmetric is not None:
+            self._range_ends = [int(sum(counts[: r + 1])) for r in range(len(counts))]
             return self._run_fused(symmetric, T_total, t0, n, P, Q, max_rows, off, cap, ret, ind, style, q, tao_nw,
                                    tao_vr, eigen)
         fr, spec, r2, status = self.b.reg(n, P, Q, max_rows, off, cap, ret, ind, style)
@@ -160,7 +168,16 @@ class RiskPipeline:
         status = torch.empty(n, dtype=torch.int32, device=dev)
         ctx.reg_by_time_gather(n, P, Q, max_rows, off, cap, ret, ind, style, fr, spec, r2, status, sg.fr_peers, t0)
         sg.h_fr.barrier()
-        nw, nw_st = self.b.newey_west_range(sg.fr_all, t0, t0 + n, q, tao_nw)
+        if sg.nw_totals is not None:
+            # every rank reduces only its own dates; one state record per rank crosses NVLink
+            nw = torch.empty((n, K, K), dtype=torch.float64, device=dev)
+            nw_st = torch.empty(n, dtype=torch.int32, device=dev)
+            ctx.newey_west_shard_totals(T_total, K, q, tao_nw, sg.fr_all, t0, t0 + n, self.rank, sg.tot_peers)
+            sg.h_tot.barrier()
+            ctx.newey_west_shard_emit(T_total, K, q, tao_nw, sg.fr_all, t0, t0 + n, self.rank,
+                                      self._range_ends[: self.rank], sg.nw_totals, nw, nw_st)
+        else:
+            nw, nw_st = self.b.newey_west_range(sg.fr_all, t0, t0 + n, q, tao_nw)
         cov, cov_st = nw, nw_st
         if eigen is not None:
             cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])

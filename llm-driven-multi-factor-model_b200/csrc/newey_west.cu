@@ -35,6 +35,13 @@ struct NwParams {
   int T, K, q, C, nchunks;
   int t0, t1, c_first;   // emit only dates [t0, t1) (chunks from c_first on), written at row t - t0
   int c_used;            // chunks 0 .. c_used-1 are needed (those up to the last emitted one)
+  int row0;              // global row of chunk 0's first row (0 unless the series is sharded by dates)
+  // date-sharded form: the chunks start at this rank's first date from a ZERO state; the decayed state of all
+  // earlier dates (`carry`, nstate doubles, as of row row0 - 1) is added when a chunk's start state is read,
+  // and the zero-start state after the rank's last row goes to slot `rank` of every peer's totals buffer
+  const double* carry;
+  int n_peer, rank;
+  double* peer_totals[8];
   double lam;
   const double* fr;   // [T][K]
   double* cov;        // [T][K][K]
@@ -71,7 +78,7 @@ __global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K]
   const int c = blockIdx.x, K = p.K, q = p.q;
-  const int r0 = c * p.C, r1 = min(p.T, r0 + p.C), len = r1 - r0;
+  const int r0 = p.row0 + c * p.C, r1 = min(p.T, r0 + p.C), len = r1 - r0;
   double* st = p.state + (size_t)c * nw_nstate(K, q);
   nw_stage_rows(p, sx, r0, len);
   __syncthreads();
@@ -125,10 +132,26 @@ __global__ void nw_chunk_scan(NwParams p) {
     for (int j = 0; j < 32; ++j) {
       if (c0 + j < p.c_used) {
         p.state[(size_t)(c0 + j) * ns + e] = run;
-        run = fma(run, fC, loc[j]);
+        // the last chunk may be shorter than C: its total already carries the right decay, the running
+        // state before it decays by lam^len
+        const bool last = c0 + j == p.nchunks - 1;
+        run = fma(run, last ? pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C)) : fC, loc[j]);
       }
     }
   }
+  for (int r = 0; r < p.n_peer; ++r) p.peer_totals[r][(size_t)p.rank * ns + e] = run;   // state after the last row
+}
+
+// carry-in of a date-sharded rank: decayed sum of the earlier ranks' zero-start totals,
+//   carry = sum_{r' < rank} lam^(t0 - end_{r'}) total_{r'}      (end_{r'} = one past rank r' 's last row)
+struct NwEnds { long long v[8]; };
+__global__ void nw_carry_kernel(int ns, int rank, double lam, const double* totals, NwEnds ends, long long t0,
+                                double* carry) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= ns) return;
+  double s = 0.0;
+  for (int r = 0; r < rank; ++r) s = fma(pow(lam, (double)(t0 - ends.v[r])), totals[(size_t)r * ns + e], s);
+  carry[e] = s;
 }
 
 // kernel 3: replay the chunk from its start state and emit V for every date in it.  Grid: chunks x element
@@ -144,7 +167,7 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
   constexpr int q = QL;
   constexpr int QN = QL > 0 ? QL : 1;
   const int c = p.c_first + blockIdx.x, K = p.K, C = p.C;
-  const int r0 = c * C, r1 = min(p.T, r0 + C), len = r1 - r0;
+  const int r0 = p.row0 + c * C, r1 = min(p.T, r0 + C), len = r1 - r0;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int nm = (1 + q) * K * K;
   const double* st = p.state + (size_t)c * nw_nstate(K, q);
@@ -154,18 +177,21 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
   double* siz = su + C * K;                            // [C]     1/Z
   double* scc = siz + C;                               // [C]     cc
   const double lam = p.lam;
+  const double* cr = p.carry;                                           // sharded form: decayed state of earlier ranks
+  const double fcar = cr ? pow(lam, (double)(r0 - p.row0)) : 0.0;
+#define NW_LD(idx) (cr ? fma(fcar, cr[idx], st[idx]) : st[idx])
   nw_stage_rows(p, sx, r0, len);
   __syncthreads();
   for (int k = tid; k < K; k += nt) {
-    double S = st[nm + k];
+    double S = NW_LD(nm + k);
     double R[QN], Pv[QN], Z[QL + 1];
 #pragma unroll
     for (int i = 0; i < QL; ++i) {
-      R[i] = st[nm + (1 + i) * K + k];
-      Pv[i] = st[nm + (1 + q + i) * K + k];
+      R[i] = NW_LD(nm + (1 + i) * K + k);
+      Pv[i] = NW_LD(nm + (1 + q + i) * K + k);
     }
 #pragma unroll
-    for (int i = 0; i <= QL; ++i) Z[i] = st[nm + (1 + 2 * q) * K + i];
+    for (int i = 0; i <= QL; ++i) Z[i] = NW_LD(nm + (1 + 2 * q) * K + i);
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
       const double x = sx[(q + j) * K + k];
@@ -204,11 +230,11 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
     for (int x = 0; x < 2; ++x)
 #pragma unroll
       for (int y = 0; y < 2; ++y) {
-        a0[x][y] = st[ia[x] * K + ib[y]];
+        a0[x][y] = NW_LD(ia[x] * K + ib[y]);
 #pragma unroll
         for (int i = 0; i < QL; ++i) {
-          bab[i][x][y] = st[(1 + i) * K * K + ia[x] * K + ib[y]];
-          bba[i][x][y] = st[(1 + i) * K * K + ib[y] * K + ia[x]];
+          bab[i][x][y] = NW_LD((1 + i) * K * K + ia[x] * K + ib[y]);
+          bba[i][x][y] = NW_LD((1 + i) * K * K + ib[y] * K + ia[x]);
         }
       }
 #pragma unroll
@@ -276,6 +302,8 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
     }
 }
 
+#undef NW_LD
+
 template <int QL>
 static int nw_launch_emit(bmfm_ctx* ctx, const NwParams& p, int nchunks_emit, size_t smem_emit) {
   if (smem_emit > 48 * 1024)
@@ -284,41 +312,57 @@ static int nw_launch_emit(bmfm_ctx* ctx, const NwParams& p, int nchunks_emit, si
   return BMFM_OK;
 }
 
-// the three launches for a filled-in NwParams (C, nchunks, state and the date range set by the caller)
-static int nw_run(bmfm_ctx* ctx, NwParams& p) {
+// chunk totals + scan for a filled-in NwParams (C, nchunks, state, row0 and the date range set by the caller)
+static int nw_run_totals(bmfm_ctx* ctx, NwParams& p) {
   const int K = p.K, q = p.q;
-  p.c_first = p.t0 / p.C;
-  const int c_last = p.t1 > p.t0 ? (p.t1 - 1) / p.C : p.c_first - 1;
+  p.c_first = (p.t0 - p.row0) / p.C;
+  const int c_last = p.t1 > p.t0 ? (p.t1 - 1 - p.row0) / p.C : p.c_first - 1;
   p.c_used = c_last + 1;   // later chunks feed nothing this call emits
   const size_t smem_local = (size_t)(p.C + q) * K * sizeof(double);
-  const size_t smem_emit = nw_emit_smem(p.C, K, q);
-  if (smem_local > (size_t)ctx->max_smem_optin || smem_emit > (size_t)ctx->max_smem_optin) {
+  if (smem_local > (size_t)ctx->max_smem_optin || nw_emit_smem(p.C, K, q) > (size_t)ctx->max_smem_optin) {
     snprintf(ctx->err, sizeof(ctx->err), "Newey-West chunk does not fit shared memory (K=%d q=%d)", K, q);
     return BMFM_E_UNSUPPORTED;
   }
-  if (c_last < p.c_first) return BMFM_OK;
+  if (c_last < p.c_first && p.n_peer == 0) return BMFM_OK;
   const int ns = nw_nstate(K, q);
-  if (smem_local > 48 * 1024)
-    BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-  nw_chunk_local<<<dim3(p.c_used, (ns + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
-  ctx->launches++;
-  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
-  ctx->launches++;
-  {
-    const int ne = c_last - p.c_first + 1;
-    int rc = BMFM_E_UNSUPPORTED;
-    switch (q) {
-      case 0: rc = nw_launch_emit<0>(ctx, p, ne, smem_emit); break;
-      case 1: rc = nw_launch_emit<1>(ctx, p, ne, smem_emit); break;
-      case 2: rc = nw_launch_emit<2>(ctx, p, ne, smem_emit); break;
-      case 3: rc = nw_launch_emit<3>(ctx, p, ne, smem_emit); break;
-      case 4: rc = nw_launch_emit<4>(ctx, p, ne, smem_emit); break;
-    }
-    if (rc) return rc;
+  if (p.c_used > 0) {
+    if (smem_local > 48 * 1024)
+      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
+    nw_chunk_local<<<dim3(p.c_used, (ns + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
+    ctx->launches++;
   }
+  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
+}
+
+// emit for the same NwParams (after nw_run_totals)
+static int nw_run_emit(bmfm_ctx* ctx, NwParams& p) {
+  const int q = p.q;
+  p.c_first = (p.t0 - p.row0) / p.C;
+  const int c_last = p.t1 > p.t0 ? (p.t1 - 1 - p.row0) / p.C : p.c_first - 1;
+  p.c_used = c_last + 1;
+  if (c_last < p.c_first) return BMFM_OK;
+  const size_t smem_emit = nw_emit_smem(p.C, p.K, q);
+  const int ne = c_last - p.c_first + 1;
+  int rc = BMFM_E_UNSUPPORTED;
+  switch (q) {
+    case 0: rc = nw_launch_emit<0>(ctx, p, ne, smem_emit); break;
+    case 1: rc = nw_launch_emit<1>(ctx, p, ne, smem_emit); break;
+    case 2: rc = nw_launch_emit<2>(ctx, p, ne, smem_emit); break;
+    case 3: rc = nw_launch_emit<3>(ctx, p, ne, smem_emit); break;
+    case 4: rc = nw_launch_emit<4>(ctx, p, ne, smem_emit); break;
+  }
+  if (rc) return rc;
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+static int nw_run(bmfm_ctx* ctx, NwParams& p) {
+  const int rc = nw_run_totals(ctx, p);
+  return rc ? rc : nw_run_emit(ctx, p);
 }
 
 }  // namespace bmfm
@@ -341,6 +385,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
+  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0;
   if (t0 < 0) t0 = 0;
   if (t1 > T) t1 = T;
   p.t0 = t0; p.t1 = t1;
@@ -457,6 +502,89 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;
   p.t0 = 0; p.t1 = T;
+  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0;
   p.state = nw_static_ptr[ctx->device];
   return nw_run(ctx, p);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Date-sharded Newey-West (one rank per block of dates) without the growing prefix
+// ---------------------------------------------------------------------------------------------
+// bmfm_newey_west_by_time_range lets a rank emit its own dates of a gathered series, but every rank still
+// reduces ALL earlier dates, so that part grows with the number of ranks.  Here every rank reduces only its
+// own dates from a zero state and the ranks exchange what the recurrences need — one state record
+// (nstate = (1+q)(K^2+1) + (1+2q)K doubles, 44 KB at K = 42, q = 2) per rank:
+//   1. bmfm_newey_west_shard_totals: chunk totals + scan of this rank's dates [t0, t1) of the gathered
+//      series (rows t0-q .. t0-1 are read for the lagged products); the state after its last row is stored
+//      into slot `rank` of every peer's totals buffer (peer_totals: HOST array of n_peer device pointers to
+//      [n_rank * nstate] doubles, peer-mapped, e.g. symmetric memory).
+//   2. the caller runs a cross-rank barrier;
+//   3. bmfm_newey_west_shard_emit: the decayed sum of the earlier ranks' totals (this rank's own copy
+//      `totals`, range_ends[r] = one past rank r's last date, HOST array) is this rank's carry-in; the
+//      covariances of [t0, t1) follow exactly as in the single-GPU pass.
+// Both calls must use the same context (the chunk states stay in its workspace in between).
+static int nw_shard_params(bmfm_ctx* ctx, NwParams& p, int T_total, int K, int q, double tao, const double* fr_all,
+                           int t0, int t1, double** carry_out) {
+  if (q > NW_MAX_Q) {
+    snprintf(ctx->err, sizeof(ctx->err), "q=%d exceeds compiled limit %d", q, NW_MAX_Q);
+    return BMFM_E_UNSUPPORTED;
+  }
+  const int n = t1 - t0;
+  p.T = t1; p.K = K; p.q = q;
+  p.C = nw_pick_chunk(n > 0 ? n : 1, K, q);
+  p.nchunks = (n + p.C - 1) / p.C;
+  p.lam = pow(0.5, 1.0 / tao);
+  p.fr = fr_all; p.cov = nullptr; p.status = nullptr;
+  p.row0 = t0; p.t0 = t0; p.t1 = t1;
+  p.carry = nullptr; p.n_peer = 0; p.rank = 0;
+  const size_t ns = (size_t)nw_nstate(K, q);
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int rc = bmfm_ws_reserve(ctx, ((size_t)(p.nchunks > 0 ? p.nchunks : 1) * ns + ns) * sizeof(double));
+  if (rc) return rc;
+  p.state = static_cast<double*>(ctx->ws);
+  *carry_out = p.state + (size_t)(p.nchunks > 0 ? p.nchunks : 1) * ns;
+  (void)T_total;
+  return BMFM_OK;
+}
+
+extern "C" size_t bmfm_newey_west_state_doubles(int K, int q) { return (size_t)nw_nstate(K, q); }
+
+extern "C" int bmfm_newey_west_shard_totals(bmfm_ctx* ctx, int T_total, int K, int q, double tao,
+                                            const double* factor_ret_all, int t0, int t1, int rank, int n_peer,
+                                            double* const* peer_totals) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && K > 0 && q >= 0 && tao > 0 && t0 >= 0 && t1 >= t0 && t1 <= T_total, "bad sizes");
+  BMFM_ARG(ctx, factor_ret_all && n_peer >= 1 && n_peer <= 8 && peer_totals && rank >= 0, "bad peer list");
+  NwParams p;
+  double* carry = nullptr;
+  int rc = nw_shard_params(ctx, p, T_total, K, q, tao, factor_ret_all, t0, t1, &carry);
+  if (rc) return rc;
+  p.n_peer = n_peer; p.rank = rank;
+  for (int r = 0; r < 8; ++r) p.peer_totals[r] = r < n_peer ? peer_totals[r] : nullptr;
+  return nw_run_totals(ctx, p);
+}
+
+extern "C" int bmfm_newey_west_shard_emit(bmfm_ctx* ctx, int T_total, int K, int q, double tao,
+                                          const double* factor_ret_all, int t0, int t1, int rank,
+                                          const int64_t* range_ends, const double* totals, double* cov,
+                                          int32_t* status) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && K > 0 && q >= 0 && tao > 0 && t0 >= 0 && t1 >= t0 && t1 <= T_total, "bad sizes");
+  BMFM_ARG(ctx, factor_ret_all && rank >= 0 && rank < 8 && (rank == 0 || (range_ends && totals)), "bad rank data");
+  BMFM_ARG(ctx, t1 == t0 || (cov && status), "NULL pointer");
+  if (t1 == t0) return BMFM_OK;
+  NwParams p;
+  double* carry = nullptr;
+  int rc = nw_shard_params(ctx, p, T_total, K, q, tao, factor_ret_all, t0, t1, &carry);
+  if (rc) return rc;
+  p.cov = cov; p.status = status;
+  if (rank > 0) {
+    NwEnds ends;
+    for (int r = 0; r < 8; ++r) ends.v[r] = r < rank ? (long long)range_ends[r] : 0;
+    const int ns = nw_nstate(K, q);
+    nw_carry_kernel<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(ns, rank, p.lam, totals, ends, (long long)t0, carry);
+    ctx->launches++;
+    p.carry = carry;
+  }
+  return nw_run_emit(ctx, p);
 }

@@ -199,3 +199,38 @@ def test_date_sharded_entry_points_match_full(ops):
     assert relerr(res["factor_ret"].cpu().numpy(), wfr) < TOL
     assert relerr(res["lamb_all"].cpu().numpy(), np.array(lamb)) < TOL
     assert relerr(res["vr"].cpu().numpy()[-1], vr[-1]) < TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,K,q,tao,world", [(500, 17, 2, 60.0, 3), (2000, 42, 2, 252.0, 8), (90, 6, 1, 20.0, 4),
+                                             (300, 12, 0, 40.0, 2)])
+def test_sharded_newey_west_exchanges_totals(ops, T, K, q, tao, world):
+    """bmfm_newey_west_shard_totals / _emit: every 'rank' reduces only its own dates and the carry-in comes
+    from the other ranks' end-of-range states.  Emulated on one GPU with one context per rank and a single
+    shared totals buffer; must agree with the un-sharded pass (different chunking, so not bit-identical)."""
+    import torch
+    from bmfm import _cabi, dist as bd
+    from bmfm.synth import make_factor_returns
+    fr = make_factor_returns(T, K, seed=3 + T)
+    cov_full, st_full = ops.newey_west_by_time(fr, q, tao)
+    d_fr = torch.from_numpy(fr).cuda()
+    ctxs = [_cabi.Context(0) for _ in range(world)]
+    ns = ctxs[0].newey_west_state_doubles(K, q)
+    totals = torch.full((world, ns), float("nan"), dtype=torch.float64, device="cuda")
+    ranges = [bd.shard_range(T, r, world) for r in range(world)]
+    for r, (lo, hi) in enumerate(ranges):
+        ctxs[r].newey_west_shard_totals(T, K, q, tao, d_fr, lo, hi, r, [totals.data_ptr()])
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(totals).all())
+    ends = [hi for (_, hi) in ranges]
+    scale = np.nanmax(np.abs(cov_full))
+    for r, (lo, hi) in enumerate(ranges):
+        cov = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
+        st = torch.empty(hi - lo, dtype=torch.int32, device="cuda")
+        ctxs[r].newey_west_shard_emit(T, K, q, tao, d_fr, lo, hi, r, ends[:r], totals, cov, st)
+        torch.cuda.synchronize()
+        assert np.array_equal(st.cpu().numpy(), st_full[lo:hi])
+        ok = st_full[lo:hi] == 0
+        got = cov.cpu().numpy()
+        assert np.isnan(got[~ok]).all()
+        assert np.max(np.abs(got[ok] - cov_full[lo:hi][ok])) < 1e-12 * scale
