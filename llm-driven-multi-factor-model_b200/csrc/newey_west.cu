@@ -123,6 +123,8 @@ __global__ void nw_chunk_scan(NwParams p) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= ns) return;
   const double fC = pow(p.lam, (double)p.C);
+  // the last chunk may be shorter than C: the running state before it decays by lam^len
+  const double fLast = pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C));
   double run = 0.0;
   for (int c0 = 0; c0 < p.c_used; c0 += 32) {
     double loc[32];
@@ -132,10 +134,7 @@ __global__ void nw_chunk_scan(NwParams p) {
     for (int j = 0; j < 32; ++j) {
       if (c0 + j < p.c_used) {
         p.state[(size_t)(c0 + j) * ns + e] = run;
-        // the last chunk may be shorter than C: its total already carries the right decay, the running
-        // state before it decays by lam^len
-        const bool last = c0 + j == p.nchunks - 1;
-        run = fma(run, last ? pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C)) : fC, loc[j]);
+        run = fma(run, c0 + j == p.nchunks - 1 ? fLast : fC, loc[j]);
       }
     }
   }

@@ -58,26 +58,46 @@ __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const
   }
 }
 
-// single CTA inclusive scan of (wb, wv) -> lamb
+// single CTA inclusive scan of (wb, wv) -> lamb: each thread owns a contiguous run of dates (its loads are
+// independent, issued eight at a time), the 1024 run totals are scanned with warp shuffles
 __global__ void __launch_bounds__(1024) vr_scan_kernel(int T, const double* wb, const double* wv, double* lamb) {
-  __shared__ double s_b[1024], s_v[1024];
-  const int tid = threadIdx.x, nt = blockDim.x;
+  __shared__ double s_b[32], s_v[32];
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
   const int per = (T + nt - 1) / nt;
   const int lo = min(T, tid * per), hi = min(T, lo + per);
   double pb = 0.0, pv = 0.0;
-  for (int t = lo; t < hi; ++t) { pb += wb[t]; pv += wv[t]; }
-  s_b[tid] = pb;
-  s_v[tid] = pv;
-  __syncthreads();
-  for (int off = 1; off < nt; off <<= 1) {
-    double ab = 0.0, av = 0.0;
-    if (tid >= off) { ab = s_b[tid - off]; av = s_v[tid - off]; }
-    __syncthreads();
-    s_b[tid] += ab;
-    s_v[tid] += av;
-    __syncthreads();
+  for (int t = lo; t < hi; t += 8) {
+    double xb[8], xv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      xb[j] = t + j < hi ? wb[t + j] : 0.0;
+      xv[j] = t + j < hi ? wv[t + j] : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { pb += xb[j]; pv += xv[j]; }
   }
-  double rb = s_b[tid] - pb, rv = s_v[tid] - pv;   // exclusive prefix of this thread's range
+  // inclusive scan of the per-thread totals: inside each warp, then over the 32 warp totals
+  double ib = pb, iv = pv;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const double ab = __shfl_up_sync(0xffffffffu, ib, off), av = __shfl_up_sync(0xffffffffu, iv, off);
+    if (lane >= off) { ib += ab; iv += av; }
+  }
+  if (lane == 31) { s_b[warp] = ib; s_v[warp] = iv; }
+  __syncthreads();
+  if (warp == 0) {
+    double wbt = lane < (nt >> 5) ? s_b[lane] : 0.0, wvt = lane < (nt >> 5) ? s_v[lane] : 0.0;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const double ab = __shfl_up_sync(0xffffffffu, wbt, off), av = __shfl_up_sync(0xffffffffu, wvt, off);
+      if (lane >= off) { wbt += ab; wvt += av; }
+    }
+    s_b[lane] = wbt;
+    s_v[lane] = wvt;
+  }
+  __syncthreads();
+  double rb = (warp > 0 ? s_b[warp - 1] : 0.0) + (ib - pb);   // exclusive prefix of this thread's run
+  double rv = (warp > 0 ? s_v[warp - 1] : 0.0) + (iv - pv);
   for (int t = lo; t < hi; ++t) {
     rb += wb[t];
     rv += wv[t];
@@ -85,15 +105,25 @@ __global__ void __launch_bounds__(1024) vr_scan_kernel(int T, const double* wb, 
   }
 }
 
-__global__ void vr_scale_kernel(int T, int KK, const double* cov, const int* cov_status, const double* lamb,
-                                double* out) {   // lamb already offset to this block of dates
-  const size_t total = (size_t)T * KK;
+// out = cov * lamb_t^2: one CTA per date (no per-element index division), 16-byte accesses when K*K is even
+__global__ void __launch_bounds__(256) vr_scale_kernel(int T, int KK, const double* cov, const int* cov_status,
+                                                       const double* lamb, double* out) {   // lamb offset to this block
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-    const int t = (int)(e / KK);
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
     const bool have = cov_status == nullptr || cov_status[t] == BMFM_ST_OK || cov_status[t] == BMFM_ST_PINV;
-    const double l = lamb[t];
-    st_stream(out + e, have ? cov[e] * (l * l) : nan);
+    const double l = lamb[t], l2 = l * l;
+    const double* src = cov + (size_t)t * KK;
+    double* dst = out + (size_t)t * KK;
+    if ((KK & 1) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+      const double2* s2 = reinterpret_cast<const double2*>(src);
+      for (int e = threadIdx.x; e < (KK >> 1); e += blockDim.x) {
+        double2 v = make_double2(nan, nan);
+        if (have) { v = __ldcs(s2 + e); v.x *= l2; v.y *= l2; }
+        st_stream2(dst + 2 * e, v.x, v.y);
+      }
+    } else {
+      for (int e = threadIdx.x; e < KK; e += blockDim.x) st_stream(dst + e, have ? __ldcs(src + e) * l2 : nan);
+    }
   }
 }
 
@@ -120,11 +150,7 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
   vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T, wb, wv, lamb);
   ctx->launches++;
   if (out_cov) {
-    const size_t total = (size_t)T * K * K;
-    int grid = (int)((total + 255) / 256);
-    const int cap = ctx->sm_count * 16;
-    if (grid > cap) grid = cap;
-    vr_scale_kernel<<<grid, 256, 0, ctx->stream>>>(T, K * K, cov, cov_status, lamb, out_cov);
+    vr_scale_kernel<<<T, 256, 0, ctx->stream>>>(T, K * K, cov, cov_status, lamb, out_cov);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());
@@ -187,11 +213,7 @@ extern "C" int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, 
   vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T_total, wb_all, wv_all, lamb_all);
   ctx->launches++;
   if (out_cov_block && n > 0) {
-    const size_t total = (size_t)n * K * K;
-    int grid = (int)((total + 255) / 256);
-    const int cap = ctx->sm_count * 16;
-    if (grid > cap) grid = cap;
-    vr_scale_kernel<<<grid, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_all + t0, out_cov_block);
+    vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_all + t0, out_cov_block);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());
