@@ -21,6 +21,7 @@
 // chunk from its true start state and streams out K x K matrices, one coalesced row-major
 // write per element.  Scratch: nchunks * ((1+q)(K^2+1) + (1+2q)K) doubles.
 #include <math.h>
+#include <stdlib.h>
 #include "bmfm_common.cuh"
 
 namespace bmfm {
@@ -57,7 +58,9 @@ __host__ __device__ inline size_t nw_emit_smem(int C, int K, int q) {
 }
 // chunk length: about NW_TARGET_CHUNKS chunks, at least 8 rows, short enough for the emit kernel's shared memory
 __host__ inline int nw_pick_chunk(int T, int K, int q) {
-  int C = (T + NW_TARGET_CHUNKS - 1) / NW_TARGET_CHUNKS;
+  int target = NW_TARGET_CHUNKS;
+  if (const char* ev = getenv("BMFM_NW_CHUNKS")) target = atoi(ev) > 0 ? atoi(ev) : target;   // tuning knob
+  int C = (T + target - 1) / target;
   if (C < 8) C = 8;
   while (C > 1 && nw_emit_smem(C, K, q) > (size_t)NW_EMIT_SMEM) --C;
   return C;
@@ -115,30 +118,59 @@ __global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
   }
 }
 
-// kernel 2: exclusive scan over chunks, one thread per state element.  Every chunk but the
-// last has length C (the total after the last chunk is never used), so the carry factor is
-// the constant lam^C; loads are issued 32 chunks at a time to overlap their latency.
-__global__ void nw_chunk_scan(NwParams p) {
+// kernel 2: exclusive scan over chunks.  Every chunk but the last has length C, so the recurrence over chunks
+// is start_{c+1} = lam^C start_c + total_c.  Eight threads share a state element: each walks one eighth of the
+// chunks from zero, the eight partial results are chained through shared memory, then each walks its part
+// again from its true start and overwrites the totals with the start states.  (One thread per element and a
+// serial walk over all chunks is a chain of global-memory latencies.)
+constexpr int NW_SCAN_GROUPS = 8;
+__global__ void __launch_bounds__(32 * NW_SCAN_GROUPS) nw_chunk_scan(NwParams p) {
+  __shared__ double s_part[NW_SCAN_GROUPS][32];
   const int ns = nw_nstate(p.K, p.q);
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= ns) return;
+  const int ex = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + ex;
+  const bool act = e < ns;
+  const int per = max(1, (p.nchunks + NW_SCAN_GROUPS - 1) / NW_SCAN_GROUPS);   // from nchunks, not c_used: a date range
+                                                                                 // then adds in the same order as the whole series
+  const int c_lo = min(p.c_used, g * per), c_hi = min(p.c_used, c_lo + per);
   const double fC = pow(p.lam, (double)p.C);
   // the last chunk may be shorter than C: the running state before it decays by lam^len
   const double fLast = pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C));
+  double* col = p.state + (act ? e : 0);
   double run = 0.0;
-  for (int c0 = 0; c0 < p.c_used; c0 += 32) {
-    double loc[32];
+  for (int c0 = c_lo; c0 < c_hi; c0 += 8) {
+    double loc[8];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) loc[j] = (c0 + j < p.c_used) ? p.state[(size_t)(c0 + j) * ns + e] : 0.0;
+    for (int j = 0; j < 8; ++j) loc[j] = (act && c0 + j < c_hi) ? col[(size_t)(c0 + j) * ns] : 0.0;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (c0 + j < p.c_used) {
-        p.state[(size_t)(c0 + j) * ns + e] = run;
+    for (int j = 0; j < 8; ++j)
+      if (c0 + j < c_hi) run = fma(run, c0 + j == p.nchunks - 1 ? fLast : fC, loc[j]);
+  }
+  s_part[g][ex] = run;
+  __syncthreads();
+  // state at the start of this thread's part: every earlier part holds exactly `per` full chunks
+  double start = 0.0;
+  {
+    const double fPer = pow(fC, (double)per);
+    for (int h = 0; h < g; ++h) start = fma(start, fPer, s_part[h][ex]);
+  }
+  run = start;
+  for (int c0 = c_lo; c0 < c_hi; c0 += 8) {
+    double loc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) loc[j] = (act && c0 + j < c_hi) ? col[(size_t)(c0 + j) * ns] : 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (c0 + j < c_hi) {
+        if (act) col[(size_t)(c0 + j) * ns] = run;
         run = fma(run, c0 + j == p.nchunks - 1 ? fLast : fC, loc[j]);
       }
     }
   }
-  for (int r = 0; r < p.n_peer; ++r) p.peer_totals[r][(size_t)p.rank * ns + e] = run;   // state after the last row
+  // the state after the last row (date-sharded form: all chunks are scanned): held by the last non-empty part
+  const int g_last = p.c_used > 0 ? (p.c_used - 1) / per : 0;
+  if (p.n_peer > 0 && act && g == g_last)
+    for (int r = 0; r < p.n_peer; ++r) p.peer_totals[r][(size_t)p.rank * ns + e] = run;
 }
 
 // carry-in of a date-sharded rank: decayed sum of the earlier ranks' zero-start totals,
@@ -330,7 +362,7 @@ static int nw_run_totals(bmfm_ctx* ctx, NwParams& p) {
     nw_chunk_local<<<dim3(p.c_used, (ns + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
     ctx->launches++;
   }
-  nw_chunk_scan<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(p);
+  nw_chunk_scan<<<(ns + 31) / 32, 32 * NW_SCAN_GROUPS, 0, ctx->stream>>>(p);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
