@@ -68,12 +68,22 @@ __host__ inline int nw_pick_chunk(int T, int K, int q) {
 
 // stage rows r0-q .. r1-1 of the series (zeros before row 0) in shared memory
 __device__ __forceinline__ void nw_stage_rows(const NwParams& p, double* sx, int r0, int len) {
+  // rows r0-q .. r0+len-1 are one contiguous piece of the series; cp.async keeps every copy in flight at once
+  // (a load-then-store loop would pay one global-memory latency per row)
   const int K = p.K, q = p.q;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  for (int j = warp; j < len + q; j += nwarps) {
-    const int r = r0 - q + j;
-    for (int k = lane; k < K; k += 32) sx[j * K + k] = r >= 0 ? p.fr[(size_t)r * K + k] : 0.0;
+  const int rlo = max(0, r0 - q);                    // first real row
+  const int zero = (rlo - (r0 - q)) * K;             // leading elements that stand for rows before row 0
+  const int n = (r0 + len - rlo) * K;                // real elements
+  for (int e = threadIdx.x; e < zero; e += blockDim.x) sx[e] = 0.0;
+  const double* src = p.fr + (size_t)rlo * K;
+  double* dst = sx + zero;
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+    for (int e = threadIdx.x; e < (n >> 1); e += blockDim.x) cp_async_16(dst + 2 * e, src + 2 * e);
+    if ((n & 1) && threadIdx.x == 0) cp_async_8(dst + n - 1, src + n - 1);
+  } else {
+    for (int e = threadIdx.x; e < n; e += blockDim.x) cp_async_8(dst + e, src + e);
   }
+  cp_async_wait_all();
 }
 
 // kernel 1: chunk totals from a zero start, one state element per thread (grid: chunks x element blocks)
@@ -213,36 +223,48 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
 #define NW_LD(idx) (cr ? fma(fcar, cr[idx], st[idx]) : st[idx])
   nw_stage_rows(p, sx, r0, len);
   __syncthreads();
+  // the scalar sums Z, Z_i do not depend on the data: closed form per date (one thread per date),
+  //   Z after j+1 more rows = Z_start lam^(j+1) + (1 - lam^cnt) / (1 - lam),  cnt = rows counted so far
+  for (int j = tid; j < len; j += nt) {
+    const double lj = pow(lam, (double)(j + 1));
+    const double inv1 = 1.0 / (1.0 - lam);
+    const double Z0 = fma(NW_LD(nm + (1 + 2 * q) * K), lj, (1.0 - lj) * inv1);
+    const double iz = 1.0 / Z0;
+    double zs = 0.0;
+#pragma unroll
+    for (int i = 0; i < QL; ++i) {
+      const int lag = i + 1;
+      const int cnt = max(0, r0 + j + 1 - max(r0, lag));          // rows r >= lag among r0 .. r0+j
+      const double Zl = fma(NW_LD(nm + (1 + 2 * q) * K + lag), lj, (1.0 - pow(lam, (double)cnt)) * inv1);
+      zs = fma(1.0 - (double)lag / (1.0 + q), Zl, zs);
+    }
+    siz[j] = iz;
+    scc[j] = 1.0 - 2.0 * zs * iz;
+  }
+  __syncthreads();
   for (int k = tid; k < K; k += nt) {
     double S = NW_LD(nm + k);
-    double R[QN], Pv[QN], Z[QL + 1];
+    double R[QN], Pv[QN];
 #pragma unroll
     for (int i = 0; i < QL; ++i) {
       R[i] = NW_LD(nm + (1 + i) * K + k);
       Pv[i] = NW_LD(nm + (1 + q + i) * K + k);
     }
-#pragma unroll
-    for (int i = 0; i <= QL; ++i) Z[i] = NW_LD(nm + (1 + 2 * q) * K + i);
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
       const double x = sx[(q + j) * K + k];
       S = fma(S, lam, x);
-      Z[0] = fma(Z[0], lam, 1.0);
-      const double iz = 1.0 / Z[0];
-      double u = 0.0, zs = 0.0;
+      double u = 0.0;
 #pragma unroll
       for (int i = 0; i < QL; ++i) {
         const int lag = i + 1;
         R[i] = fma(R[i], lam, r >= lag ? x : 0.0);
         Pv[i] = fma(Pv[i], lam, sx[(q + j - lag) * K + k]);      // zero-filled before row 0
-        Z[lag] = fma(Z[lag], lam, r >= lag ? 1.0 : 0.0);
-        const double w = 1.0 - (double)lag / (1.0 + q);
-        u = fma(w, Pv[i] + R[i], u);
-        zs = fma(w, Z[lag], zs);
+        u = fma(1.0 - (double)lag / (1.0 + q), Pv[i] + R[i], u);
       }
+      const double iz = siz[j];
       sm[j * K + k] = S * iz;
       su[j * K + k] = u * iz;
-      if (k == 0) { siz[j] = iz; scc[j] = 1.0 - 2.0 * zs * iz; }
     }
   }
   __syncthreads();
