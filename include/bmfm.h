@@ -246,6 +246,24 @@ int bmfm_beta_hsigma(bmfm_ctx* ctx, int L, int S, const double* ret, const doubl
 int bmfm_dastd(bmfm_ctx* ctx, int L, int S, const double* ret, const double* mkt, int window,
                double half_life, int min_periods, double* out);
 int bmfm_cmra(bmfm_ctx* ctx, int L, int S, const double* log_ret, int window, double* out);
+/*
+ * The remaining rolling descriptors, same [L * S] panels:
+ * bmfm_rstr: FactorCalculator.compute_rstr (factor_calculator.py:127-153): log_ret shifted by `lag` rows,
+ *   window T - lag, weights 0.5^(pos / half_life) by POSITION in the window (the oldest row has weight 1, as
+ *   the reference's weights_arr[:len(window)] does), NaN rows dropped with their weights, NaN unless
+ *   >= min_periods valid rows.  Reference constants: T = 504, lag = 21, half_life = 126, min_periods = 42.
+ * bmfm_rolling_log_sum: one of STOM / STOQ / STOA of compute_liquidity (factor_calculator.py:324-367):
+ *   log(rolling(window, min_periods).sum() of x / divisor), NaN where the sum is 0.  Reference:
+ *   divisor = 100 and (window, min_periods) = (21, 15), (63, 42), (252, 126).
+ * bmfm_nlsize: compute_nlsize (factor_calculator.py:237-293) on the long table grouped by date
+ *   (date_off int64 [T+1]): minus the OLS residual of size^3 on [1, size] over the rows with size present,
+ *   all NaN on dates with fewer than 2 such rows.
+ */
+int bmfm_rstr(bmfm_ctx* ctx, int L, int S, const double* log_ret, int T, int lag, double half_life,
+              int min_periods, double* out);
+int bmfm_rolling_log_sum(bmfm_ctx* ctx, int L, int S, const double* x, double divisor, int window,
+                         int min_periods, double* out);
+int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* size, double* out);
 
 /*
  * Per-date post-processing on the long table grouped by date (date_off int64 [T+1], one fp64 array

@@ -1,8 +1,8 @@
 # factor_calculator.py
 """Drop-in for the hot-path methods of Barra_factor_cal/factor_calculator.py:
 ``FactorCalculator(prices_df, index_df)``, ``_prepare_data``,
-``compute_beta_hsigma``, ``compute_dastd``, ``compute_cmra`` and ``run`` for
-those factors — same DataFrame in / DataFrame out contract (results keyed by
+``compute_beta_hsigma``, ``compute_dastd``, ``compute_cmra``, ``compute_rstr``,
+``compute_liquidity``, ``compute_nlsize`` and ``run`` for those factors — same DataFrame in / DataFrame out contract (results keyed by
 ``original_index``), rolling windows on the GPU.
 
 The long table is pivoted once into a dense [row-of-stock, stock] panel (each
@@ -81,13 +81,52 @@ class FactorCalculator:
         return pd.DataFrame({'original_index': self.master_df['original_index'].values,
                              'CMRA': self._gather(out)})
 
+    def _panel(self, column):
+        """[row-of-stock, stock] panel of a master_df column (NaN where the stock has no such row)."""
+        p = np.full((self._L, self._S), np.nan)
+        p[self._rows, self._codes] = self.master_df[column].values.astype(np.float64)
+        return p
+
+    def compute_rstr(self):
+        """factor_calculator.py:127-153 (T 504, lag 21, half-life 126, min_periods 42; the oldest row of the
+        window carries weight 1, as in the reference)"""
+        print("Computing RSTR factor...")
+        out = _ops.rstr(self._log_ret, 504, 21, 126, 42)
+        return pd.DataFrame({'original_index': self.master_df['original_index'].values, 'RSTR': self._gather(out)})
+
+    def compute_liquidity(self):
+        """factor_calculator.py:324-367: STOM, STOQ, STOA; None when 'turnover_rate' is missing (:333-335)"""
+        print("Computing base Liquidity factors (STOM, STOQ, STOA)...")
+        if 'turnover_rate' not in self.master_df.columns:
+            print("\nERROR: 'turnover_rate' column not found in the input data.\n")
+            return None
+        stom, stoq, stoa = _ops.liquidity(self._panel('turnover_rate'))
+        return pd.DataFrame({'original_index': self.master_df.index,
+                             'STOM': self._gather(stom), 'STOQ': self._gather(stoq), 'STOA': self._gather(stoa)})
+
+    def compute_nlsize(self):
+        """factor_calculator.py:237-293: per-date OLS of SIZE^3 on SIZE, minus the residual"""
+        print("Computing NonLinear Size (NLSIZE) factor...")
+        with np.errstate(invalid='ignore', divide='ignore'):
+            size = np.log(self.master_df['total_mv'].values.astype(np.float64))
+        # rows grouped by trade_date for the per-date kernel; results go back to master_df's row order
+        codes, _ = pd.factorize(self.master_df['trade_date'].values, sort=True)
+        order = np.argsort(codes, kind='stable')
+        date_off = np.concatenate([[0], np.cumsum(np.bincount(codes))]).astype(np.int64)
+        res = np.empty(len(size))
+        res[order] = _ops.nlsize(date_off, size[order])
+        return pd.DataFrame({'original_index': self.master_df['original_index'].values, 'NLSIZE': res})
+
     def run(self, factors_to_compute: list) -> pd.DataFrame:
         """factor_calculator.py:515-577 for the hot-path factors: merge results on original_index."""
-        methods = {'BETA': self.compute_beta_hsigma, 'DASTD': self.compute_dastd, 'CMRA': self.compute_cmra}
+        methods = {'BETA': self.compute_beta_hsigma, 'DASTD': self.compute_dastd, 'CMRA': self.compute_cmra,
+                   'RSTR': self.compute_rstr, 'LIQUIDITY': self.compute_liquidity, 'NLSIZE': self.compute_nlsize}
         final = self.master_df[['original_index', 'ts_code', 'trade_date', 'ret']].copy()
         for name in factors_to_compute:
             key = name.upper()
             if key not in methods:
                 raise NotImplementedError(f"factor {name!r} is outside the accelerated hot path (SURVEY.md §8(f))")
-            final = pd.merge(final, methods[key](), on='original_index', how='left')
+            res = methods[key]()
+            if res is not None:
+                final = pd.merge(final, res, on='original_index', how='left')
         return final.drop(columns=['original_index'])

@@ -51,6 +51,9 @@ _SIGNATURES = {
     "bmfm_eigen_finalize": ([_P, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_bayes_shrink": ([_P, _I, _I, _P, _P, _P, _I, _D, _P, _P], _I),
     "bmfm_prepare_returns": ([_P, _I, _I, _P, _P, _P], _I),
+    "bmfm_rstr": ([_P, _I, _I, _P, _I, _I, _D, _I, _P], _I),
+    "bmfm_rolling_log_sum": ([_P, _I, _I, _P, _D, _I, _I, _P], _I),
+    "bmfm_nlsize": ([_P, _I, _P, _P, _P], _I),
     "bmfm_beta_hsigma": ([_P, _I, _I, _P, _P, _I, _D, _I, _P, _P], _I),
     "bmfm_dastd": ([_P, _I, _I, _P, _P, _I, _D, _I, _P], _I),
     "bmfm_cmra": ([_P, _I, _I, _P, _I, _P], _I),
@@ -250,6 +253,17 @@ class Context:
 
     def cmra(self, L, S, log_ret, window, out):
         self.check(self._L.bmfm_cmra(self._h, L, S, ptr(log_ret), int(window), ptr(out)))
+
+    def rstr(self, L, S, log_ret, T, lag, half_life, min_periods, out):
+        self.check(self._L.bmfm_rstr(self._h, L, S, ptr(log_ret), int(T), int(lag), float(half_life),
+                                     int(min_periods), ptr(out)))
+
+    def rolling_log_sum(self, L, S, x, divisor, window, min_periods, out):
+        self.check(self._L.bmfm_rolling_log_sum(self._h, L, S, ptr(x), float(divisor), int(window),
+                                                int(min_periods), ptr(out)))
+
+    def nlsize(self, T, date_off, size, out):
+        self.check(self._L.bmfm_nlsize(self._h, T, ptr(date_off), ptr(size), ptr(out)))
 
     def winsorize(self, T, date_off, x, n_std, out):
         self.check(self._L.bmfm_winsorize(self._h, T, ptr(date_off), ptr(x), float(n_std), ptr(out)))

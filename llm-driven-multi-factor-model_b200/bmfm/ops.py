@@ -215,6 +215,42 @@ def cmra(log_ret, window=252, ctx=None):
     return o.cpu().numpy()
 
 
+def rstr(log_ret, T=504, lag=21, half_life=126, min_periods=42, ctx=None):
+    """compute_rstr on a [row-of-stock, stock] panel of log returns."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    r = _dev(np.asarray(log_ret, dtype=np.float64))
+    L, S = r.shape
+    o = torch.empty_like(r)
+    ctx.rstr(L, S, r, T, lag, half_life, min_periods, o)
+    return o.cpu().numpy()
+
+
+def liquidity(turnover_rate, windows=((21, 15), (63, 42), (252, 126)), divisor=100.0, ctx=None):
+    """compute_liquidity on a [row-of-stock, stock] panel of turnover in percent: (STOM, STOQ, STOA)."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    x = _dev(np.asarray(turnover_rate, dtype=np.float64))
+    L, S = x.shape
+    outs = []
+    for (window, minp) in windows:
+        o = torch.empty_like(x)
+        ctx.rolling_log_sum(L, S, x, divisor, window, minp, o)
+        outs.append(o.cpu().numpy())
+    return tuple(outs)
+
+
+def nlsize(date_off, size, ctx=None):
+    """compute_nlsize on the long table grouped by date."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    date_off = np.asarray(date_off, dtype=np.int64)
+    xd = _dev(np.asarray(size, dtype=np.float64))
+    o = torch.empty_like(xd)
+    ctx.nlsize(len(date_off) - 1, _dev(date_off), xd, o)
+    return o.cpu().numpy()
+
+
 def winsorize(date_off, x, n_std=2.5, ctx=None):
     torch = _torch()
     ctx = ctx or _cabi.default_context()

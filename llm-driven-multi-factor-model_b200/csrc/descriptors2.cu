@@ -1,0 +1,179 @@
+// The remaining rolling descriptors and the per-date size regression.
+//
+// Replaces, for all stocks / dates at once:
+//   FactorCalculator.compute_rstr        Barra_factor_cal/factor_calculator.py:127-153
+//   FactorCalculator.compute_liquidity   Barra_factor_cal/factor_calculator.py:324-367
+//   FactorCalculator.compute_nlsize      Barra_factor_cal/factor_calculator.py:237-293
+//
+// Panels are [L][S] (row of the stock's own history x stock, stock contiguous) as in descriptors.cu: one
+// thread per stock keeps every load coalesced, blockIdx.y cuts the rows into chunks of DESC2_CHUNK so that all
+// SMs work; each chunk rebuilds its window sums from the rows before it and then slides (add the entering row,
+// subtract the leaving one), which also bounds the rounding drift of the running sums to one chunk.
+#include <math.h>
+#include "bmfm_common.cuh"
+
+namespace bmfm {
+
+constexpr int DESC2_CHUNK = 256;
+
+__device__ __forceinline__ double qnan2() { return __longlong_as_double(0x7ff8000000000000LL); }
+
+// RSTR: y = x.shift(lag); window of W rows ending at r; weights BY POSITION IN THE WINDOW, decay^(pos), so the
+// oldest row has weight 1 (factor_calculator.py:137-144: weights_arr[:len(window)]); NaN rows are dropped with
+// their weights; NaN unless >= minp valid rows.  The normalisation cancels any common factor of the weights,
+// so a chunk uses decay^(row - a0) with a0 = first row of the chunk's first window.
+__global__ void __launch_bounds__(128) rstr_kernel(int L, int S, int W, int lag, int minp, double decay,
+                                                   const double* x, double* out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  const int r0 = blockIdx.y * DESC2_CHUNK, r1 = min(L, r0 + DESC2_CHUNK);
+  const int a0 = max(0, r0 - W + 1);
+  double num = 0.0, den = 0.0;
+  int cnt = 0;
+  double wadd = 1.0;                       // decay^(row - a0) of the row being added
+  for (int r = a0; r < r0; ++r) {          // rows of the first window that precede the chunk
+    const double v = r >= lag ? x[(size_t)(r - lag) * S + s] : qnan2();
+    if (!isnan(v)) { num = fma(wadd, v, num); den += wadd; ++cnt; }
+    wadd *= decay;
+  }
+  double wrem = 1.0;                       // decay^(row - a0) of the row being removed
+  for (int r = r0; r < r1; ++r) {
+    const double v = r >= lag ? x[(size_t)(r - lag) * S + s] : qnan2();
+    if (!isnan(v)) { num = fma(wadd, v, num); den += wadd; ++cnt; }
+    wadd *= decay;
+    const int gone = r - W;                // row that left the window
+    if (gone >= a0) {
+      const double u = gone >= lag ? x[(size_t)(gone - lag) * S + s] : qnan2();
+      if (!isnan(u)) { num = fma(-wrem, u, num); den -= wrem; --cnt; }
+      wrem *= decay;
+    }
+    st_stream(out + (size_t)r * S + s, cnt >= minp ? num / den : qnan2());
+  }
+}
+
+// STOM / STOQ / STOA: log of the rolling sum of x / divisor over W rows, NaN rows skipped, NaN unless >= minp
+// valid rows, and NaN where the sum is 0 (.replace(0, nan), factor_calculator.py:350-352).  A window whose valid
+// values are all exact zeros (a suspended stock) must give exactly 0 whatever was added and removed before, so
+// the number of non-zero values in the window is tracked beside the sum.
+__global__ void __launch_bounds__(128) roll_logsum_kernel(int L, int S, int W, int minp, double divisor,
+                                                          const double* x, double* out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  const int r0 = blockIdx.y * DESC2_CHUNK, r1 = min(L, r0 + DESC2_CHUNK);
+  const int a0 = max(0, r0 - W + 1);
+  double sum = 0.0;
+  int cnt = 0, nnz = 0;
+  for (int r = a0; r < r0; ++r) {
+    const double v = x[(size_t)r * S + s] / divisor;
+    if (!isnan(v)) { sum += v; ++cnt; nnz += v != 0.0; }
+  }
+  for (int r = r0; r < r1; ++r) {
+    const double v = x[(size_t)r * S + s] / divisor;
+    if (!isnan(v)) { sum += v; ++cnt; nnz += v != 0.0; }
+    const int gone = r - W;
+    if (gone >= a0) {
+      const double u = x[(size_t)gone * S + s] / divisor;
+      if (!isnan(u)) { sum -= u; --cnt; nnz -= u != 0.0; }
+    }
+    double o = qnan2();
+    if (cnt >= minp && nnz > 0 && sum != 0.0) o = log(sum);     // log of a negative sum is NaN as in numpy
+    st_stream(out + (size_t)r * S + s, o);
+  }
+}
+
+// NLSIZE: per date, OLS of size^3 on [1, size] over the rows with size present; out = -(residual); all NaN
+// when fewer than 2 such rows.  Centred form (the raw normal equations of x ~ 15, x^3 ~ 4000 lose digits):
+//   b = sum (x-mx)(y-my) / sum (x-mx)^2,  residual = (y-my) - b (x-mx);  a constant column of x gives b = 0
+//   (statsmodels' pinv solution has the same residuals).
+__device__ __forceinline__ double block_sum_128(double v, double* red) {
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+  return t;
+}
+
+__global__ void __launch_bounds__(128) nlsize_kernel(int T, const long long* date_off, const double* size, double* out) {
+  __shared__ double red[4];
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const long long a = date_off[t];
+    const int n = (int)(date_off[t + 1] - a);
+    double sx = 0.0, sy = 0.0, c = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const double x = size[a + i];
+      if (!isnan(x)) { sx += x; sy += x * x * x; c += 1.0; }
+    }
+    sx = block_sum_128(sx, red);
+    sy = block_sum_128(sy, red);
+    c = block_sum_128(c, red);
+    if (c < 2.0) {
+      for (int i = threadIdx.x; i < n; i += blockDim.x) out[a + i] = qnan2();
+      continue;
+    }
+    const double mx = sx / c, my = sy / c;
+    double sxx = 0.0, sxy = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const double x = size[a + i];
+      if (!isnan(x)) {
+        const double dx = x - mx, dy = x * x * x - my;
+        sxx = fma(dx, dx, sxx);
+        sxy = fma(dx, dy, sxy);
+      }
+    }
+    sxx = block_sum_128(sxx, red);
+    sxy = block_sum_128(sxy, red);
+    const double b = sxx > 0.0 ? sxy / sxx : 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const double x = size[a + i];
+      out[a + i] = isnan(x) ? qnan2() : -((x * x * x - my) - b * (x - mx));
+    }
+  }
+}
+
+}  // namespace bmfm
+
+using namespace bmfm;
+
+extern "C" int bmfm_rstr(bmfm_ctx* ctx, int L, int S, const double* log_ret, int T, int lag, double half_life,
+                         int min_periods, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, L >= 0 && S >= 0 && T > lag && lag >= 0 && half_life > 0 && min_periods >= 1, "bad sizes");
+  BMFM_ARG(ctx, (log_ret && out) || (size_t)L * S == 0, "NULL pointer");
+  if ((size_t)L * S == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const dim3 grid((S + 127) / 128, (L + DESC2_CHUNK - 1) / DESC2_CHUNK);
+  rstr_kernel<<<grid, 128, 0, ctx->stream>>>(L, S, T - lag, lag, min_periods, pow(0.5, 1.0 / half_life), log_ret, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_rolling_log_sum(bmfm_ctx* ctx, int L, int S, const double* x, double divisor, int window,
+                                    int min_periods, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, L >= 0 && S >= 0 && window >= 1 && min_periods >= 1 && divisor != 0.0, "bad sizes");
+  BMFM_ARG(ctx, (x && out) || (size_t)L * S == 0, "NULL pointer");
+  if ((size_t)L * S == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const dim3 grid((S + 127) / 128, (L + DESC2_CHUNK - 1) / DESC2_CHUNK);
+  roll_logsum_kernel<<<grid, 128, 0, ctx->stream>>>(L, S, window, min_periods, divisor, x, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* size, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0, "bad sizes");
+  BMFM_ARG(ctx, T == 0 || (date_off && size && out), "NULL pointer");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  nlsize_kernel<<<grid, 128, 0, ctx->stream>>>(T, reinterpret_cast<const long long*>(date_off), size, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}

@@ -396,6 +396,74 @@ def cmra(log_ret, window=252):
     return out
 
 
+def rstr(log_ret, T=504, L=21, half_life=126, min_periods=42):
+    """Barra_factor_cal/factor_calculator.py:127-153 for ONE stock (own rows in date order):
+    ``x.shift(L).rolling(T - L, min_periods).apply(_rstr_calc)``.  The weight table is
+    ``decay**arange(window)`` and the window takes ``weights[:len(window)]`` BY POSITION, so the OLDEST
+    row of the window has weight 1 and the newest ``decay**(len-1)`` (SURVEY.md §8(f) [probed]); NaN
+    rows are dropped together with their weights (no re-ranking); NaN unless >= min_periods valid."""
+    x = np.asarray(log_ret, dtype=np.float64)
+    n = len(x)
+    window = T - L
+    decay = 0.5 ** (1 / half_life)
+    weights = decay ** np.arange(0, window)
+    y = np.full(n, np.nan)
+    if n > L:
+        y[L:] = x[:n - L]
+    out = np.full(n, np.nan)
+    ok = ~np.isnan(y)
+    for t in range(n):
+        a = max(0, t - window + 1)
+        sel = ok[a:t + 1]
+        if int(sel.sum()) < min_periods:
+            continue
+        v = y[a:t + 1][sel]
+        w = weights[:t + 1 - a][sel]
+        out[t] = np.sum(v * (w / np.sum(w)))
+    return out
+
+
+def liquidity(turnover_rate, windows=((21, 15), (63, 42), (252, 126))):
+    """Barra_factor_cal/factor_calculator.py:324-367 for ONE stock: ``dtv = turnover_rate / 100``;
+    pandas ``rolling(window, min_periods).sum()`` (NaN skipped, NaN unless >= min_periods valid);
+    ``log(sum.replace(0, nan))``.  Returns (STOM, STOQ, STOA)."""
+    dtv = np.asarray(turnover_rate, dtype=np.float64) / 100.0
+    n = len(dtv)
+    ok = ~np.isnan(dtv)
+    outs = []
+    for (window, minp) in windows:
+        o = np.full(n, np.nan)
+        for t in range(n):
+            a = max(0, t - window + 1)
+            sel = ok[a:t + 1]
+            if int(sel.sum()) < minp:
+                continue
+            sm = float(np.sum(dtv[a:t + 1][sel]))
+            if sm != 0.0:
+                with np.errstate(invalid="ignore"):
+                    o[t] = np.log(sm)
+        outs.append(o)
+    return tuple(outs)
+
+
+def nlsize(size):
+    """Barra_factor_cal/factor_calculator.py:237-293 for ONE date: OLS (statsmodels, pinv) of
+    ``SIZE**3`` on ``[1, SIZE]`` over the rows with SIZE present, NLSIZE = -residual; all-NaN when
+    fewer than 2 such rows."""
+    x = np.asarray(size, dtype=np.float64)
+    out = np.full_like(x, np.nan)
+    ok = ~np.isnan(x)
+    if int(ok.sum()) < 2:
+        return out
+    xv = x[ok]
+    yv = xv ** 3
+    const = (np.ptp(xv) == 0) and np.all(xv != 0)          # add_constant(has_constant='skip')
+    A = xv[:, None] if const else np.column_stack([np.ones(len(xv)), xv])
+    beta = np.linalg.pinv(A) @ yv
+    out[ok] = -(yv - A @ beta)
+    return out
+
+
 def prepare_returns(close):
     """Barra_factor_cal/factor_calculator.py:50-53 for one stock's closes in
     date order: ``pct_change`` (pandas 3: no forward fill) and log-return."""

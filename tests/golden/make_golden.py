@@ -189,6 +189,17 @@ def golden_descriptors():
         for t in np.nonzero(keep)[0]:
             rows.append((f"{s:06d}.SZ", dates[t], close[t, s], t, s))
     prices = pd.DataFrame(rows, columns=["ts_code", "trade_date", "close", "t", "s"])
+    # columns of the "next" descriptors: turnover in percent with suspension runs of exact
+    # zeros and missing days; total market value with a few missing rows
+    rng2 = np.random.default_rng(77)
+    to = np.exp(rng2.normal(0.3, 0.8, size=len(prices)))
+    to[rng2.random(len(prices)) < 0.03] = np.nan
+    susp = (prices["s"].values == 2) & (prices["t"].values >= 100) & (prices["t"].values < 170)
+    to[susp] = 0.0
+    prices["turnover_rate"] = to
+    mv = np.exp(rng2.normal(13.0, 1.2, size=S))[prices["s"].values] * np.exp(rng2.normal(0, 0.02, size=len(prices)))
+    mv[rng2.random(len(prices)) < 0.02] = np.nan
+    prices["total_mv"] = mv
     prices = prices.sample(frac=1.0, random_state=1).reset_index(drop=True)   # arbitrary input order
     index_df = pd.DataFrame({"trade_date": dates, "close": idx_close})
     with quiet():
@@ -196,15 +207,41 @@ def golden_descriptors():
         bh = calc.compute_beta_hsigma()
         da = calc.compute_dastd()
         cm = calc.compute_cmra()
+        rs = calc.compute_rstr()
+        lq = calc.compute_liquidity()
+        nl = calc.compute_nlsize()
     m = calc.master_df
-    res = m[["original_index", "t", "s", "close", "ret", "log_ret", "market_ret"]].merge(bh, on="original_index") \
-        .merge(da, on="original_index").merge(cm, on="original_index")
+    res = m[["original_index", "t", "s", "close", "ret", "log_ret", "market_ret", "turnover_rate", "total_mv"]] \
+        .merge(bh, on="original_index").merge(da, on="original_index").merge(cm, on="original_index") \
+        .merge(rs, on="original_index").merge(lq, on="original_index").merge(nl, on="original_index")
     res = res.sort_values(["s", "t"])
     for c in ["t", "s"]:
         out[c] = res[c].values.astype(np.int64)
-    for c in ["close", "ret", "log_ret", "market_ret", "BETA", "HSIGMA", "DASTD", "CMRA"]:
+    for c in ["close", "ret", "log_ret", "market_ret", "BETA", "HSIGMA", "DASTD", "CMRA", "turnover_rate", "total_mv",
+              "RSTR", "STOM", "STOQ", "STOA", "NLSIZE"]:
         out[c] = res[c].values.astype(float)
     out["index_close"] = idx_close
+
+    # a series longer than the RSTR window (483 rows) so that rows leave the window, two stocks
+    T2, S2 = 640, 2
+    close2, idx2 = make_price_panel(T2, S2, seed=52, missing=0.02, late=1)
+    dates2 = pd.to_datetime(make_dates(T2), format="%Y/%m/%d")
+    rows2 = [(f"{s:06d}.SZ", dates2[t], close2[t, s], t, s) for s in range(S2) for t in range(T2)]
+    prices2 = pd.DataFrame(rows2, columns=["ts_code", "trade_date", "close", "t", "s"])
+    rng3 = np.random.default_rng(78)
+    to2 = np.exp(rng3.normal(0.0, 0.7, size=len(prices2)))
+    to2[rng3.random(len(prices2)) < 0.05] = np.nan
+    prices2["turnover_rate"] = to2
+    with quiet():
+        calc2 = ref_fc.FactorCalculator(prices2.copy(), pd.DataFrame({"trade_date": dates2, "close": idx2}))
+        rs2 = calc2.compute_rstr()
+        lq2 = calc2.compute_liquidity()
+    res2 = calc2.master_df[["original_index", "t", "s", "log_ret", "turnover_rate"]].merge(rs2, on="original_index") \
+        .merge(lq2, on="original_index").sort_values(["s", "t"])
+    for c in ["t", "s"]:
+        out["long_" + c] = res2[c].values.astype(np.int64)
+    for c in ["log_ret", "turnover_rate", "RSTR", "STOM", "STOQ", "STOA"]:
+        out["long_" + c] = res2[c].values.astype(float)
 
     # post-processing on a small long table
     rng = np.random.default_rng(61)

@@ -70,6 +70,80 @@ def test_descriptors_oracle_long_series(ops):
         assert relerr(cm[:, s], orc.cmra(l)) < TOL
 
 
+def _panel_of(desc, key, pre=""):
+    s = desc[pre + "s"]
+    stocks = np.unique(s)
+    rows = np.concatenate([np.arange((s == k).sum()) for k in stocks])
+    out = np.full((rows.max() + 1, len(stocks)), np.nan)
+    cols = np.searchsorted(stocks, s)
+    out[rows, cols] = desc[pre + key]
+    return out, rows, cols
+
+
+@pytest.mark.parametrize("pre", ["", "long_"])
+def test_next_descriptors_golden(ops, desc, pre):
+    """RSTR and STOM/STOQ/STOA against the unmodified reference (short panel with a suspension run of exact
+    zeros / absent rows / late listing, and a series longer than the 483-row RSTR window)."""
+    lr, rows, cols = _panel_of(desc, "log_ret", pre)
+    got = ops.rstr(lr)[rows, cols]
+    assert np.array_equal(np.isnan(got), np.isnan(desc[pre + "RSTR"]))
+    assert relerr(got, desc[pre + "RSTR"]) < TOL
+    to, _, _ = _panel_of(desc, "turnover_rate", pre)
+    for name, o in zip(("STOM", "STOQ", "STOA"), ops.liquidity(to)):
+        g = o[rows, cols]
+        assert np.array_equal(np.isnan(g), np.isnan(desc[pre + name])), name
+        assert relerr(g, desc[pre + name]) < TOL, name
+
+
+def test_nlsize_golden_and_edges(ops, desc):
+    from oracle import barra_oracle as orc
+    t = desc["t"]
+    with np.errstate(invalid="ignore"):
+        size = np.log(desc["total_mv"])
+    order = np.argsort(t, kind="stable")
+    off = np.concatenate([[0], np.cumsum(np.bincount(t))]).astype(np.int64)
+    got = np.empty(len(t))
+    got[order] = ops.nlsize(off, size[order])
+    assert np.array_equal(np.isnan(got), np.isnan(desc["NLSIZE"]))
+    assert relerr(got, desc["NLSIZE"], scale=np.nanmax(np.abs(size ** 3))) < TOL
+    # dates with 0, 1, 2 valid rows, a constant cross-section, and a full A-share cross-section
+    rng = np.random.default_rng(4)
+    blocks = [np.array([np.nan, np.nan]), np.array([15.0, np.nan]), np.array([14.0, 16.5, np.nan]),
+              np.full(7, 13.25), rng.normal(15.5, 1.4, size=5000)]
+    blocks[-1][rng.random(5000) < 0.01] = np.nan
+    off2 = np.concatenate([[0], np.cumsum([len(b) for b in blocks])]).astype(np.int64)
+    x = np.concatenate(blocks)
+    g2 = ops.nlsize(off2, x)
+    want = np.concatenate([orc.nlsize(b) for b in blocks])
+    assert np.array_equal(np.isnan(g2), np.isnan(want))
+    assert relerr(g2, want, scale=np.nanmax(np.abs(x ** 3))) < TOL
+
+
+def test_next_descriptors_oracle_long_series(ops):
+    """Several row chunks per stock (window rebuilt at every chunk), NaN runs, zero runs, late listings."""
+    from oracle import barra_oracle as orc
+    rng = np.random.default_rng(12)
+    L, S = 1300, 6
+    lr = rng.normal(0, 0.02, size=(L, S))
+    lr[rng.random((L, S)) < 0.03] = np.nan
+    lr[:200, 1] = np.nan
+    lr[600:700, 2] = np.nan
+    to = np.exp(rng.normal(0.2, 0.9, size=(L, S)))
+    to[rng.random((L, S)) < 0.04] = np.nan
+    to[300:420, 3] = 0.0
+    to[:, 4] = 0.0
+    got = ops.rstr(lr)
+    liq = ops.liquidity(to)
+    for s in range(S):
+        want = orc.rstr(lr[:, s])
+        assert np.array_equal(np.isnan(got[:, s]), np.isnan(want))
+        assert relerr(got[:, s], want) < TOL
+        for g, w in zip(liq, orc.liquidity(to[:, s])):
+            assert np.array_equal(np.isnan(g[:, s]), np.isnan(w))
+            if np.isfinite(w).any():
+                assert relerr(g[:, s], w) < TOL
+
+
 def test_post_processing_golden(ops, desc):
     d = desc["pp_date_idx"]
     off = np.concatenate([[0], np.cumsum(np.bincount(d))]).astype(np.int64)
@@ -172,3 +246,37 @@ def test_factor_calculator_dropin(desc):
         assert relerr(res.loc[sel, "CMRA"].values, orc.cmra(l)) < TOL
     for date, grp in res.groupby("trade_date"):
         assert relerr(wz.loc[grp.index, "BETA"].values, orc.winsorize(grp["BETA"].values)) < 1e-12
+
+
+def test_factor_calculator_next_descriptors_dropin(desc):
+    """FactorCalculator.run(['RSTR', 'LIQUIDITY', 'NLSIZE']) of the drop-in on the golden panel (rows shuffled)
+    against what the unmodified reference returned for it."""
+    import contextlib, io, sys
+    import pandas as pd
+    from bmfm.synth import make_dates
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                       "llm-driven-multi-factor-model_b200", "Barra_factor_cal")
+    sys.path.insert(0, pkg)
+    try:
+        import factor_calculator as fc
+    finally:
+        sys.path.remove(pkg)
+    T = len(desc["index_close"])
+    dates = pd.to_datetime(make_dates(T), format="%Y/%m/%d")
+    prices = pd.DataFrame({"ts_code": [f"{k:06d}.SZ" for k in desc["s"]], "trade_date": dates[desc["t"]],
+                           "close": desc["close"], "turnover_rate": desc["turnover_rate"],
+                           "total_mv": desc["total_mv"], "key": np.arange(len(desc["s"]))})
+    prices = prices.sample(frac=1.0, random_state=5).reset_index(drop=True)
+    index_df = pd.DataFrame({"trade_date": dates, "close": desc["index_close"]})
+    with contextlib.redirect_stdout(io.StringIO()):
+        calc = fc.FactorCalculator(prices.copy(), index_df.copy())
+        res = calc.run(["RSTR", "LIQUIDITY", "NLSIZE"])
+    res = res.merge(calc.master_df[["ts_code", "trade_date", "key"]], on=["ts_code", "trade_date"]).sort_values("key")
+    for c in ["RSTR", "STOM", "STOQ", "STOA"]:
+        got = res[c].values
+        assert np.array_equal(np.isnan(got), np.isnan(desc[c])), c
+        assert relerr(got, desc[c]) < TOL, c
+    with np.errstate(invalid="ignore"):
+        scale = np.nanmax(np.abs(np.log(desc["total_mv"]) ** 3))
+    assert np.array_equal(np.isnan(res["NLSIZE"].values), np.isnan(desc["NLSIZE"]))
+    assert relerr(res["NLSIZE"].values, desc["NLSIZE"], scale=scale) < TOL

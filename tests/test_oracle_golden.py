@@ -162,6 +162,28 @@ def test_descriptors(desc):
         assert relerr(orc.cmra(lr), desc["CMRA"][sel]) < 1e-12
 
 
+def test_next_descriptors(desc):
+    """RSTR, STOM/STOQ/STOA, NLSIZE against the unmodified reference: the short panel
+    (suspension run of exact-zero turnover, absent rows, late listing) and a series longer than the RSTR window."""
+    for pre in ("", "long_"):
+        s_all = desc[pre + "s"]
+        for s in np.unique(s_all):
+            sel = s_all == s
+            assert relerr(orc.rstr(desc[pre + "log_ret"][sel]), desc[pre + "RSTR"][sel]) < 1e-13
+            stom, stoq, stoa = orc.liquidity(desc[pre + "turnover_rate"][sel])
+            assert relerr(stom, desc[pre + "STOM"][sel]) < 1e-13
+            assert relerr(stoq, desc[pre + "STOQ"][sel]) < 1e-13
+            assert relerr(stoa, desc[pre + "STOA"][sel]) < 1e-13
+    t = desc["t"]
+    with np.errstate(invalid="ignore"):
+        size = np.log(desc["total_mv"])
+    out = np.full(len(t), np.nan)
+    for d in np.unique(t):
+        out[t == d] = orc.nlsize(size[t == d])
+    assert np.array_equal(np.isnan(out), np.isnan(desc["NLSIZE"]))
+    assert relerr(out, desc["NLSIZE"], scale=np.nanmax(np.abs(size ** 3))) < 1e-13
+
+
 def test_post_processing(desc):
     d = desc["pp_date_idx"]
     cols = ["DASTD", "CMRA", "HSIGMA", "BETA", "SIZE", "STOM", "STOQ", "STOA"]
