@@ -213,6 +213,19 @@ int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double scale_coef, c
                         const double* U0, const double* vsum, const int32_t* status, double* out);
 
 /*
+ * Replaces utils.eigenfactor_bias_stat (Barra-master/mfm/utils.py:97-117, used MFM.py:203-204), the
+ * reference's validation metric for the eigen adjustment: for every date i < T - predlen with a covariance,
+ * b_i = U' retlen_i / sigma over the eigenfactor portfolios of cov_i (U scaled to unit column sums, returns
+ * compounded over the next predlen dates), bias_stat = np.std(b, axis 0) over those dates.
+ *   cov double [T*K*K] with cov_status [T] (NULL = every date present); factor_ret double [T*K];
+ *   bias_stat double [K], column k = k-th LARGEST eigenvalue (canonical order);
+ *   b_out optional double [(T-predlen)*K] (NULL to skip).  Uses the context workspace.
+ */
+int bmfm_eigenfactor_bias_stat(bmfm_ctx* ctx, int T, int K, int predlen, const double* cov,
+                               const int32_t* cov_status, const double* factor_ret, double* bias_stat,
+                               double* b_out);
+
+/*
  * Replaces utils.bayes_shrink with group_mean_std / shrink (Barra-master/mfm/utils.py:133-168),
  * batched over dates.  The reference defines no caller; inputs are whatever
  * specific-volatility and capital vectors the caller has, grouped by date like the regression.

@@ -49,6 +49,7 @@ _SIGNATURES = {
     "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_eigen_mc_accumulate": ([_P, _I, _I, _I, _P, _P, _P, _P, _I], _I),
     "bmfm_eigen_finalize": ([_P, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
+    "bmfm_eigenfactor_bias_stat": ([_P, _I, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_bayes_shrink": ([_P, _I, _I, _P, _P, _P, _I, _D, _P, _P], _I),
     "bmfm_prepare_returns": ([_P, _I, _I, _P, _P, _P], _I),
     "bmfm_rstr": ([_P, _I, _I, _P, _I, _I, _D, _I, _P], _I),
@@ -218,6 +219,10 @@ class Context:
     def vol_regime_adj_by_time(self, T, K, tao, fr, cov, cov_status, out_cov, lamb):
         self.check(self._L.bmfm_vol_regime_adj_by_time(self._h, T, K, float(tao), ptr(fr), ptr(cov),
                                                        ptr(cov_status), ptr(out_cov), ptr(lamb)))
+
+    def eigenfactor_bias_stat(self, T, K, predlen, cov, cov_status, fr, bias_stat, b_out=None):
+        self.check(self._L.bmfm_eigenfactor_bias_stat(self._h, T, K, int(predlen), ptr(cov), ptr(cov_status), ptr(fr),
+                                                      ptr(bias_stat), ptr(b_out)))
 
     def gauss_cov(self, m0, nsim, T_sim, K, Cmat):
         self.check(self._L.bmfm_gauss_cov(self._h, m0, nsim, T_sim, K, ptr(Cmat)))

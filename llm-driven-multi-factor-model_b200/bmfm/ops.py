@@ -215,6 +215,19 @@ def cmra(log_ret, window=252, ctx=None):
     return o.cpu().numpy()
 
 
+def eigenfactor_bias_stat(cov, cov_status, factor_ret, predlen=1, ctx=None):
+    """cov [T, K, K] (+ status [T] or None), factor_ret [T, K] -> bias_stat [K] (canonical eigen order)."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    c = _dev(np.asarray(cov, dtype=np.float64))
+    f = _dev(np.asarray(factor_ret, dtype=np.float64))
+    st = None if cov_status is None else _dev(np.asarray(cov_status, dtype=np.int32))
+    T, K = f.shape
+    out = torch.empty(K, dtype=torch.float64, device=c.device)
+    ctx.eigenfactor_bias_stat(T, K, predlen, c, st, f, out)
+    return out.cpu().numpy()
+
+
 def rstr(log_ret, T=504, lag=21, half_life=126, min_periods=42, ctx=None):
     """compute_rstr on a [row-of-stock, stock] panel of log returns."""
     torch = _torch()

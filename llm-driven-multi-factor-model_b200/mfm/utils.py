@@ -48,28 +48,22 @@ def eigen_risk_adj(covmat, T=1000, M=100, scale_coef=1.4):
 
 def eigenfactor_bias_stat(cov, ret, predlen=1):
     '''
-    计算特征因子组合的bias统计量 (utils.py:97-117); host-side diagnostic, canonical eigen order
+    计算特征因子组合的bias统计量 (utils.py:97-117) on the GPU: `cov` list of K x K DataFrames (empty frames where a
+    date has none: skipped, as the reference's try/except does), `ret` DataFrame T x K.  Canonical eigen order.
     '''
-    b = []
-    for i in range(len(cov) - predlen):
-        try:
-            c = np.asarray(cov[i], dtype=float)
-            w, v = np.linalg.eigh(0.5 * (c + c.T))
-            order = np.argsort(-w, kind="stable")
-            U = v[:, order]
-            idx = np.argmax(np.abs(U), axis=0)
-            sgn = np.sign(U[idx, np.arange(U.shape[1])])
-            sgn[sgn == 0] = 1.0
-            U = U * sgn[None, :]
-            U = U / np.sum(U, axis=0)
-            sigma = np.sqrt(predlen * np.diag(U.T @ c @ U))
-            retlen = (ret.values[(i + 1):(i + predlen + 1)] + 1).prod(axis=0) - 1
-            r = U.T @ retlen
-            b.append(r / sigma)
-        except Exception:
-            pass
-    b = np.array(b)
-    bias_stat = np.std(b, axis=0)
+    vals = ret.values if hasattr(ret, "values") else np.asarray(ret)
+    vals = np.ascontiguousarray(vals, dtype=np.float64)
+    T, K = vals.shape
+    arr = np.full((T, K, K), np.nan)
+    status = np.full(T, _cabi.ST_SHORT, dtype=np.int32)
+    for i in range(min(len(cov), T)):
+        c = np.asarray(cov[i], dtype=np.float64)
+        if c.shape == (K, K):
+            arr[i] = c
+            status[i] = _cabi.ST_OK
+    # the reference walks range(len(cov) - predlen): dates beyond len(cov) carry no covariance
+    bias_stat = _ops.eigenfactor_bias_stat(arr[:len(cov)], status[:len(cov)], vals[:len(cov)] if len(cov) <= T else vals,
+                                           predlen)
     try:
         import matplotlib.pyplot as plt
         plt.plot(bias_stat)

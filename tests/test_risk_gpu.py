@@ -234,3 +234,31 @@ def test_sharded_newey_west_exchanges_totals(ops, T, K, q, tao, world):
         got = cov.cpu().numpy()
         assert np.isnan(got[~ok]).all()
         assert np.max(np.abs(got[ok] - cov_full[lo:hi][ok])) < 1e-12 * scale
+
+
+@pytest.mark.gpu
+def test_eigenfactor_bias_stat(ops, golden_dir):
+    """bmfm_eigenfactor_bias_stat against the reference's output on the pipeline panel (dates without a
+    covariance are skipped as the reference's try/except does) and against the oracle on a longer series;
+    then through the mfm.utils drop-in with a list of DataFrames."""
+    import pandas as pd
+    from oracle import barra_oracle as orc
+    from bmfm.synth import make_factor_returns
+    g = np.load(os.path.join(golden_dir, "pipeline.npz"))
+    ok = g["nw_ok"][40:].astype(bool)
+    st = np.where(ok, 0, 1).astype(np.int32)
+    got = ops.eigenfactor_bias_stat(np.nan_to_num(g["nw"][40:]), st, g["factor_ret"][40:], predlen=5)
+    assert relerr(got, g["bias_stat_nw"]) < 1e-8
+    T, K = 400, 17
+    fr = make_factor_returns(T, K, seed=23)
+    cov, status = ops.newey_west_by_time(fr, 2, 90.0)
+    covs = [cov[t] if status[t] == 0 else None for t in range(T)]
+    for predlen in (1, 21):
+        want = orc.eigenfactor_bias_stat(covs, fr, predlen=predlen)
+        got = ops.eigenfactor_bias_stat(np.nan_to_num(cov), status, fr, predlen=predlen)
+        assert relerr(got, want) < 1e-8
+    from mfm import utils as mu
+    frames = [pd.DataFrame(cov[t]) if status[t] == 0 else pd.DataFrame() for t in range(T)]
+    got = mu.eigenfactor_bias_stat(frames[100:], pd.DataFrame(fr[100:]), predlen=21)
+    want = orc.eigenfactor_bias_stat(covs[100:], fr[100:], predlen=21)
+    assert relerr(got, want) < 1e-8
