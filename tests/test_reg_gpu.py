@@ -88,6 +88,29 @@ def test_oracle_parity(ops, T, N, P, Q, ragged, scale, mode, monkeypatch):
     assert np.max(np.abs(r2 - want_r2)) < tol
 
 
+@pytest.mark.parametrize("T,N,P,Q", [
+    (6, 800, 31, 10),     # ~20 industries in every 32-row chunk: the match.any group path
+    (5, 400, 5, 9),       # at most 6 industries per chunk, rows interleaved: indicator-column products
+    (4, 1500, 12, 7),     # two warps per date
+    (3, 333, 40, 8),      # more than 32 industries
+])
+@pytest.mark.parametrize("mode", ["3", "4", "5"])
+def test_oracle_parity_rows_not_grouped(ops, T, N, P, Q, mode, monkeypatch):
+    """The C-ABI accepts any row order inside a date; the packer's grouping by industry is an optimisation only."""
+    monkeypatch.setenv("BMFM_REG_MODE", mode)
+    from bmfm.synth import make_panel
+    from oracle import barra_oracle as orc
+    pan = make_panel(T, N, P, Q, seed=7 + N, ragged=0.03, scale_log10=(-1, 1))
+    csr = pan.to_csr()
+    want_fr, want_spec, want_r2 = orc.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P)
+    fr, spec, r2, status, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], P,
+                                              group_by_industry=False)
+    assert (status == 0).all()
+    assert relerr(fr, want_fr) < TOL
+    assert relerr(spec, want_spec, scale=np.max(np.abs(csr["ret"]))) < TOL
+    assert np.max(np.abs(r2 - want_r2)) < TOL
+
+
 def test_host_buffer_entry_point(ops):
     """bmfm_reg_by_time_host: host pointers in/out (the e2e path of bench.py)."""
     from bmfm import _cabi
