@@ -276,6 +276,10 @@ int bmfm_rstr(bmfm_ctx* ctx, int L, int S, const double* log_ret, int T, int lag
               int min_periods, double* out);
 int bmfm_rolling_log_sum(bmfm_ctx* ctx, int L, int S, const double* x, double divisor, int window,
                          int min_periods, double* out);
+/* the three windows of compute_liquidity in one pass: windows / min_periods HOST int [3], outs HOST array of
+ * 3 device pointers [L * S] each (STOM, STOQ, STOA in the reference's order) */
+int bmfm_rolling_log_sum3(bmfm_ctx* ctx, int L, int S, const double* x, double divisor, const int* windows,
+                          const int* min_periods, double* const* outs);
 int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* size, double* out);
 
 /*

@@ -54,6 +54,7 @@ _SIGNATURES = {
     "bmfm_prepare_returns": ([_P, _I, _I, _P, _P, _P], _I),
     "bmfm_rstr": ([_P, _I, _I, _P, _I, _I, _D, _I, _P], _I),
     "bmfm_rolling_log_sum": ([_P, _I, _I, _P, _D, _I, _I, _P], _I),
+    "bmfm_rolling_log_sum3": ([_P, _I, _I, _P, _D, _P, _P, _P], _I),
     "bmfm_nlsize": ([_P, _I, _P, _P, _P], _I),
     "bmfm_beta_hsigma": ([_P, _I, _I, _P, _P, _I, _D, _I, _P, _P], _I),
     "bmfm_dastd": ([_P, _I, _I, _P, _P, _I, _D, _I, _P], _I),
@@ -266,6 +267,12 @@ class Context:
     def rolling_log_sum(self, L, S, x, divisor, window, min_periods, out):
         self.check(self._L.bmfm_rolling_log_sum(self._h, L, S, ptr(x), float(divisor), int(window),
                                                 int(min_periods), ptr(out)))
+
+    def rolling_log_sum3(self, L, S, x, divisor, windows, min_periods, outs):
+        w = (C.c_int * 3)(*[int(v) for v in windows])
+        m = (C.c_int * 3)(*[int(v) for v in min_periods])
+        o = (C.c_void_p * 3)(*[int(t.data_ptr()) for t in outs])
+        self.check(self._L.bmfm_rolling_log_sum3(self._h, L, S, ptr(x), float(divisor), w, m, o))
 
     def nlsize(self, T, date_off, size, out):
         self.check(self._L.bmfm_nlsize(self._h, T, ptr(date_off), ptr(size), ptr(out)))

@@ -245,12 +245,13 @@ def liquidity(turnover_rate, windows=((21, 15), (63, 42), (252, 126)), divisor=1
     ctx = ctx or _cabi.default_context()
     x = _dev(np.asarray(turnover_rate, dtype=np.float64))
     L, S = x.shape
-    outs = []
-    for (window, minp) in windows:
-        o = torch.empty_like(x)
-        ctx.rolling_log_sum(L, S, x, divisor, window, minp, o)
-        outs.append(o.cpu().numpy())
-    return tuple(outs)
+    outs = [torch.empty_like(x) for _ in windows]
+    if len(windows) == 3:
+        ctx.rolling_log_sum3(L, S, x, divisor, [w for (w, _) in windows], [m for (_, m) in windows], outs)
+    else:
+        for (window, minp), o in zip(windows, outs):
+            ctx.rolling_log_sum(L, S, x, divisor, window, minp, o)
+    return tuple(o.cpu().numpy() for o in outs)
 
 
 def nlsize(date_off, size, ctx=None):

@@ -81,6 +81,43 @@ __global__ void __launch_bounds__(128) roll_logsum_kernel(int L, int S, int W, i
   }
 }
 
+// STOM, STOQ and STOA in one pass: the entering row is loaded and divided once for the three windows
+struct Roll3 { int W[3], minp[3]; double* out[3]; };
+__global__ void __launch_bounds__(128) roll_logsum3_kernel(int L, int S, Roll3 q, double divisor, const double* x) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  const int r0 = blockIdx.y * DESC2_CHUNK, r1 = min(L, r0 + DESC2_CHUNK);
+  double sum[3] = {0.0, 0.0, 0.0};
+  int cnt[3] = {0, 0, 0}, nnz[3] = {0, 0, 0}, a0[3];
+#pragma unroll
+  for (int w = 0; w < 3; ++w) a0[w] = max(0, r0 - q.W[w] + 1);
+  const int amin = min(a0[0], min(a0[1], a0[2]));
+  for (int r = amin; r < r0; ++r) {
+    const double v = x[(size_t)r * S + s] / divisor;
+    if (!isnan(v)) {
+#pragma unroll
+      for (int w = 0; w < 3; ++w)
+        if (r >= a0[w]) { sum[w] += v; ++cnt[w]; nnz[w] += v != 0.0; }
+    }
+  }
+  for (int r = r0; r < r1; ++r) {
+    const double v = x[(size_t)r * S + s] / divisor;
+    const bool vok = !isnan(v);
+#pragma unroll
+    for (int w = 0; w < 3; ++w) {
+      if (vok) { sum[w] += v; ++cnt[w]; nnz[w] += v != 0.0; }
+      const int gone = r - q.W[w];
+      if (gone >= a0[w]) {
+        const double u = x[(size_t)gone * S + s] / divisor;
+        if (!isnan(u)) { sum[w] -= u; --cnt[w]; nnz[w] -= u != 0.0; }
+      }
+      double o = qnan2();
+      if (cnt[w] >= q.minp[w] && nnz[w] > 0 && sum[w] != 0.0) o = log(sum[w]);
+      st_stream(q.out[w] + (size_t)r * S + s, o);
+    }
+  }
+}
+
 // NLSIZE: per date, OLS of size^3 on [1, size] over the rows with size present; out = -(residual); all NaN
 // when fewer than 2 such rows.  Centred form (the raw normal equations of x ~ 15, x^3 ~ 4000 lose digits):
 //   b = sum (x-mx)(y-my) / sum (x-mx)^2,  residual = (y-my) - b (x-mx);  a constant column of x gives b = 0
@@ -160,6 +197,25 @@ extern "C" int bmfm_rolling_log_sum(bmfm_ctx* ctx, int L, int S, const double* x
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   const dim3 grid((S + 127) / 128, (L + DESC2_CHUNK - 1) / DESC2_CHUNK);
   roll_logsum_kernel<<<grid, 128, 0, ctx->stream>>>(L, S, window, min_periods, divisor, x, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_rolling_log_sum3(bmfm_ctx* ctx, int L, int S, const double* x, double divisor,
+                                     const int* windows, const int* min_periods, double* const* outs) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, L >= 0 && S >= 0 && divisor != 0.0 && windows && min_periods && outs, "bad arguments");
+  if ((size_t)L * S == 0) return BMFM_OK;
+  Roll3 q;
+  for (int w = 0; w < 3; ++w) {
+    BMFM_ARG(ctx, windows[w] >= 1 && min_periods[w] >= 1 && outs[w], "bad window");
+    q.W[w] = windows[w]; q.minp[w] = min_periods[w]; q.out[w] = outs[w];
+  }
+  BMFM_ARG(ctx, x != nullptr, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const dim3 grid((S + 127) / 128, (L + DESC2_CHUNK - 1) / DESC2_CHUNK);
+  roll_logsum3_kernel<<<grid, 128, 0, ctx->stream>>>(L, S, q, divisor, x);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;

@@ -134,6 +134,9 @@ def test_next_descriptors_oracle_long_series(ops):
     to[:, 4] = 0.0
     got = ops.rstr(lr)
     liq = ops.liquidity(to)
+    # the single-window entry point gives the same numbers as the fused three-window pass
+    one = ops.liquidity(to, windows=((63, 42),))[0]
+    assert np.array_equal(np.isnan(one), np.isnan(liq[1])) and relerr(one, liq[1]) < 1e-14
     for s in range(S):
         want = orc.rstr(lr[:, s])
         assert np.array_equal(np.isnan(got[:, s]), np.isnan(want))

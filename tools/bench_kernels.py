@@ -175,6 +175,15 @@ def main():
     ls = lr[:, 0].cpu().numpy()
     c = cpu_time(lambda: orc.cmra(ls[:1500]))
     add("cmra", f"C5: S={S} L={L} window 252", ms, S * L, "stock-days", 16, 1500 / c, "1 stock x 1500 days")
+    ms = timeit(lambda: ctx.rstr(L, S, lr, 504, 21, 126, 42, b), reps=5)
+    c = cpu_time(lambda: orc.rstr(ls[:1500]))
+    add("rstr", f"C5: S={S} L={L} window 483", ms, S * L, "stock-days", 16, 1500 / c, "1 stock x 1500 days")
+    dto = dv(np.exp(rng.normal(0.2, 0.8, size=(L, S))))
+    o3 = [torch.empty_like(dto) for _ in range(3)]
+    ms = timeit(lambda: ctx.rolling_log_sum3(L, S, dto, 100.0, [21, 63, 252], [15, 42, 126], o3), reps=5)
+    tos = dto[:, 0].cpu().numpy()
+    c = cpu_time(lambda: orc.liquidity(tos[:1500]))
+    add("liquidity (STOM+STOQ+STOA)", f"C5: S={S} L={L}", ms, S * L, "stock-days", 32, 1500 / c, "1 stock x 1500 days")
     # post-processing on the long table grouped by date (T dates x N stocks)
     N, T = 5000, 750
     off = (np.arange(T + 1) * N).astype(np.int64)
@@ -193,6 +202,11 @@ def main():
     ms = timeit(lambda: ctx.orthogonalize(T, doff, dx, [dy2, dz2], o))
     c = cpu_time(lambda: [orc.orthogonalize(x[i * N:(i + 1) * N], np.column_stack([y2[i * N:(i + 1) * N], z2[i * N:(i + 1) * N]])) for i in range(50)])
     add("orthogonalize", f"N={N} T={T}, k=2", ms, N * T, "rows", 32, 50 * N / c, "50 dates")
+    sz = rng.normal(15.5, 1.4, size=N * T)
+    dsz = dv(sz)
+    ms = timeit(lambda: ctx.nlsize(T, doff, dsz, o))
+    c = cpu_time(lambda: [orc.nlsize(sz[i * N:(i + 1) * N]) for i in range(50)])
+    add("nlsize", f"N={N} T={T}", ms, N * T, "rows", 16, 50 * N / c, "50 dates")
     if args.out:
         json.dump({"peak_hbm_GBps": PEAK, "cpu_cores": os.cpu_count(), "rows": rows_out}, open(args.out, "w"), indent=1)
 

@@ -33,13 +33,18 @@ spec = torch.empty(rows, dtype=torch.float64, device="cuda")
 r2 = torch.empty(T, dtype=torch.float64, device="cuda")
 st = torch.empty(T, dtype=torch.int32, device="cuda")
 ctx = _cabi.default_context()
+GATHER = int(os.environ.get("BENCH_GATHER", "0"))
+fr_all = torch.empty((T, K), dtype=torch.float64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 times = []
 for i in range(8):
     flush.fill_(i)        # evict the panel from L2 between iterations
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    ctx.reg_by_time(T, P, Q, N, off, cap, ret, ind, style, fr, spec, r2, st)
+    if GATHER:      # the fused-gather entry point with this GPU's own buffer as the only "peer"
+        ctx.reg_by_time_gather(T, P, Q, N, off, cap, ret, ind, style, fr, spec, r2, st, [fr_all.data_ptr()] * GATHER, 0)
+    else:
+        ctx.reg_by_time(T, P, Q, N, off, cap, ret, ind, style, fr, spec, r2, st)
     e1.record()
     torch.cuda.synchronize()
     times.append(e0.elapsed_time(e1))
