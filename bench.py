@@ -271,7 +271,7 @@ def run_gpu(args):
     torch.cuda.set_stream(gs)
     ctx = _cabi.Context(local_rank, stream=gs.cuda_stream)
     nocoll = os.environ.get("BENCH_NO_COLL") == "1"     # timing experiment only (results are wrong)
-    use_graph = os.environ.get("BENCH_GRAPH", "1" if world > 1 else "0") == "1"
+    use_graph = os.environ.get("BENCH_GRAPH", "1") == "1"     # one captured step replayed (BENCH_GRAPH=0: eager launches)
 
     # this rank's block of dates (weak scaling: 2500 dates per rank)
     pan = make_panel(N_DATES, N_STOCKS, P, Q, seed=20240002 + rank, scale_log10=(-2, 2))
