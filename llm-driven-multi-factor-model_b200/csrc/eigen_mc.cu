@@ -381,7 +381,8 @@ __global__ void __launch_bounds__(64) eig_split_apply_kernel(EigSplit sp, int nb
   double* lamv = Z + K * ld;    // K
   double* d0 = lamv + K;        // K
   double* vacc = d0 + K;        // K
-  double2* s_win = reinterpret_cast<double2*>(vacc + K + (K & 1));   // EIG_WIN rotations
+  // 16-byte aligned whatever the parity of K (K * ld is odd when K is odd)
+  double2* s_win = reinterpret_cast<double2*>(Z + ((K * ld + 3 * K + 1) & ~1));   // EIG_WIN rotations
   int* s_hdr = reinterpret_cast<int*>(s_win + EIG_WIN);              // smax sweep headers
   const int per = (sp.nsim + nblk - 1) / nblk;
   const int nd = sp.P / sp.nsim;

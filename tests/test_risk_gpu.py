@@ -262,3 +262,18 @@ def test_eigenfactor_bias_stat(ops, golden_dir):
     got = mu.eigenfactor_bias_stat(frames[100:], pd.DataFrame(fr[100:]), predlen=21)
     want = orc.eigenfactor_bias_stat(covs[100:], fr[100:], predlen=21)
     assert relerr(got, want) < 1e-8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("K", [13, 17, 5])
+def test_eigen_by_time_odd_factor_counts(ops, K):
+    """Odd K: the shared-memory layouts of the split solver must keep their 16-byte pieces aligned."""
+    from bmfm.synth import make_factor_returns
+    from oracle import barra_oracle as orc
+    T = 3 * K + 8
+    fr = make_factor_returns(T, K, seed=K)
+    cov, st = ops.newey_west_by_time(fr, 1, 30.0)
+    got, est = ops.eigen_risk_adj_by_time(cov[-3:], st[-3:], 60, 5, 1.4)
+    assert (est == 0).all()
+    for i in range(3):
+        assert relerr(got[i], orc.eigen_risk_adj(cov[T - 3 + i], 60, 5, 1.4)) < TOL
