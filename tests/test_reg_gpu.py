@@ -225,3 +225,26 @@ def test_fused_gather_entry_points_single_gpu(ops):
     torch.cuda.synchronize()
     assert torch.equal(wba[row0:row0 + T], wb) and torch.equal(wva[row0:row0 + T], wv)
     assert wba.sum() == wb.sum()
+
+
+@pytest.mark.parametrize("mode", ["3", "4", "5"])
+def test_oracle_parity_shape_sweep(ops, mode, monkeypatch):
+    """Odd and even style counts on both sides of the one-tile / two-tile split of the MMA kernel, industry
+    counts around the 32-lane boundary, cross-sections shorter than a chunk, ragged dates (unaligned starts)."""
+    monkeypatch.setenv("BMFM_REG_MODE", mode)
+    from bmfm.synth import make_panel
+    from oracle import barra_oracle as orc
+    shapes = [(3, 45, 1, 1), (3, 33, 2, 2), (2, 130, 31, 6), (2, 129, 32, 7), (2, 200, 33, 9), (2, 257, 5, 11),
+              (2, 90, 3, 4), (2, 64, 12, 8), (4, 31, 2, 0), (2, 300, 50, 10)]
+    for (T, N, P, Q) in shapes:
+        for grouped in (True, False):
+            pan = make_panel(T, N, P, Q, seed=N + P + Q, ragged=0.07, scale_log10=(-1, 1))
+            csr = pan.to_csr()
+            want_fr, want_spec, want_r2 = orc.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"],
+                                                          csr["style"], P)
+            fr, spec, r2, status, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"],
+                                                      csr["style"], P, group_by_industry=grouped)
+            tag = (T, N, P, Q, grouped)
+            assert relerr(fr, want_fr) < TOL, tag
+            assert relerr(spec, want_spec, scale=np.max(np.abs(csr["ret"]))) < TOL, tag
+            assert np.max(np.abs(r2 - want_r2)) < TOL, tag

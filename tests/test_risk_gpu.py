@@ -277,3 +277,26 @@ def test_eigen_by_time_odd_factor_counts(ops, K):
     assert (est == 0).all()
     for i in range(3):
         assert relerr(got[i], orc.eigen_risk_adj(cov[T - 3 + i], 60, 5, 1.4)) < TOL
+
+
+@pytest.mark.gpu
+def test_newey_west_and_vol_regime_shape_sweep(ops):
+    """Odd / even K, every supported lag count, series shorter than one chunk and not a multiple of it."""
+    from bmfm.synth import make_factor_returns
+    from oracle import barra_oracle as orc
+    for (T, K, q, tao) in [(9, 3, 0, 5.0), (30, 5, 4, 12.0), (77, 13, 3, 40.0), (150, 8, 1, 60.0), (301, 21, 2, 90.0),
+                           (1000, 7, 2, 252.0)]:
+        fr = make_factor_returns(T, K, seed=T + K) + 0.002
+        cov, st = ops.newey_west_by_time(fr, q, tao)
+        want = orc.newey_west_by_time(fr, q, tao)
+        for t in list(range(0, T, max(1, T // 25))) + [T - 1]:
+            if want[t] is None:
+                assert st[t] != 0, (T, K, q, t)
+            else:
+                assert st[t] == 0 and relerr(cov[t], want[t]) < TOL, (T, K, q, t)
+        vr, lamb = ops.vol_regime_adj_by_time(fr, np.nan_to_num(cov), st, 21.0)
+        wv, wl = orc.vol_regime_adj_by_time(fr, want, 21.0)
+        assert relerr(np.asarray(lamb), np.asarray(wl)) < TOL, (T, K, q)
+        for t in (T - 1, T // 2):
+            if wv[t] is not None:
+                assert relerr(vr[t], wv[t]) < TOL, (T, K, q, t)
