@@ -29,7 +29,7 @@ namespace bmfm {
 constexpr int NW_MAX_Q = 4;
 constexpr int NW_LOCAL_THREADS = 512;   // chunk-total kernel: one state element per thread
 constexpr int NW_EMIT_THREADS = 128;    // emit kernel: one 2 x 2 block of the covariance per thread
-constexpr int NW_TARGET_CHUNKS = 72;    // chunks per series aimed at (state traffic ~ nchunks * 44 KB at K = 42)
+constexpr int NW_TARGET_CHUNKS = 144;   // chunks per series aimed at (state traffic ~ nchunks * 44 KB at K = 42)
 constexpr int NW_EMIT_SMEM = 56 * 1024; // shared memory the emit kernel may use (several CTAs per SM)
 
 struct NwParams {
@@ -271,9 +271,13 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
   // one 2 x 2 block of V per thread: rows a, a+1 and columns b, b+1 share their loads
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
   const int KB = (K + 1) >> 1;
+  // V is symmetric: only blocks on or above the block diagonal are computed (row-major enumeration of the
+  // upper triangle of the KB x KB block grid), each thread also stores the transpose of its block
   const int e = blockIdx.y * nt + tid;
-  if (e < KB * KB) {
-    const int a = 2 * (e / KB), b = 2 * (e - (e / KB) * KB);
+  if (e < KB * (KB + 1) / 2) {
+    int ba = 0, rem = e;
+    while (rem >= KB - ba) { rem -= KB - ba; ++ba; }
+    const int a = 2 * ba, b = 2 * (ba + rem);
     const int a1 = a + 1 < K ? a + 1 : a, b1 = b + 1 < K ? b + 1 : b;     // clamped partner (stores are guarded)
     const bool aok = a + 1 < K, bok = b + 1 < K;
     const bool keven = (K & 1) == 0 && (reinterpret_cast<uintptr_t>(p.cov) & 15) == 0;
@@ -296,6 +300,7 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
     const int jnan = min(jhi, max(q, K) - r0);                      // dates with L = r + 1 <= max(q, K): NaN
     const long long kk = (long long)K * K;
     double* dst = p.cov + (((long long)(r0 - p.t0) * K + a) * K + b);   // date r0 (dereferenced for emitted dates only)
+    double* dstT = p.cov + (((long long)(r0 - p.t0) * K + b) * K + a);
     for (int j = 0; j < jhi; ++j) {
       const double* xr = sx + (q + j) * K;
       const double va[2] = {xr[a], xr[a1]}, vb[2] = {xr[b], xr[b1]};
@@ -333,9 +338,13 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
           o10 = acc[1][0] * iz - ma[1] * mb[0] * cc - mb[0] * ua[1] - ma[1] * ub[0];
           o11 = acc[1][1] * iz - ma[1] * mb[1] * cc - mb[1] * ua[1] - ma[1] * ub[1];
         }
-        if (keven) {                       // b even and K even: 16-byte aligned pairs
+        if (keven) {                       // a, b even and K even: 16-byte aligned pairs
           st_stream2(dst, o00, o01);
           st_stream2(dst + K, o10, o11);
+          if (a != b) {                    // the transposed block, rows b, b+1 and columns a, a+1
+            st_stream2(dstT, o00, o10);
+            st_stream2(dstT + K, o01, o11);
+          }
         } else {
           st_stream(dst, o00);
           if (bok) st_stream(dst + 1, o01);
@@ -343,9 +352,18 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
             st_stream(dst + K, o10);
             if (bok) st_stream(dst + K + 1, o11);
           }
+          if (a != b) {
+            st_stream(dstT, o00);
+            if (aok) st_stream(dstT + 1, o10);
+            if (bok) {
+              st_stream(dstT + K, o01);
+              if (aok) st_stream(dstT + K + 1, o11);
+            }
+          }
         }
       }
       dst += kk;
+      dstT += kk;
     }
   }
   if (blockIdx.y == 0)
@@ -361,7 +379,7 @@ template <int QL>
 static int nw_launch_emit(bmfm_ctx* ctx, const NwParams& p, int nchunks_emit, size_t smem_emit) {
   if (smem_emit > 48 * 1024)
     BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_emit<QL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_emit));
-  nw_emit<QL><<<dim3(nchunks_emit, (((p.K + 1) / 2) * ((p.K + 1) / 2) + NW_EMIT_THREADS - 1) / NW_EMIT_THREADS), NW_EMIT_THREADS, smem_emit, ctx->stream>>>(p);
+  nw_emit<QL><<<dim3(nchunks_emit, (((p.K + 1) / 2) * ((p.K + 1) / 2 + 1) / 2 + NW_EMIT_THREADS - 1) / NW_EMIT_THREADS), NW_EMIT_THREADS, smem_emit, ctx->stream>>>(p);
   return BMFM_OK;
 }
 
