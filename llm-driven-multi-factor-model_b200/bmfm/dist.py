@@ -100,6 +100,25 @@ class GpuBackend:
         self.ctx.newey_west_by_time_range(T, K, q, tao, fr_all, t0, t1, cov, st)
         return cov, st
 
+    def nw_shard_total(self, fr_all, t0, t1, q, tao, rank, world):
+        """State record (1-D tensor) of this rank's dates reduced from a zero state
+        (bmfm_newey_west_shard_totals with this GPU's own buffer as the only destination)."""
+        import torch
+        T, K = fr_all.shape
+        ns = self.ctx.newey_west_state_doubles(K, q)
+        buf = torch.zeros((world, ns), dtype=torch.float64, device=fr_all.device)
+        self.ctx.newey_west_shard_totals(T, K, q, tao, fr_all, t0, t1, rank, [buf.data_ptr()])
+        return buf[rank]
+
+    def nw_shard_emit(self, fr_all, t0, t1, q, tao, rank, range_ends, totals):
+        """Covariances of [t0, t1) from the chunk states left by nw_shard_total and every rank's record."""
+        import torch
+        T, K = fr_all.shape
+        cov = torch.empty((t1 - t0, K, K), dtype=torch.float64, device=fr_all.device)
+        st = torch.empty(t1 - t0, dtype=torch.int32, device=fr_all.device)
+        self.ctx.newey_west_shard_emit(T, K, q, tao, fr_all, t0, t1, rank, range_ends[:rank], totals.contiguous(), cov, st)
+        return cov, st
+
     def eigen(self, cov, status, T_sim, M, scale, sim_range=None, allreduce=None):
         from .ops import eigen_risk_adj_device
         return eigen_risk_adj_device(self.ctx, cov, status, T_sim, M, scale, sim_range, allreduce)
@@ -130,10 +149,12 @@ class RiskPipeline:
         self.rank, self.world, self.group = rank, world, group
 
     def run(self, counts, P, Q, max_rows, off, cap, ret, ind, style, q=2, tao_nw=252, tao_vr=84,
-            eigen=None, symmetric=None):
+            eigen=None, symmetric=None, shard_nw=False):
         """`counts[r]` = number of dates owned by rank r (date order = rank order); the panel arrays are
         this rank's block.  `eigen` = None (vol-regime directly on the Newey-West covariances, BASELINE
-        config 2) or dict(T_sim=, M=, scale_coef=).  Returns a dict of this rank's blocks + lamb_all."""
+        config 2) or dict(T_sim=, M=, scale_coef=).  `shard_nw`: Newey-West by exchanged state records (see
+        bmfm_newey_west_shard_totals) instead of the whole-series pass.  Returns a dict of this rank's blocks +
+        lamb_all."""
         T_total = int(sum(counts))
         t0 = int(sum(counts[: self.rank]))
         n = int(counts[self.rank])
@@ -143,7 +164,15 @@ class RiskPipeline:
                                    tao_vr, eigen)
         fr, spec, r2, status = self.b.reg(n, P, Q, max_rows, off, cap, ret, ind, style)
         fr_all = all_gather_rows(fr, counts, self.group)
-        nw, nw_st = self.b.newey_west_range(fr_all, t0, t0 + n, q, tao_nw)
+        if shard_nw and self.world > 1:
+            # every rank reduces its own dates only and the ranks exchange one state record each (instead of
+            # every rank reducing all earlier dates of the gathered series)
+            rec = self.b.nw_shard_total(fr_all, t0, t0 + n, q, tao_nw, self.rank, self.world)
+            totals = all_gather_rows(rec.reshape(1, -1), [1] * self.world, self.group)
+            ends = [int(sum(counts[: r + 1])) for r in range(self.world)]
+            nw, nw_st = self.b.nw_shard_emit(fr_all, t0, t0 + n, q, tao_nw, self.rank, ends, totals)
+        else:
+            nw, nw_st = self.b.newey_west_range(fr_all, t0, t0 + n, q, tao_nw)
         cov, cov_st = nw, nw_st
         if eigen is not None:
             cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])

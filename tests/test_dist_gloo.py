@@ -35,6 +35,76 @@ class OracleBackend:
                 pass
         return torch.from_numpy(cov), torch.from_numpy(st)
 
+    # -- Newey-West by exchanged state records: the recurrence form of csrc/newey_west.cu restated in numpy --
+    @staticmethod
+    def _nw_zero(K, q):
+        return {"A": np.zeros((1 + q, K, K)), "S": np.zeros(K), "R": np.zeros((q, K)), "P": np.zeros((q, K)),
+                "Z": 0.0, "Zi": np.zeros(q)}
+
+    @staticmethod
+    def _nw_advance(s, fr, r, lam, q):
+        x = fr[r]
+        s["A"][0] = lam * s["A"][0] + np.outer(x, x)
+        s["S"] = lam * s["S"] + x
+        s["Z"] = lam * s["Z"] + 1.0
+        for i in range(1, q + 1):
+            xl = fr[r - i] if r - i >= 0 else np.zeros_like(x)
+            s["A"][i] = lam * s["A"][i] + np.outer(xl, x)
+            s["P"][i - 1] = lam * s["P"][i - 1] + xl
+            s["R"][i - 1] = lam * s["R"][i - 1] + (x if r >= i else 0.0)
+            s["Zi"][i - 1] = lam * s["Zi"][i - 1] + (1.0 if r >= i else 0.0)
+
+    @staticmethod
+    def _nw_cov(s, q):
+        Z = s["Z"]
+        m = s["S"] / Z
+        V = s["A"][0] / Z - np.outer(m, m)
+        for i in range(1, q + 1):
+            G = (s["A"][i] - np.outer(s["P"][i - 1], m) - np.outer(m, s["R"][i - 1]) + np.outer(m, m) * s["Zi"][i - 1]) / Z
+            V = V + (1 - i / (1 + q)) * (G + G.T)
+        return V
+
+    @staticmethod
+    def _nw_flat(s):
+        return np.concatenate([s["A"].ravel(), s["S"], s["R"].ravel(), s["P"].ravel(), [s["Z"]], s["Zi"]])
+
+    @staticmethod
+    def _nw_unflat(v, K, q):
+        s = OracleBackend._nw_zero(K, q)
+        o = 0
+        for key in ("A", "S", "R", "P"):
+            n = s[key].size
+            s[key] = v[o:o + n].reshape(s[key].shape).copy()
+            o += n
+        s["Z"] = float(v[o])
+        s["Zi"] = v[o + 1:o + 1 + q].copy()
+        return s
+
+    def nw_shard_total(self, fr_all, t0, t1, q, tao, rank, world):
+        fr = fr_all.numpy()
+        lam = 0.5 ** (1.0 / tao)
+        s = self._nw_zero(fr.shape[1], q)
+        for r in range(t0, t1):
+            self._nw_advance(s, fr, r, lam, q)
+        return torch.from_numpy(self._nw_flat(s))
+
+    def nw_shard_emit(self, fr_all, t0, t1, q, tao, rank, range_ends, totals):
+        fr, tot = fr_all.numpy(), totals.numpy()
+        K = fr.shape[1]
+        lam = 0.5 ** (1.0 / tao)
+        carry = np.zeros(tot.shape[1])
+        for r in range(rank):
+            carry += lam ** (t0 - range_ends[r]) * tot[r]
+        s = self._nw_unflat(carry, K, q)
+        cov = np.full((t1 - t0, K, K), np.nan)
+        st = np.ones(t1 - t0, dtype=np.int32)
+        for r in range(t0, t1):
+            self._nw_advance(s, fr, r, lam, q)
+            if r + 1 > max(q, K):
+                cov[r - t0] = self._nw_cov(s, q)
+                st[r - t0] = 0
+        return torch.from_numpy(cov), torch.from_numpy(st)
+
     def eigen(self, cov, status, T_sim, M, scale, sim_range=None, allreduce=None):
         cov, status = cov.numpy(), status.numpy()
         T, K = cov.shape[0], cov.shape[1]
@@ -93,7 +163,7 @@ def _panel():
     return make_panel(T=40, N=30, P=3, Q=2, seed=77, ragged=0.1)
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, shard_nw=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -109,7 +179,7 @@ def _worker(rank, world, port, q):
         pipe = bd.RiskPipeline(OracleBackend(), rank, world)
         res = pipe.run(counts, pan.P, pan.Q, pan.N, off, tt(csr["cap"][a:b]), tt(csr["ret"][a:b]),
                        tt(csr["ind"][a:b]), tt(csr["style"][a:b]), q=2, tao_nw=15, tao_vr=8,
-                       eigen=dict(T_sim=30, M=4, scale_coef=1.4))
+                       eigen=dict(T_sim=30, M=4, scale_coef=1.4), shard_nw=shard_nw)
         # config-4 style: all dates on every rank, simulations sharded
         fr_all = res["factor_ret_all"]
         nw_all, st_all = OracleBackend().newey_west_range(fr_all, 0, T, 2, 15)
@@ -129,13 +199,35 @@ def test_shard_range_partitions():
             assert max(sizes) - min(sizes) <= 1 and sizes == bd.shard_counts(n, world)
 
 
+def test_newey_west_recurrence_and_record_exchange():
+    """The recurrence form behind the date-sharded Newey-West (one state record per rank, decayed and summed
+    into the next ranks' carry-in) against the reference's from-scratch weighted covariance, in numpy."""
+    from bmfm.synth import make_factor_returns
+    ob = OracleBackend()
+    for (T, K, q, tao, world) in [(60, 4, 2, 9.0, 3), (45, 3, 0, 20.0, 2), (80, 5, 3, 14.0, 4)]:
+        fr = torch.from_numpy(make_factor_returns(T, K, seed=T + K) + 0.004)
+        ranges = [bd.shard_range(T, r, world) for r in range(world)]
+        ends = [hi for (_, hi) in ranges]
+        totals = torch.stack([ob.nw_shard_total(fr, lo, hi, q, tao, r, world) for r, (lo, hi) in enumerate(ranges)])
+        for r, (lo, hi) in enumerate(ranges):
+            cov, st = ob.nw_shard_emit(fr, lo, hi, q, tao, r, ends, totals)
+            for t in range(lo, hi):
+                if t + 1 > max(q, K):
+                    want = orc.newey_west(fr.numpy()[:t + 1], q, tao)
+                    assert st[t - lo] == 0
+                    assert np.max(np.abs(cov[t - lo].numpy() - want)) < 1e-12 * np.max(np.abs(want))
+                else:
+                    assert st[t - lo] != 0
+
+
 @pytest.mark.timeout(300)
-def test_sharded_pipeline_matches_single_process():
+@pytest.mark.parametrize("shard_nw", [False, True])
+def test_sharded_pipeline_matches_single_process(shard_nw):
     world = 2
     port = _free_port()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, shard_nw)) for r in range(world)]
     for p in procs:
         p.start()
     got = {}

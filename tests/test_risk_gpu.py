@@ -300,3 +300,26 @@ def test_newey_west_and_vol_regime_shape_sweep(ops):
         for t in (T - 1, T // 2):
             if wv[t] is not None:
                 assert relerr(vr[t], wv[t]) < TOL, (T, K, q, t)
+
+
+@pytest.mark.gpu
+def test_backend_record_exchange_path(ops):
+    """GpuBackend.nw_shard_total / nw_shard_emit (what RiskPipeline.run(shard_nw=True) drives over NCCL or gloo),
+    three emulated ranks with a context each, against the un-sharded pass."""
+    import torch
+    from bmfm import _cabi, dist as bd
+    from bmfm.synth import make_factor_returns
+    T, K, q, tao, world = 420, 11, 2, 50.0, 3
+    fr = make_factor_returns(T, K, seed=9)
+    cov_full, st_full = ops.newey_west_by_time(fr, q, tao)
+    d_fr = torch.from_numpy(fr).cuda()
+    bes = [bd.GpuBackend(_cabi.Context(0)) for _ in range(world)]
+    ranges = [bd.shard_range(T, r, world) for r in range(world)]
+    ends = [hi for (_, hi) in ranges]
+    totals = torch.stack([bes[r].nw_shard_total(d_fr, lo, hi, q, tao, r, world) for r, (lo, hi) in enumerate(ranges)])
+    scale = np.nanmax(np.abs(cov_full))
+    for r, (lo, hi) in enumerate(ranges):
+        cov, st = bes[r].nw_shard_emit(d_fr, lo, hi, q, tao, r, ends, totals)
+        assert np.array_equal(st.cpu().numpy(), st_full[lo:hi])
+        ok = st_full[lo:hi] == 0
+        assert np.max(np.abs(cov.cpu().numpy()[ok] - cov_full[lo:hi][ok])) < 1e-12 * scale
