@@ -154,7 +154,7 @@ int bmfm_newey_west_shard_emit(bmfm_ctx* ctx, int T_total, int K, int q, double 
  * Same arguments and results as bmfm_newey_west_by_time, but the chunk-state scratch is a fixed
  * 16 MiB array inside the library image (held by every GPU that loads the library, until exit)
  * and no path through the call allocates.  Sizes whose state does not fit are refused with
- * BMFM_E_UNSUPPORTED (K = 42, q = 2 fits for any T up to about 35 000).  The first call on a
+ * BMFM_E_UNSUPPORTED (K = 42, q = 2 fits for any T up to about 85 000).  The first call on a
  * device looks up the array's device address — make it before any stream capture.  Calls on one
  * device share the array: nothing in it needs clearing between calls, but calls that overlap on
  * the GPU race on it, so serialise them.

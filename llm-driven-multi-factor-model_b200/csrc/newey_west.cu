@@ -531,7 +531,7 @@ static int nw_static_chunk(int T, int K, int q) {
 // Same computation and results as bmfm_newey_west_by_time, with no cudaMalloc, cudaFree or other
 // allocating call on any path.
 //   * Limits: q <= 4, and (1+q)(K^2+1) + (1+2q)K doubles of state per chunk must fit the 16 MiB
-//     array with chunks short enough for shared memory (K = 42, q = 2: any T up to ~35 000);
+//     array with chunks short enough for shared memory (K = 42, q = 2: any T up to ~85 000);
 //     larger problems are rejected with BMFM_E_UNSUPPORTED and a message, nothing is launched.
 //   * The first call on a device resolves the array's device address (cudaGetSymbolAddress);
 //     make that first call before starting any stream capture.
