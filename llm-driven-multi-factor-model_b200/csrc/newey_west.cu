@@ -487,12 +487,12 @@ extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, doubl
                                        const double* factor_ret, double* cov, int32_t* status) {
   if (!ctx) return BMFM_E_ARG;
   BMFM_ARG(ctx, T >= 0 && K > 0 && q >= 0 && tao > 0, "bad sizes");
-  BMFM_ARG(ctx, factor_ret && cov && status, "NULL pointer");
   if (q > NW_MAX_Q) {
     snprintf(ctx->err, sizeof(ctx->err), "q=%d exceeds compiled limit %d", q, NW_MAX_Q);
     return BMFM_E_UNSUPPORTED;
   }
-  if (T == 0) return BMFM_OK;
+  if (T == 0) return BMFM_OK;      // an empty series needs no buffers
+  BMFM_ARG(ctx, factor_ret && cov && status, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
   if (rc) return rc;

@@ -1311,6 +1311,7 @@ static int reg_by_time_impl(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per
                             int64_t peer_row0) {
   if (!ctx) return BMFM_E_ARG;
   BMFM_ARG(ctx, T >= 0 && P >= 0 && Q >= 0, "T, P, Q must be non-negative");
+  if (T == 0 && Q <= REG_MAX_Q && P <= REG_MAX_P) return BMFM_OK;   // an empty panel needs no buffers
   BMFM_ARG(ctx, date_off && cap && ret && ind && (style || Q == 0), "NULL input");
   BMFM_ARG(ctx, factor_ret && specific_ret && r2 && status, "NULL output");
   BMFM_ARG(ctx, n_peer >= 0 && n_peer <= REG_MAX_PEERS && (n_peer == 0 || peer_bufs) && peer_row0 >= 0, "bad peer list");
