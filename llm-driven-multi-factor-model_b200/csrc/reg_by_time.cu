@@ -5,25 +5,22 @@
 //   CrossSection.__init__ / .reg         Barra-master/mfm/CrossSection.py:35-108
 //   style_factor_norm                    Barra-master/mfm/CrossSection.py:12-20
 //
-// Design (B200): one CTA per date, grid-stride over dates.  A date's rows are
-// staged ONCE into shared memory with cp.async (the per-date tile of N=800
-// stocks x 100 B is 80 KB, two CTAs per SM), so HBM sees each input byte once:
-//   pass A   thread-per-row register accumulation of the structured weighted
-//            Gram: style x style (packed), style x ret, cap-weighted style sums
-//            and the moments of the scalar np.std — the one-hot block never
-//            becomes a dense matrix;
-//   buckets  per-industry sums (weights, w*ret, cap, w*style) by half-warp per
-//            industry segment when rows are grouped by industry, shared-memory
-//            atomics otherwise (any row order is correct);
-//   solve    the industry block of the normal equations is diagonal, so the
-//            K-1 = 41 unknowns reduce by block elimination to a Q x Q SPD
-//            system (Cholesky) plus a 2 x 2 for (country, multiplier) — solved
-//            by warp 0.  Dates whose reduced system is not safely definite are
-//            flagged and redone by the dense kernel below, which forms the
-//            reference's R^T G R explicitly and applies numpy's pinv semantics
-//            (eigen-decomposition, cutoff 1e-15 * max) — CrossSection.py:69-76;
-//   pass C   specific returns + R2 from the rows still resident in shared memory.
-// Dates larger than the tile are streamed tile by tile (pass C re-reads them).
+// Design (B200).  The default kernel is reg_mma_kernel (reg_mma.cuh): 1, 2 or 4 warps own a date end to end,
+// rows stream through per-warp cp.async rings of 32-row chunks, the weighted Gram and the per-industry sums are
+// formed by FP64 tensor-core MMA, HBM sees each input byte once (the second pass for the residuals is served
+// mostly by L2).  Common to all kernels of this file:
+//   sums     structured weighted Gram: style x style (packed), style x ret, cap-weighted style sums, the
+//            moments of the scalar np.std, and per-industry sums (weights, w*ret, cap, w*style) — the one-hot
+//            block never becomes a dense matrix; any row order inside a date is correct;
+//   solve    the industry block of the normal equations is diagonal, so the K-1 = 41 unknowns reduce by block
+//            elimination to a Q x Q SPD system (Gauss-Jordan in the registers of one warp) plus a 2 x 2 for
+//            (country, multiplier).  Dates whose reduced system is not safely definite are flagged and redone
+//            by the dense kernel below, which forms the reference's R^T G R explicitly and applies numpy's
+//            pinv semantics (eigen-decomposition, cutoff 1e-15 * max) — CrossSection.py:69-76;
+//   pass C   specific returns + R2.
+// Two earlier designs are kept behind BMFM_REG_MODE for comparison and as parity cross-checks: reg_fast_kernel
+// (1: one CTA per date with the date resident in shared memory, tiles if larger) and reg_stream_kernel (2: one
+// warp per date with 97 register accumulators per lane).
 #include <stdlib.h>
 #include "bmfm_common.cuh"
 #include "jacobi.cuh"

@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Time the regression entry point alone on a synthetic panel of a given shape (CUDA events).
 
-    python tools/bench_reg.py N T [mode]        mode: BMFM_REG_MODE (0 auto, 1 CTA kernel, 2 stream kernel)
+    python tools/bench_reg.py N T [mode]        mode: BMFM_REG_MODE (0 auto; 3 / 5 / 4 = FP64-MMA kernel with 1 / 2 / 4 warps per date;
+                                                1 CTA kernel, 2 register-Gram stream kernel: earlier designs)
+    BENCH_UNGROUPED=1: rows not grouped by industry; BENCH_GATHER=n: the fused-gather entry point with n local "peers"
 """
 import os
 import sys
