@@ -129,11 +129,11 @@ __global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
 }
 
 // kernel 2: exclusive scan over chunks.  Every chunk but the last has length C, so the recurrence over chunks
-// is start_{c+1} = lam^C start_c + total_c.  Eight threads share a state element: each walks one eighth of the
-// chunks from zero, the eight partial results are chained through shared memory, then each walks its part
+// is start_{c+1} = lam^C start_c + total_c.  Sixteen threads share a state element: each walks one sixteenth of the
+// chunks from zero, the sixteen partial results are chained through shared memory, then each walks its part
 // again from its true start and overwrites the totals with the start states.  (One thread per element and a
 // serial walk over all chunks is a chain of global-memory latencies.)
-constexpr int NW_SCAN_GROUPS = 8;
+constexpr int NW_SCAN_GROUPS = 16;
 __global__ void __launch_bounds__(32 * NW_SCAN_GROUPS) nw_chunk_scan(NwParams p) {
   __shared__ double s_part[NW_SCAN_GROUPS][32];
   const int ns = nw_nstate(p.K, p.q);
