@@ -66,3 +66,36 @@ def test_short_series_status_not_error(env):
     st = torch.zeros(T, dtype=torch.int32, device="cuda")
     ctx.newey_west_by_time(T, K, 2, 10.0, fr, cov, st)
     assert (st.cpu().numpy() == _cabi.ST_SHORT).all() and bool(torch.isnan(cov).all())
+
+
+@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5"])
+def test_empty_date_inside_a_panel(env, mode, monkeypatch):
+    """A date with no rows gets NaN factor returns and BMFM_ST_NONFINITE; its neighbours are unaffected."""
+    torch, _cabi, ctx = env
+    monkeypatch.setenv("BMFM_REG_MODE", mode)
+    from bmfm.panel import pack_arrays
+    from bmfm.synth import make_panel
+    pan = make_panel(4, 90, 6, 9, seed=31)
+    csr = pan.to_csr()
+    (cap, ret, ind, style), _ = pack_arrays(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P)
+    off = csr["date_off"]
+    off2 = np.concatenate([off[:2], [off[1]], off[2:]]).astype(np.int64)      # an empty date after the first one
+    T, K = len(off2) - 1, 1 + pan.P + pan.Q
+    dv = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+    def run(o):
+        n = len(o) - 1
+        fr = torch.empty((n, K), dtype=torch.float64, device="cuda")
+        spec = torch.empty(len(cap), dtype=torch.float64, device="cuda")
+        r2 = torch.empty(n, dtype=torch.float64, device="cuda")
+        st = torch.empty(n, dtype=torch.int32, device="cuda")
+        ctx.reg_by_time(n, pan.P, pan.Q, pan.N, dv(o), dv(cap), dv(ret), dv(ind), dv(style), fr, spec, r2, st)
+        return fr.cpu().numpy(), spec.cpu().numpy(), r2.cpu().numpy(), st.cpu().numpy()
+
+    fr0, spec0, r20, st0 = run(off)
+    fr1, spec1, r21, st1 = run(off2)
+    assert (st0 == 0).all()
+    assert st1[1] == _cabi.ST_NONFINITE and np.isnan(fr1[1]).all() and np.isnan(r21[1])
+    keep = [0, 2, 3, 4]
+    assert (st1[keep] == 0).all()
+    assert np.array_equal(fr1[keep], fr0) and np.array_equal(spec1, spec0) and np.array_equal(r21[keep], r20)
