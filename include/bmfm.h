@@ -281,6 +281,12 @@ int bmfm_rolling_log_sum(bmfm_ctx* ctx, int L, int S, const double* x, double di
 int bmfm_rolling_log_sum3(bmfm_ctx* ctx, int L, int S, const double* x, double divisor, const int* windows,
                           const int* min_periods, double* const* outs);
 int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* size, double* out);
+/* The element-wise descriptors on a column of n values:
+ *   BMFM_OP_LOG      SIZE = ln(total_mv)                      compute_size  factor_calculator.py:68-77
+ *   BMFM_OP_INV_POS  BP = 1 / pb where pb > 0, NaN otherwise  compute_bp    factor_calculator.py:295-321 */
+#define BMFM_OP_LOG 0
+#define BMFM_OP_INV_POS 1
+int bmfm_elementwise(bmfm_ctx* ctx, int op, int64_t n, const double* x, double* out);
 
 /*
  * Per-date post-processing on the long table grouped by date (date_off int64 [T+1], one fp64 array

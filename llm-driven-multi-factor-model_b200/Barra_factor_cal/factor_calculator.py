@@ -2,7 +2,7 @@
 """Drop-in for the hot-path methods of Barra_factor_cal/factor_calculator.py:
 ``FactorCalculator(prices_df, index_df)``, ``_prepare_data``,
 ``compute_beta_hsigma``, ``compute_dastd``, ``compute_cmra``, ``compute_rstr``,
-``compute_liquidity``, ``compute_nlsize`` and ``run`` for those factors — same DataFrame in / DataFrame out contract (results keyed by
+``compute_liquidity``, ``compute_nlsize``, ``compute_size``, ``compute_bp`` and ``run`` for those factors — same DataFrame in / DataFrame out contract (results keyed by
 ``original_index``), rolling windows on the GPU.
 
 The long table is pivoted once into a dense [row-of-stock, stock] panel (each
@@ -87,6 +87,22 @@ class FactorCalculator:
         p[self._rows, self._codes] = self.master_df[column].values.astype(np.float64)
         return p
 
+    def compute_size(self):
+        """factor_calculator.py:68-77"""
+        print("Computing SIZE factor...")
+        return pd.DataFrame({'original_index': self.master_df['original_index'].values,
+                             'SIZE': _ops.size_factor(self.master_df['total_mv'].values)})
+
+    def compute_bp(self):
+        """factor_calculator.py:295-321: None when 'pb' is missing (:305-308)"""
+        print("Computing Value (BP) factor...")
+        if 'pb' not in self.master_df.columns:
+            print("\nERROR: 'pb' column not found in the input data.")
+            print("To compute the BP factor, you must provide Price-to-Book ratio data.\n")
+            return None
+        return pd.DataFrame({'original_index': self.master_df['original_index'].values,
+                             'BP': _ops.bp_factor(self.master_df['pb'].values)})
+
     def compute_rstr(self):
         """factor_calculator.py:127-153 (T 504, lag 21, half-life 126, min_periods 42; the oldest row of the
         window carries weight 1, as in the reference)"""
@@ -120,7 +136,8 @@ class FactorCalculator:
     def run(self, factors_to_compute: list) -> pd.DataFrame:
         """factor_calculator.py:515-577 for the hot-path factors: merge results on original_index."""
         methods = {'BETA': self.compute_beta_hsigma, 'DASTD': self.compute_dastd, 'CMRA': self.compute_cmra,
-                   'RSTR': self.compute_rstr, 'LIQUIDITY': self.compute_liquidity, 'NLSIZE': self.compute_nlsize}
+                   'RSTR': self.compute_rstr, 'LIQUIDITY': self.compute_liquidity, 'NLSIZE': self.compute_nlsize,
+                   'SIZE': self.compute_size, 'BP': self.compute_bp}
         final = self.master_df[['original_index', 'ts_code', 'trade_date', 'ret']].copy()
         for name in factors_to_compute:
             key = name.upper()

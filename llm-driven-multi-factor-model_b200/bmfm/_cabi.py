@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libbmfm.so")
 
 # status codes (include/bmfm.h)
 ST_OK, ST_SHORT, ST_NOT_PSD, ST_NONFINITE, ST_PINV, ST_DUP_EDGES = 0, 1, 2, 3, 4, 5
+OP_LOG, OP_INV_POS = 0, 1
 
 _lib = None
 _lock = threading.Lock()
@@ -56,6 +57,7 @@ _SIGNATURES = {
     "bmfm_rolling_log_sum": ([_P, _I, _I, _P, _D, _I, _I, _P], _I),
     "bmfm_rolling_log_sum3": ([_P, _I, _I, _P, _D, _P, _P, _P], _I),
     "bmfm_nlsize": ([_P, _I, _P, _P, _P], _I),
+    "bmfm_elementwise": ([_P, _I, C.c_int64, _P, _P], _I),
     "bmfm_beta_hsigma": ([_P, _I, _I, _P, _P, _I, _D, _I, _P, _P], _I),
     "bmfm_dastd": ([_P, _I, _I, _P, _P, _I, _D, _I, _P], _I),
     "bmfm_cmra": ([_P, _I, _I, _P, _I, _P], _I),
@@ -273,6 +275,9 @@ class Context:
         m = (C.c_int * 3)(*[int(v) for v in min_periods])
         o = (C.c_void_p * 3)(*[int(t.data_ptr()) for t in outs])
         self.check(self._L.bmfm_rolling_log_sum3(self._h, L, S, ptr(x), float(divisor), w, m, o))
+
+    def elementwise(self, op, n, x, out):
+        self.check(self._L.bmfm_elementwise(self._h, int(op), int(n), ptr(x), ptr(out)))
 
     def nlsize(self, T, date_off, size, out):
         self.check(self._L.bmfm_nlsize(self._h, T, ptr(date_off), ptr(size), ptr(out)))

@@ -254,6 +254,26 @@ def liquidity(turnover_rate, windows=((21, 15), (63, 42), (252, 126)), divisor=1
     return tuple(o.cpu().numpy() for o in outs)
 
 
+def size_factor(total_mv, ctx=None):
+    """compute_size: ln(total_mv)."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    x = _dev(np.asarray(total_mv, dtype=np.float64))
+    o = torch.empty_like(x)
+    ctx.elementwise(_cabi.OP_LOG, x.numel(), x, o)
+    return o.cpu().numpy()
+
+
+def bp_factor(pb, ctx=None):
+    """compute_bp: 1 / pb where pb > 0, NaN otherwise."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    x = _dev(np.asarray(pb, dtype=np.float64))
+    o = torch.empty_like(x)
+    ctx.elementwise(_cabi.OP_INV_POS, x.numel(), x, o)
+    return o.cpu().numpy()
+
+
 def nlsize(date_off, size, ctx=None):
     """compute_nlsize on the long table grouped by date."""
     torch = _torch()

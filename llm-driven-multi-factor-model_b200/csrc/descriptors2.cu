@@ -170,6 +170,15 @@ __global__ void __launch_bounds__(128) nlsize_kernel(int T, const long long* dat
   }
 }
 
+// SIZE = ln(total_mv) (factor_calculator.py:68-77) and BP = 1 / pb where pb > 0, NaN otherwise (:295-321):
+// one pass, 16 B per element
+__global__ void elementwise_kernel(int op, long long n, const double* x, double* out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const double v = x[i];
+    out[i] = op == 0 ? log(v) : (v > 0.0 ? 1.0 / v : qnan2());
+  }
+}
+
 }  // namespace bmfm
 
 using namespace bmfm;
@@ -229,6 +238,21 @@ extern "C" int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const 
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
   nlsize_kernel<<<grid, 128, 0, ctx->stream>>>(T, reinterpret_cast<const long long*>(date_off), size, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_elementwise(bmfm_ctx* ctx, int op, int64_t n, const double* x, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, (op == BMFM_OP_LOG || op == BMFM_OP_INV_POS) && n >= 0, "bad arguments");
+  if (n == 0) return BMFM_OK;
+  BMFM_ARG(ctx, x && out, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  long long blocks = (n + 255) / 256;
+  const long long cap = (long long)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  elementwise_kernel<<<(int)blocks, 256, 0, ctx->stream>>>(op, (long long)n, x, out);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;

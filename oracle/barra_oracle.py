@@ -464,6 +464,19 @@ def nlsize(size):
     return out
 
 
+def size_factor(total_mv):
+    """Barra_factor_cal/factor_calculator.py:68-77: ``SIZE = ln(total_mv)``."""
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.log(np.asarray(total_mv, dtype=np.float64))
+
+
+def bp_factor(pb):
+    """Barra_factor_cal/factor_calculator.py:295-321: ``BP = 1 / pb`` where ``pb > 0``, NaN otherwise."""
+    pb = np.asarray(pb, dtype=np.float64)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.where(pb > 0, 1.0 / pb, np.nan)
+
+
 def prepare_returns(close):
     """Barra_factor_cal/factor_calculator.py:50-53 for one stock's closes in
     date order: ``pct_change`` (pandas 3: no forward fill) and log-return."""

@@ -200,6 +200,11 @@ def golden_descriptors():
     mv = np.exp(rng2.normal(13.0, 1.2, size=S))[prices["s"].values] * np.exp(rng2.normal(0, 0.02, size=len(prices)))
     mv[rng2.random(len(prices)) < 0.02] = np.nan
     prices["total_mv"] = mv
+    pb = np.exp(rng2.normal(0.7, 0.6, size=len(prices)))
+    pb[rng2.random(len(prices)) < 0.04] *= -1.0          # negative book value: BP undefined (factor_calculator.py:313)
+    pb[rng2.random(len(prices)) < 0.01] = 0.0
+    pb[rng2.random(len(prices)) < 0.02] = np.nan
+    prices["pb"] = pb
     prices = prices.sample(frac=1.0, random_state=1).reset_index(drop=True)   # arbitrary input order
     index_df = pd.DataFrame({"trade_date": dates, "close": idx_close})
     with quiet():
@@ -210,15 +215,18 @@ def golden_descriptors():
         rs = calc.compute_rstr()
         lq = calc.compute_liquidity()
         nl = calc.compute_nlsize()
+        sz = calc.compute_size()
+        bp = calc.compute_bp()
     m = calc.master_df
-    res = m[["original_index", "t", "s", "close", "ret", "log_ret", "market_ret", "turnover_rate", "total_mv"]] \
+    res = m[["original_index", "t", "s", "close", "ret", "log_ret", "market_ret", "turnover_rate", "total_mv", "pb"]] \
+        .merge(sz, on="original_index").merge(bp, on="original_index") \
         .merge(bh, on="original_index").merge(da, on="original_index").merge(cm, on="original_index") \
         .merge(rs, on="original_index").merge(lq, on="original_index").merge(nl, on="original_index")
     res = res.sort_values(["s", "t"])
     for c in ["t", "s"]:
         out[c] = res[c].values.astype(np.int64)
     for c in ["close", "ret", "log_ret", "market_ret", "BETA", "HSIGMA", "DASTD", "CMRA", "turnover_rate", "total_mv",
-              "RSTR", "STOM", "STOQ", "STOA", "NLSIZE"]:
+              "RSTR", "STOM", "STOQ", "STOA", "NLSIZE", "pb", "SIZE", "BP"]:
         out[c] = res[c].values.astype(float)
     out["index_close"] = idx_close
 

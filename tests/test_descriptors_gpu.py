@@ -95,6 +95,13 @@ def test_next_descriptors_golden(ops, desc, pre):
         assert relerr(g, desc[pre + name]) < TOL, name
 
 
+def test_size_and_bp_golden(ops, desc):
+    for got, key in ((ops.size_factor(desc["total_mv"]), "SIZE"), (ops.bp_factor(desc["pb"]), "BP")):
+        assert np.array_equal(np.isnan(got), np.isnan(desc[key])), key
+        assert relerr(got, desc[key]) < 1e-14, key
+    assert np.isnan(ops.bp_factor(np.array([-2.0, 0.0, np.nan, np.inf]))[:3]).all()
+
+
 def test_nlsize_golden_and_edges(ops, desc):
     from oracle import barra_oracle as orc
     t = desc["t"]
@@ -273,9 +280,9 @@ def test_factor_calculator_next_descriptors_dropin(desc):
     index_df = pd.DataFrame({"trade_date": dates, "close": desc["index_close"]})
     with contextlib.redirect_stdout(io.StringIO()):
         calc = fc.FactorCalculator(prices.copy(), index_df.copy())
-        res = calc.run(["RSTR", "LIQUIDITY", "NLSIZE"])
+        res = calc.run(["RSTR", "LIQUIDITY", "NLSIZE", "SIZE"])
     res = res.merge(calc.master_df[["ts_code", "trade_date", "key"]], on=["ts_code", "trade_date"]).sort_values("key")
-    for c in ["RSTR", "STOM", "STOQ", "STOA"]:
+    for c in ["RSTR", "STOM", "STOQ", "STOA", "SIZE"]:
         got = res[c].values
         assert np.array_equal(np.isnan(got), np.isnan(desc[c])), c
         assert relerr(got, desc[c]) < TOL, c

@@ -182,6 +182,9 @@ def test_next_descriptors(desc):
         out[t == d] = orc.nlsize(size[t == d])
     assert np.array_equal(np.isnan(out), np.isnan(desc["NLSIZE"]))
     assert relerr(out, desc["NLSIZE"], scale=np.nanmax(np.abs(size ** 3))) < 1e-13
+    for got, key in ((orc.size_factor(desc["total_mv"]), "SIZE"), (orc.bp_factor(desc["pb"]), "BP")):
+        assert np.array_equal(np.isnan(got), np.isnan(desc[key]))
+        assert relerr(got, desc[key]) < 1e-15
 
 
 def test_post_processing(desc):
