@@ -59,6 +59,15 @@ int bmfm_ctx_sync(bmfm_ctx* ctx);
 const char* bmfm_last_error(const bmfm_ctx* ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 long long bmfm_launch_count(const bmfm_ctx* ctx);
+/* Experiment switches of ONE context (no counterpart in the reference; they select alternative kernels
+ * for comparisons and parity cross-checks and never change results beyond rounding).  Names:
+ *   "reg_mode"  0 = automatic, 1 CTA-per-date kernel, 2 register-Gram warp kernel, 3 / 5 / 4 = FP64-MMA
+ *               kernel with 1 / 2 / 4 warps per date;   "reg_smma" 0/1;   "reg_warps", "reg_ctas";
+ *   "nw_chunks" target number of time chunks of the Newey-West pass (0 = default);
+ *   "eig_mode"  eigen Monte-Carlo solver (0 = default).
+ * bmfm_ctx_get_option also reads "last_reg_mode": the kernel form the last regression call launched. */
+int bmfm_ctx_set_option(bmfm_ctx* ctx, const char* name, int value);
+int bmfm_ctx_get_option(bmfm_ctx* ctx, const char* name, int* value);
 /* compiled limits: max styles Q, max industries P, max factors K */
 void bmfm_limits(int* max_Q, int* max_P, int* max_K);
 const char* bmfm_version(void);

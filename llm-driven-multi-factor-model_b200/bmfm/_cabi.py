@@ -30,6 +30,8 @@ _SIGNATURES = {
     "bmfm_ctx_sync": ([_P], _I),
     "bmfm_last_error": ([_P], C.c_char_p),
     "bmfm_launch_count": ([_P], C.c_longlong),
+    "bmfm_ctx_set_option": ([_P, C.c_char_p, _I], _I),
+    "bmfm_ctx_get_option": ([_P, C.c_char_p, C.POINTER(_I)], _I),
     "bmfm_limits": ([C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)], None),
     "bmfm_version": ([], C.c_char_p),
     "bmfm_reg_by_time": ([_P, _I, _I, _I, _I] + [_P] * 10, _I),
@@ -135,6 +137,15 @@ class Context:
 
     def sync(self):
         self.check(self._L.bmfm_ctx_sync(self._h))
+
+    def set_option(self, name, value):
+        """Experiment switch of this context (include/bmfm.h: bmfm_ctx_set_option)."""
+        self.check(self._L.bmfm_ctx_set_option(self._h, name.encode(), int(value)))
+
+    def get_option(self, name):
+        v = C.c_int(0)
+        self.check(self._L.bmfm_ctx_get_option(self._h, name.encode(), C.byref(v)))
+        return int(v.value)
 
     @property
     def launches(self):
@@ -301,10 +312,21 @@ _default_ctx = {}
 
 
 def default_context():
-    """A per-device context on torch's current stream, created on first use."""
+    """The context of (current device, torch's CURRENT stream), created on first use.
+
+    A context enqueues on the stream it was created with, while the wrappers in ops.py / mfm allocate, upload
+    and read back on torch's current stream at call time; keying the cache on the stream keeps kernels and
+    copies on one stream whatever ``torch.cuda.stream(...)`` block the caller is in."""
     import torch
 
-    dev = torch.cuda.current_device() if torch.cuda.is_available() else -1
-    if dev not in _default_ctx:
-        _default_ctx[dev] = Context(dev if dev >= 0 else None)
-    return _default_ctx[dev]
+    if not torch.cuda.is_available():
+        return Context(None)        # raises: there is no CPU fallback
+    dev = torch.cuda.current_device()
+    key = (dev, int(torch.cuda.current_stream().cuda_stream))
+    ctx = _default_ctx.get(key)
+    if ctx is None:
+        if len(_default_ctx) >= 16:      # side streams come and go: keep the table small
+            for k in [k for k in _default_ctx if k[0] == dev and k != (dev, 0)][:8]:
+                _default_ctx.pop(k).close()
+        ctx = _default_ctx[key] = Context(dev)
+    return ctx

@@ -192,3 +192,47 @@ def make_price_panel(T, S, seed=20240005, missing=0.005, late=0):
         for s in who:
             close[: rng.integers(1, max(2, T // 2)), s] = np.nan
     return close, index_close
+
+
+def write_demo_csv_pair(dirpath, T=1400, N=300, P=28, Q=10, seed=20240001, nan_frac=0.002, ragged=0.03):
+    """Stand-ins for the two files ``Barra-master/demo.py:22,31`` reads (the real ones are not in the
+    reference tree): ``barra_data_csi.csv`` with columns date, stocknames, capital, ret,
+    industry (a code), then Q style columns, in shuffled row order and with a few NaN cells so that
+    demo.py's NaN-row drop (:25-27) does something; ``industry_info.csv`` with columns code,
+    industry_names, start_date (P rows, the order of the one-hot block, demo.py:33-34).
+    Floats are written with ``repr`` precision, so the CSV round trip is exact.
+    Returns the two paths."""
+    import os
+    import pandas as pd
+
+    pan = make_panel(T=T, N=N, P=P, Q=Q, seed=seed, ragged=ragged, scale_log10=(-2.0, 2.0))
+    rng = np.random.default_rng(seed + 7)
+    tt, nn = np.nonzero(pan.present)
+    perm = rng.permutation(len(tt))
+    tt, nn = tt[perm], nn[perm]
+    codes = np.array([f"8011{p:02d}.SI" for p in range(P)], dtype=object)
+    style_names = ["size", "beta", "momentum", "residual_volatility", "non_linear_size",
+                   "book_to_price_ratio", "liquidity", "earnings_yield", "growth", "leverage"]
+    style_names = (style_names + [f"style_{q:02d}" for q in range(10, Q)])[:Q]
+    cols = {
+        "date": np.asarray(pan.dates, dtype=object)[tt],
+        "stocknames": np.asarray(pan.stocknames, dtype=object)[nn],
+        "capital": pan.cap[tt, nn],
+        "ret": pan.ret[tt, nn],
+        "industry": codes[pan.ind[nn]],
+    }
+    # NaN cells never fall on stocks 0..P-1, so every industry stays populated on every date after the drop
+    lead = nn < P
+    for q, name in enumerate(style_names):
+        v = pan.style[tt, nn, q].copy()
+        if nan_frac > 0:
+            v[(rng.random(len(v)) < nan_frac / Q) & ~lead] = np.nan
+        cols[name] = v
+    df = pd.DataFrame(cols)
+    os.makedirs(dirpath, exist_ok=True)
+    data_path = os.path.join(dirpath, "barra_data_csi.csv")
+    ind_path = os.path.join(dirpath, "industry_info.csv")
+    df.to_csv(data_path, index=False, float_format="%.17g")
+    pd.DataFrame({"code": codes, "industry_names": [f"SW_{p:02d}" for p in range(P)],
+                  "start_date": ["2014/01/01"] * P}).to_csv(ind_path, index=False)
+    return data_path, ind_path

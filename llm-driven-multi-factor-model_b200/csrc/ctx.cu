@@ -17,7 +17,36 @@ extern "C" int bmfm_ctx_create(bmfm_ctx** out, int device, void* stream) {
   c->own_stream = false;
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   cudaDeviceGetAttribute(&c->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  c->opt_reg_smma = -1;
   *out = c;
+  return BMFM_OK;
+}
+
+// Experiment switches, per context (so one caller's choice never changes another's kernels).
+static int* bmfm_opt_slot(bmfm_ctx* c, const char* name) {
+  if (!strcmp(name, "reg_mode")) return &c->opt_reg_mode;
+  if (!strcmp(name, "reg_smma")) return &c->opt_reg_smma;
+  if (!strcmp(name, "reg_warps")) return &c->opt_reg_warps;
+  if (!strcmp(name, "reg_ctas")) return &c->opt_reg_ctas;
+  if (!strcmp(name, "nw_chunks")) return &c->opt_nw_chunks;
+  if (!strcmp(name, "eig_mode")) return &c->opt_eig_mode;
+  if (!strcmp(name, "last_reg_mode")) return &c->last_reg_mode;
+  return nullptr;
+}
+
+extern "C" int bmfm_ctx_set_option(bmfm_ctx* c, const char* name, int value) {
+  if (!c || !name) return BMFM_E_ARG;
+  int* slot = bmfm_opt_slot(c, name);
+  BMFM_ARG(c, slot && slot != &c->last_reg_mode, "unknown option name");
+  *slot = value;
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_ctx_get_option(bmfm_ctx* c, const char* name, int* value) {
+  if (!c || !name || !value) return BMFM_E_ARG;
+  int* slot = bmfm_opt_slot(c, name);
+  BMFM_ARG(c, slot, "unknown option name");
+  *value = *slot;
   return BMFM_OK;
 }
 

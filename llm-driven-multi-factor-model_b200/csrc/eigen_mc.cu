@@ -559,8 +559,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   // solver choice (BMFM_EIG_MODE): 0 split tridiagonal QL (default, K <= 64), 2 fused tridiagonal QL,
   // 1 block Jacobi (any K)
-  int mode = 0;
-  if (const char* ev = getenv("BMFM_EIG_MODE")) mode = atoi(ev);
+  const int mode = ctx->opt_eig_mode;   // bmfm_ctx_set_option "eig_mode"
   const size_t budget = (size_t)3 << 29;   // 1.5 GiB of scratch for the split form
   const int rmax = 2 * K * K, smax = 8 * K;
   const size_t per_problem = (size_t)K * K * 8 + (size_t)3 * K * 8 + (size_t)rmax * 16 + (size_t)smax * 4 + 4;
@@ -616,8 +615,7 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
     }
   } else if (use_ql) {
     BMFM_CUDA(ctx, cudaFuncSetAttribute(eig_mc_tql_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int dbg = 0;
-    if (const char* ev = getenv("BMFM_EIG_DEBUG_STAGE")) dbg = atoi(ev);   // timing experiments only
+    const int dbg = 0;
     eig_mc_tql_kernel<<<grid, 64, smem, ctx->stream>>>(T, K, nsim, nblk, C, D0, status, partial, dbg);
     ctx->launches++;
   } else if (K == 42) {   // the flagship factor count (31 industries + 10 styles + country): compile-time loops

@@ -22,6 +22,7 @@
 // write per element.  Scratch: nchunks * ((1+q)(K^2+1) + (1+2q)K) doubles.
 #include <math.h>
 #include <stdlib.h>
+#include <mutex>
 #include "bmfm_common.cuh"
 
 namespace bmfm {
@@ -57,9 +58,8 @@ __host__ __device__ inline size_t nw_emit_smem(int C, int K, int q) {
   return ((size_t)(C + q) * K + 2 * (size_t)C * K + 2 * (size_t)C) * sizeof(double);
 }
 // chunk length: about NW_TARGET_CHUNKS chunks, at least 8 rows, short enough for the emit kernel's shared memory
-__host__ inline int nw_pick_chunk(int T, int K, int q) {
-  int target = NW_TARGET_CHUNKS;
-  if (const char* ev = getenv("BMFM_NW_CHUNKS")) target = atoi(ev) > 0 ? atoi(ev) : target;   // tuning knob
+__host__ inline int nw_pick_chunk(int T, int K, int q, int target_opt = 0) {
+  const int target = target_opt > 0 ? target_opt : NW_TARGET_CHUNKS;   // bmfm_ctx_set_option "nw_chunks": tuning knob
   int C = (T + target - 1) / target;
   if (C < 8) C = 8;
   while (C > 1 && nw_emit_smem(C, K, q) > (size_t)NW_EMIT_SMEM) --C;
@@ -448,11 +448,16 @@ extern "C" size_t bmfm_newey_west_scratch_bytes(int T, int K, int q) {
   return (size_t)nchunks * nw_nstate(K, q) * sizeof(double);
 }
 
+static size_t nw_scratch_bytes_ctx(const bmfm_ctx* ctx, int T, int K, int q) {
+  const int C = nw_pick_chunk(T, K, q, ctx->opt_nw_chunks);
+  return (size_t)((T + C - 1) / C) * nw_nstate(K, q) * sizeof(double);
+}
+
 static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const double* fr, double* cov,
                      int32_t* status, double* scratch, int t0, int t1) {
   NwParams p;
   p.T = T; p.K = K; p.q = q;
-  p.C = nw_pick_chunk(T, K, q);
+  p.C = nw_pick_chunk(T, K, q, ctx->opt_nw_chunks);
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
@@ -478,7 +483,7 @@ extern "C" int bmfm_newey_west_by_time_range(bmfm_ctx* ctx, int T, int K, int q,
   }
   if (T == 0 || t1 == t0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
+  int rc = bmfm_ws_reserve(ctx, nw_scratch_bytes_ctx(ctx, T, K, q));
   if (rc) return rc;
   return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws, t0, t1);
 }
@@ -494,7 +499,7 @@ extern "C" int bmfm_newey_west_by_time(bmfm_ctx* ctx, int T, int K, int q, doubl
   if (T == 0) return BMFM_OK;      // an empty series needs no buffers
   BMFM_ARG(ctx, factor_ret && cov && status, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  int rc = bmfm_ws_reserve(ctx, bmfm_newey_west_scratch_bytes(T, K, q));
+  int rc = bmfm_ws_reserve(ctx, nw_scratch_bytes_ctx(ctx, T, K, q));
   if (rc) return rc;
   return nw_launch(ctx, T, K, q, tao, factor_ret, cov, status, (double*)ctx->ws, 0, T);
 }
@@ -516,6 +521,7 @@ static __device__ __align__(256) double nw_static_scratch[NW_STATIC_DOUBLES];
 // address is looked up once per device (with that device current) and cached here.
 constexpr int NW_MAX_DEVICES = 64;
 static double* nw_static_ptr[NW_MAX_DEVICES];
+static std::mutex nw_static_mutex;
 
 // chunk length that keeps nchunks * nstate inside the static array (0 if impossible)
 static int nw_static_chunk(int T, int K, int q) {
@@ -565,10 +571,14 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   }
   p.nchunks = (T + p.C - 1) / p.C;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (nw_static_ptr[ctx->device] == nullptr) {
-    double* dptr = nullptr;
-    BMFM_CUDA(ctx, cudaGetSymbolAddress((void**)&dptr, nw_static_scratch));
-    nw_static_ptr[ctx->device] = dptr;
+  {
+    // contexts are one per host thread, so two threads may make their first call on a device together
+    std::lock_guard<std::mutex> guard(nw_static_mutex);
+    if (nw_static_ptr[ctx->device] == nullptr) {
+      double* dptr = nullptr;
+      BMFM_CUDA(ctx, cudaGetSymbolAddress((void**)&dptr, nw_static_scratch));
+      nw_static_ptr[ctx->device] = dptr;
+    }
   }
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;

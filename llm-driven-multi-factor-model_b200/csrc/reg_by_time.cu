@@ -1197,12 +1197,12 @@ template <int Q, int NSTAGE, int WPD>
 static int launch_reg_mma(bmfm_ctx* ctx, const RegParams& p) {
   int warps = WPD > 1 ? WPD : RM_WARPS;
   if (WPD == 1)
-    if (const char* ev = getenv("BMFM_REG_WARPS")) warps = atoi(ev) >= 1 && atoi(ev) <= RM_WARPS ? atoi(ev) : warps;
+    if (ctx->opt_reg_warps >= 1 && ctx->opt_reg_warps <= RM_WARPS) warps = ctx->opt_reg_warps;
   const int smem_s = rm_cta_bytes<Q, NSTAGE>(p.P, WPD, warps);
   BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_mma_kernel<Q, NSTAGE, WPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
   int per_sm = (228 * 1024) / (smem_s + 1024);
   if (per_sm < 1) per_sm = 1;
-  if (const char* ev = getenv("BMFM_REG_CTAS")) per_sm = atoi(ev) > 0 ? atoi(ev) : per_sm;
+  if (ctx->opt_reg_ctas > 0) per_sm = ctx->opt_reg_ctas;
   int grid = ctx->sm_count * per_sm;
   const int dates_per_cta = WPD > 1 ? 1 : warps;
   if (grid * dates_per_cta > p.T) grid = (p.T + dates_per_cta - 1) / dates_per_cta;
@@ -1236,8 +1236,7 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   // L2 footprint of the dates in flight) or when there are too few dates to fill the SMs.  BMFM_REG_MODE
   // forces a kernel: 1 = CTA kernel with the date resident in shared memory, 2 = warp-per-date kernel with
   // register accumulators (the two earlier designs, kept for comparison).
-  int mode = 0;
-  if (const char* ev = getenv("BMFM_REG_MODE")) mode = atoi(ev);
+  int mode = ctx->opt_reg_mode;
   if (mode < 1 || mode > 5) {
     int wpd = (max_rows > 0 && max_rows <= 1024) ? 1 : 2;
     const long long slots = (long long)ctx->sm_count * 12;      // warps the SMs hold with one warp per date
@@ -1245,6 +1244,7 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
     mode = wpd == 1 ? 3 : (wpd == 2 ? 5 : 4);
   }
   const bool use_stream = mode == 2;
+  ctx->last_reg_mode = p.all_dense ? 0 : mode;
   if (!p.all_dense && mode >= 3) {
     const int rc = mode == 3 ? launch_reg_mma<Q, 3, 1>(ctx, p)
                  : mode == 5 ? launch_reg_mma<Q, 2, 2>(ctx, p) : launch_reg_mma<Q, 2, RM_WARPS>(ctx, p);
@@ -1328,7 +1328,7 @@ static int reg_by_time_impl(bmfm_ctx* ctx, int T, int P, int Q, int max_rows_per
   p.n_peer = n_peer;
   p.peer_row0 = peer_row0;
   p.smma = 1;
-  if (const char* ev = getenv("BMFM_REG_SMMA")) p.smma = atoi(ev);
+  if (ctx->opt_reg_smma >= 0) p.smma = ctx->opt_reg_smma;
   for (int r = 0; r < REG_MAX_PEERS; ++r) p.peer_fr[r] = r < n_peer ? peer_bufs[r] : nullptr;
   switch (Q) {
 #define CASE(q) case q: return launch_reg<q>(ctx, p, max_rows_per_date);

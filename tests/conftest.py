@@ -37,6 +37,37 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip)
 
 
+def pytest_sessionfinish(session, exitstatus):
+    """Write the errors the parity checks observed (tests/util.py:record) where gpurun collects them."""
+    try:
+        sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+        import json
+        import util
+        if util.OBSERVED:
+            out = os.path.join(ROOT, "gpurun_out")
+            os.makedirs(out, exist_ok=True)
+            with open(os.path.join(out, "parity_observed.json"), "w") as f:
+                json.dump(dict(sorted(util.OBSERVED.items())), f, indent=1)
+    except Exception:
+        pass
+
+
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture
+def bmfm_option():
+    """Set experiment switches on the default context for one test (bmfm_ctx_set_option); reset afterwards."""
+    from bmfm import _cabi
+    ctx = _cabi.default_context()
+    touched = []
+
+    def setter(name, value):
+        ctx.set_option(name, int(value))
+        touched.append(name)
+
+    yield setter
+    for name in touched:
+        ctx.set_option(name, -1 if name == "reg_smma" else 0)

@@ -281,7 +281,87 @@ def golden_descriptors():
     print("descriptors.npz", len(out), "beta valid:", int(np.isfinite(out["BETA"]).sum()))
 
 
+DEMO_CASE = dict(T=1400, N=300, P=28, Q=10, seed=20240001)     # config C1; demo.py:38 hard-codes MFM(data, 28, 10)
+
+
+def _run_reference_demo(workdir, canonical):
+    """Execute the reference's own Barra-master/demo.py, byte-unchanged, from a scratch copy of its directory
+    layout (demo.py next to data_new/), with the reference `mfm` first on sys.path."""
+    import runpy
+    import shutil
+    bm = os.path.join(workdir, "Barra-master")
+    os.makedirs(bm, exist_ok=True)
+    shutil.copyfile("/root/reference/Barra-master/demo.py", os.path.join(bm, "demo.py"))
+    sys.path.insert(0, "/root/reference/Barra-master")
+    for name in [m for m in sys.modules if m == "mfm" or m.startswith("mfm.")]:
+        del sys.modules[name]
+    try:
+        import mfm.utils as live_utils
+        assert live_utils.__file__.startswith("/root/reference"), live_utils.__file__
+        import contextlib
+        cm = patched_eig(live_utils) if canonical else contextlib.nullcontext()
+        with quiet(), cm:
+            runpy.run_path(os.path.join(bm, "demo.py"), run_name="__main__")
+    finally:
+        sys.path.remove("/root/reference/Barra-master")
+        for name in [m for m in sys.modules if m == "mfm" or m.startswith("mfm.")]:
+            del sys.modules[name]
+    return os.path.join(bm, "results")
+
+
+def read_demo_results(results_dir):
+    """The five CSVs demo.py:59-94 writes -> arrays (index / column labels as strings)."""
+    out = {}
+    fr = pd.read_csv(os.path.join(results_dir, "factor_returns.csv"), index_col=0)
+    out["factor_ret"] = fr.values.astype(float)
+    out["factor_ret_index"] = np.asarray(fr.index.astype(str))
+    out["factor_ret_columns"] = np.asarray(fr.columns.astype(str))
+    r2 = pd.read_csv(os.path.join(results_dir, "r_squared.csv"), index_col=0)
+    out["R2"] = r2.values[:, 0].astype(float)
+    sp = pd.read_csv(os.path.join(results_dir, "specific_returns.csv"), index_col=0)
+    out["specific_columns"] = np.asarray(sp.columns.astype(str))
+    out["specific_index"] = np.asarray(sp.index.astype(str))
+    out["specific_full"] = sp.values.astype(float)
+    cov = pd.read_csv(os.path.join(results_dir, "final_vol_regime_adj_covariance.csv"), index_col=0)
+    out["final_cov"] = cov.values.astype(float)
+    out["final_cov_labels"] = np.asarray(cov.columns.astype(str))
+    lam = pd.read_csv(os.path.join(results_dir, "volatility_multiplier_lambda.csv"), index_col=0)
+    out["lamb"] = lam.values[:, 0].astype(float)
+    return out
+
+
+def golden_demo():
+    """Config C1 / row g: the reference's demo.py run UNCHANGED on the stand-in CSV pair (the
+    real files are not in the tree), eigen order canonical.  The fixture also carries demo.py's bytes so the
+    GPU test can execute the very same file where /root/reference does not exist."""
+    import hashlib
+    import tempfile
+    from bmfm.synth import write_demo_csv_pair
+    out = {}
+    with tempfile.TemporaryDirectory() as wd:
+        dpath, ipath = write_demo_csv_pair(os.path.join(wd, "Barra-master", "data_new"), **DEMO_CASE)
+        out["csv_sha256"] = np.array([hashlib.sha256(open(p, "rb").read()).hexdigest() for p in (dpath, ipath)])
+        res = read_demo_results(_run_reference_demo(wd, canonical=True))
+    src = open("/root/reference/Barra-master/demo.py", "rb").read()
+    out["demo_py"] = np.frombuffer(src, dtype=np.uint8)
+    out["demo_py_sha256"] = np.array(hashlib.sha256(src).hexdigest())
+    for k, v in DEMO_CASE.items():
+        out["case_" + k] = np.int64(v)
+    # specific returns: every 8th date and the last 40 in full, per-date sums of all dates as a checksum
+    full = res.pop("specific_full")
+    T = full.shape[0]
+    keep = np.unique(np.concatenate([np.arange(0, T, 8), np.arange(max(0, T - 40), T)]))
+    out["specific_keep"] = keep.astype(np.int64)
+    out["specific_rows"] = full[keep]
+    out["specific_sum"] = np.nansum(full, axis=1)
+    out["specific_sumsq"] = np.nansum(full * full, axis=1)
+    out["specific_count"] = np.isfinite(full).sum(axis=1).astype(np.int64)
+    out.update(res)
+    np.savez_compressed(os.path.join(HERE, "demo.npz"), **out)
+    print("demo.npz", {k: getattr(v, "shape", None) for k, v in out.items()})
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["reg", "risk", "pipeline", "descriptors"]
+    which = sys.argv[1:] or ["reg", "risk", "pipeline", "descriptors", "demo"]
     for w in which:
         globals()[f"golden_{w}"]()

@@ -69,10 +69,10 @@ def test_short_series_status_not_error(env):
 
 
 @pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5"])
-def test_empty_date_inside_a_panel(env, mode, monkeypatch):
+def test_empty_date_inside_a_panel(env, mode, bmfm_option):
     """A date with no rows gets NaN factor returns and BMFM_ST_NONFINITE; its neighbours are unaffected."""
     torch, _cabi, ctx = env
-    monkeypatch.setenv("BMFM_REG_MODE", mode)
+    bmfm_option("reg_mode", mode)
     from bmfm.panel import pack_arrays
     from bmfm.synth import make_panel
     pan = make_panel(4, 90, 6, 9, seed=31)

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from util import relerr
+from util import record, relerr, relerr_cols, relerr_cov
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-9
@@ -37,11 +37,12 @@ def test_newey_west_golden(ops, risk, q, tao):
     assert np.array_equal(status == 0, ok)
     assert (status[~ok] == 1).all()   # BMFM_ST_SHORT
     for t in np.nonzero(ok)[0]:
-        assert relerr(cov[t], want[t]) < 1e-11, t
+        assert record("nw.golden[per element / sqrt(diag diag)]", relerr_cov(cov[t], want[t])) < 1e-11, t
     assert np.isnan(cov[~ok]).all()
 
 
-@pytest.mark.parametrize("T,K,q,tao", [(700, 42, 2, 252), (300, 12, 4, 30), (50, 3, 1, 5)])
+@pytest.mark.parametrize("T,K,q,tao", [(700, 42, 2, 252), (300, 12, 4, 30), (50, 3, 1, 5),
+                                       (2500, 42, 2, 252), (3750, 42, 2, 252)])     # configs C2 and C3 / C4
 def test_newey_west_oracle(ops, T, K, q, tao):
     """Chunked recurrence (several chunks, chunk boundaries crossing the lags) vs the direct sums."""
     from bmfm.synth import make_factor_returns
@@ -53,7 +54,8 @@ def test_newey_west_oracle(ops, T, K, q, tao):
             assert status[t] == 1
         else:
             assert status[t] == 0
-            assert relerr(cov[t], orc.newey_west(fr[:t + 1], q, tao)) < 1e-11, t
+            assert record(f"nw.oracle.T{T}_K{K}[per element / sqrt(diag diag)]",
+                          relerr_cov(cov[t], orc.newey_west(fr[:t + 1], q, tao))) < 1e-11, t
 
 
 def test_vol_regime_golden(ops, pipe):
@@ -82,12 +84,13 @@ def test_gauss_cov_legacy_stream(ops):
 
 @pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
 @pytest.mark.parametrize("solver", ["0", "1", "2"])     # 0: split tridiagonal QL (default), 1: block Jacobi, 2: fused QL
-def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, monkeypatch):
-    monkeypatch.setenv("BMFM_EIG_MODE", solver)
+def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, bmfm_option):
+    bmfm_option("eig_mode", solver)
     cov = risk["eig_cov_in"]
     out, status = ops.eigen_risk_adj_by_time(cov[None], None, T, M, 1.4)
     assert status[0] == 0
-    assert relerr(out[0], risk[f"eig_T{T}_M{M}_canonical"]) < TOL
+    assert record(f"eigen.golden.T{T}_M{M}[per element / sqrt(diag diag)]",
+                  relerr_cov(out[0], risk[f"eig_T{T}_M{M}_canonical"])) < TOL
     # the literal reference output depends on LAPACK's eigenvalue order:
     # report the gap, do not assert on it
     gap = relerr(out[0], risk[f"eig_T{T}_M{M}_literal"])
@@ -95,9 +98,9 @@ def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, monkeypatch):
 
 
 @pytest.mark.parametrize("solver", ["0", "1", "2"])
-def test_eigen_by_time_oracle(ops, solver, monkeypatch):
+def test_eigen_by_time_oracle(ops, solver, bmfm_option):
     """K = 42 factor covariances from an expanding Newey-West run, simulation length 252."""
-    monkeypatch.setenv("BMFM_EIG_MODE", solver)
+    bmfm_option("eig_mode", solver)
     from bmfm.synth import make_factor_returns
     from oracle import barra_oracle as orc
     K, T = 42, 140
@@ -108,12 +111,29 @@ def test_eigen_by_time_oracle(ops, solver, monkeypatch):
     for j, t in enumerate(sel):
         assert status[j] == 0
         want = orc.eigen_risk_adj(nw[t], 252, 12, 1.4)
-        assert relerr(out[j], want) < TOL, t
+        assert record("eigen.oracle.K42_M12[per element / sqrt(diag diag)]", relerr_cov(out[j], want)) < TOL, t
     # short windows stay invalid, non-PSD input is gated (utils.py:67-68)
     bad = -np.eye(K)[None]
     o2, s2 = ops.eigen_risk_adj_by_time(np.concatenate([np.nan_to_num(nw[:2]), bad]),
                                         np.array([1, 1, 0], dtype=np.int32), 50, 3, 1.4)
     assert list(s2) == [1, 1, 2] and np.isnan(o2).all()
+
+
+def test_eigen_config_size_simulation_count(ops):
+    """Seeds far beyond the small cases (m = 1 .. 2000: the legacy stream of every simulation is its own
+    MT19937 sequence) and a problem count that spans several batches of the solver: two dates x 2000
+    simulations, K = 42, window 252, against the oracle."""
+    from bmfm.synth import make_factor_returns
+    from oracle import barra_oracle as orc
+    K, T = 42, 120
+    fr = make_factor_returns(T, K, seed=17)
+    nw, nw_status = ops.newey_west_by_time(fr, 2, 60)
+    sel = [80, 119]
+    out, status = ops.eigen_risk_adj_by_time(nw[sel], nw_status[sel], 252, 2000, 1.4)
+    assert (status == 0).all()
+    for j, t in enumerate(sel):
+        want = orc.eigen_risk_adj(nw[t], 252, 2000, 1.4)
+        assert record("eigen.oracle.K42_M2000[per element / sqrt(diag diag)]", relerr_cov(out[j], want)) < TOL, t
 
 
 def test_mfm_dropin_full_pipeline(pipe):
@@ -141,11 +161,11 @@ def test_mfm_dropin_full_pipeline(pipe):
     assert [len(c) > 0 for c in vr] == list(pipe["vr_ok"])
     for t in range(pan.T):
         if pipe["nw_ok"][t]:
-            assert relerr(nw[t].values, pipe["nw"][t]) < TOL
+            assert record("pipeline.nw", relerr_cov(nw[t].values, pipe["nw"][t])) < TOL
             assert list(nw[t].columns) == list(model.factor_ret.columns)
         if pipe["er_ok"][t]:
-            assert relerr(er[t].values, pipe["er"][t]) < TOL
-            assert relerr(vr[t].values, pipe["vr"][t]) < TOL
+            assert record("pipeline.er", relerr_cov(er[t].values, pipe["er"][t])) < TOL
+            assert record("pipeline.vr", relerr_cov(vr[t].values, pipe["vr"][t])) < TOL
     assert relerr(np.array(lamb), pipe["lamb"]) < TOL
     assert isinstance(lamb, list) and isinstance(lamb[0], float)
 
@@ -248,7 +268,7 @@ def test_eigenfactor_bias_stat(ops, golden_dir):
     ok = g["nw_ok"][40:].astype(bool)
     st = np.where(ok, 0, 1).astype(np.int32)
     got = ops.eigenfactor_bias_stat(np.nan_to_num(g["nw"][40:]), st, g["factor_ret"][40:], predlen=5)
-    assert relerr(got, g["bias_stat_nw"]) < 1e-8
+    assert record("bias_stat.golden", relerr_cols(got[None], g["bias_stat_nw"][None])) < TOL
     T, K = 400, 17
     fr = make_factor_returns(T, K, seed=23)
     cov, status = ops.newey_west_by_time(fr, 2, 90.0)
@@ -256,12 +276,12 @@ def test_eigenfactor_bias_stat(ops, golden_dir):
     for predlen in (1, 21):
         want = orc.eigenfactor_bias_stat(covs, fr, predlen=predlen)
         got = ops.eigenfactor_bias_stat(np.nan_to_num(cov), status, fr, predlen=predlen)
-        assert relerr(got, want) < 1e-8
+        assert record(f"bias_stat.oracle.predlen{predlen}", relerr_cols(got[None], want[None])) < TOL
     from mfm import utils as mu
     frames = [pd.DataFrame(cov[t]) if status[t] == 0 else pd.DataFrame() for t in range(T)]
     got = mu.eigenfactor_bias_stat(frames[100:], pd.DataFrame(fr[100:]), predlen=21)
     want = orc.eigenfactor_bias_stat(covs[100:], fr[100:], predlen=21)
-    assert relerr(got, want) < 1e-8
+    assert relerr_cols(got[None], want[None]) < TOL
 
 
 @pytest.mark.gpu

@@ -44,6 +44,32 @@ def test_noalloc_matches_regular_entry_twice_in_a_row():
         assert np.abs(got[ok] - want[ok]).max() <= 1e-11 * scale     # same tolerance as test_risk_gpu.py
 
 
+def test_noalloc_leaves_free_device_memory_unchanged():
+    """cudaMemGetInfo before and after: with the outputs allocated up front, a call of the allocation-free
+    entry point must not change the free device memory (its first call on the device is made beforehand: that
+    one loads the kernels and looks the array's address up).  The regular entry point on a fresh context is
+    measured the same way to show that the probe does see a library-side cudaMalloc."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.synth import make_factor_returns
+    T, K, q, tao = 2500, 42, 2, 252.0
+    d_fr = torch.from_numpy(make_factor_returns(T, K, seed=4)).cuda()
+    cov = torch.empty((T, K, K), dtype=torch.float64, device="cuda")
+    st = torch.empty(T, dtype=torch.int32, device="cuda")
+    ctx = _cabi.Context(torch.cuda.current_device())          # fresh: no workspace yet
+    ctx.newey_west_by_time_noalloc(T, K, q, tao, d_fr, cov, st)   # first call: module load + address look-up
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for _ in range(2):
+        ctx.newey_west_by_time_noalloc(T, K, q, tao, d_fr, cov, st)
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free0
+    ctx.newey_west_by_time(T, K, q, tao, d_fr, cov, st)       # grows the context workspace with cudaMalloc
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] < free0
+    ctx.close()
+
+
 def test_noalloc_rejects_oversized_problems():
     import torch
     from bmfm import _cabi

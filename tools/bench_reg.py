@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Time the regression entry point alone on a synthetic panel of a given shape (CUDA events).
 
-    python tools/bench_reg.py N T [mode]        mode: BMFM_REG_MODE (0 auto; 3 / 5 / 4 = FP64-MMA kernel with 1 / 2 / 4 warps per date;
+    python tools/bench_reg.py N T [mode]        mode: the reg_mode context option (0 auto; 3 / 5 / 4 = FP64-MMA kernel with 1 / 2 / 4 warps per date;
                                                 1 CTA kernel, 2 register-Gram stream kernel: earlier designs)
     BENCH_UNGROUPED=1: rows not grouped by industry; BENCH_GATHER=n: the fused-gather entry point with n local "peers"
 """
@@ -18,8 +18,7 @@ from bmfm.panel import pack_arrays  # noqa: E402
 from bmfm.synth import make_panel   # noqa: E402
 
 N, T = int(sys.argv[1]), int(sys.argv[2])
-if len(sys.argv) > 3:
-    os.environ["BMFM_REG_MODE"] = sys.argv[3]
+MODE = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 P, Q = 31, 10
 K = 1 + P + Q
 pan = make_panel(T, N, P, Q, seed=3, scale_log10=(-2, 2))
@@ -35,6 +34,10 @@ spec = torch.empty(rows, dtype=torch.float64, device="cuda")
 r2 = torch.empty(T, dtype=torch.float64, device="cuda")
 st = torch.empty(T, dtype=torch.int32, device="cuda")
 ctx = _cabi.default_context()
+ctx.set_option("reg_mode", MODE)
+for name in ("reg_smma", "reg_warps", "reg_ctas"):
+    if os.environ.get("BENCH_" + name.upper()):
+        ctx.set_option(name, int(os.environ["BENCH_" + name.upper()]))
 GATHER = int(os.environ.get("BENCH_GATHER", "0"))
 fr_all = torch.empty((T, K), dtype=torch.float64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -51,5 +54,5 @@ for i in range(8):
     torch.cuda.synchronize()
     times.append(e0.elapsed_time(e1))
 ms = float(np.median(times[3:]))
-print(f"{'grouped' if GROUPED else 'ungrouped'} N={N} T={T} mode={os.environ.get('BMFM_REG_MODE', '0')}: {ms:.3f} ms, {rows * 108 / ms / 1e6:.0f} GB/s "
+print(f"{'grouped' if GROUPED else 'ungrouped'} N={N} T={T} mode={MODE} (ran {ctx.get_option('last_reg_mode')}): {ms:.3f} ms, {rows * 108 / ms / 1e6:.0f} GB/s "
       f"({rows * 108 / ms / 1e6 / 6538:.3f} of measured HBM), {T / ms * 1e3:.0f} dates/s, status ok={bool((st == 0).all())}")
