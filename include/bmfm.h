@@ -295,7 +295,24 @@ int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* siz
  *   BMFM_OP_INV_POS  BP = 1 / pb where pb > 0, NaN otherwise  compute_bp    factor_calculator.py:295-321 */
 #define BMFM_OP_LOG 0
 #define BMFM_OP_INV_POS 1
+/*   BMFM_OP_PERCENT  YOYProfit / YOYSales = x / 100           select_growth_factors  factor_calculator.py:436-462
+ *   (BMFM_OP_INV_POS is also ETOP = 1 / pe_ttm where pe_ttm > 0, compute_earnings_yield :417-419) */
+#define BMFM_OP_PERCENT 2
 int bmfm_elementwise(bmfm_ctx* ctx, int op, int64_t n, const double* x, double* out);
+/* Two-column descriptors, out = f(x, y):
+ *   BMFM_OP2_RATIO_POS   CETOP = x / y where x > 0 and y > 0 (x = TTM cash flow, y = total_mv), NaN otherwise
+ *                        compute_earnings_yield  factor_calculator.py:409-415
+ *   BMFM_OP2_LEV_FINITE  MLEV = (y + x) / y with +-inf -> NaN (x = total_ncl, y = total_mv)
+ *                        compute_leverage  factor_calculator.py:481-484
+ *   BMFM_OP2_LEV_POS     BLEV = (y + x) / y where y > 0, NaN otherwise (x = total_ncl, y = book value)  :488-496 */
+#define BMFM_OP2_RATIO_POS 10
+#define BMFM_OP2_LEV_FINITE 11
+#define BMFM_OP2_LEV_POS 12
+int bmfm_elementwise2(bmfm_ctx* ctx, int op, int64_t n, const double* x, const double* y, double* out);
+/* pandas rolling(window, min_periods).sum() down the rows of an [L * S] panel (NaN rows skipped; NaN with fewer
+ * than min_periods valid rows): the trailing-four-quarter cash flow of compute_earnings_yield
+ * (factor_calculator.py:394-396: window = min_periods = 4 over each stock's report periods).  window <= 64. */
+int bmfm_rolling_sum(bmfm_ctx* ctx, int L, int S, const double* x, int window, int min_periods, double* out);
 
 /*
  * Per-date post-processing on the long table grouped by date (date_off int64 [T+1], one fp64 array

@@ -2,14 +2,16 @@
 """Drop-in for the hot-path methods of Barra_factor_cal/factor_calculator.py:
 ``FactorCalculator(prices_df, index_df)``, ``_prepare_data``,
 ``compute_beta_hsigma``, ``compute_dastd``, ``compute_cmra``, ``compute_rstr``,
-``compute_liquidity``, ``compute_nlsize``, ``compute_size``, ``compute_bp`` and ``run`` for those factors — same DataFrame in / DataFrame out contract (results keyed by
-``original_index``), rolling windows on the GPU.
+``compute_liquidity``, ``compute_nlsize``, ``compute_size``, ``compute_bp``, ``compute_earnings_yield``,
+``select_growth_factors``, ``compute_leverage`` and ``run`` — same DataFrame in / DataFrame out contract (results
+keyed by ``original_index``), rolling windows and element-wise arithmetic on the GPU.
 
 The long table is pivoted once into a dense [row-of-stock, stock] panel (each
 stock's own rows in date order, which is what ``groupby('ts_code').rolling``
 walks); kernels write the same layout and the results are scattered back to
-``original_index``.  Other ``compute_*`` methods of the reference are outside
-the hot path and raise NotImplementedError.
+``original_index``.  The report-period alignment of the financial-statement
+factors (drop_duplicates / merge on (ts_code, end_date)) stays pandas glue as in
+the reference; their arithmetic runs through bmfm_rolling_sum / bmfm_elementwise*.
 """
 import numpy as np
 import pandas as pd
@@ -133,17 +135,85 @@ class FactorCalculator:
         res[order] = _ops.nlsize(date_off, size[order])
         return pd.DataFrame({'original_index': self.master_df['original_index'].values, 'NLSIZE': res})
 
-    def run(self, factors_to_compute: list) -> pd.DataFrame:
-        """factor_calculator.py:515-577 for the hot-path factors: merge results on original_index."""
-        methods = {'BETA': self.compute_beta_hsigma, 'DASTD': self.compute_dastd, 'CMRA': self.compute_cmra,
-                   'RSTR': self.compute_rstr, 'LIQUIDITY': self.compute_liquidity, 'NLSIZE': self.compute_nlsize,
-                   'SIZE': self.compute_size, 'BP': self.compute_bp}
-        final = self.master_df[['original_index', 'ts_code', 'trade_date', 'ret']].copy()
-        for name in factors_to_compute:
-            key = name.upper()
-            if key not in methods:
-                raise NotImplementedError(f"factor {name!r} is outside the accelerated hot path (SURVEY.md §8(f))")
-            res = methods[key]()
-            if res is not None:
-                final = pd.merge(final, res, on='original_index', how='left')
-        return final.drop(columns=['original_index'])
+    def compute_earnings_yield(self):
+        """factor_calculator.py:371-433: CETOP = trailing-four-quarter operating cash flow / total_mv (both > 0),
+        ETOP = 1 / pe_ttm (pe_ttm > 0).  None when a required column is missing (:382-387)."""
+        print("Computing Earnings Yield factors (CETOP, ETOP)...")
+        required_cols = ['n_cashflow_act', 'end_date', 'total_mv', 'pe_ttm']
+        if not all(col in self.master_df.columns for col in required_cols):
+            missing = [col for col in required_cols if col not in self.master_df.columns]
+            print(f"\nERROR: Missing required columns for earnings yield calculation. "
+                  f"Please ensure your merged data contains: {missing}\n")
+            return None
+        # one row per (stock, report period), in period order (:391-394)
+        financial_data = self.master_df[['ts_code', 'end_date', 'n_cashflow_act']].drop_duplicates().copy()
+        financial_data.sort_values(by=['ts_code', 'end_date'], inplace=True)
+        codes, _ = pd.factorize(financial_data['ts_code'].values, sort=True)
+        rows = financial_data.groupby('ts_code', sort=False).cumcount().values
+        S = int(codes.max()) + 1 if len(codes) else 0
+        L = int(rows.max()) + 1 if len(rows) else 0
+        panel = np.full((L, S), np.nan)
+        panel[rows, codes] = financial_data['n_cashflow_act'].values.astype(np.float64)
+        ttm = _ops.rolling_sum(panel, 4, 4) if L and S else panel            # rolling(4, min_periods=4).sum() (:395-397)
+        financial_data['n_cashflow_act_ttm'] = ttm[rows, codes]
+        temp_df = pd.merge(self.master_df[['original_index', 'ts_code', 'end_date', 'total_mv', 'pe_ttm']],
+                           financial_data[['ts_code', 'end_date', 'n_cashflow_act_ttm']],
+                           on=['ts_code', 'end_date'], how='left')
+        temp_df.sort_values(by='original_index', inplace=True)
+        return pd.DataFrame({
+            'original_index': temp_df['original_index'],
+            'CETOP': _ops.cetop_factor(temp_df['n_cashflow_act_ttm'].values, temp_df['total_mv'].values),
+            'ETOP': _ops.etop_factor(temp_df['pe_ttm'].values)})
+
+    def select_growth_factors(self):
+        """factor_calculator.py:436-462: YOYProfit / YOYSales = q_profit_yoy / 100, q_sales_yoy / 100."""
+        print("Selecting Growth factors (YOYProfit, YOYSales)...")
+        required_cols = ['q_profit_yoy', 'q_sales_yoy']
+        if not all(col in self.master_df.columns for col in required_cols):
+            print(f"\nERROR: Missing required columns for growth factors. "
+                  f"Please ensure your merged data contains: {required_cols}\n")
+            return None
+        return pd.DataFrame({'original_index': self.master_df['original_index'].values,
+                             'YOYProfit': _ops.percent_factor(self.master_df['q_profit_yoy'].values),
+                             'YOYSales': _ops.percent_factor(self.master_df['q_sales_yoy'].values)})
+
+    def compute_leverage(self):
+        """factor_calculator.py:464-509: MLEV, DTOA (passed through), BLEV."""
+        print("Computing Leverage factors (MLEV, DTOA, BLEV)...")
+        required_cols = ['total_mv', 'total_ncl', 'total_hldr_eqy_inc_min_int', 'debt_to_assets']
+        if not all(col in self.master_df.columns for col in required_cols):
+            print(f"\nERROR: Missing required columns for leverage calculation. "
+                  f"Please ensure your merged data contains: {required_cols}\n")
+            return None
+        m = self.master_df
+        return pd.DataFrame({
+            'original_index': m['original_index'],
+            'MLEV': _ops.mlev_factor(m['total_ncl'].values, m['total_mv'].values),
+            'DTOA': m['debt_to_assets'],
+            'BLEV': _ops.blev_factor(m['total_ncl'].values, m['total_hldr_eqy_inc_min_int'].values)})
+
+    def run(self, factors: list) -> pd.DataFrame:
+        """factor_calculator.py:515-577: compute each requested factor and left-merge it on original_index;
+        an unknown name or a method that returns None is reported and skipped, as in the reference."""
+        print(f"\nStarting factor calculation for: {factors}")
+        factor_methods = {
+            'SIZE': self.compute_size, 'BETA': self.compute_beta_hsigma, 'RSTR': self.compute_rstr,
+            'DASTD': self.compute_dastd, 'CMRA': self.compute_cmra, 'NLSIZE': self.compute_nlsize,
+            'BP': self.compute_bp, 'LIQUIDITY': self.compute_liquidity, 'EARNINGS': self.compute_earnings_yield,
+            'GROWTH': self.select_growth_factors, 'LEVERAGE': self.compute_leverage,
+        }
+        final_df = self.master_df[['ts_code', 'trade_date', 'original_index', 'ret', 'circ_mv']].copy()
+        print("\nIteratively computing and merging factors...")
+        for factor_name in factors:
+            method = factor_methods.get(factor_name.upper())
+            if not method:
+                print(f"Warning: Factor '{factor_name}' not found.")
+                continue
+            factor_df = method()
+            if factor_df is not None:
+                final_df = pd.merge(final_df, factor_df, on='original_index', how='left')
+            else:
+                print(f"Warning: Method for '{factor_name}' returned None.")
+        final_df.drop(columns='original_index', inplace=True)
+        print("Factor calculation complete.")
+        return final_df

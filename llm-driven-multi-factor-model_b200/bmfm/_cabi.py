@@ -15,7 +15,8 @@ LIB_PATH = os.path.join(_HERE, "libbmfm.so")
 
 # status codes (include/bmfm.h)
 ST_OK, ST_SHORT, ST_NOT_PSD, ST_NONFINITE, ST_PINV, ST_DUP_EDGES = 0, 1, 2, 3, 4, 5
-OP_LOG, OP_INV_POS = 0, 1
+OP_LOG, OP_INV_POS, OP_PERCENT = 0, 1, 2
+OP2_RATIO_POS, OP2_LEV_FINITE, OP2_LEV_POS = 10, 11, 12
 
 _lib = None
 _lock = threading.Lock()
@@ -60,6 +61,8 @@ _SIGNATURES = {
     "bmfm_rolling_log_sum3": ([_P, _I, _I, _P, _D, _P, _P, _P], _I),
     "bmfm_nlsize": ([_P, _I, _P, _P, _P], _I),
     "bmfm_elementwise": ([_P, _I, C.c_int64, _P, _P], _I),
+    "bmfm_elementwise2": ([_P, _I, C.c_int64, _P, _P, _P], _I),
+    "bmfm_rolling_sum": ([_P, _I, _I, _P, _I, _I, _P], _I),
     "bmfm_beta_hsigma": ([_P, _I, _I, _P, _P, _I, _D, _I, _P, _P], _I),
     "bmfm_dastd": ([_P, _I, _I, _P, _P, _I, _D, _I, _P], _I),
     "bmfm_cmra": ([_P, _I, _I, _P, _I, _P], _I),
@@ -289,6 +292,12 @@ class Context:
 
     def elementwise(self, op, n, x, out):
         self.check(self._L.bmfm_elementwise(self._h, int(op), int(n), ptr(x), ptr(out)))
+
+    def elementwise2(self, op, n, x, y, out):
+        self.check(self._L.bmfm_elementwise2(self._h, int(op), int(n), ptr(x), ptr(y), ptr(out)))
+
+    def rolling_sum(self, L, S, x, window, min_periods, out):
+        self.check(self._L.bmfm_rolling_sum(self._h, L, S, ptr(x), int(window), int(min_periods), ptr(out)))
 
     def nlsize(self, T, date_off, size, out):
         self.check(self._L.bmfm_nlsize(self._h, T, ptr(date_off), ptr(size), ptr(out)))

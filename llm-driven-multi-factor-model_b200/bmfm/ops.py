@@ -274,6 +274,61 @@ def bp_factor(pb, ctx=None):
     return o.cpu().numpy()
 
 
+def _unary(op, x, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    xd = _dev(np.asarray(x, dtype=np.float64))
+    o = torch.empty_like(xd)
+    ctx.elementwise(op, xd.numel(), xd, o)
+    return o.cpu().numpy()
+
+
+def _binary(op, x, y, ctx=None):
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    xd = _dev(np.asarray(x, dtype=np.float64))
+    yd = _dev(np.asarray(y, dtype=np.float64))
+    o = torch.empty_like(xd)
+    ctx.elementwise2(op, xd.numel(), xd, yd, o)
+    return o.cpu().numpy()
+
+
+def etop_factor(pe_ttm, ctx=None):
+    """compute_earnings_yield: ETOP = 1 / pe_ttm where pe_ttm > 0 (factor_calculator.py:417-419)."""
+    return _unary(_cabi.OP_INV_POS, pe_ttm, ctx)
+
+
+def cetop_factor(cash_flow_ttm, total_mv, ctx=None):
+    """compute_earnings_yield: CETOP = ttm / total_mv where both > 0 (factor_calculator.py:409-415)."""
+    return _binary(_cabi.OP2_RATIO_POS, cash_flow_ttm, total_mv, ctx)
+
+
+def percent_factor(x, ctx=None):
+    """select_growth_factors: percent -> ratio (factor_calculator.py:454-456)."""
+    return _unary(_cabi.OP_PERCENT, x, ctx)
+
+
+def mlev_factor(total_ncl, total_mv, ctx=None):
+    """compute_leverage: MLEV = (total_mv + total_ncl) / total_mv, inf -> NaN (factor_calculator.py:481-484)."""
+    return _binary(_cabi.OP2_LEV_FINITE, total_ncl, total_mv, ctx)
+
+
+def blev_factor(total_ncl, book_value, ctx=None):
+    """compute_leverage: BLEV = (book + total_ncl) / book where book > 0 (factor_calculator.py:488-496)."""
+    return _binary(_cabi.OP2_LEV_POS, total_ncl, book_value, ctx)
+
+
+def rolling_sum(x, window, min_periods, ctx=None):
+    """pandas rolling(window, min_periods).sum() down the rows of a [row-of-stock, stock] panel."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    xd = _dev(np.asarray(x, dtype=np.float64))
+    L, S = xd.shape
+    o = torch.empty_like(xd)
+    ctx.rolling_sum(L, S, xd, window, min_periods, o)
+    return o.cpu().numpy()
+
+
 def nlsize(date_off, size, ctx=None):
     """compute_nlsize on the long table grouped by date."""
     torch = _torch()

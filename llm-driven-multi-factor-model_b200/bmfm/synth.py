@@ -236,3 +236,51 @@ def write_demo_csv_pair(dirpath, T=1400, N=300, P=28, Q=10, seed=20240001, nan_f
     pd.DataFrame({"code": codes, "industry_names": [f"SW_{p:02d}" for p in range(P)],
                   "start_date": ["2014/01/01"] * P}).to_csv(ind_path, index=False)
     return data_path, ind_path
+
+
+def make_financial_inputs(T=330, S=8, seed=91):
+    """Long daily table with every column FactorCalculator.run(FACTORS_TO_RUN) touches, an index series and
+    a Shenwan industry table (what load_and_prepare_data hands to main.py:47): prices, market values, pb / pe,
+    turnover, and report-period fundamentals forward-filled between report dates (quarterly end_date,
+    single-quarter cash flow, growth rates in percent, liabilities, book value)."""
+    import pandas as pd
+
+    close, idx_close = make_price_panel(T, S, seed=seed, missing=0.01, late=1)
+    dates = pd.to_datetime(make_dates(T), format="%Y/%m/%d")
+    rng = np.random.default_rng(seed + 1)
+    rows = []
+    for s in range(S):
+        base_mv = np.exp(rng.normal(13.0, 1.0))
+        nq = T // 60 + 2
+        cash = rng.normal(2e3, 3e3, size=nq)                 # single-quarter operating cash flow, some negative
+        cash[rng.random(nq) < 0.1] = np.nan
+        prof = rng.normal(15.0, 40.0, size=nq)
+        sales = rng.normal(10.0, 25.0, size=nq)
+        ncl = np.abs(rng.normal(0.3, 0.2, size=nq)) * base_mv
+        book = rng.normal(0.5, 0.35, size=nq) * base_mv      # occasionally <= 0: BLEV undefined
+        dta = np.clip(rng.normal(45.0, 20.0, size=nq), 1.0, 99.0)
+        for t in range(T):
+            if s == 3 and 70 <= t < 95:
+                continue                                     # absent rows
+            qi = t // 60
+            mv = base_mv * np.exp(0.01 * rng.normal()) * (close[t, s] / 10.0 if np.isfinite(close[t, s]) else 1.0)
+            rows.append(dict(ts_code=f"{s:06d}.SZ", trade_date=dates[t], close=close[t, s],
+                             total_mv=mv, circ_mv=0.6 * mv, pb=np.exp(rng.normal(0.7, 0.6)) * (1 if rng.random() > 0.04 else -1),
+                             pe_ttm=rng.normal(25.0, 30.0), turnover_rate=np.exp(rng.normal(0.3, 0.8)),
+                             end_date=f"{2009 + (qi + 3) // 4}{[3, 6, 9, 12][(qi + 3) % 4]:02d}{[31, 30, 30, 31][(qi + 3) % 4]}",
+                             n_cashflow_act=cash[qi], q_profit_yoy=prof[qi], q_sales_yoy=sales[qi],
+                             total_ncl=ncl[qi], total_hldr_eqy_inc_min_int=book[qi], debt_to_assets=dta[qi]))
+    prices = pd.DataFrame(rows)
+    for c in ("total_mv", "pe_ttm", "turnover_rate", "total_ncl"):
+        v = prices[c].values.copy()
+        v[rng.random(len(v)) < 0.02] = np.nan
+        prices[c] = v
+    # (total_mv == 0 would make MLEV inf -> NaN, but the reference's own NLSIZE regression then fails on
+    #  ln(0) = -inf, so that branch is exercised against the oracle only)
+    prices = prices.sample(frac=1.0, random_state=2).reset_index(drop=True)
+    index_df = pd.DataFrame({"trade_date": dates, "close": idx_close})
+    sw = pd.DataFrame({"ts_code": [f"{s:06d}.SZ" for s in range(S)],
+                       "l1_code": [f"8011{s % 3:02d}.SI" for s in range(S)],
+                       "l1_name": [f"SW_{s % 3:02d}" for s in range(S)],
+                       "in_date": ["20140101"] * S})
+    return prices, index_df, sw

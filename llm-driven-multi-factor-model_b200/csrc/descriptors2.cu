@@ -175,7 +175,43 @@ __global__ void __launch_bounds__(128) nlsize_kernel(int T, const long long* dat
 __global__ void elementwise_kernel(int op, long long n, const double* x, double* out) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const double v = x[i];
-    out[i] = op == 0 ? log(v) : (v > 0.0 ? 1.0 / v : qnan2());
+    out[i] = op == BMFM_OP_LOG ? log(v) : (op == BMFM_OP_INV_POS ? (v > 0.0 ? 1.0 / v : qnan2()) : v / 100.0);
+  }
+}
+
+// Two-column element-wise descriptors (earnings yield and leverage, factor_calculator.py:371-509); 24 B per element
+__global__ void elementwise2_kernel(int op, long long n, const double* x, const double* y, double* out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const double a = x[i], b = y[i];
+    double r;
+    if (op == BMFM_OP2_RATIO_POS) {               // CETOP: a / b where both are > 0 (:411-415)
+      r = (b > 0.0 && a > 0.0) ? a / b : qnan2();
+    } else if (op == BMFM_OP2_LEV_FINITE) {       // MLEV: (b + a) / b, +-inf -> NaN (:483-484)
+      r = (b + a) / b;
+      if (isinf(r)) r = qnan2();
+    } else {                                      // BLEV: (b + a) / b where b > 0 (:492-496)
+      r = b > 0.0 ? (b + a) / b : qnan2();
+    }
+    out[i] = r;
+  }
+}
+
+// pandas rolling(window, min_periods).sum() down the rows of an [L][S] panel, thread = stock: the trailing-four-
+// quarter cash flow of compute_earnings_yield (factor_calculator.py:394-396).  NaN rows are skipped and the
+// result is NaN with fewer than min_periods valid rows in the window; the sum is re-formed per row from the
+// window's rows (windows are a few rows long), so nothing drifts.
+__global__ void rolling_sum_kernel(int L, int S, int window, int minp, const double* x, double* out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  for (int r = 0; r < L; ++r) {
+    double acc = 0.0;
+    int cnt = 0;
+    const int lo = r - window + 1 > 0 ? r - window + 1 : 0;
+    for (int j = lo; j <= r; ++j) {
+      const double v = x[(size_t)j * S + s];
+      if (!isnan(v)) { acc += v; ++cnt; }
+    }
+    out[(size_t)r * S + s] = cnt >= minp ? acc : qnan2();
   }
 }
 
@@ -245,7 +281,7 @@ extern "C" int bmfm_nlsize(bmfm_ctx* ctx, int T, const int64_t* date_off, const 
 
 extern "C" int bmfm_elementwise(bmfm_ctx* ctx, int op, int64_t n, const double* x, double* out) {
   if (!ctx) return BMFM_E_ARG;
-  BMFM_ARG(ctx, (op == BMFM_OP_LOG || op == BMFM_OP_INV_POS) && n >= 0, "bad arguments");
+  BMFM_ARG(ctx, (op == BMFM_OP_LOG || op == BMFM_OP_INV_POS || op == BMFM_OP_PERCENT) && n >= 0, "bad arguments");
   if (n == 0) return BMFM_OK;
   BMFM_ARG(ctx, x && out, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -253,6 +289,33 @@ extern "C" int bmfm_elementwise(bmfm_ctx* ctx, int op, int64_t n, const double* 
   const long long cap = (long long)ctx->sm_count * 16;
   if (blocks > cap) blocks = cap;
   elementwise_kernel<<<(int)blocks, 256, 0, ctx->stream>>>(op, (long long)n, x, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_elementwise2(bmfm_ctx* ctx, int op, int64_t n, const double* x, const double* y, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, op >= BMFM_OP2_RATIO_POS && op <= BMFM_OP2_LEV_POS && n >= 0, "bad arguments");
+  if (n == 0) return BMFM_OK;
+  BMFM_ARG(ctx, x && y && out, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  long long blocks = (n + 255) / 256;
+  const long long cap = (long long)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  elementwise2_kernel<<<(int)blocks, 256, 0, ctx->stream>>>(op, (long long)n, x, y, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_rolling_sum(bmfm_ctx* ctx, int L, int S, const double* x, int window, int min_periods, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, L >= 0 && S >= 0 && window >= 1 && window <= 64 && min_periods >= 1, "bad sizes (window <= 64)");
+  if ((size_t)L * S == 0) return BMFM_OK;
+  BMFM_ARG(ctx, x && out, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  rolling_sum_kernel<<<(S + 127) / 128, 128, 0, ctx->stream>>>(L, S, window, min_periods, x, out);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;

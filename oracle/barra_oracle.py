@@ -477,6 +477,55 @@ def bp_factor(pb):
         return np.where(pb > 0, 1.0 / pb, np.nan)
 
 
+def etop_factor(pe_ttm):
+    """Barra_factor_cal/factor_calculator.py:417-419: ``ETOP = 1 / pe_ttm`` where ``pe_ttm > 0``."""
+    return bp_factor(pe_ttm)
+
+
+def rolling_sum(x, window=4, min_periods=4):
+    """``Series.rolling(window, min_periods).sum()`` over one stock's report periods
+    (factor_calculator.py:394-396): NaN entries are skipped, NaN below ``min_periods`` valid ones."""
+    x = np.asarray(x, dtype=np.float64)
+    out = np.full_like(x, np.nan)
+    for r in range(len(x)):
+        w = x[max(0, r - window + 1): r + 1]
+        w = w[~np.isnan(w)]
+        if len(w) >= min_periods:
+            out[r] = w.sum()
+    return out
+
+
+def cetop_factor(cash_flow_ttm, total_mv):
+    """factor_calculator.py:409-415: ``ttm / total_mv`` where both are > 0, NaN otherwise."""
+    a = np.asarray(cash_flow_ttm, dtype=np.float64)
+    b = np.asarray(total_mv, dtype=np.float64)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.where((b > 0) & (a > 0), a / b, np.nan)
+
+
+def percent_factor(x):
+    """factor_calculator.py:454-456: growth rates in percent -> ratios."""
+    return np.asarray(x, dtype=np.float64) / 100
+
+
+def mlev_factor(total_ncl, total_mv):
+    """factor_calculator.py:481-484: ``(total_mv + total_ncl) / total_mv`` with +-inf replaced by NaN."""
+    a = np.asarray(total_ncl, dtype=np.float64)
+    b = np.asarray(total_mv, dtype=np.float64)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        r = (b + a) / b
+    r[np.isinf(r)] = np.nan
+    return r
+
+
+def blev_factor(total_ncl, book_value):
+    """factor_calculator.py:488-496: ``(book + total_ncl) / book`` where ``book > 0``, NaN otherwise."""
+    a = np.asarray(total_ncl, dtype=np.float64)
+    b = np.asarray(book_value, dtype=np.float64)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.where(b > 0, (b + a) / b, np.nan)
+
+
 def prepare_returns(close):
     """Barra_factor_cal/factor_calculator.py:50-53 for one stock's closes in
     date order: ``pct_change`` (pandas 3: no forward fill) and log-return."""

@@ -23,7 +23,9 @@ sys.path.insert(0, HERE)
 sys.path.insert(0, os.path.join(ROOT, "llm-driven-multi-factor-model_b200"))
 
 from ref_harness import load_reference, quiet, patched_eig, canonical_eig  # noqa: E402
-from bmfm.synth import make_panel, make_factor_returns, make_price_panel, make_dates  # noqa: E402
+from bmfm.synth import make_panel, make_factor_returns, make_price_panel, make_dates, make_financial_inputs  # noqa: E402
+
+from bmfm.handoff import read_results  # noqa: E402
 
 ref_mfm, ref_cs, ref_utils, ref_fc, ref_pp, ref_cfg = load_reference()
 
@@ -281,6 +283,48 @@ def golden_descriptors():
     print("descriptors.npz", len(out), "beta valid:", int(np.isfinite(out["BETA"]).sum()))
 
 
+def golden_financial():
+    """Rows f3/f4: FactorCalculator.run(config.FACTORS_TO_RUN) (all eleven entries, incl. EARNINGS / GROWTH /
+    LEVERAGE, factor_calculator.py:371-509), then main.py's own sequence with the reference's functions and
+    constants — winsorise every column but the keys (main.py:71-72), composites (:79), orthogonalise (:86),
+    industry merge and next-day return (:98-99), rename (:107), column order (:111-112), industry table
+    (:128-137) — without the MongoDB calls around it."""
+    out = {}
+    prices, index_df, sw = make_financial_inputs()
+    with quiet():
+        calc = ref_fc.FactorCalculator(prices.copy(), index_df.copy())
+        raw = calc.run(ref_cfg.FACTORS_TO_RUN)
+        factor_columns = [c for c in raw.columns if c not in ['ts_code', 'trade_date']]
+        wz = ref_pp.winsorize_factors(raw, factor_columns)
+        comp = ref_pp.calculate_composite_factors(wz, ref_cfg.COMPOSITE_CONFIG)
+        proc = ref_pp.orthogonalize_factors(comp, ref_cfg.ORTHO_RULES)
+        barra = pd.merge(proc, sw[['ts_code', 'l1_code']], on='ts_code', how='left')
+        barra['ret'] = barra.groupby('ts_code')['ret'].shift(-1)
+        barra.rename(columns=ref_cfg.COLUMN_RENAME_MAP, inplace=True)
+        final_columns = [c for c in ref_cfg.BARRA_OUTPUT_COLUMNS if c in barra.columns]
+        final = barra[final_columns]
+        stk = final[['stocknames']].drop_duplicates().rename(columns={'stocknames': 'ts_code'})
+        ind_info = pd.merge(stk, sw[['ts_code', 'l1_code', 'l1_name', 'in_date']], on='ts_code', how='left')
+        ind_info = ind_info.drop_duplicates(subset=['l1_code', 'l1_name']).rename(
+            columns={'l1_code': 'code', 'l1_name': 'industry_names', 'in_date': 'start_date'})[['code', 'industry_names', 'start_date']]
+    out["raw_columns"] = np.asarray(raw.columns.astype(str)).astype("U")
+    out["raw_keys"] = np.asarray(raw["ts_code"].astype(str) + "|" + raw["trade_date"].astype(str)).astype("U")
+    for c in raw.columns:
+        if c not in ("ts_code", "trade_date"):
+            out["raw__" + c] = raw[c].values.astype(float)
+    out["final_columns"] = np.asarray(final.columns.astype(str)).astype("U")
+    out["final_keys"] = np.asarray(final["stocknames"].astype(str) + "|" + final["date"].astype(str)).astype("U")
+    out["final_industry"] = np.asarray(final["industry"].astype(str)).astype("U")
+    for c in final.columns:
+        if c not in ("date", "stocknames", "industry"):
+            out["final__" + c] = final[c].values.astype(float)
+    out["ind_info_code"] = np.asarray(ind_info["code"].astype(str)).astype("U")
+    out["ind_info_names"] = np.asarray(ind_info["industry_names"].astype(str)).astype("U")
+    np.savez_compressed(os.path.join(HERE, "financial.npz"), **out)
+    print("financial.npz", len(out), list(out["final_columns"]),
+          {c: int(np.isfinite(out["raw__" + c]).sum()) for c in ("CETOP", "ETOP", "MLEV", "BLEV", "YOYProfit")})
+
+
 DEMO_CASE = dict(T=1400, N=300, P=28, Q=10, seed=20240001)     # config C1; demo.py:38 hard-codes MFM(data, 28, 10)
 
 
@@ -309,27 +353,6 @@ def _run_reference_demo(workdir, canonical):
     return os.path.join(bm, "results")
 
 
-def read_demo_results(results_dir):
-    """The five CSVs demo.py:59-94 writes -> arrays (index / column labels as strings)."""
-    out = {}
-    fr = pd.read_csv(os.path.join(results_dir, "factor_returns.csv"), index_col=0)
-    out["factor_ret"] = fr.values.astype(float)
-    out["factor_ret_index"] = np.asarray(fr.index.astype(str))
-    out["factor_ret_columns"] = np.asarray(fr.columns.astype(str))
-    r2 = pd.read_csv(os.path.join(results_dir, "r_squared.csv"), index_col=0)
-    out["R2"] = r2.values[:, 0].astype(float)
-    sp = pd.read_csv(os.path.join(results_dir, "specific_returns.csv"), index_col=0)
-    out["specific_columns"] = np.asarray(sp.columns.astype(str))
-    out["specific_index"] = np.asarray(sp.index.astype(str))
-    out["specific_full"] = sp.values.astype(float)
-    cov = pd.read_csv(os.path.join(results_dir, "final_vol_regime_adj_covariance.csv"), index_col=0)
-    out["final_cov"] = cov.values.astype(float)
-    out["final_cov_labels"] = np.asarray(cov.columns.astype(str))
-    lam = pd.read_csv(os.path.join(results_dir, "volatility_multiplier_lambda.csv"), index_col=0)
-    out["lamb"] = lam.values[:, 0].astype(float)
-    return out
-
-
 def golden_demo():
     """Config C1 / row g: the reference's demo.py run UNCHANGED on the stand-in CSV pair (the
     real files are not in the tree), eigen order canonical.  The fixture also carries demo.py's bytes so the
@@ -341,7 +364,7 @@ def golden_demo():
     with tempfile.TemporaryDirectory() as wd:
         dpath, ipath = write_demo_csv_pair(os.path.join(wd, "Barra-master", "data_new"), **DEMO_CASE)
         out["csv_sha256"] = np.array([hashlib.sha256(open(p, "rb").read()).hexdigest() for p in (dpath, ipath)])
-        res = read_demo_results(_run_reference_demo(wd, canonical=True))
+        res = read_results(_run_reference_demo(wd, canonical=True))
     src = open("/root/reference/Barra-master/demo.py", "rb").read()
     out["demo_py"] = np.frombuffer(src, dtype=np.uint8)
     out["demo_py_sha256"] = np.array(hashlib.sha256(src).hexdigest())
@@ -362,6 +385,6 @@ def golden_demo():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["reg", "risk", "pipeline", "descriptors", "demo"]
+    which = sys.argv[1:] or ["reg", "risk", "pipeline", "descriptors", "financial", "demo"]
     for w in which:
         globals()[f"golden_{w}"]()

@@ -240,6 +240,7 @@ def test_factor_calculator_dropin(desc):
     dates = pd.to_datetime(make_dates(T), format="%Y/%m/%d")
     rows = [(f"{s:06d}.SZ", dates[t], close[t, s]) for s in range(S) for t in range(T) if not (s == 2 and 40 <= t < 60)]
     prices = pd.DataFrame(rows, columns=["ts_code", "trade_date", "close"]).sample(frac=1.0, random_state=0)
+    prices["circ_mv"] = 1.0e6            # run() carries circ_mv in its base frame (factor_calculator.py:541)
     index_df = pd.DataFrame({"trade_date": dates, "close": idx})
     with contextlib.redirect_stdout(io.StringIO()):
         calc = fc.FactorCalculator(prices.copy(), index_df.copy())
@@ -275,7 +276,8 @@ def test_factor_calculator_next_descriptors_dropin(desc):
     dates = pd.to_datetime(make_dates(T), format="%Y/%m/%d")
     prices = pd.DataFrame({"ts_code": [f"{k:06d}.SZ" for k in desc["s"]], "trade_date": dates[desc["t"]],
                            "close": desc["close"], "turnover_rate": desc["turnover_rate"],
-                           "total_mv": desc["total_mv"], "key": np.arange(len(desc["s"]))})
+                           "total_mv": desc["total_mv"], "circ_mv": 0.5 * desc["total_mv"],
+                           "key": np.arange(len(desc["s"]))})
     prices = prices.sample(frac=1.0, random_state=5).reset_index(drop=True)
     index_df = pd.DataFrame({"trade_date": dates, "close": desc["index_close"]})
     with contextlib.redirect_stdout(io.StringIO()):
@@ -290,3 +292,106 @@ def test_factor_calculator_next_descriptors_dropin(desc):
         scale = np.nanmax(np.abs(np.log(desc["total_mv"]) ** 3))
     assert np.array_equal(np.isnan(res["NLSIZE"].values), np.isnan(desc["NLSIZE"]))
     assert relerr(res["NLSIZE"].values, desc["NLSIZE"], scale=scale) < TOL
+
+
+def _import_factor_cal():
+    import importlib
+    import sys
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                       "llm-driven-multi-factor-model_b200", "Barra_factor_cal")
+    sys.path.insert(0, pkg)
+    try:
+        for name in ("config", "factor_calculator", "post_processing", "main"):
+            sys.modules.pop(name, None)
+        return importlib.import_module("main")
+    finally:
+        sys.path.remove(pkg)
+
+
+def test_full_factor_pipeline_against_reference(golden_dir):
+    """Rows f3 / f4: FactorCalculator.run(FACTORS_TO_RUN) with all eleven entries (incl. EARNINGS, GROWTH,
+    LEVERAGE) and main.py's post-processing / Barra-format sequence (main.py:51-137) through the drop-ins,
+    against the tables the unmodified reference produced for the same seeded inputs; then the in-memory
+    hand-off to the risk model (demo.py:25-35) and the result writers (demo.py:59-94)."""
+    import contextlib
+    import io
+    import tempfile
+    import pandas as pd
+    from bmfm.handoff import barra_frame_for_mfm, write_results
+    from bmfm.synth import make_financial_inputs
+    from mfm.MFM import MFM
+    from util import record, relerr_cols
+    g = np.load(os.path.join(golden_dir, "financial.npz"))
+    main = _import_factor_cal()
+    prices, index_df, sw = make_financial_inputs()
+    with contextlib.redirect_stdout(io.StringIO()):
+        calc = main.FactorCalculator(prices.copy(), index_df.copy())
+        raw = calc.run(main.config.FACTORS_TO_RUN)
+    assert list(raw.columns) == list(g["raw_columns"])
+    key = (raw["ts_code"].astype(str) + "|" + raw["trade_date"].astype(str)).values
+    assert np.array_equal(key, g["raw_keys"])                       # same rows in the same order
+    for c in raw.columns:
+        if c in ("ts_code", "trade_date"):
+            continue
+        scale = None
+        if c == "NLSIZE":
+            with np.errstate(invalid="ignore", divide="ignore"):
+                scale = np.nanmax(np.abs(g["raw__SIZE"] ** 3))
+        assert record(f"factors.raw.{c}", relerr(raw[c].values.astype(float), g["raw__" + c], scale=scale)) < TOL, c
+    with contextlib.redirect_stdout(io.StringIO()):
+        final, ind_info = main.run_factor_pipeline(prices.copy(), index_df.copy(), sw)
+    assert list(final.columns) == list(g["final_columns"])
+    fkey = (final["stocknames"].astype(str) + "|" + final["date"].astype(str)).values
+    assert np.array_equal(fkey, g["final_keys"])
+    assert np.array_equal(final["industry"].astype(str).values, g["final_industry"])
+    for c in final.columns:
+        if c in ("date", "stocknames", "industry"):
+            continue
+        got = final[c].values.astype(float)
+        want = g["final__" + c]
+        # residuals of small per-date regressions: errors scale with the regressand, not the residual
+        scale = None
+        if c == "non_linear_size":
+            with np.errstate(invalid="ignore", divide="ignore"):
+                scale = np.nanmax(np.abs(g["raw__SIZE"] ** 3))
+        assert record(f"factors.final.{c}", relerr(got, want, scale=scale)) < TOL, c
+    assert list(ind_info["code"].astype(str)) == list(g["ind_info_code"])
+    assert list(ind_info["industry_names"].astype(str)) == list(g["ind_info_names"])
+    # hand-off: the in-memory table goes into the risk model the way demo.py feeds the CSV pair
+    frame, P, Q = barra_frame_for_mfm(final, ind_info)
+    assert (P, Q) == (len(ind_info), 10) and frame.shape[1] == 4 + P + Q and not frame.isna().any().any()
+    assert set(np.unique(frame.iloc[:, 4:4 + P].values)) <= {0, 1}
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = MFM(frame, P, Q)
+        fr, spec, r2 = model.reg_by_time()
+    assert fr.shape == (model.T, 1 + P + Q) and np.isfinite(fr.values).all()
+    with tempfile.TemporaryDirectory() as d:
+        files = write_results(d, model, fr, spec, r2, [fr.cov()], [1.0] * model.T)
+        assert sorted(os.path.basename(f) for f in files) == sorted([
+            "factor_returns.csv", "r_squared.csv", "specific_returns.csv",
+            "final_vol_regime_adj_covariance.csv", "volatility_multiplier_lambda.csv"])
+        back = pd.read_csv(os.path.join(d, "factor_returns.csv"), index_col=0)
+        assert relerr_cols(back.values, fr.values) < 1e-15
+
+
+def test_two_column_elementwise_ops(ops):
+    """bmfm_elementwise2 / bmfm_rolling_sum / BMFM_OP_PERCENT against the oracle, incl. the branches the
+    reference run cannot reach (total_mv == 0 makes its own NLSIZE step fail)."""
+    from oracle import barra_oracle as orc
+    rng = np.random.default_rng(3)
+    a = rng.normal(size=5000) * 10
+    b = rng.normal(size=5000) * 3
+    a[::17] = np.nan; b[::23] = np.nan; b[::29] = 0.0; a[::31] = 0.0
+    for got, want in ((ops.cetop_factor(a, b), orc.cetop_factor(a, b)), (ops.mlev_factor(a, b), orc.mlev_factor(a, b)),
+                      (ops.blev_factor(a, b), orc.blev_factor(a, b)), (ops.percent_factor(a), orc.percent_factor(a)),
+                      (ops.etop_factor(b), orc.etop_factor(b))):
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        assert relerr(got, want) < 1e-15
+    panel = rng.normal(size=(23, 40))
+    panel[rng.random(panel.shape) < 0.1] = np.nan
+    got = ops.rolling_sum(panel, 4, 4)
+    want = np.column_stack([orc.rolling_sum(panel[:, s], 4, 4) for s in range(panel.shape[1])])
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and relerr(got, want) < 1e-15
+    got = ops.rolling_sum(panel, 5, 2)
+    want = np.column_stack([orc.rolling_sum(panel[:, s], 5, 2) for s in range(panel.shape[1])])
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and relerr(got, want) < 1e-14
