@@ -361,6 +361,11 @@ def test_full_factor_pipeline_against_reference(golden_dir):
     frame, P, Q = barra_frame_for_mfm(final, ind_info)
     assert (P, Q) == (len(ind_info), 10) and frame.shape[1] == 4 + P + Q and not frame.isna().any().any()
     assert set(np.unique(frame.iloc[:, 4:4 + P].values)) <= {0, 1}
+    # (an empty LAST industry makes the reference's constraint row -cap/0, CrossSection.py:70, and numpy raise:
+    #  keep the dates on which every industry of this 8-stock universe is present)
+    full = frame.groupby("date")[list(frame.columns[4:4 + P])].sum().min(axis=1) > 0
+    frame = frame[frame["date"].map(full)].reset_index(drop=True)
+    assert frame["date"].nunique() > 20
     with contextlib.redirect_stdout(io.StringIO()):
         model = MFM(frame, P, Q)
         fr, spec, r2 = model.reg_by_time()
