@@ -220,6 +220,15 @@ int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, const double
                              const int32_t* status, double* vsum, int accumulate);
 int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double scale_coef, const double* D0,
                         const double* U0, const double* vsum, const int32_t* status, double* out);
+/* Injected-literal eigen order (SURVEY.md 8(c) mode (iii)).  utils.py:64,79-84 calls the GENERAL solver
+ * np.linalg.eig and averages the simulated bias by the POSITION LAPACK's dgeev left each eigenpair at, so the
+ * literal output of the reference depends on that order.  This variant of bmfm_eigen_mc_accumulate takes the
+ * order from the caller: D0 [T*K] descending as before, perm int32 [T * nsim * K] with perm[t][m][r] = the
+ * position at which numpy's eig(Fm) returned the eigenpair of descending rank r for (date t, simulation m);
+ * vsum is accumulated by position.  bmfm_eigen_finalize then takes D0 / U0 in numpy's order for F0 and the
+ * result reproduces the unpatched reference.  K <= 48. */
+int bmfm_eigen_mc_accumulate_perm(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0,
+                                  const int32_t* status, const int32_t* perm, double* vsum, int accumulate);
 
 /*
  * Replaces utils.eigenfactor_bias_stat (Barra-master/mfm/utils.py:97-117, used MFM.py:203-204), the

@@ -52,6 +52,7 @@ _SIGNATURES = {
     "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
     "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_eigen_mc_accumulate": ([_P, _I, _I, _I, _P, _P, _P, _P, _I], _I),
+    "bmfm_eigen_mc_accumulate_perm": ([_P, _I, _I, _I, _P, _P, _P, _P, _P, _I], _I),
     "bmfm_eigen_finalize": ([_P, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_eigenfactor_bias_stat": ([_P, _I, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_bayes_shrink": ([_P, _I, _I, _P, _P, _P, _I, _D, _P, _P], _I),
@@ -251,6 +252,10 @@ class Context:
     def eigen_mc_accumulate(self, T, K, nsim, Cmat, D0, status, vsum, accumulate=False):
         self.check(self._L.bmfm_eigen_mc_accumulate(self._h, T, K, nsim, ptr(Cmat), ptr(D0), ptr(status),
                                                     ptr(vsum), int(bool(accumulate))))
+
+    def eigen_mc_accumulate_perm(self, T, K, nsim, Cmat, D0, status, perm, vsum, accumulate=False):
+        self.check(self._L.bmfm_eigen_mc_accumulate_perm(self._h, T, K, nsim, ptr(Cmat), ptr(D0), ptr(status),
+                                                         ptr(perm), ptr(vsum), int(bool(accumulate))))
 
     def eigen_finalize(self, T, K, M, scale_coef, D0, U0, vsum, status, out):
         self.check(self._L.bmfm_eigen_finalize(self._h, T, K, M, float(scale_coef), ptr(D0), ptr(U0), ptr(vsum),

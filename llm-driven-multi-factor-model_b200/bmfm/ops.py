@@ -154,6 +154,43 @@ def eigen_risk_adj_by_time(cov, cov_status, T_sim, M=100, scale_coef=1.4, ctx=No
     return out.cpu().numpy(), status.cpu().numpy()
 
 
+def literal_eig_order(covmat, T_sim, M):
+    """What only LAPACK can tell: the order in which ``np.linalg.eig`` (dgeev) returns the eigenpairs of F0
+    and of every simulated covariance Fm of ``utils.eigen_risk_adj`` (utils.py:64,73-79), for the
+    injected-literal mode.  Follows the reference's construction of Fm step by step so that dgeev sees the
+    very same matrix.  Returns (D0 [K], U0 [K,K] in numpy's order, perm int32 [M,K] with perm[m][r] = the
+    position of the eigenpair of descending rank r).  Host numpy: one K x K ``eig`` per simulation."""
+    F0 = np.asarray(covmat, dtype=np.float64)
+    K = F0.shape[0]
+    D0, U0 = np.linalg.eig(F0)
+    perm = np.empty((M, K), dtype=np.int32)
+    for m in range(M):
+        rs = np.random.RandomState(m + 1)
+        bm = rs.multivariate_normal(mean=K * [0], cov=np.diag(D0), size=T_sim).T
+        Dm, _ = np.linalg.eig(np.cov(U0 @ bm))
+        perm[m] = np.argsort(-np.real(Dm), kind="stable")
+    return np.real(D0), np.real(U0), perm
+
+
+def eigen_risk_adj_literal(cov, T_sim, M, scale_coef, D0, U0, perm, ctx=None):
+    """Eigenfactor adjustment with the eigen ORDER injected (SURVEY.md 8(c) mode (iii)): cov [T,K,K],
+    D0 [T,K] / U0 [T,K,K] as ``np.linalg.eig`` returned them, perm [T,M,K] from ``literal_eig_order``.
+    Reproduces the unpatched reference (utils.py:55-92).  Returns out [T,K,K]."""
+    torch = _torch()
+    ctx = ctx or _cabi.default_context()
+    D0 = np.asarray(D0, dtype=np.float64)
+    T, K = D0.shape
+    order = np.argsort(-D0, axis=1, kind="stable")
+    d_desc = _dev(np.take_along_axis(D0, order, axis=1))
+    status = torch.zeros(T, dtype=torch.int32, device=d_desc.device)
+    vsum = torch.zeros((T, K), dtype=torch.float64, device=d_desc.device)
+    Cm = gauss_cov_device(ctx, 0, M, T_sim, K)
+    ctx.eigen_mc_accumulate_perm(T, K, M, Cm, d_desc, status, _dev(np.asarray(perm, dtype=np.int32)), vsum, False)
+    out = torch.empty((T, K, K), dtype=torch.float64, device=d_desc.device)
+    ctx.eigen_finalize(T, K, M, scale_coef, _dev(D0), _dev(np.asarray(U0, dtype=np.float64)), vsum, status, out)
+    return out.cpu().numpy()
+
+
 def bayes_shrink_by_time(date_off, volatility, capital, ngroup=10, q=1, ctx=None):
     """utils.bayes_shrink on every date of a date-major table -> (out [rows], status [T])."""
     torch = _torch()

@@ -25,6 +25,7 @@
 #include "bmfm_common.cuh"
 #include "jacobi.cuh"
 #include "tridiag_ql.cuh"
+#include "eigen_tile.cuh"
 
 namespace bmfm {
 
@@ -499,6 +500,117 @@ __global__ void __launch_bounds__(256) eig_finalize_kernel(int T, int K, int M, 
   }
 }
 
+
+// vsum[t][k] += sum over the blocks of one batch (dates t0 .. t0 + nd - 1); stream order makes the sum over
+// batches deterministic
+__global__ void et_batch_reduce_kernel(int t0, int nd, int K, int nblk, const double* partial, const int* status,
+                                       double* vsum) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nd * K) return;
+  const int dt = e / K, k = e - dt * K, t = t0 + dt;
+  if (status[t] != BMFM_ST_OK) return;
+  double s = 0.0;
+  for (int b = 0; b < nblk; ++b) s += partial[((size_t)dt * nblk + b) * K + k];
+  vsum[(size_t)t * K + k] += s;
+}
+
+__global__ void et_zero_kernel(size_t n, double* x) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] = 0.0;
+}
+
+constexpr int ET_BATCH_PROBLEMS = 1 << 15;
+
+template <int NT>
+static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0, const int32_t* status,
+                  const int32_t* perm, double* vsum, int accumulate) {
+  constexpr int LD = 8 * NT;
+  const int G = ET_CTHREADS / K;
+  // batch shape: whole simulation ranges of a block of dates, or a block of simulations of one date
+  int nm_b = nsim < ET_BATCH_PROBLEMS ? nsim : ET_BATCH_PROBLEMS;
+  int nd_b = ET_BATCH_PROBLEMS / nm_b;
+  if (nd_b > T) nd_b = T;
+  if (nd_b < 1) nd_b = 1;
+  const size_t Pmax = (size_t)nd_b * nm_b;
+  // blocks of simulations per date in kernel C: about 48 simulations each, more blocks when there are few dates
+  int nblk = (nm_b + 47) / 48;
+  const int want = 4 * ctx->sm_count;
+  if (nd_b * nblk < want) {
+    nblk = (want + nd_b - 1) / nd_b;
+    const int most = (nm_b + G - 1) / G;
+    if (nblk > most) nblk = most;
+  }
+  if (nblk < 1) nblk = 1;
+  const size_t off_de = 0;
+  const size_t off_lam = off_de + bmfm_align_up(Pmax * 2 * LD * 8, 256);
+  const size_t off_V = off_lam + bmfm_align_up(Pmax * LD * 8, 256);
+  const size_t off_h = off_V + bmfm_align_up(Pmax * et_vsz(NT) * 8, 256);
+  const size_t off_part = off_h + bmfm_align_up(Pmax * LD * 8, 256);
+  const size_t off_retry = off_part + bmfm_align_up((size_t)nd_b * nblk * K * 8, 256);
+  const size_t total = off_retry + bmfm_align_up((size_t)(ET_RETRY_CAP + 1) * 4, 256);
+  int rc = bmfm_ws_reserve(ctx, total);
+  if (rc) return rc;
+  char* base = (char*)ctx->ws;
+  EtBatch b;
+  b.K = K; b.LD = LD; b.nsim = nsim; b.C = C; b.D0 = D0; b.status = status;
+  b.de = (double*)(base + off_de); b.lam = (double*)(base + off_lam); b.V = (double*)(base + off_V);
+  b.hinv = (double*)(base + off_h); b.retry = (int*)(base + off_retry);
+  b.fail_every = ctx->opt_eig_fail_every;
+  double* partial = (double*)(base + off_part);
+  BMFM_CUDA(ctx, cudaMemsetAsync(b.retry, 0, 4, ctx->stream));
+  if (!accumulate) {
+    et_zero_kernel<<<(T * K + 255) / 256, 256, 0, ctx->stream>>>((size_t)T * K, vsum);
+    ctx->launches++;
+  }
+  const size_t smem_b = (size_t)2 * K * ET_BTHREADS * 8;
+  const size_t smem_c = ((size_t)G * (et_slot_doubles<NT>() + 2) + (size_t)G * LD) * 8;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(et_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(et_vectors_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
+  int occ_a = 1, occ_c = 1;
+  BMFM_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, et_tridiag_kernel<NT>, ET_WARPS * 32, 0));
+  BMFM_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, et_vectors_kernel<NT>, ET_CTHREADS, smem_c));
+  if (occ_a < 1) occ_a = 1;
+  if (occ_c < 1) occ_c = 1;
+  for (int t0 = 0; t0 < T; t0 += nd_b) {
+    const int nd = T - t0 < nd_b ? T - t0 : nd_b;
+    for (int m0 = 0; m0 < nsim; m0 += nm_b) {
+      const int nm = nsim - m0 < nm_b ? nsim - m0 : nm_b;
+      b.t0 = t0; b.nd = nd; b.m0 = m0; b.nm = nm; b.P = nd * nm;
+      int ga = (b.P + ET_WARPS - 1) / ET_WARPS;
+      if (ga > ctx->sm_count * occ_a) ga = ctx->sm_count * occ_a;
+      et_tridiag_kernel<NT><<<ga, ET_WARPS * 32, 0, ctx->stream>>>(b);
+      et_chain_kernel<<<(b.P + ET_BTHREADS - 1) / ET_BTHREADS, ET_BTHREADS, smem_b, ctx->stream>>>(b);
+      // kernel C sees the batch as its own simulation range: partial sums are per batch
+      EtBatch bc = b;
+      int gc = nd * nblk;
+      if (gc > ctx->sm_count * occ_c) gc = ctx->sm_count * occ_c;
+      et_vectors_kernel<NT><<<gc, ET_CTHREADS, smem_c, ctx->stream>>>(bc, nblk, perm, partial);
+      et_batch_reduce_kernel<<<(nd * K + 255) / 256, 256, 0, ctx->stream>>>(t0, nd, K, nblk, partial, status, vsum);
+      ctx->launches += 4;
+    }
+  }
+  const size_t smem_r = ((size_t)2 * K * (K | 1) + 3 * K + 2) * 8 + 64;
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(et_retry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r));
+  et_retry_kernel<<<ctx->sm_count, 128, smem_r, ctx->stream>>>(K, nsim, C, D0, b.retry, perm, vsum);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+static int et_dispatch(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0, const int32_t* status,
+                       const int32_t* perm, double* vsum, int accumulate) {
+  const int NT = (K + 7) / 8;
+  switch (NT) {
+    case 1: return et_run<1>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 2: return et_run<2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 3: return et_run<3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 4: return et_run<4>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 5: return et_run<5>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 6: return et_run<6>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+  }
+  snprintf(ctx->err, sizeof(ctx->err), "K=%d exceeds the register-tile solver (K <= %d)", K, 8 * ET_MAX_NT);
+  return BMFM_E_UNSUPPORTED;
+}
+
 }  // namespace bmfm
 
 using namespace bmfm;
@@ -557,9 +669,17 @@ extern "C" int bmfm_eigen_mc_accumulate(bmfm_ctx* ctx, int T, int K, int nsim, c
   BMFM_ARG(ctx, T >= 0 && K > 0 && nsim >= 0 && D0 && status && vsum && (C || nsim == 0), "bad arguments");
   if (T == 0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  // solver choice (BMFM_EIG_MODE): 0 split tridiagonal QL (default, K <= 64), 2 fused tridiagonal QL,
-  // 1 block Jacobi (any K)
-  const int mode = ctx->opt_eig_mode;   // bmfm_ctx_set_option "eig_mode"
+  // solver choice (bmfm_ctx_set_option "eig_mode"): 0 automatic = register-tile solver (eigen_tile.cuh) for
+  // K <= 48, else split tridiagonal QL; 1 block Jacobi (any K); 2 fused tridiagonal QL; 3 split tridiagonal QL
+  // (K <= 64); 4 register-tile solver
+  int mode = ctx->opt_eig_mode;
+  if (nsim == 0) {
+    if (!accumulate) BMFM_CUDA(ctx, cudaMemsetAsync(vsum, 0, (size_t)T * K * 8, ctx->stream));
+    return BMFM_OK;
+  }
+  if (mode == 4 || (mode == 0 && K <= 8 * ET_MAX_NT && K * 2 <= ET_CTHREADS))
+    return et_dispatch(ctx, T, K, nsim, C, D0, status, nullptr, vsum, accumulate);
+  if (mode == 3) mode = 0;
   const size_t budget = (size_t)3 << 29;   // 1.5 GiB of scratch for the split form
   const int rmax = 2 * K * K, smax = 8 * K;
   const size_t per_problem = (size_t)K * K * 8 + (size_t)3 * K * 8 + (size_t)rmax * 16 + (size_t)smax * 4 + 4;
@@ -646,4 +766,25 @@ extern "C" int bmfm_eigen_finalize(bmfm_ctx* ctx, int T, int K, int M, double sc
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
+}
+
+// Injected-literal eigen order (SURVEY.md 8(c) mode (iii)): the reference averages the simulated bias by the
+// POSITION LAPACK's dgeev put each eigenpair at (utils.py:79-84).  perm [T][nsim][K]: perm[t][m][r] = that
+// position for the eigenpair of descending rank r of (date t, simulation m), computed by the caller with numpy.
+extern "C" int bmfm_eigen_mc_accumulate_perm(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0,
+                                             const int32_t* status, const int32_t* perm, double* vsum, int accumulate) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && K > 0 && nsim >= 0 && D0 && status && vsum && (C || nsim == 0) && (perm || nsim == 0),
+           "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (nsim == 0) {
+    if (!accumulate) BMFM_CUDA(ctx, cudaMemsetAsync(vsum, 0, (size_t)T * K * 8, ctx->stream));
+    return BMFM_OK;
+  }
+  if (K * 2 > ET_CTHREADS) {
+    snprintf(ctx->err, sizeof(ctx->err), "K=%d: the injected-order entry point needs K <= %d", K, 8 * ET_MAX_NT);
+    return BMFM_E_UNSUPPORTED;
+  }
+  return et_dispatch(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
 }

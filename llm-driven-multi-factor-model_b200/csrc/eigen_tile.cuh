@@ -1,0 +1,606 @@
+// Register-tile eigen solver of the Monte-Carlo loop (default solver of bmfm_eigen_mc_accumulate, K <= 48).
+//
+// Per (date, simulation) the adjustment needs, for every eigenpair (lambda_j, w_j) of the K x K matrix
+//   S = D0^1/2 C_m D0^1/2        (orthogonally similar to the reference's Fm, utils.py:74-79),
+// the ratio  v_j = (w_j' D0 w_j) / lambda_j  (utils.py:80-84).  Three kernels per batch of problems, the
+// intermediate data (about 15 KB per problem) sized to stay in L2:
+//
+//   A  et_tridiag_kernel<NT>   one WARP per problem.  S lives in REGISTERS as NT x NT tiles of 8 x 8 in the
+//                              layout of an FP64 MMA accumulator (lane = (row g = lane / 4, column pair
+//                              c = lane % 4), two doubles per tile), full symmetric storage, so every lane
+//                              holds the same share and all tile indices are compile-time.  Householder
+//                              reduction to tridiagonal form: per step the column is passed through shared
+//                              memory to get it in both the row and the column layout, the symmetric
+//                              matrix-vector product is 2 FMAs per tile and a 4-lane reduction, the rank-2
+//                              update 4 FMAs per tile.  The step loop is unrolled in phases of 8 columns,
+//                              each phase touching only the tiles that are still active.  Output: the
+//                              tridiagonal (d, e) and the reflectors (v_k, 1 / h_k) — Q is never formed.
+//   B  et_chain_kernel         one THREAD per problem: implicit QL on (d, e), eigenvalues only (the chain is
+//                              serial per problem, 32 problems per warp).  A problem that does not converge
+//                              is put on a retry list.
+//   C  et_vectors_kernel<NT>   one THREAD per eigenpair, floor(128 / K) problems per CTA: the eigenvector of
+//                              the tridiagonal by twisted factorisation (forward and backward pivots, twist at
+//                              the smallest |gamma|; O(K) per vector, reciprocals instead of divisions), the
+//                              reflectors applied to it from shared memory (broadcast loads), then
+//                              v_j = sum_i D0_i w_ij^2 / lambda_j accumulated at the eigenvalue's rank
+//                              (descending; or at an injected position, SURVEY.md 8(c) mode (iii)).
+//   R  et_retry_kernel         problems on the retry list are redone with the shared-memory Jacobi solver.
+//
+// Measured against numpy's eigh on factor covariances of regression panels the ratios agree to 1e-13
+// (tests/test_risk_gpu.py pins the end result against the reference to 1e-9).
+#pragma once
+#include "bmfm_common.cuh"
+#include "jacobi.cuh"
+
+namespace bmfm {
+
+constexpr int ET_MAX_NT = 6;          // K <= 48
+constexpr int ET_WARPS = 4;           // warps (= problems in flight) per CTA of kernel A
+constexpr int ET_CTHREADS = 128;      // threads per CTA of kernel C
+constexpr int ET_RETRY_CAP = 1 << 16;
+
+struct EtBatch {
+  int K, LD;               // LD = 8 * NT
+  int nsim;                // simulations in this call
+  int m0, nm;              // simulations [m0, m0 + nm) of the call are in this batch
+  int t0, nd;              // dates [t0, t0 + nd)
+  int P;                   // nd * nm problems; problem p = dt * nm + (m - m0)
+  const double* C;         // [nsim][K][K]
+  const double* D0;        // [T][K]
+  const int* status;       // [T]
+  double* de;              // [2 * LD][P]   d then e, problem-minor
+  double* lam;             // [LD][P]       eigenvalues (unordered), problem-minor
+  double* V;               // [P][VSZ]      reflector k packed by phase: entries 8 * (k / 8) .. LD - 1 (see et_voff)
+  double* hinv;            // [P][LD]       1 / h_k (0: identity reflector)
+  int* retry;              // [0] = count, then ET_RETRY_CAP entries (t * nsim + m)
+  int fail_every;          // test hook: treat every fail_every-th problem as not converged (0 = off)
+};
+
+__device__ __forceinline__ double et_rcp(double x) { return 1.0 / x; }
+
+// Reflector k is stored from index 8 * TK (TK = k / 8, the first row of its phase's tiles) to LD - 1:
+// doubles per problem and the offset of v_k[0] (an address such that v_k[i] is at et_voff + i).
+__host__ __device__ constexpr int et_vsz(int NT) { return 32 * NT * (NT + 1); }
+__host__ __device__ constexpr int et_vrow(int NT, int k) {
+  // start of row k's storage
+  return 64 * ((k / 8) * NT - (k / 8) * ((k / 8) - 1) / 2) + (k % 8) * (8 * NT - 8 * (k / 8));
+}
+__host__ __device__ constexpr int et_voff(int NT, int k) { return et_vrow(NT, k) - 8 * (k / 8); }
+
+// ---------------------------------------------------------------------------------------------------------
+// A: Householder tridiagonalisation, matrix in registers
+// ---------------------------------------------------------------------------------------------------------
+template <int NT>
+struct EtTiles {
+  double a[NT][NT][2];
+};
+
+// one Householder step: column k = 8 * TK + 2 * kp + EK (EK compile-time so that the tile element is a register)
+template <int NT, int TK, int EK>
+__device__ __forceinline__ void et_step(EtTiles<NT>& M, int kp, int n, int lane, double* sx, double* sw, double* Vp,
+                                        double* hinv_p, double* e_out /* smem [LD] */) {
+  const int g = lane >> 2, c = lane & 3;
+  const int kk = 2 * kp + EK, k = 8 * TK + kk;
+  double* vout = Vp + et_voff(NT, 8 * TK) + kk * (8 * NT - 8 * TK);
+  // 1. column k below the diagonal -> shared memory (rows <= k as zeros)
+  if (c == kp) {
+#pragma unroll
+    for (int ti = TK; ti < NT; ++ti) sx[8 * ti + g] = (8 * ti + g > k) ? M.a[ti][TK][EK] : 0.0;
+  }
+  __syncwarp();
+  double vr[NT], vc[NT][2];
+  double s = 0.0;
+#pragma unroll
+  for (int ti = TK; ti < NT; ++ti) {
+    vr[ti] = sx[8 * ti + g];
+    const double2 t2 = *reinterpret_cast<const double2*>(sx + 8 * ti + 2 * c);
+    vc[ti][0] = t2.x; vc[ti][1] = t2.y;
+    s = fma(vr[ti], vr[ti], s);
+  }
+  const double alpha = sx[k + 1];
+  if (k == n - 2) {          // the last sub-diagonal element is never eliminated: it only has to be read out
+    if (lane == 0) e_out[k] = alpha;
+    __syncwarp();
+    return;
+  }
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 8);
+  s += __shfl_xor_sync(0xffffffffu, s, 16);
+  const double sigma = s - alpha * alpha;
+  if (!(sigma > 0.0)) {     // nothing below the sub-diagonal: identity reflector
+    if (lane == 0) { e_out[k] = alpha; hinv_p[k] = 0.0; }
+    if (c == 0) {
+#pragma unroll
+      for (int ti = TK; ti < NT; ++ti) vout[8 * ti + g] = 0.0;
+    }
+    __syncwarp();
+    return;
+  }
+  const double rn = rsqrt(s);
+  double norm = s * rn;
+  norm = fma(fma(-norm, norm, s), 0.5 * rn, norm);       // one Newton step: sqrt(s) to full precision
+  const double beta = alpha >= 0.0 ? -norm : norm;
+  const double v0 = alpha - beta;
+  const double h = fma(fabs(alpha), norm, s);            // v'v / 2
+  const double ih = et_rcp(h);
+  if (lane == 0) { e_out[k] = beta; hinv_p[k] = ih; }
+  // the leading entry of v: index k + 1 lies in tile row TK or TK + 1
+#pragma unroll
+  for (int ti = TK; ti < NT && ti <= TK + 1; ++ti) {
+    if (8 * ti + g == k + 1) vr[ti] = v0;
+    if (8 * ti + 2 * c == k + 1) vc[ti][0] = v0;
+    if (8 * ti + 2 * c + 1 == k + 1) vc[ti][1] = v0;
+  }
+  // the reflector goes out in the row layout (lanes c == 0: 8 consecutive doubles per tile row)
+  if (c == 0) {
+#pragma unroll
+    for (int ti = TK; ti < NT; ++ti) vout[8 * ti + g] = vr[ti];
+  }
+  // 2. p = S v / h   (rows <= k masked), K = v'p / (2h), w = p - K v
+  double pr[NT];
+  double vp = 0.0;
+#pragma unroll
+  for (int ti = TK; ti < NT; ++ti) {
+    double acc = 0.0;
+#pragma unroll
+    for (int tj = TK; tj < NT; ++tj) {
+      acc = fma(M.a[ti][tj][0], vc[tj][0], acc);
+      acc = fma(M.a[ti][tj][1], vc[tj][1], acc);
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    pr[ti] = (8 * ti + g > k) ? acc * ih : 0.0;
+    vp = fma(vr[ti], pr[ti], vp);
+  }
+  vp += __shfl_xor_sync(0xffffffffu, vp, 4);
+  vp += __shfl_xor_sync(0xffffffffu, vp, 8);
+  vp += __shfl_xor_sync(0xffffffffu, vp, 16);
+  const double kc = 0.5 * vp * ih;
+  double wr[NT], wc[NT][2];
+#pragma unroll
+  for (int ti = TK; ti < NT; ++ti) {
+    wr[ti] = fma(-kc, vr[ti], pr[ti]);
+    if (c == 0) sw[8 * ti + g] = wr[ti];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int tj = TK; tj < NT; ++tj) {
+    const double2 t2 = *reinterpret_cast<const double2*>(sw + 8 * tj + 2 * c);
+    wc[tj][0] = t2.x; wc[tj][1] = t2.y;
+  }
+  // 3. S -= v w' + w v'
+#pragma unroll
+  for (int ti = TK; ti < NT; ++ti) {
+#pragma unroll
+    for (int tj = TK; tj < NT; ++tj) {
+      M.a[ti][tj][0] = fma(-vr[ti], wc[tj][0], fma(-wr[ti], vc[tj][0], M.a[ti][tj][0]));
+      M.a[ti][tj][1] = fma(-vr[ti], wc[tj][1], fma(-wr[ti], vc[tj][1], M.a[ti][tj][1]));
+    }
+  }
+  __syncwarp();     // sx / sw are rewritten by the next step
+}
+
+// one phase: columns k = 8 * TK .. 8 * TK + 7 (those <= n - 2; column n - 2 is only read out)
+template <int NT, int TK>
+__device__ __forceinline__ void et_phase(EtTiles<NT>& M, int n, int lane, double* sx, double* sw, double* Vp,
+                                         double* hinv_p, double* e_out) {
+#pragma unroll 1
+  for (int kp = 0; kp < 4; ++kp) {
+    const int k = 8 * TK + 2 * kp;
+    if (k > n - 2) break;
+    et_step<NT, TK, 0>(M, kp, n, lane, sx, sw, Vp, hinv_p, e_out);
+    if (k + 1 > n - 2) break;
+    et_step<NT, TK, 1>(M, kp, n, lane, sx, sw, Vp, hinv_p, e_out);
+  }
+}
+
+template <int NT, int TK>
+struct EtPhases {
+  static __device__ __forceinline__ void run(EtTiles<NT>& M, int n, int lane, double* sx, double* sw, double* Vp,
+                                             double* hinv_p, double* e_out) {
+    if (8 * TK <= n - 2) {
+      et_phase<NT, TK>(M, n, lane, sx, sw, Vp, hinv_p, e_out);
+      EtPhases<NT, TK + 1>::run(M, n, lane, sx, sw, Vp, hinv_p, e_out);
+    }
+  }
+};
+template <int NT>
+struct EtPhases<NT, NT> {
+  static __device__ __forceinline__ void run(EtTiles<NT>&, int, int, double*, double*, double*, double*, double*) {}
+};
+
+template <int NT>
+__global__ void __launch_bounds__(ET_WARPS * 32) et_tridiag_kernel(EtBatch b) {
+  constexpr int LD = 8 * NT;
+  __shared__ __align__(16) double s_buf[ET_WARPS][4 * LD];     // per warp: x, w, e, d
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  const int n = b.K;
+  double* sx = s_buf[warp];
+  double* sw = sx + LD;
+  double* se = sw + LD;
+  double* sd = se + LD;
+  const bool vec2 = (n & 1) == 0;
+  for (int p = blockIdx.x * ET_WARPS + warp; p < b.P; p += gridDim.x * ET_WARPS) {
+    const int dt = p / b.nm, mi = p - dt * b.nm;
+    const int t = b.t0 + dt, m = b.m0 + mi;
+    if (b.status[t] != BMFM_ST_OK) continue;
+    const double* D0 = b.D0 + (size_t)t * n;
+    const double* Cm = b.C + (size_t)m * n * n;
+    double sr[NT], sc[NT][2];
+#pragma unroll
+    for (int ti = 0; ti < NT; ++ti) {
+      const int r = 8 * ti + g, q = 8 * ti + 2 * c;
+      sr[ti] = r < n ? sqrt(D0[r]) : 0.0;
+      sc[ti][0] = q < n ? sqrt(D0[q]) : 0.0;
+      sc[ti][1] = q + 1 < n ? sqrt(D0[q + 1]) : 0.0;
+    }
+    EtTiles<NT> M;
+#pragma unroll
+    for (int ti = 0; ti < NT; ++ti) {
+      const int r = 8 * ti + g;
+#pragma unroll
+      for (int tj = 0; tj < NT; ++tj) {
+        const int q = 8 * tj + 2 * c;
+        double x0 = 0.0, x1 = 0.0;
+        if (r < n) {
+          if (vec2) {
+            if (q < n) { const double2 t2 = *reinterpret_cast<const double2*>(Cm + (size_t)r * n + q); x0 = t2.x; x1 = t2.y; }
+          } else {
+            if (q < n) x0 = Cm[(size_t)r * n + q];
+            if (q + 1 < n) x1 = Cm[(size_t)r * n + q + 1];
+          }
+        }
+        M.a[ti][tj][0] = sr[ti] * x0 * sc[tj][0];
+        M.a[ti][tj][1] = sr[ti] * x1 * sc[tj][1];
+      }
+    }
+    double* Vp = b.V + (size_t)p * et_vsz(NT);
+    double* hp = b.hinv + (size_t)p * LD;
+    EtPhases<NT, 0>::run(M, n, lane, sx, sw, Vp, hp, se);
+    // the diagonal
+#pragma unroll
+    for (int ti = 0; ti < NT; ++ti) {
+      if (2 * c == g) sd[8 * ti + g] = M.a[ti][ti][0];
+      if (2 * c + 1 == g) sd[8 * ti + g] = M.a[ti][ti][1];
+    }
+    __syncwarp();
+    for (int k = lane; k < LD; k += 32) {
+      b.de[(size_t)k * b.P + p] = k < n ? sd[k] : 0.0;
+      b.de[(size_t)(LD + k) * b.P + p] = k < n - 1 ? se[k] : 0.0;
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// B: implicit QL, eigenvalues only, one thread per problem; (d, e) in shared memory [k][thread]
+// ---------------------------------------------------------------------------------------------------------
+__device__ inline bool et_ql_values(double* d, double* e, int st, int n) {
+  for (int l = 0; l < n; ++l) {
+    for (int iter = 0;; ++iter) {
+      int m = l;
+      for (; m < n - 1; ++m) {
+        const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
+        if (fabs(e[m * st]) <= 2.220446049250313e-16 * dd) break;
+      }
+      if (m == l) break;
+      if (iter >= 60) return false;
+      double g = (d[(l + 1) * st] - d[l * st]) / (2.0 * e[l * st]);
+      double r = sqrt(g * g + 1.0);
+      g = d[m * st] - d[l * st] + e[l * st] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
+      double s = 1.0, c = 1.0, p = 0.0;
+      int i = m - 1;
+      bool brk = false;
+      double e_i = e[i * st], d_i = d[i * st], d_ip1 = d[(i + 1) * st];
+      for (; i >= l; --i) {
+        const double e_nx = i > l ? e[(i - 1) * st] : 0.0, d_nx = i > l ? d[(i - 1) * st] : 0.0;
+        const double f = s * e_i;
+        const double bb = c * e_i;
+        const double h2 = f * f + g * g;
+        const double ir = rsqrt(h2);
+        r = h2 * ir;
+        e[(i + 1) * st] = h2 > 0.0 ? r : 0.0;
+        if (!(h2 > 0.0)) {
+          d[(i + 1) * st] = d_ip1 - p;
+          e[m * st] = 0.0;
+          brk = true;
+          break;
+        }
+        s = f * ir;
+        c = g * ir;
+        g = d_ip1 - p;
+        r = (d_i - g) * s + 2.0 * c * bb;
+        p = s * r;
+        d[(i + 1) * st] = g + p;
+        g = c * r - bb;
+        d_ip1 = d_i;
+        d_i = d_nx;
+        e_i = e_nx;
+      }
+      if (!brk) {
+        d[l * st] = d_ip1 - p;
+        e[l * st] = g;
+        e[m * st] = 0.0;
+      }
+    }
+  }
+  return true;
+}
+
+constexpr int ET_BTHREADS = 64;
+
+__global__ void __launch_bounds__(ET_BTHREADS) et_chain_kernel(EtBatch b) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= b.P) return;
+  const int n = b.K, st = blockDim.x, LD = b.LD;
+  const int dt = p / b.nm, mi = p - dt * b.nm;
+  const int t = b.t0 + dt;
+  if (b.status[t] != BMFM_ST_OK) return;
+  double* d = reinterpret_cast<double*>(smem) + threadIdx.x;
+  double* e = d + (size_t)n * st;
+  for (int k = 0; k < n; ++k) {
+    d[k * st] = b.de[(size_t)k * b.P + p];
+    e[k * st] = b.de[(size_t)(LD + k) * b.P + p];
+  }
+  bool ok = et_ql_values(d, e, st, n);
+  if (b.fail_every > 0 && (p % b.fail_every) == 0) ok = false;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int k = 0; k < n; ++k) b.lam[(size_t)k * b.P + p] = ok ? d[k * st] : nan;
+  if (!ok) {
+    const int slot = atomicAdd(b.retry, 1);
+    if (slot < ET_RETRY_CAP) b.retry[1 + slot] = t * b.nsim + (b.m0 + mi);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// C: eigenvectors by twisted factorisation + reflectors + ratio; one thread per eigenpair
+// ---------------------------------------------------------------------------------------------------------
+// Shared memory per problem slot: d[LD] e[LD] d0[LD] lam[LD] hinv[LD] ratio[LD] rank(int)[LD] V[VSZ]
+template <int NT>
+__host__ __device__ constexpr int et_slot_doubles() { return 8 * NT * 7 + et_vsz(NT); }
+
+template <int NT>
+__global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int nblk, const int* perm, double* partial) {
+  constexpr int LD = 8 * NT;
+  constexpr int SLOT = et_slot_doubles<NT>() + 2;     // +2 doubles: shifts the next slot by two banks
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int n = b.K;
+  const int G = ET_CTHREADS / n;                       // problems per round (>= 2 for K <= 48)
+  const int tid = threadIdx.x;
+  const int slot = tid / n, j = tid - slot * n;        // threads >= G * n idle in the per-eigenpair part
+  const bool active = slot < G;
+  double* S0 = reinterpret_cast<double*>(smem);
+  double* vacc = S0 + (size_t)G * SLOT;                // [G][LD] accumulators
+  double* my = S0 + (size_t)(active ? slot : 0) * SLOT;
+  double* s_d = my;
+  double* s_e = s_d + LD;
+  double* s_d0 = s_e + LD;
+  double* s_lam = s_d0 + LD;
+  double* s_hinv = s_lam + LD;
+  double* s_ratio = s_hinv + LD;
+  int* s_rank = reinterpret_cast<int*>(s_ratio + LD);   // LD ints
+  double* s_V = s_ratio + 2 * LD;
+  const int per = (b.nm + nblk - 1) / nblk;
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int w = blockIdx.x; w < b.nd * nblk; w += gridDim.x) {
+    const int dt = w / nblk, blk = w - dt * nblk, t = b.t0 + dt;
+    double* out = partial + ((size_t)t * nblk + blk) * n;
+    if (b.status[t] != BMFM_ST_OK) {
+      // (the partial sums of an invalid date are never read; keep them defined)
+      if (b.m0 == 0) for (int k = tid; k < n; k += ET_CTHREADS) out[k] = 0.0;
+      continue;
+    }
+    __syncthreads();
+    for (int e = tid; e < G * LD; e += ET_CTHREADS) vacc[e] = 0.0;
+    const int mi_lo = blk * per, mi_hi = min(b.nm, mi_lo + per);
+    for (int mi0 = mi_lo; mi0 < mi_hi; mi0 += G) {
+      __syncthreads();
+      // stage the round's problems (all threads): d, e, lam, hinv, V; D0 of the date
+      for (int s = 0; s < G; ++s) {
+        const int mi = mi0 + s;
+        if (mi >= mi_hi) break;
+        const int p = dt * b.nm + mi;
+        double* dst = S0 + (size_t)s * SLOT;
+        for (int k = tid; k < LD; k += ET_CTHREADS) {
+          dst[k] = b.de[(size_t)k * b.P + p];
+          dst[LD + k] = b.de[(size_t)(LD + k) * b.P + p];
+          dst[2 * LD + k] = k < n ? b.D0[(size_t)t * n + k] : 0.0;
+          dst[3 * LD + k] = b.lam[(size_t)k * b.P + p];
+          dst[4 * LD + k] = b.hinv[(size_t)p * LD + k];
+        }
+        const double2* src = reinterpret_cast<const double2*>(b.V + (size_t)p * et_vsz(NT));
+        double2* dv = reinterpret_cast<double2*>(dst + 7 * LD);
+        const int nv = n >= 3 ? et_vrow(NT, n - 2) / 2 : 0;         // reflector rows 0 .. n-3
+        for (int e = tid; e < nv; e += ET_CTHREADS) dv[e] = src[e];
+      }
+      __syncthreads();
+      const int mi = mi0 + slot;
+      const bool work = active && mi < mi_hi;
+      double ratio = 0.0, lam = 0.0;
+      if (work) {
+        lam = s_lam[j];
+        // forward pivots D+_i and backward pivots D-_i of T - lam I, kept as reciprocals
+        double zp[LD], zm[LD];
+        double tiny;
+        {
+          double nrm = 0.0;
+#pragma unroll
+          for (int i = 0; i < LD; ++i) nrm = fmax(nrm, fmax(fabs(s_d[i]), fabs(s_e[i])));
+          tiny = fmax(nrm * 1e-300, 1e-300) + nrm * 4.9e-32;     // pivot floor: eps^2 * |T|
+        }
+        double dp = s_d[0] - lam;
+#pragma unroll
+        for (int i = 0; i < LD - 1; ++i) {
+          if (i < n - 1) {
+            if (fabs(dp) < tiny) dp = dp < 0.0 ? -tiny : tiny;
+            const double r = et_rcp(dp);
+            zp[i] = r;
+            const double ei = s_e[i];
+            dp = fma(-ei * ei, r, s_d[i + 1] - lam);
+          }
+        }
+        // gamma at the last row: D+_{n-1} + D-_{n-1} - (d_{n-1} - lam) = D+_{n-1}, which dp now holds
+        double gbest = fabs(dp);
+        int rbest = n - 1;
+        {
+          double dm = s_d[n - 1] - lam;
+#pragma unroll
+          for (int i = LD - 2; i >= 0; --i) {
+            if (i < n - 1) {
+              if (fabs(dm) < tiny) dm = dm < 0.0 ? -tiny : tiny;
+              const double r = et_rcp(dm);
+              zm[i + 1] = r;
+              const double ei = s_e[i];
+              const double base = s_d[i] - lam;
+              dm = fma(-ei * ei, r, base);                       // D-_i
+              // gamma_i = base - e_{i-1}^2 / D+_{i-1} - e_i^2 / D-_{i+1}
+              double gam = dm;
+              if (i > 0) { const double em = s_e[i - 1]; gam = fma(-em * em, zp[i - 1], gam); }
+              if (fabs(gam) < gbest) { gbest = fabs(gam); rbest = i; }
+            }
+          }
+        }
+        // z: 1 at the twist, z_i = -e_i / D+_i z_{i+1} below it, z_{i+1} = -e_i / D-_{i+1} z_i above it
+        double z[LD];
+        {
+          double cur = 1.0;
+#pragma unroll
+          for (int i = LD - 2; i >= 0; --i) {
+            // downward sweep: valid for i < rbest
+            if (i < n - 1) {
+              const double nxt = (i + 1 == rbest) ? 1.0 : cur;
+              cur = -s_e[i] * zp[i] * nxt;
+              zp[i] = cur;          // z_i if i < rbest
+            }
+          }
+          cur = 1.0;
+#pragma unroll
+          for (int i = 0; i < LD - 1; ++i) {
+            if (i < n - 1) {
+              const double prv = (i == rbest) ? 1.0 : cur;
+              cur = -s_e[i] * zm[i + 1] * prv;
+              zm[i + 1] = cur;      // z_{i+1} if i >= rbest
+            }
+          }
+          double nz = 0.0;
+#pragma unroll
+          for (int i = 0; i < LD; ++i) {
+            double v = 0.0;
+            if (i < n) v = i == rbest ? 1.0 : (i < rbest ? zp[i] : zm[i]);
+            z[i] = v;
+            nz = fma(v, v, nz);
+          }
+          const double sc = rsqrt(nz);
+#pragma unroll
+          for (int i = 0; i < LD; ++i) z[i] *= sc;
+          // (rsqrt is accurate to ~1 ulp after the refinement the compiler emits; the ratio below divides
+          //  by sum w^2 again, so the scale only keeps the numbers in range)
+        }
+        // reflectors: w = H_0 H_1 ... H_{n-3} z, H_k = I - v_k v_k' / h_k, v_k in row k of V (entries i > k)
+#pragma unroll
+        for (int k = LD - 3; k >= 0; --k) {
+          if (k <= n - 3) {
+            const double* vk = s_V + et_voff(NT, k);
+            double dot = 0.0;
+#pragma unroll
+            for (int i = (k + 1) & ~1; i < LD; i += 2) {
+              const double2 v2 = *reinterpret_cast<const double2*>(vk + i);
+              if (i > k) dot = fma(v2.x, z[i], dot);
+              dot = fma(v2.y, z[i + 1], dot);
+            }
+            const double f = dot * s_hinv[k];
+#pragma unroll
+            for (int i = (k + 1) & ~1; i < LD; i += 2) {
+              const double2 v2 = *reinterpret_cast<const double2*>(vk + i);
+              if (i > k) z[i] = fma(-f, v2.x, z[i]);
+              z[i + 1] = fma(-f, v2.y, z[i + 1]);
+            }
+          }
+        }
+        double num = 0.0, den = 0.0;
+#pragma unroll
+        for (int i = 0; i < LD; ++i) {
+          const double zz = z[i] * z[i];
+          num = fma(s_d0[i], zz, num);
+          den += zz;
+        }
+        ratio = num / (den * lam);
+      }
+      // rank of every eigenvalue of the problem (descending, ties by index), then accumulate by position
+      if (work) {
+        int r = 0;
+        for (int i = 0; i < n; ++i) {
+          const double o = s_lam[i];
+          r += (o > lam) || (o == lam && i < j);
+        }
+        if (isnan(lam)) { r = j; ratio = 0.0; }       // not converged: the retry kernel adds this problem
+        int pos = r;
+        if (perm) pos = perm[((size_t)t * b.nsim + (b.m0 + mi)) * n + r];
+        s_rank[j] = pos;
+        s_ratio[j] = ratio;
+      }
+      __syncthreads();
+      if (work) {
+        // thread j collects position j's contribution (a permutation: exactly one source)
+        for (int i = 0; i < n; ++i)
+          if (s_rank[i] == j) vacc[slot * LD + j] += s_ratio[i];
+      }
+    }
+    __syncthreads();
+    for (int k = tid; k < n; k += ET_CTHREADS) {
+      double s = 0.0;
+      for (int q = 0; q < G; ++q) s += vacc[q * LD + k];
+      out[k] = (b.m0 == 0 ? 0.0 : out[k]) + s;
+    }
+    (void)qnan;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// R: problems whose QL iteration did not converge, redone by the shared-memory Jacobi solver (one CTA each)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) et_retry_kernel(int K, int nsim, const double* C, const double* D0,
+                                                       const int* retry, const int* perm, double* vsum) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int ld = K | 1, tid = threadIdx.x, nt = blockDim.x;
+  double* A = reinterpret_cast<double*>(smem);
+  double* V = A + K * ld;
+  double* cs = V + K * ld;          // K + 2
+  double* d0 = cs + K + 2;          // K
+  double* lam = d0 + K;             // K
+  int* flag = reinterpret_cast<int*>(lam + K);   // 8
+  int cnt = retry[0];
+  if (cnt > ET_RETRY_CAP) cnt = ET_RETRY_CAP;
+  for (int q = blockIdx.x; q < cnt; q += gridDim.x) {
+    const int id = retry[1 + q], t = id / nsim, m = id - t * nsim;
+    __syncthreads();
+    if (tid < K) d0[tid] = D0[(size_t)t * K + tid];
+    __syncthreads();
+    const double* Cm = C + (size_t)m * K * K;
+    for (int e = tid; e < K * K; e += nt) {
+      const int a = e / K, bcol = e - a * K;
+      A[a * ld + bcol] = sqrt(d0[a]) * Cm[e] * sqrt(d0[bcol]);
+    }
+    __syncthreads();
+    jacobi_eig_cta(A, V, K, ld, cs, flag);
+    __syncthreads();
+    if (tid < K) lam[tid] = A[tid * ld + tid];
+    __syncthreads();
+    if (tid < K) {
+      const double me = lam[tid];
+      int r = 0;
+      for (int i = 0; i < K; ++i) r += (lam[i] > me) || (lam[i] == me && i < tid);
+      double num = 0.0;
+      for (int i = 0; i < K; ++i) {
+        const double v = V[i * ld + tid];
+        num = fma(d0[i] * v, v, num);
+      }
+      const int pos = perm ? perm[((size_t)t * nsim + m) * K + r] : r;
+      atomicAdd(&vsum[(size_t)t * K + pos], num / me);
+    }
+  }
+}
+
+}  // namespace bmfm

@@ -83,7 +83,7 @@ def test_gauss_cov_legacy_stream(ops):
 
 
 @pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
-@pytest.mark.parametrize("solver", ["0", "1", "2"])     # 0: split tridiagonal QL (default), 1: block Jacobi, 2: fused QL
+@pytest.mark.parametrize("solver", ["0", "1", "2", "3"])     # 0: register-tile solver (default), 1: block Jacobi, 2: fused QL, 3: split QL
 def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, bmfm_option):
     bmfm_option("eig_mode", solver)
     cov = risk["eig_cov_in"]
@@ -97,7 +97,7 @@ def test_eigen_risk_adj_golden_canonical(ops, risk, T, M, solver, bmfm_option):
     print(f"literal-vs-canonical gap T={T} M={M}: {gap:.3e}")
 
 
-@pytest.mark.parametrize("solver", ["0", "1", "2"])
+@pytest.mark.parametrize("solver", ["0", "1", "2", "3"])
 def test_eigen_by_time_oracle(ops, solver, bmfm_option):
     """K = 42 factor covariances from an expanding Newey-West run, simulation length 252."""
     bmfm_option("eig_mode", solver)
@@ -117,6 +117,43 @@ def test_eigen_by_time_oracle(ops, solver, bmfm_option):
     o2, s2 = ops.eigen_risk_adj_by_time(np.concatenate([np.nan_to_num(nw[:2]), bad]),
                                         np.array([1, 1, 0], dtype=np.int32), 50, 3, 1.4)
     assert list(s2) == [1, 1, 2] and np.isnan(o2).all()
+
+
+@pytest.mark.parametrize("T,M", [(40, 5), (252, 8)])
+def test_eigen_risk_adj_golden_literal_injected_order(ops, risk, T, M):
+    """SURVEY.md 8(c) mode (iii): with the eigen order of numpy's general solver injected (D0 / U0 of F0 as
+    np.linalg.eig returns them, and for every simulation the positions dgeev left the eigenpairs at), the GPU
+    reproduces the UNPATCHED reference output."""
+    cov = risk["eig_cov_in"]
+    D0, U0, perm = ops.literal_eig_order(cov, T, M)
+    out = ops.eigen_risk_adj_literal(cov[None], T, M, 1.4, D0[None], U0[None], perm[None])
+    assert record(f"eigen.golden.literal.T{T}_M{M}[per element / sqrt(diag diag)]",
+                  relerr_cov(out[0], risk[f"eig_T{T}_M{M}_literal"])) < TOL
+
+
+def test_eigen_literal_injected_order_pipeline(ops, pipe):
+    """The same on the pipeline panel: every valid date of the unpatched reference run (M = 6)."""
+    nw, ok = pipe["nw"], pipe["er_literal_ok"].astype(bool)
+    sel = np.nonzero(ok)[0]
+    T_sim = len(pipe["factor_ret"])                   # MFM.py:119 passes self.T
+    parts = [ops.literal_eig_order(nw[t], T_sim, 6) for t in sel]
+    out = ops.eigen_risk_adj_literal(nw[sel], T_sim, 6, 1.4, np.stack([p[0] for p in parts]),
+                                     np.stack([p[1] for p in parts]), np.stack([p[2] for p in parts]))
+    assert record("eigen.pipeline.literal[per element / sqrt(diag diag)]", relerr_cov(out, pipe["er_literal"][sel])) < TOL
+
+
+def test_eigen_retry_path_for_unconverged_problems(ops, bmfm_option):
+    """A problem whose QL iteration does not converge is redone by the Jacobi kernel; the test hook marks
+    every third problem as unconverged, the result must not change beyond rounding."""
+    from bmfm.synth import make_factor_returns
+    K, T = 42, 110
+    fr = make_factor_returns(T, K, seed=29)
+    nw, st = ops.newey_west_by_time(fr, 2, 60)
+    want, s0 = ops.eigen_risk_adj_by_time(nw[-2:], st[-2:], 252, 20, 1.4)
+    bmfm_option("eig_fail_every", 3)
+    got, s1 = ops.eigen_risk_adj_by_time(nw[-2:], st[-2:], 252, 20, 1.4)
+    assert (s0 == 0).all() and (s1 == 0).all()
+    assert record("eigen.retry_vs_direct", relerr_cov(got, want)) < 1e-11
 
 
 def test_eigen_config_size_simulation_count(ops):
