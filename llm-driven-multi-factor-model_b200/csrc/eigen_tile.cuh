@@ -386,12 +386,8 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
   const double qnan = __longlong_as_double(0x7ff8000000000000LL);
   for (int w = blockIdx.x; w < b.nd * nblk; w += gridDim.x) {
     const int dt = w / nblk, blk = w - dt * nblk, t = b.t0 + dt;
-    double* out = partial + ((size_t)t * nblk + blk) * n;
-    if (b.status[t] != BMFM_ST_OK) {
-      // (the partial sums of an invalid date are never read; keep them defined)
-      if (b.m0 == 0) for (int k = tid; k < n; k += ET_CTHREADS) out[k] = 0.0;
-      continue;
-    }
+    double* out = partial + ((size_t)dt * nblk + blk) * n;      // partial sums are per batch
+    if (b.status[t] != BMFM_ST_OK) continue;                   // (never read for an invalid date)
     __syncthreads();
     for (int e = tid; e < G * LD; e += ET_CTHREADS) vacc[e] = 0.0;
     const int mi_lo = blk * per, mi_hi = min(b.nm, mi_lo + per);
@@ -552,7 +548,7 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
     for (int k = tid; k < n; k += ET_CTHREADS) {
       double s = 0.0;
       for (int q = 0; q < G; ++q) s += vacc[q * LD + k];
-      out[k] = (b.m0 == 0 ? 0.0 : out[k]) + s;
+      out[k] = s;
     }
     (void)qnan;
   }

@@ -376,7 +376,7 @@ def test_full_factor_pipeline_against_reference(golden_dir):
             "factor_returns.csv", "r_squared.csv", "specific_returns.csv",
             "final_vol_regime_adj_covariance.csv", "volatility_multiplier_lambda.csv"])
         back = pd.read_csv(os.path.join(d, "factor_returns.csv"), index_col=0)
-        assert relerr_cols(back.values, fr.values) < 1e-15
+        assert relerr_cols(back.values, fr.values) < 1e-13      # pandas' fast float parser is not exactly round-trip
 
 
 def test_two_column_elementwise_ops(ops):
