@@ -31,6 +31,7 @@ static int* bmfm_opt_slot(bmfm_ctx* c, const char* name) {
   if (!strcmp(name, "nw_chunks")) return &c->opt_nw_chunks;
   if (!strcmp(name, "eig_mode")) return &c->opt_eig_mode;
   if (!strcmp(name, "eig_fail_every")) return &c->opt_eig_fail_every;
+  if (!strcmp(name, "eig_c_blocks")) return &c->opt_eig_c_blocks;
   if (!strcmp(name, "last_reg_mode")) return &c->last_reg_mode;
   return nullptr;
 }

@@ -520,7 +520,7 @@ __global__ void et_zero_kernel(size_t n, double* x) {
 
 constexpr int ET_BATCH_PROBLEMS = 1 << 15;
 
-template <int NT>
+template <int NT, int N, int MINB>
 static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0, const int32_t* status,
                   const int32_t* perm, double* vsum, int accumulate) {
   constexpr int LD = 8 * NT;
@@ -564,10 +564,10 @@ static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const 
   const size_t smem_b = (size_t)2 * K * ET_BTHREADS * 8;
   const size_t smem_c = ((size_t)G * (et_slot_doubles<NT>() + 2) + (size_t)G * LD) * 8;
   BMFM_CUDA(ctx, cudaFuncSetAttribute(et_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
-  BMFM_CUDA(ctx, cudaFuncSetAttribute(et_vectors_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
+  BMFM_CUDA(ctx, cudaFuncSetAttribute(et_vectors_kernel<NT, N, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
   int occ_a = 1, occ_c = 1;
   BMFM_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, et_tridiag_kernel<NT>, ET_WARPS * 32, 0));
-  BMFM_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, et_vectors_kernel<NT>, ET_CTHREADS, smem_c));
+  BMFM_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, et_vectors_kernel<NT, N, MINB>, ET_CTHREADS, smem_c));
   if (occ_a < 1) occ_a = 1;
   if (occ_c < 1) occ_c = 1;
   for (int t0 = 0; t0 < T; t0 += nd_b) {
@@ -583,7 +583,7 @@ static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const 
       EtBatch bc = b;
       int gc = nd * nblk;
       if (gc > ctx->sm_count * occ_c) gc = ctx->sm_count * occ_c;
-      et_vectors_kernel<NT><<<gc, ET_CTHREADS, smem_c, ctx->stream>>>(bc, nblk, perm, partial);
+      et_vectors_kernel<NT, N, MINB><<<gc, ET_CTHREADS, smem_c, ctx->stream>>>(bc, nblk, perm, partial);
       et_batch_reduce_kernel<<<(nd * K + 255) / 256, 256, 0, ctx->stream>>>(t0, nd, K, nblk, partial, status, vsum);
       ctx->launches += 4;
     }
@@ -599,13 +599,18 @@ static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const 
 static int et_dispatch(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const double* D0, const int32_t* status,
                        const int32_t* perm, double* vsum, int accumulate) {
   const int NT = (K + 7) / 8;
+  // the factor counts of the reference's own runs get compile-time loop bounds: 42 = 1 + 31 + 10 (BASELINE
+  // configs), 39 = 1 + 28 + 10 (demo.py:38)
+  if (K == 42) return ctx->opt_eig_c_blocks == 2 ? et_run<6, 42, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate)
+                                                  : et_run<6, 42, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+  if (K == 39) return et_run<5, 39, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
   switch (NT) {
-    case 1: return et_run<1>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 2: return et_run<2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 3: return et_run<3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 4: return et_run<4>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 5: return et_run<5>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 6: return et_run<6>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 1: return et_run<1, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 2: return et_run<2, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 3: return et_run<3, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 4: return et_run<4, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 5: return et_run<5, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 6: return et_run<6, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
   }
   snprintf(ctx->err, sizeof(ctx->err), "K=%d exceeds the register-tile solver (K <= %d)", K, 8 * ET_MAX_NT);
   return BMFM_E_UNSUPPORTED;

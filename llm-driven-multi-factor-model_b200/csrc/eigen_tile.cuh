@@ -15,10 +15,10 @@
 //                              update 4 FMAs per tile.  The step loop is unrolled in phases of 8 columns,
 //                              each phase touching only the tiles that are still active.  Output: the
 //                              tridiagonal (d, e) and the reflectors (v_k, 1 / h_k) — Q is never formed.
-//   B  et_chain_kernel         one THREAD per problem: implicit QL on (d, e), eigenvalues only (the chain is
-//                              serial per problem, 32 problems per warp).  A problem that does not converge
-//                              is put on a retry list.
-//   C  et_vectors_kernel<NT>   one THREAD per eigenpair, floor(128 / K) problems per CTA: the eigenvector of
+//   B  et_chain_kernel         one THREAD per problem: square-root-free QL (Pal-Walker-Kahan, as LAPACK's dsterf)
+//                              on (d, e^2), eigenvalues only (the chain is serial per problem, 32 problems per
+//                              warp).  A problem that does not converge is put on a retry list.
+//   C  et_vectors_kernel<NT,N> one THREAD per eigenpair, floor(128 / K) problems per CTA: the eigenvector of
 //                              the tridiagonal by twisted factorisation (forward and backward pivots, twist at
 //                              the smallest |gamma|; O(K) per vector, reciprocals instead of divisions), the
 //                              reflectors applied to it from shared memory (broadcast loads), then
@@ -56,7 +56,16 @@ struct EtBatch {
   int fail_every;          // test hook: treat every fail_every-th problem as not converged (0 = off)
 };
 
-__device__ __forceinline__ double et_rcp(double x) { return 1.0 / x; }
+// reciprocal to ~1 ulp without the division's special-case path: hardware seed + two Newton steps.  The callers
+// keep x away from 0, inf and the denormal range.
+__device__ __forceinline__ double et_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
 
 // Reflector k is stored from index 8 * TK (TK = k / 8, the first row of its phase's tiles) to LD - 1:
 // doubles per problem and the offset of v_k[0] (an address such that v_k[i] is at et_voff + i).
@@ -276,54 +285,62 @@ __global__ void __launch_bounds__(ET_WARPS * 32) et_tridiag_kernel(EtBatch b) {
 // ---------------------------------------------------------------------------------------------------------
 // B: implicit QL, eigenvalues only, one thread per problem; (d, e) in shared memory [k][thread]
 // ---------------------------------------------------------------------------------------------------------
-__device__ inline bool et_ql_values(double* d, double* e, int st, int n) {
-  for (int l = 0; l < n; ++l) {
-    for (int iter = 0;; ++iter) {
-      int m = l;
-      for (; m < n - 1; ++m) {
-        const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
-        if (fabs(e[m * st]) <= 2.220446049250313e-16 * dd) break;
-      }
-      if (m == l) break;
-      if (iter >= 60) return false;
-      double g = (d[(l + 1) * st] - d[l * st]) / (2.0 * e[l * st]);
-      double r = sqrt(g * g + 1.0);
-      g = d[m * st] - d[l * st] + e[l * st] / (g + (g >= 0.0 ? fabs(r) : -fabs(r)));
-      double s = 1.0, c = 1.0, p = 0.0;
-      int i = m - 1;
-      bool brk = false;
-      double e_i = e[i * st], d_i = d[i * st], d_ip1 = d[(i + 1) * st];
-      for (; i >= l; --i) {
-        const double e_nx = i > l ? e[(i - 1) * st] : 0.0, d_nx = i > l ? d[(i - 1) * st] : 0.0;
-        const double f = s * e_i;
-        const double bb = c * e_i;
-        const double h2 = f * f + g * g;
-        const double ir = rsqrt(h2);
-        r = h2 * ir;
-        e[(i + 1) * st] = h2 > 0.0 ? r : 0.0;
-        if (!(h2 > 0.0)) {
-          d[(i + 1) * st] = d_ip1 - p;
-          e[m * st] = 0.0;
-          brk = true;
-          break;
-        }
-        s = f * ir;
-        c = g * ir;
-        g = d_ip1 - p;
-        r = (d_i - g) * s + 2.0 * c * bb;
-        p = s * r;
-        d[(i + 1) * st] = g + p;
-        g = c * r - bb;
-        d_ip1 = d_i;
-        d_i = d_nx;
-        e_i = e_nx;
-      }
-      if (!brk) {
-        d[l * st] = d_ip1 - p;
-        e[l * st] = g;
-        e[m * st] = 0.0;
-      }
+// Square-root-free QL (Pal-Walker-Kahan, the iteration of LAPACK's dsterf) on d and the SQUARED off-diagonal e2:
+// eigenvalues only, two reciprocals per rotation and no square root inside the chain.
+__device__ inline bool et_ql_values(double* d, double* e2, int st, int n) {
+  const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
+  int budget = 60 * n;
+  for (int l = 0; l < n;) {
+    int m = l;
+    for (; m < n - 1; ++m) {
+      const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
+      if (e2[m * st] <= eps2 * dd * dd) break;
     }
+    if (m < n - 1) e2[m * st] = 0.0;
+    if (m == l) { ++l; continue; }
+    double p = d[l * st];
+    if (m == l + 1) {                 // 2 x 2 block: closed form (dlae2)
+      const double a = p, c2 = d[(l + 1) * st], b2 = e2[l * st];
+      const double sm = a + c2, df = a - c2;
+      const double rt = sqrt(fma(df, df, 4.0 * b2));
+      double rt1, rt2;
+      const double amx = fabs(a) > fabs(c2) ? a : c2, amn = fabs(a) > fabs(c2) ? c2 : a;
+      if (sm < 0.0) { rt1 = 0.5 * (sm - rt); rt2 = (amx / rt1) * amn - (b2 / rt1); }
+      else if (sm > 0.0) { rt1 = 0.5 * (sm + rt); rt2 = (amx / rt1) * amn - (b2 / rt1); }
+      else { rt1 = 0.5 * rt; rt2 = -0.5 * rt; }
+      d[l * st] = rt1;
+      d[(l + 1) * st] = rt2;
+      e2[l * st] = 0.0;
+      l += 2;
+      continue;
+    }
+    if (--budget < 0) return false;
+    // shift
+    const double rte = sqrt(e2[l * st]);
+    double sigma = (d[(l + 1) * st] - p) / (2.0 * rte);
+    const double r0 = sqrt(fma(sigma, sigma, 1.0));
+    sigma = p - rte / (sigma + (sigma >= 0.0 ? r0 : -r0));
+    double c = 1.0, sn = 0.0;
+    double gamma = d[m * st] - sigma;
+    p = gamma * gamma;
+    double bb = e2[(m - 1) * st], alpha = d[(m - 1) * st];
+    for (int i = m - 1; i >= l; --i) {
+      const double bb_nx = i > l ? e2[(i - 1) * st] : 0.0, alpha_nx = i > l ? d[(i - 1) * st] : 0.0;
+      const double r = p + bb;
+      if (i != m - 1) e2[(i + 1) * st] = sn * r;
+      const double oldc = c;
+      const double ir = r > 0.0 ? et_rcp(r) : 0.0;
+      c = p * ir;
+      sn = bb * ir;
+      const double oldgam = gamma;
+      gamma = c * (alpha - sigma) - sn * oldgam;
+      d[(i + 1) * st] = oldgam + (alpha - gamma);
+      p = c != 0.0 ? gamma * gamma * et_rcp(c) : oldc * bb;
+      bb = bb_nx;
+      alpha = alpha_nx;
+    }
+    e2[l * st] = sn * p;
+    d[l * st] = sigma + gamma;
   }
   return true;
 }
@@ -342,7 +359,8 @@ __global__ void __launch_bounds__(ET_BTHREADS) et_chain_kernel(EtBatch b) {
   double* e = d + (size_t)n * st;
   for (int k = 0; k < n; ++k) {
     d[k * st] = b.de[(size_t)k * b.P + p];
-    e[k * st] = b.de[(size_t)(LD + k) * b.P + p];
+    const double ek = b.de[(size_t)(LD + k) * b.P + p];
+    e[k * st] = ek * ek;
   }
   bool ok = et_ql_values(d, e, st, n);
   if (b.fail_every > 0 && (p % b.fail_every) == 0) ok = false;
@@ -361,12 +379,15 @@ __global__ void __launch_bounds__(ET_BTHREADS) et_chain_kernel(EtBatch b) {
 template <int NT>
 __host__ __device__ constexpr int et_slot_doubles() { return 8 * NT * 7 + et_vsz(NT); }
 
-template <int NT>
-__global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int nblk, const int* perm, double* partial) {
+// N = the factor count as a compile-time constant (the common ones are instantiated), or 0: run-time count,
+// loops padded to LD
+template <int NT, int N, int MINB>
+__global__ void __launch_bounds__(ET_CTHREADS, MINB) et_vectors_kernel(EtBatch b, int nblk, const int* perm, double* partial) {
   constexpr int LD = 8 * NT;
+  constexpr int NL = N > 0 ? N : LD;                  // trip count of the unrolled loops
   constexpr int SLOT = et_slot_doubles<NT>() + 2;     // +2 doubles: shifts the next slot by two banks
   extern __shared__ __align__(16) unsigned char smem[];
-  const int n = b.K;
+  const int n = N > 0 ? N : b.K;
   const int G = ET_CTHREADS / n;                       // problems per round (>= 2 for K <= 48)
   const int tid = threadIdx.x;
   const int slot = tid / n, j = tid - slot * n;        // threads >= G * n idle in the per-eigenpair part
@@ -374,16 +395,15 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
   double* S0 = reinterpret_cast<double*>(smem);
   double* vacc = S0 + (size_t)G * SLOT;                // [G][LD] accumulators
   double* my = S0 + (size_t)(active ? slot : 0) * SLOT;
-  double* s_d = my;
-  double* s_e = s_d + LD;
-  double* s_d0 = s_e + LD;
-  double* s_lam = s_d0 + LD;
-  double* s_hinv = s_lam + LD;
-  double* s_ratio = s_hinv + LD;
+  const double* s_d = my;
+  const double* s_e = s_d + LD;
+  const double* s_d0 = s_e + LD;
+  const double* s_lam = s_d0 + LD;
+  const double* s_hinv = s_lam + LD;
+  double* s_ratio = my + 5 * LD;
   int* s_rank = reinterpret_cast<int*>(s_ratio + LD);   // LD ints
-  double* s_V = s_ratio + 2 * LD;
+  const double* s_V = s_ratio + 2 * LD;
   const int per = (b.nm + nblk - 1) / nblk;
-  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
   for (int w = blockIdx.x; w < b.nd * nblk; w += gridDim.x) {
     const int dt = w / nblk, blk = w - dt * nblk, t = b.t0 + dt;
     double* out = partial + ((size_t)dt * nblk + blk) * n;      // partial sums are per batch
@@ -394,11 +414,11 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
     for (int mi0 = mi_lo; mi0 < mi_hi; mi0 += G) {
       __syncthreads();
       // stage the round's problems (all threads): d, e, lam, hinv, V; D0 of the date
-      for (int s = 0; s < G; ++s) {
-        const int mi = mi0 + s;
+      for (int sl = 0; sl < G; ++sl) {
+        const int mi = mi0 + sl;
         if (mi >= mi_hi) break;
         const int p = dt * b.nm + mi;
-        double* dst = S0 + (size_t)s * SLOT;
+        double* dst = S0 + (size_t)sl * SLOT;
         for (int k = tid; k < LD; k += ET_CTHREADS) {
           dst[k] = b.de[(size_t)k * b.P + p];
           dst[LD + k] = b.de[(size_t)(LD + k) * b.P + p];
@@ -417,107 +437,116 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
       double ratio = 0.0, lam = 0.0;
       if (work) {
         lam = s_lam[j];
-        // forward pivots D+_i and backward pivots D-_i of T - lam I, kept as reciprocals
-        double zp[LD], zm[LD];
-        double tiny;
-        {
-          double nrm = 0.0;
+        // Twisted factorisation of T - lam I.  z[i] first holds 1 / D+_i (forward pivots); the backward pivots
+        // D-_i are streamed once to find the twist r = argmin |gamma_i| and a second time to overwrite z[i],
+        // i > r, with 1 / D-_i — one array instead of two, for one more pass of cheap reciprocals.
+        double z[NL];
+        double nrm = 0.0;
 #pragma unroll
-          for (int i = 0; i < LD; ++i) nrm = fmax(nrm, fmax(fabs(s_d[i]), fabs(s_e[i])));
-          tiny = fmax(nrm * 1e-300, 1e-300) + nrm * 4.9e-32;     // pivot floor: eps^2 * |T|
-        }
+        for (int i = 0; i < NL; ++i) nrm = fmax(nrm, fmax(fabs(s_d[i]), fabs(s_e[i])));
+        const double tiny = fmax(nrm * 4.9e-32, 1e-290);          // pivot floor: eps^2 |T|
         double dp = s_d[0] - lam;
 #pragma unroll
-        for (int i = 0; i < LD - 1; ++i) {
-          if (i < n - 1) {
+        for (int i = 0; i < NL - 1; ++i) {
+          if (N > 0 || i < n - 1) {
             if (fabs(dp) < tiny) dp = dp < 0.0 ? -tiny : tiny;
             const double r = et_rcp(dp);
-            zp[i] = r;
+            z[i] = r;
             const double ei = s_e[i];
             dp = fma(-ei * ei, r, s_d[i + 1] - lam);
           }
         }
-        // gamma at the last row: D+_{n-1} + D-_{n-1} - (d_{n-1} - lam) = D+_{n-1}, which dp now holds
+        // gamma_i = (d_i - lam) - e_{i-1}^2 / D+_{i-1} - e_i^2 / D-_{i+1};  at the last row it is D+_{n-1} = dp
         double gbest = fabs(dp);
         int rbest = n - 1;
         {
           double dm = s_d[n - 1] - lam;
 #pragma unroll
-          for (int i = LD - 2; i >= 0; --i) {
-            if (i < n - 1) {
+          for (int i = NL - 2; i >= 0; --i) {
+            if (N > 0 || i < n - 1) {
               if (fabs(dm) < tiny) dm = dm < 0.0 ? -tiny : tiny;
               const double r = et_rcp(dm);
-              zm[i + 1] = r;
               const double ei = s_e[i];
-              const double base = s_d[i] - lam;
-              dm = fma(-ei * ei, r, base);                       // D-_i
-              // gamma_i = base - e_{i-1}^2 / D+_{i-1} - e_i^2 / D-_{i+1}
+              dm = fma(-ei * ei, r, s_d[i] - lam);               // D-_i
               double gam = dm;
-              if (i > 0) { const double em = s_e[i - 1]; gam = fma(-em * em, zp[i - 1], gam); }
+              if (i > 0) { const double em = s_e[i - 1]; gam = fma(-em * em, z[i - 1], gam); }
               if (fabs(gam) < gbest) { gbest = fabs(gam); rbest = i; }
             }
           }
         }
+        // second backward pass: z_{i+1} = -e_i / D-_{i+1} z_i above the twist needs 1 / D-_{i+1} for i >= r
+        {
+          double dm = s_d[n - 1] - lam;
+#pragma unroll
+          for (int i = NL - 2; i >= 0; --i) {
+            if (N > 0 || i < n - 1) {
+              if (fabs(dm) < tiny) dm = dm < 0.0 ? -tiny : tiny;
+              const double r = et_rcp(dm);
+              if (i + 1 > rbest) z[i + 1] = r;                   // 1 / D-_{i+1}
+              const double ei = s_e[i];
+              dm = fma(-ei * ei, r, s_d[i] - lam);
+            }
+          }
+        }
         // z: 1 at the twist, z_i = -e_i / D+_i z_{i+1} below it, z_{i+1} = -e_i / D-_{i+1} z_i above it
-        double z[LD];
         {
           double cur = 1.0;
 #pragma unroll
-          for (int i = LD - 2; i >= 0; --i) {
-            // downward sweep: valid for i < rbest
-            if (i < n - 1) {
+          for (int i = NL - 2; i >= 0; --i) {
+            if (N > 0 || i < n - 1) {
               const double nxt = (i + 1 == rbest) ? 1.0 : cur;
-              cur = -s_e[i] * zp[i] * nxt;
-              zp[i] = cur;          // z_i if i < rbest
+              cur = -s_e[i] * z[i] * nxt;
+              if (i < rbest) z[i] = cur;
             }
           }
           cur = 1.0;
 #pragma unroll
-          for (int i = 0; i < LD - 1; ++i) {
-            if (i < n - 1) {
+          for (int i = 0; i < NL - 1; ++i) {
+            if (N > 0 || i < n - 1) {
               const double prv = (i == rbest) ? 1.0 : cur;
-              cur = -s_e[i] * zm[i + 1] * prv;
-              zm[i + 1] = cur;      // z_{i+1} if i >= rbest
+              cur = -s_e[i] * z[i + 1] * prv;
+              if (i + 1 > rbest) z[i + 1] = cur;
             }
           }
+#pragma unroll
+          for (int i = 0; i < NL; ++i) {
+            if (i == rbest) z[i] = 1.0;
+            if (N == 0 && i >= n) z[i] = 0.0;
+          }
+        }
+        // keep the numbers in range (the ratio below divides by sum w^2, so the scale itself drops out)
+        {
           double nz = 0.0;
 #pragma unroll
-          for (int i = 0; i < LD; ++i) {
-            double v = 0.0;
-            if (i < n) v = i == rbest ? 1.0 : (i < rbest ? zp[i] : zm[i]);
-            z[i] = v;
-            nz = fma(v, v, nz);
-          }
+          for (int i = 0; i < NL; ++i) nz = fma(z[i], z[i], nz);
           const double sc = rsqrt(nz);
 #pragma unroll
-          for (int i = 0; i < LD; ++i) z[i] *= sc;
-          // (rsqrt is accurate to ~1 ulp after the refinement the compiler emits; the ratio below divides
-          //  by sum w^2 again, so the scale only keeps the numbers in range)
+          for (int i = 0; i < NL; ++i) z[i] *= sc;
         }
         // reflectors: w = H_0 H_1 ... H_{n-3} z, H_k = I - v_k v_k' / h_k, v_k in row k of V (entries i > k)
 #pragma unroll
-        for (int k = LD - 3; k >= 0; --k) {
-          if (k <= n - 3) {
+        for (int k = NL - 3; k >= 0; --k) {
+          if (N > 0 || k <= n - 3) {
             const double* vk = s_V + et_voff(NT, k);
             double dot = 0.0;
 #pragma unroll
-            for (int i = (k + 1) & ~1; i < LD; i += 2) {
+            for (int i = (k + 1) & ~1; i < NL; i += 2) {
               const double2 v2 = *reinterpret_cast<const double2*>(vk + i);
               if (i > k) dot = fma(v2.x, z[i], dot);
-              dot = fma(v2.y, z[i + 1], dot);
+              if (i + 1 < NL) dot = fma(v2.y, z[i + 1], dot);
             }
             const double f = dot * s_hinv[k];
 #pragma unroll
-            for (int i = (k + 1) & ~1; i < LD; i += 2) {
+            for (int i = (k + 1) & ~1; i < NL; i += 2) {
               const double2 v2 = *reinterpret_cast<const double2*>(vk + i);
               if (i > k) z[i] = fma(-f, v2.x, z[i]);
-              z[i + 1] = fma(-f, v2.y, z[i + 1]);
+              if (i + 1 < NL) z[i + 1] = fma(-f, v2.y, z[i + 1]);
             }
           }
         }
         double num = 0.0, den = 0.0;
 #pragma unroll
-        for (int i = 0; i < LD; ++i) {
+        for (int i = 0; i < NL; ++i) {
           const double zz = z[i] * z[i];
           num = fma(s_d0[i], zz, num);
           den += zz;
@@ -546,11 +575,10 @@ __global__ void __launch_bounds__(ET_CTHREADS) et_vectors_kernel(EtBatch b, int 
     }
     __syncthreads();
     for (int k = tid; k < n; k += ET_CTHREADS) {
-      double s = 0.0;
-      for (int q = 0; q < G; ++q) s += vacc[q * LD + k];
-      out[k] = s;
+      double sacc = 0.0;
+      for (int q = 0; q < G; ++q) sacc += vacc[q * LD + k];
+      out[k] = sacc;
     }
-    (void)qnan;
   }
 }
 

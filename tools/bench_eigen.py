@@ -40,7 +40,8 @@ for m in range(M):
     want += ((d0[:, None] * W * W).sum(0) / lam)[::-1]
 ref = None
 for mode in modes:
-    ctx.set_option("eig_mode", mode)
+    ctx.set_option("eig_mode", mode % 10)
+    ctx.set_option("eig_c_blocks", mode // 10)        # e.g. 20 = tile solver with 2 CTAs / SM in the vector kernel
     vsum = torch.zeros((T_e, K), dtype=torch.float64, device="cuda")
     ctx.eigen_mc_accumulate(T_e, K, M, Cm, D0, est, vsum, False)
     torch.cuda.synchronize()
