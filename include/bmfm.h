@@ -72,6 +72,17 @@ int bmfm_ctx_get_option(bmfm_ctx* ctx, const char* name, int* value);
 void bmfm_limits(int* max_Q, int* max_P, int* max_K);
 const char* bmfm_version(void);
 
+/* One whole step with HOST buffers (bench config C2; the e2e leg of bench.py): MFM.reg_by_time (MFM.py:48-76),
+ * MFM.Newey_West_by_time (MFM.py:80-101) and the volatility-regime adjustment of MFM.vol_regime_adj_by_time
+ * (MFM.py:130-167) applied to the Newey-West covariances.  Inputs as bmfm_reg_by_time_host; outputs
+ * factor_ret [T*K], specific_ret [rows], r2 [T], status [T], nw_cov [T*K*K] + nw_status [T], vr_cov [T*K*K],
+ * lamb [T].  The panel is copied in blocks of dates on a copy stream while earlier blocks are regressed and
+ * their results copied back on another (use pinned host memory); synchronises before returning. */
+int bmfm_risk_step_host(bmfm_ctx* ctx, int T, int P, int Q, const int64_t* date_off, const double* cap,
+                        const double* ret, const int32_t* ind, const double* style, int q, double tao_nw,
+                        double tao_vr, double* factor_ret, double* specific_ret, double* r2, int32_t* status,
+                        double* nw_cov, int32_t* nw_status, double* vr_cov, double* lamb);
+
 /* ---- part 1: cross-sectional regression ---------------------------------- */
 /*
  * Replaces MFM.reg_by_time (Barra-master/mfm/MFM.py:48-76) and, per date,

@@ -39,6 +39,7 @@ _SIGNATURES = {
     "bmfm_reg_by_time_gather": ([_P, _I, _I, _I, _I] + [_P] * 9 + [_I, _P, C.c_int64], _I),
     "bmfm_vol_regime_bias_gather": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _I, _P, _P], _I),
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
+    "bmfm_risk_step_host": ([_P, _I, _I, _I] + [_P] * 5 + [_I, _D, _D] + [_P] * 8, _I),
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
     "bmfm_newey_west_by_time_range": ([_P, _I, _I, _I, _D, _P, _I, _I, _P, _P], _I),
@@ -194,6 +195,13 @@ class Context:
                                                  ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
                                                  ptr(exposure), ptr(status)))
 
+
+    def risk_step_host(self, T, P, Q, date_off, cap, ret, ind, style, q, tao_nw, tao_vr,
+                       factor_ret, spec, r2, status, nw_cov, nw_status, vr_cov, lamb):
+        """reg_by_time + Newey_West_by_time + vol-regime on HOST buffers, copies overlapped with the kernels."""
+        self.check(self._L.bmfm_risk_step_host(self._h, T, P, Q, ptr(date_off), ptr(cap), ptr(ret), ptr(ind), ptr(style),
+                                               int(q), float(tao_nw), float(tao_vr), ptr(factor_ret), ptr(spec), ptr(r2),
+                                               ptr(status), ptr(nw_cov), ptr(nw_status), ptr(vr_cov), ptr(lamb)))
 
     # ------------------------------------------------------------------ part 3
     def newey_west_by_time(self, T, K, q, tao, fr, cov, status):

@@ -19,6 +19,10 @@ struct bmfm_ctx {
   void* stage[16];
   size_t stage_bytes[16];
   long long launches;
+  // copy streams and events of the pipelined host entry point (bmfm_risk_step_host), created on first use
+  cudaStream_t copy_in, copy_out;
+  cudaEvent_t pipe_ev[40];
+  bool pipe_ready;
   // per-context experiment switches (bmfm_ctx_set_option); 0 / negative = library default
   int opt_reg_mode, opt_reg_smma, opt_reg_warps, opt_reg_ctas, opt_nw_chunks, opt_eig_mode, opt_eig_fail_every, opt_eig_c_blocks;
   int last_reg_mode;   // kernel form the last bmfm_reg_by_time call launched (bmfm_ctx_get_option "last_reg_mode")

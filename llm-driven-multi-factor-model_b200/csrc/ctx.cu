@@ -59,6 +59,11 @@ extern "C" int bmfm_ctx_destroy(bmfm_ctx* c) {
   if (c->ws) cudaFree(c->ws);
   for (int i = 0; i < 16; ++i)
     if (c->stage[i]) cudaFree(c->stage[i]);
+  if (c->pipe_ready) {
+    cudaStreamDestroy(c->copy_in);
+    cudaStreamDestroy(c->copy_out);
+    for (int i = 0; i < 40; ++i) cudaEventDestroy(c->pipe_ev[i]);
+  }
   if (c->own_stream) cudaStreamDestroy(c->stream);
   free(c);
   return BMFM_OK;
@@ -151,6 +156,112 @@ extern "C" int bmfm_reg_by_time_host(bmfm_ctx* ctx, int T, int P, int Q,
   D2H(r2, 7, T * 8);
   D2H(status, 8, T * 4);
   if (exposure) D2H(exposure, 9, T * K * K * 8);
+  BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return BMFM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// One whole step with HOST buffers, copies overlapped with the kernels
+// ---------------------------------------------------------------------------------------------------------
+// MFM.reg_by_time (MFM.py:48-76) + MFM.Newey_West_by_time (MFM.py:80-101) + the volatility-regime adjustment of
+// MFM.vol_regime_adj_by_time (MFM.py:130-167) applied to the Newey-West covariances — bench config C2 — for a
+// caller whose panel and results live in host memory.  The panel goes to the device in blocks of dates on a
+// copy stream; each block's regression starts as soon as its rows have landed and its specific returns leave
+// on a second copy stream while the next block is still arriving (PCIe is full duplex); the 2 x T x K x K
+// covariance outputs leave while the following kernel runs.  Synchronises before returning.  Pinned host
+// memory is needed for the copies to overlap; pageable memory works but serialises.
+extern "C" int bmfm_risk_step_host(bmfm_ctx* ctx, int T, int P, int Q, const int64_t* date_off, const double* cap,
+                                   const double* ret, const int32_t* ind, const double* style, int q, double tao_nw,
+                                   double tao_vr, double* factor_ret, double* specific_ret, double* r2, int32_t* status,
+                                   double* nw_cov, int32_t* nw_status, double* vr_cov, double* lamb) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && P >= 0 && Q >= 0 && date_off && q >= 0 && tao_nw > 0 && tao_vr > 0, "bad sizes");
+  if (T == 0) return BMFM_OK;
+  BMFM_ARG(ctx, cap && ret && ind && (style || Q == 0) && factor_ret && specific_ret && r2 && status && nw_cov &&
+                nw_status && vr_cov && lamb, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->pipe_ready) {
+    BMFM_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    BMFM_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 40; ++i) BMFM_CUDA(ctx, cudaEventCreateWithFlags(&ctx->pipe_ev[i], cudaEventDisableTiming));
+    ctx->pipe_ready = true;
+  }
+  const size_t rows = (size_t)date_off[T];
+  const size_t K = 1 + (size_t)P + Q;
+  int max_rows = 0;
+  for (int t = 0; t < T; ++t) {
+    const int64_t n = date_off[t + 1] - date_off[t];
+    if (n > max_rows) max_rows = (int)n;
+  }
+  DEVBUF(0, (T + 1) * sizeof(int64_t));
+  DEVBUF(1, rows * 8);
+  DEVBUF(2, rows * 8);
+  DEVBUF(3, rows * 4);
+  DEVBUF(4, rows * Q * 8);
+  DEVBUF(5, T * K * 8);
+  DEVBUF(6, rows * 8);
+  DEVBUF(7, T * 8);
+  DEVBUF(8, T * 4);
+  DEVBUF(10, T * K * K * 8);
+  DEVBUF(11, T * 4);
+  DEVBUF(12, T * K * K * 8);
+  DEVBUF(13, T * 8);
+  const int64_t* d_off = (const int64_t*)ctx->stage[0];
+  double* d_cap = (double*)ctx->stage[1];
+  double* d_ret = (double*)ctx->stage[2];
+  int32_t* d_ind = (int32_t*)ctx->stage[3];
+  double* d_style = (double*)ctx->stage[4];
+  double* d_fr = (double*)ctx->stage[5];
+  double* d_spec = (double*)ctx->stage[6];
+  double* d_r2 = (double*)ctx->stage[7];
+  int32_t* d_st = (int32_t*)ctx->stage[8];
+  double* d_nw = (double*)ctx->stage[10];
+  int32_t* d_nwst = (int32_t*)ctx->stage[11];
+  double* d_vr = (double*)ctx->stage[12];
+  double* d_lamb = (double*)ctx->stage[13];
+  cudaEvent_t* ev = ctx->pipe_ev;
+  // whatever the compute stream still does with the staging buffers comes first
+  BMFM_CUDA(ctx, cudaEventRecord(ev[39], ctx->stream));
+  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, ev[39], 0));
+  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[39], 0));
+  BMFM_CUDA(ctx, cudaMemcpyAsync((void*)d_off, date_off, (T + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->copy_in));
+  const int nchunk = T < 16 ? 1 : 16;
+  for (int c = 0; c < nchunk; ++c) {
+    const int t0 = (int)((long long)T * c / nchunk), t1 = (int)((long long)T * (c + 1) / nchunk);
+    const size_t r0 = (size_t)date_off[t0], r1 = (size_t)date_off[t1];
+    if (r1 > r0) {
+      BMFM_CUDA(ctx, cudaMemcpyAsync(d_cap + r0, cap + r0, (r1 - r0) * 8, cudaMemcpyHostToDevice, ctx->copy_in));
+      BMFM_CUDA(ctx, cudaMemcpyAsync(d_ret + r0, ret + r0, (r1 - r0) * 8, cudaMemcpyHostToDevice, ctx->copy_in));
+      BMFM_CUDA(ctx, cudaMemcpyAsync(d_ind + r0, ind + r0, (r1 - r0) * 4, cudaMemcpyHostToDevice, ctx->copy_in));
+      if (Q > 0)
+        BMFM_CUDA(ctx, cudaMemcpyAsync(d_style + r0 * Q, style + r0 * Q, (r1 - r0) * Q * 8, cudaMemcpyHostToDevice, ctx->copy_in));
+    }
+    BMFM_CUDA(ctx, cudaEventRecord(ev[c], ctx->copy_in));
+    BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev[c], 0));
+    int rc = bmfm_reg_by_time(ctx, t1 - t0, P, Q, max_rows, d_off + t0, d_cap, d_ret, d_ind, d_style, d_fr + (size_t)t0 * K,
+                              d_spec, d_r2 + t0, nullptr, d_st + t0);
+    if (rc) return rc;
+    BMFM_CUDA(ctx, cudaEventRecord(ev[16 + c], ctx->stream));
+    BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[16 + c], 0));
+    if (r1 > r0)
+      BMFM_CUDA(ctx, cudaMemcpyAsync(specific_ret + r0, d_spec + r0, (r1 - r0) * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  }
+  BMFM_CUDA(ctx, cudaMemcpyAsync(factor_ret, d_fr, T * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(r2, d_r2, T * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(status, d_st, T * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
+  int rc = bmfm_newey_west_by_time(ctx, T, (int)K, q, tao_nw, d_fr, d_nw, d_nwst);
+  if (rc) return rc;
+  BMFM_CUDA(ctx, cudaEventRecord(ev[32], ctx->stream));
+  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[32], 0));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(nw_cov, d_nw, T * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(nw_status, d_nwst, T * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
+  rc = bmfm_vol_regime_adj_by_time(ctx, T, (int)K, tao_vr, d_fr, d_nw, d_nwst, d_vr, d_lamb);
+  if (rc) return rc;
+  BMFM_CUDA(ctx, cudaEventRecord(ev[33], ctx->stream));
+  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[33], 0));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(vr_cov, d_vr, T * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  BMFM_CUDA(ctx, cudaMemcpyAsync(lamb, d_lamb, T * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+  BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
   BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return BMFM_OK;
 }

@@ -150,6 +150,39 @@ def test_host_buffer_entry_point(ops):
     assert relerr(fr, fr2) < 1e-12 and relerr(spec, spec2) < 1e-12 and np.max(np.abs(r2 - r22)) < 1e-12
 
 
+def test_host_buffer_whole_step(ops):
+    """bmfm_risk_step_host (pinned host buffers, copies in blocks of dates overlapped with the kernels) against
+    the three device-pointer calls it chains; run twice to cover the reuse of its staging buffers."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.synth import make_panel
+    pan = make_panel(40, 200, 31, 10, seed=17, ragged=0.04)
+    csr = pan.to_csr()
+    T, K = pan.T, 1 + pan.P + pan.Q
+    rows = len(csr["cap"])
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    h = {k: pin(v) for k, v in csr.items()}
+    out = dict(fr=torch.empty((T, K), dtype=torch.float64).pin_memory(), spec=torch.empty(rows, dtype=torch.float64).pin_memory(),
+               r2=torch.empty(T, dtype=torch.float64).pin_memory(), st=torch.empty(T, dtype=torch.int32).pin_memory(),
+               nw=torch.empty((T, K, K), dtype=torch.float64).pin_memory(), nwst=torch.empty(T, dtype=torch.int32).pin_memory(),
+               vr=torch.empty((T, K, K), dtype=torch.float64).pin_memory(), lamb=torch.empty(T, dtype=torch.float64).pin_memory())
+    ctx = _cabi.default_context()
+    fr, spec, r2, status, _ = ops.reg_by_time(csr["date_off"], csr["cap"], csr["ret"], csr["ind"], csr["style"], pan.P,
+                                              group_by_industry=False)
+    nw, nwst = ops.newey_west_by_time(fr, 2, 10.0)
+    vr, lamb = ops.vol_regime_adj_by_time(fr, np.nan_to_num(nw), nwst, 7.0)
+    for _ in range(2):
+        for v in out.values():
+            v.fill_(-7)
+        ctx.risk_step_host(T, pan.P, pan.Q, h["date_off"], h["cap"], h["ret"], h["ind"], h["style"], 2, 10.0, 7.0,
+                           out["fr"], out["spec"], out["r2"], out["st"], out["nw"], out["nwst"], out["vr"], out["lamb"])
+        assert np.array_equal(out["st"].numpy(), status) and np.array_equal(out["nwst"].numpy(), nwst)
+        assert relerr(out["fr"].numpy(), fr) < 1e-12 and relerr(out["spec"].numpy(), spec) < 1e-12
+        assert relerr(out["r2"].numpy(), r2) < 1e-12
+        assert relerr(out["nw"].numpy(), nw) < 1e-11 and relerr(out["vr"].numpy(), vr) < 1e-11
+        assert relerr(out["lamb"].numpy(), lamb) < 1e-11
+
+
 def test_last_industry_empty_raises(ops):
     """-cap/0 in the constraint row (CrossSection.py:70): numpy's pinv raises LinAlgError."""
     from bmfm.synth import make_panel
