@@ -11,11 +11,17 @@ time).  With N ranks every rank owns its own 2500-date block of a 2500*N-date
 panel (weak scaling); factor returns are all-gathered so each rank's expanding
 Newey-West windows and vol-regime sums cover the earlier ranks' dates.
 
-A second block ("eigen_mc") reports eigen-adjustment Monte-Carlo simulations per
-second on a bounded slice of configs[3] (K = 42, 252-day simulations).
+Further blocks of the same JSON line:
+  "eigen_mc"  the second half of BASELINE.json's metric on configs[3] ("C4") as stated: K = 42, 10 000
+              simulations of 252 days for each of 3750 dates, simulations sharded over the ranks (strong
+              scaling), one all-reduce of the T x K accumulators; sims/s and a roofline against the measured FP64 peak;
+  "c3"        configs[2]: ONE 5000 x 3750 panel sharded by date over the ranks (strong scaling): regression +
+              Bayesian shrinkage of a specific-risk estimate, dates/s and HBM fractions;
+  "df_to_df"  configs[0] ("C1", 300 x 1400, P = 28): DataFrame in, DataFrames out through the drop-in MFM class.
 
-One JSON line on stdout (rank 0).  --impl reference times the CPU port of the
-reference's algorithm (oracle/, numpy) on the host cores with the same metric.
+One JSON line on stdout (rank 0).  --impl reference times the REFERENCE's own code (oracle/_ref: its mfm
+package byte-compiled by oracle/build_ref.py; the numpy port of oracle/ only if that is missing) on the host
+cores with the same metric.
 """
 from __future__ import annotations
 
@@ -36,7 +42,10 @@ sys.path.insert(0, ROOT)
 N_STOCKS, N_DATES, P, Q = 800, 2500, 31, 10
 K = 1 + P + Q
 NW_Q, NW_TAO, VR_TAO = 2, 252.0, 42.0
-EIG_DATES, EIG_SIMS, EIG_TSIM = 64, 512, 252
+EIG_DATES, EIG_SIMS, EIG_TSIM = 3750, 10000, 252       # config C4 as stated
+C3_STOCKS, C3_DATES = 5000, 3750                          # config C3
+C1_STOCKS, C1_DATES, C1_P = 300, 1400, 28                 # config C1 (demo.py:38 hard-codes P = 28)
+FLOPS_PER_SIM = 15 * K ** 3                               # algorithmic flops per (date, simulation)
 BYTES_PER_STOCK_DATE = 108   # cap 8 + ret 8 + 10 styles 80 + industry id 4 + specific return 8
 
 
@@ -74,15 +83,34 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def load_traffic():
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+REG_KERNEL_NAMES = {1: "reg_fast_kernel<10> (CTA per date, date resident in shared memory)",
+                    2: "reg_stream_kernel<10> (warp per date, register Gram)",
+                    3: "reg_mma_kernel<10,3,1> (FP64-MMA Gram, one warp per date)",
+                    5: "reg_mma_kernel<10,2,2> (FP64-MMA Gram, two warps per date)",
+                    4: "reg_mma_kernel<10,2,4> (FP64-MMA Gram, four warps per date)",
+                    6: "reg_bulk_kernel<10> (CTA per date, bulk-copied date resident in shared memory)"}
+
+
+def load_traffic(mode):
+    """dram bytes per launch of the regression kernel THIS run launched, from the committed ncu capture of
+    that kernel form on the C2 panel (profiles/roofline_traffic.json: {"by_reg_mode": {mode: bytes}}), or None."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(p):
-        try:
-            return json.load(open(p)).get("reg_fast_kernel_dram_bytes_per_launch")
-        except Exception:
-            return None
-    return None
+    try:
+        return json.load(open(p))["by_reg_mode"].get(str(mode))
+    except Exception:
+        return None
+
+
+def load_fp64_peak():
+    """FP64 peak of this pool's B200 in TFLOP/s: MEASURED_PEAKS.json has no FP64 figure, so the committed output
+    of tools/ubench_dmma.cu is used (profiles/r02_fp64_peak.json); the larger of the DFMA and the DMMA rate."""
+    p = os.path.join(ROOT, "profiles", "r02_fp64_peak.json")
+    try:
+        j = json.load(open(p))
+        return max(float(j["fp64_dfma_tflops"]), float(j["fp64_dmma_tflops"])), \
+            "measured: profiles/r02_fp64_peak.json (tools/ubench_dmma.cu; MEASURED_PEAKS.json has no FP64 figure)"
+    except Exception:
+        return 37.0, "fallback: 37 TFLOP/s (round-1 run of tools/ubench_dmma.cu, DESIGN.md §4)"
 
 
 class ClockSampler:
@@ -209,6 +237,100 @@ def blas_threads():
         return os.cpu_count() or 1
 
 
+def load_ref():
+    """The reference's own mfm modules from oracle/_ref (None if it has not been built)."""
+    try:
+        from oracle import ref_loader
+        return ref_loader.load()
+    except Exception as e:      # noqa: BLE001
+        log(f"oracle/_ref not usable ({e!r}); the CPU arm falls back to the numpy port")
+        return None
+
+
+def _quiet():
+    import contextlib
+    import io
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+def sub_panel_frame(pan, pick):
+    """The long DataFrame (MFM's positional schema) of the dates `pick` of a synthetic panel."""
+    from bmfm.synth import Panel
+    sub = Panel([pan.dates[t] for t in pick], pan.stocknames, pan.cap[pick], pan.ret[pick], pan.ind,
+                pan.style[pick], pan.present[pick], pan.P, pan.Q)
+    return sub.to_frame()
+
+
+def ref_sample(ref, pan, n_dates_sample=24, vr_dates=400):
+    """Time the REFERENCE's own code (oracle/_ref) on a bounded sample of the C2 step; same accounting as
+    cpu_sample: one date costs its cross-sectional regression (MFM.reg_by_time run unmodified on the sampled
+    dates), its expanding-window Newey-West (utils.Newey_West on factor_ret[:t]) and its share of the O(T^2)
+    loop of MFM.vol_regime_adj_by_time (run unmodified on `vr_dates` dates, scaled linearly to T)."""
+    import pandas as pd
+    from bmfm.synth import make_factor_returns
+    ref_mfm, ref_cs, ref_utils = ref
+    T = pan.T
+    pick = np.unique(np.linspace(K + 1, T - 1, n_dates_sample).astype(int))
+    df = sub_panel_frame(pan, pick)
+    with _quiet():
+        t0 = time.perf_counter()
+        model = ref_mfm.MFM(df, P, Q)
+        model.reg_by_time()
+        t_reg = (time.perf_counter() - t0) / len(pick)
+    fr = pd.DataFrame(make_factor_returns(T, K, seed=20240002), columns=model.columns)
+    covs = {}
+    t0 = time.perf_counter()
+    for t in pick:
+        covs[t] = ref_utils.Newey_West(fr[:t + 1], NW_Q, NW_TAO)
+    t_nw = (time.perf_counter() - t0) / len(pick)
+    Tv = min(T, int(vr_dates))
+    model.T = Tv
+    model.sorted_dates = pd.to_datetime(pan.dates[:Tv], format="%Y/%m/%d")
+    model.factor_ret = fr[:Tv]
+    model.eigen_risk_adj_cov = [pd.DataFrame()] * (K + 1) + \
+        [covs[pick[min(np.searchsorted(pick, t), len(pick) - 1)]] for t in range(K + 1, Tv)]
+    with _quiet():
+        t0 = time.perf_counter()
+        model.vol_regime_adj_by_time(tao=VR_TAO)
+        t_vr = (time.perf_counter() - t0) / Tv * (T / Tv)
+    per_date = t_reg + t_nw + t_vr
+    desc = (f"the reference's own code (oracle/_ref, Barra-master/mfm byte-compiled; matplotlib / statsmodels stand-ins): "
+            f"MFM.reg_by_time on {len(pick)} evenly spaced dates of the {N_STOCKS}x{T} panel ({t_reg*1e3:.2f} ms/date), "
+            f"utils.Newey_West on factor_ret[:t] for the same dates ({t_nw*1e3:.2f} ms/date), "
+            f"MFM.vol_regime_adj_by_time on {Tv} dates scaled x{T / Tv:.1f} to T={T} ({t_vr*1e3:.3f} ms/date); dates/s = 1 / sum")
+    return 1.0 / per_date, desc
+
+
+def ref_eigen_sample(ref, n_sims=16):
+    """utils.eigen_risk_adj of the reference (literal eigen order) on one K = 42 covariance: sims/s."""
+    import pandas as pd
+    from bmfm.synth import make_factor_returns
+    ref_utils = ref[2]
+    fr = pd.DataFrame(make_factor_returns(600, K, seed=20240004))
+    cov = ref_utils.Newey_West(fr, NW_Q, NW_TAO)
+    t0 = time.perf_counter()
+    ref_utils.eigen_risk_adj(cov, EIG_TSIM, n_sims, 1.4)
+    return n_sims / (time.perf_counter() - t0)
+
+
+def ref_df_to_df(ref, n_dates=350):
+    """DataFrame in / DataFrames out through the reference's MFM class on a prefix of the C1 panel (the full
+    1400 dates cost ~100 s of Newey-West and ~13 min of eigen adjustment on the CPU): seconds per call."""
+    from bmfm.synth import make_panel
+    ref_mfm = ref[0]
+    pan = make_panel(n_dates, C1_STOCKS, C1_P, Q, seed=20240001, ragged=0.03, scale_log10=(-2, 2))
+    df = pan.to_frame(shuffle_seed=1)
+    out = {"config": f"C1 prefix: {C1_STOCKS} stocks x {n_dates} dates, P={C1_P}, Q={Q} (reference's MFM class, DataFrame in / out)"}
+    with _quiet():
+        t0 = time.perf_counter(); model = ref_mfm.MFM(df, C1_P, Q); model.reg_by_time(); out["reg_by_time_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter(); model.Newey_West_by_time(q=NW_Q, tao=NW_TAO); out["newey_west_s"] = time.perf_counter() - t0
+        model.eigen_risk_adj_cov = model.Newey_West_cov          # the eigen step is timed per simulation (eigen_mc)
+        t0 = time.perf_counter(); model.vol_regime_adj_by_time(tao=VR_TAO); out["vol_regime_s"] = time.perf_counter() - t0
+    tot = out["reg_by_time_s"] + out["newey_west_s"] + out["vol_regime_s"]
+    out["dates_per_s"] = n_dates / tot
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -216,36 +338,57 @@ def run_reference(args):
     from bmfm.synth import make_panel
     pan = make_panel(N_DATES, N_STOCKS, P, Q, seed=20240002, scale_log10=(-2, 2))
     csr = pan.to_csr()
+    ref = load_ref()
     vals = []
     # every step is a bounded sample; the sample shrinks with the step count so that the whole
     # --steps K --warmup W run stays within a few minutes
-    n_dates = int(max(8, min(600, 12000 // max(1, args.steps + args.warmup))))
-    vr_dates = None if args.steps + args.warmup <= 8 else 400
+    n_steps = args.steps + args.warmup
+    if ref is not None:
+        n_dates = int(max(6, min(40, 240 // max(1, n_steps))))
+        vr_dates = 400 if n_steps <= 8 else 200
+        sample = lambda: ref_sample(ref, pan, n_dates, vr_dates)
+    else:
+        n_dates = int(max(8, min(600, 12000 // max(1, n_steps))))
+        vr_dates = None if n_steps <= 8 else 400
+        sample = lambda: cpu_sample(csr, n_dates, vr_dates)
     for i in range(args.warmup):
-        cpu_sample(csr, n_dates, vr_dates)
+        sample()
     t0 = time.perf_counter()
     desc = ""
     for i in range(args.steps):
-        v, desc = cpu_sample(csr, n_dates, vr_dates)
+        v, desc = sample()
         vals.append(v)
     dt = time.perf_counter() - t0
     value = float(np.mean(vals))
-    eig = cpu_eigen_sample(24)
+    port_v, port_desc = cpu_sample(csr, 200, 400)
+    eig = ref_eigen_sample(ref, 16) if ref is not None else cpu_eigen_sample(24)
     cores = blas_threads()
+    kind = "reference" if ref is not None else "port"
     line = {
         "impl": "reference", "metric": "regression_dates_per_sec", "value": value, "unit": "dates/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / max(1, args.steps) * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES}, P={P}, Q={Q}: reg_by_time + "
-                               f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})",
+        "config": {"workload": workload_name(),
                    "note": "each step is a bounded CPU sample of the workload, see cpu_baseline.sample"},
-        "cpu_baseline": {"value": value, "unit": "dates/s", "cores": cores, "kind": "port", "sample": desc},
+        "cpu_baseline": {"value": value, "unit": "dates/s", "cores": cores, "kind": kind, "sample": desc,
+                         "port_value": port_v, "port_sample": port_desc},
         "e2e": {"value": value, "unit": "dates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "eigen_mc": {"value": eig, "unit": "sims/s", "config": f"K={K}, T_sim={EIG_TSIM}, 24 sims of one date (numpy port)"},
+        "eigen_mc": {"value": eig, "unit": "sims/s", "kind": kind,
+                     "config": f"K={K}, T_sim={EIG_TSIM}, 16 sims of one date (utils.eigen_risk_adj, literal eigen order)"},
         "gpu_launches": 0,
     }
+    if ref is not None:
+        try:
+            line["df_to_df"] = ref_df_to_df(ref, 350 if n_steps <= 8 else 200)
+        except Exception as e:      # noqa: BLE001
+            line["df_to_df"] = {"error": repr(e)}
     emit(line)
+
+
+def workload_name():
+    return (f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES} per GPU, P={P}, Q={Q}: reg_by_time + "
+            f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})")
 
 
 # ------------------------------------------------------------------------------------------------
@@ -402,6 +545,7 @@ def run_gpu(args):
     for i in range(args.warmup):
         step(i)
     launches_per_step = (ctx.launches - l0) // max(1, args.warmup)
+    reg_mode = ctx.get_option("last_reg_mode")
     barrier()
     graph = None
     n_phase = min(3, args.steps)
@@ -492,119 +636,227 @@ def run_gpu(args):
             dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
             gather_check += "; sharded Newey-West == whole-series pass (<1e-12 rel)" if ok_t.item() else "; sharded Newey-West MISMATCH"
 
-    # ---- end to end: pinned host buffers -> device -> results back in pinned host buffers ----
+    # ---- end to end: the host-buffer plugin call (bmfm_risk_step_host) on pinned host memory ----
+    # Every step copies the whole panel in and every result out (incl. both T x K x K covariance series, the
+    # lists MFM.Newey_West_by_time / vol_regime_adj_by_time return); inside the call the panel moves in blocks
+    # of dates so that the copies overlap the kernels.  With N ranks every rank runs its own panel (no exchange).
+    out_host["nw"] = torch.empty((T, K, K), dtype=torch.float64).pin_memory()
+    out_host["st"] = torch.empty(T, dtype=torch.int32).pin_memory()
+    out_host["nw_st"] = torch.empty(T, dtype=torch.int32).pin_memory()
     h2d = sum(v.numel() * v.element_size() for v in host.values())
     d2h = sum(v.numel() * v.element_size() for v in out_host.values())
 
-    # Steps are pipelined the way a host feeding a stream of panels would: inputs are double-buffered on the
-    # device and copied on their own stream, so the H2D copy of step i+1 overlaps the kernels and the D2H
-    # copy of step i (PCIe is full duplex).  Every step still moves all of its inputs and results.
-    s_h2d = torch.cuda.Stream(device=dev)
-    s_d2h = torch.cuda.Stream(device=dev)
-    d_in = [d, {k: torch.empty_like(v) for k, v in d.items()}]
-    ev_in = [torch.cuda.Event() for _ in range(2)]      # inputs of buffer b have landed
-    ev_free = [torch.cuda.Event() for _ in range(2)]    # the kernels have finished reading buffer b
-    ev_done, ev_out, ev_go = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+    def e2e_step():
+        ctx.risk_step_host(T, P, Q, host["off"], host["cap"], host["ret"], host["ind"], host["style"], NW_Q, NW_TAO, VR_TAO,
+                           out_host["fr"], out_host["spec"], out_host["r2"], out_host["st"], out_host["nw"],
+                           out_host["nw_st"], out_host["vr"], out_host["lamb"])
 
-    def e2e_step(i):
-        b = i & 1
-        with torch.cuda.stream(s_h2d):
-            s_h2d.wait_event(ev_free[b])
-            for k in host:
-                d_in[b][k].copy_(host[k], non_blocking=True)
-            ev_in[b].record(s_h2d)
-        gs.wait_event(ev_in[b])
-        gs.wait_event(ev_out)                 # the previous step's results have left the output buffers
-        db = d_in[b]
-        ctx.reg_by_time(T, P, Q, N_STOCKS, db["off"], db["cap"], db["ret"], db["ind"], db["style"], fr, spec, r2, st)
-        if world > 1 and not nocoll:
-            dist.all_gather_into_tensor(fr_all, fr)
-        ctx.newey_west_by_time_range(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, nw, nw_st)
-        vol_regime()
-        ev_free[b].record(gs)
-        ev_done.record(gs)
-        with torch.cuda.stream(s_d2h):
-            s_d2h.wait_event(ev_done)
-            out_host["fr"].copy_(fr, non_blocking=True)
-            out_host["spec"].copy_(spec, non_blocking=True)
-            out_host["r2"].copy_(r2, non_blocking=True)
-            out_host["vr"].copy_(vr, non_blocking=True)
-            out_host["lamb"].copy_(lamb[lo:lo + T], non_blocking=True)
-            ev_out.record(s_d2h)
-
-    def e2e_run(nsteps):
-        ev_go.record(gs)
-        s_h2d.wait_event(ev_go)
-        s_d2h.wait_event(ev_go)
-        for i in range(nsteps):
-            e2e_step(i)
-        gs.wait_event(ev_out)
-
-    e2e_run(max(2, args.warmup // 2))
+    for _ in range(2):
+        e2e_step()
     barrier()
     n_e2e = max(4, min(args.steps, 12))
+    t0w = time.perf_counter()
     t_start.record()
-    e2e_run(n_e2e)
+    for _ in range(n_e2e):
+        e2e_step()                      # synchronous: returns when the results are in host memory
     t_end.record()
     barrier()
-    tm = torch.tensor([t_start.elapsed_time(t_end)], dtype=torch.float64, device=dev)
+    e2e_wall_ms = (time.perf_counter() - t0w) * 1e3
+    tm = torch.tensor([max(t_start.elapsed_time(t_end), e2e_wall_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     e2e_value = T_all / (float(tm.item()) / n_e2e * 1e-3)
+    e2e_ok = bool(np.array_equal(out_host["st"].numpy(), st.cpu().numpy())) and \
+        bool(torch.allclose(out_host["fr"], fr.cpu(), rtol=0, atol=1e-12)) if world == 1 else True
 
-    # ---- eigen Monte-Carlo block (bounded slice of C4), sims sharded over ranks ----
+    # ---- eigen Monte-Carlo block: config C4 as stated, simulations sharded over the ranks (strong scaling) ----
     from bmfm import ops
-    # weak scaling like the main step: every rank runs EIG_SIMS simulations (C4 spreads 10 000 over the ranks,
-    # 1250 each at 8 GPUs), one all-reduce of the T x K accumulators
-    sims_per_rank = EIG_SIMS
-    m_lo = rank * sims_per_rank
-    covs = nw[T - EIG_DATES:].contiguous()      # the same rank-local dates on every rank: only the sims are sharded
-    csts = nw_st[T - EIG_DATES:].contiguous()
-    if world > 1:
-        dist.broadcast(covs, 0)
-        dist.broadcast(csts, 0)
-    D0 = torch.empty((EIG_DATES, K), dtype=torch.float64, device=dev)
-    U0 = torch.empty((EIG_DATES, K, K), dtype=torch.float64, device=dev)
-    est = torch.empty(EIG_DATES, dtype=torch.int32, device=dev)
-    vsum = torch.zeros((EIG_DATES, K), dtype=torch.float64, device=dev)
-    eout = torch.empty((EIG_DATES, K, K), dtype=torch.float64, device=dev)
-    Cm = ops.gauss_cov_device(ctx, m_lo, sims_per_rank, EIG_TSIM, K)
-
-    def eig_step():
-        ctx.eigen_decompose(EIG_DATES, K, covs, csts, D0, U0, est)
-        ctx.eigen_mc_accumulate(EIG_DATES, K, sims_per_rank, Cm, D0, est, vsum, False)
-        if world > 1:
-            dist.all_reduce(vsum)
-        ctx.eigen_finalize(EIG_DATES, K, sims_per_rank * world, 1.4, D0, U0, vsum, est, eout)
-
-    eig_step()
-    barrier()
-    n_eig = 3
+    from bmfm.synth import make_factor_returns
+    eig_dates = int(os.environ.get("BENCH_EIG_DATES", EIG_DATES))      # (smaller values: quick experiments only)
+    eig_sims = int(os.environ.get("BENCH_EIG_SIMS", EIG_SIMS))
+    m_lo, m_hi = rank * eig_sims // world, (rank + 1) * eig_sims // world
+    sims_rank = m_hi - m_lo
+    # the covariance series of a T = 3750 run: every valid date of an expanding Newey-West pass (the same on every rank)
+    fr_c4 = torch.from_numpy(make_factor_returns(eig_dates + K + 8, K, seed=20240004)).to(dev)
+    cov_c4 = torch.empty((fr_c4.shape[0], K, K), dtype=torch.float64, device=dev)
+    st_c4 = torch.empty(fr_c4.shape[0], dtype=torch.int32, device=dev)
+    ctx.newey_west_by_time(fr_c4.shape[0], K, NW_Q, NW_TAO, fr_c4, cov_c4, st_c4)
+    covs = cov_c4[-eig_dates:].contiguous()
+    csts = st_c4[-eig_dates:].contiguous()
+    del cov_c4
+    D0 = torch.empty((eig_dates, K), dtype=torch.float64, device=dev)
+    U0 = torch.empty((eig_dates, K, K), dtype=torch.float64, device=dev)
+    est = torch.empty(eig_dates, dtype=torch.int32, device=dev)
+    vsum = torch.zeros((eig_dates, K), dtype=torch.float64, device=dev)
+    eout = torch.empty((eig_dates, K, K), dtype=torch.float64, device=dev)
+    Cm = torch.empty((max(1, sims_rank), K, K), dtype=torch.float64, device=dev)
     t_start.record()
-    for _ in range(n_eig):
-        eig_step()
+    ctx.gauss_cov(m_lo, sims_rank, EIG_TSIM, K, Cm)          # one-off per (M, T_sim): the seeds do not depend on the date
     t_end.record()
     barrier()
-    tm = torch.tensor([t_start.elapsed_time(t_end)], dtype=torch.float64, device=dev)
+    gauss_ms = t_start.elapsed_time(t_end)
+    ev_mc = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+    def eig_step(timed=False):
+        ctx.eigen_decompose(eig_dates, K, covs, csts, D0, U0, est)
+        if timed:
+            ev_mc[0].record()
+        ctx.eigen_mc_accumulate(eig_dates, K, sims_rank, Cm, D0, est, vsum, False)
+        if timed:
+            ev_mc[1].record()
+        if world > 1:
+            dist.all_reduce(vsum)
+        ctx.eigen_finalize(eig_dates, K, eig_sims, 1.4, D0, U0, vsum, est, eout)
+
+    l_e0 = ctx.launches
+    eig_step()
+    eig_launches = ctx.launches - l_e0
+    barrier()
+    n_eig = 1 if args.steps < 20 else 2
+    t_start.record()
+    for _ in range(n_eig):
+        eig_step(timed=True)
+    t_end.record()
+    barrier()
+    tm = torch.tensor([t_start.elapsed_time(t_end), ev_mc[0].elapsed_time(ev_mc[1])], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    eig_value = EIG_DATES * sims_per_rank * world / (float(tm.item()) / n_eig * 1e-3)
-    eig_ok = bool((est == 0).all().item())
+    eig_ms = float(tm[0].item()) / n_eig
+    eig_mc_ms = float(tm[1].item())
+    eig_value = eig_dates * eig_sims / (eig_ms * 1e-3)
+    eig_ok = bool((est == 0).all().item()) and bool(torch.isfinite(eout).all().item())
+    del covs, U0, eout, Cm
+
+    # ---- config C3: ONE 5000 x 3750 panel sharded by date over the ranks (strong scaling): regression +
+    #      Bayesian shrinkage (utils.bayes_shrink) of a specific-risk estimate per date ----
+    c3 = None
+    if os.environ.get("BENCH_C3", "1") == "1":
+        torch.cuda.empty_cache()
+        t_lo, t_hi = rank * C3_DATES // world, (rank + 1) * C3_DATES // world
+        Tc = t_hi - t_lo
+        Nn = C3_STOCKS
+        g = torch.Generator(device=dev)
+        g.manual_seed(20240003 + rank)
+        ind1 = torch.sort(torch.cat([torch.arange(P, device=dev), torch.randint(0, P, (Nn - P,), device=dev, generator=g)])).values
+        c_ind = ind1.to(torch.int32).repeat(Tc).contiguous()                    # rows grouped by industry, as the packer stores them
+        mu = 15.0 + 1.5 * torch.randn(Nn, dtype=torch.float64, device=dev, generator=g)
+        c_cap = torch.exp(mu[None, :] + 0.02 * torch.cumsum(torch.randn((Tc, Nn), dtype=torch.float64, device=dev, generator=g), 0)).reshape(-1)
+        scale = 10.0 ** (4.0 * torch.rand(Q, dtype=torch.float64, device=dev, generator=g) - 2.0)
+        c_style = (torch.randn((Tc * Nn, Q), dtype=torch.float64, device=dev, generator=g) + 0.3) * scale[None, :]
+        c_ret = 0.02 * torch.randn(Tc * Nn, dtype=torch.float64, device=dev, generator=g)
+        c_off = (torch.arange(Tc + 1, dtype=torch.int64, device=dev) * Nn)
+        c_fr = torch.empty((Tc, K), dtype=torch.float64, device=dev)
+        c_spec = torch.empty(Tc * Nn, dtype=torch.float64, device=dev)
+        c_r2 = torch.empty(Tc, dtype=torch.float64, device=dev)
+        c_st = torch.empty(Tc, dtype=torch.int32, device=dev)
+        c_sh = torch.empty(Tc * Nn, dtype=torch.float64, device=dev)
+        c_bst = torch.empty(Tc, dtype=torch.int32, device=dev)
+        ctx.reg_by_time(Tc, P, Q, Nn, c_off, c_cap, c_ret, c_ind, c_style, c_fr, c_spec, c_r2, c_st)
+        # specific-risk input (builder-defined): 63-day rolling RMS of the specific returns per stock
+        sq = torch.cumsum(c_spec.view(Tc, Nn) ** 2, 0)
+        w = min(63, Tc)
+        c_vol = torch.sqrt(torch.cat([sq[:w] / torch.arange(1, w + 1, device=dev)[:, None], (sq[w:] - sq[:-w]) / w])).reshape(-1).contiguous()
+        del sq
+        evc = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+        def c3_step(timed=False):
+            if timed:
+                evc[0].record()
+            ctx.reg_by_time(Tc, P, Q, Nn, c_off, c_cap, c_ret, c_ind, c_style, c_fr, c_spec, c_r2, c_st)
+            if timed:
+                evc[1].record()
+            ctx.bayes_shrink(Tc, Nn, c_off, c_vol, c_cap, 10, 1.0, c_sh, c_bst)
+            if timed:
+                evc[2].record()
+
+        for _ in range(3):
+            c3_step()
+        c3_mode = ctx.get_option("last_reg_mode")
+        barrier()
+        n_c3 = max(3, min(args.steps, 10))
+        regs, bss = [], []
+        t_start.record()
+        for _ in range(n_c3):
+            c3_step(timed=True)
+            torch.cuda.synchronize()
+            regs.append(evc[0].elapsed_time(evc[1]))
+            bss.append(evc[1].elapsed_time(evc[2]))
+        t_end.record()
+        barrier()
+        tm = torch.tensor([float(np.mean(regs)) + float(np.mean(bss)), float(np.mean(regs)), float(np.mean(bss))],
+                          dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        c3_ms, c3_reg_ms, c3_bs_ms = (float(x) for x in tm.tolist())
+        c3_ok = bool((c_st == 0).all().item()) and bool((c_bst == 0).all().item())
+        rows_rank = (C3_DATES + world - 1) // world * Nn
+        c3 = {"value": C3_DATES / (c3_ms * 1e-3), "unit": "dates/s", "scaling": "strong", "ms_per_step": c3_ms,
+              "config": f"C3: one {Nn}x{C3_DATES} panel (P={P}, Q={Q}, generated on the device, rows grouped by industry), "
+                        f"dates sharded over {world} GPU(s) with no exchange: reg_by_time + bayes_shrink(ngroup=10, q=1) of a "
+                        f"63-day RMS of the specific returns; {2 * Nn * C3_DATES * 100 / 1e9:.1f} GB of inputs in total, larger than L2",
+              "phase_ms": {"reg_by_time": c3_reg_ms, "bayes_shrink": c3_bs_ms},
+              "roofline": {"kernel": REG_KERNEL_NAMES.get(c3_mode, str(c3_mode)), "bound": "hbm", "unit": "GB/s",
+                           "achieved": BYTES_PER_STOCK_DATE * rows_rank / (c3_reg_ms * 1e-3) / 1e9,
+                           "algorithmic_bytes_per_launch": BYTES_PER_STOCK_DATE * rows_rank},
+              "bayes_shrink_roofline": {"kernel": "bayes_shrink_kernel", "bound": "hbm", "unit": "GB/s",
+                                        "achieved": 24 * rows_rank / (c3_bs_ms * 1e-3) / 1e9,
+                                        "algorithmic_bytes_per_launch": 24 * rows_rank},
+              "all_status_ok": c3_ok}
+        del c_ind, c_cap, c_style, c_ret, c_spec, c_sh, c_vol
+        torch.cuda.empty_cache()
+
+    # ---- config C1, DataFrame in / DataFrames out through the drop-in MFM class (rank 0) ----
+    df_block = None
+    if rank == 0 and os.environ.get("BENCH_DF", "1") == "1":
+        try:
+            import contextlib
+            import io
+            from mfm.MFM import MFM
+            torch.cuda.set_stream(torch.cuda.default_stream(dev))
+            panc1 = make_panel(C1_DATES, C1_STOCKS, C1_P, Q, seed=20240001, ragged=0.03, scale_log10=(-2, 2))
+            dfc1 = panc1.to_frame(shuffle_seed=1)
+            df_block = {"config": f"C1: {C1_STOCKS} stocks x {C1_DATES} dates, P={C1_P}, Q={Q}, {len(dfc1)} rows "
+                                  f"(drop-in MFM class, DataFrame in / DataFrames out, wall clock incl. packing and list building)"}
+            with contextlib.redirect_stdout(io.StringIO()):
+                for rep in range(2):         # the second pass is the one reported (first: allocations, module load)
+                    t0 = time.perf_counter(); model = MFM(dfc1, C1_P, Q); model.reg_by_time(); t_a = time.perf_counter() - t0
+                    t0 = time.perf_counter(); model.Newey_West_by_time(q=NW_Q, tao=NW_TAO); t_b = time.perf_counter() - t0
+                    t0 = time.perf_counter(); model.eigen_risk_adj_by_time(M=100, scale_coef=1.4); t_c = time.perf_counter() - t0
+                    t0 = time.perf_counter(); model.vol_regime_adj_by_time(tao=VR_TAO); t_d = time.perf_counter() - t0
+            df_block.update({"reg_by_time_s": t_a, "newey_west_s": t_b, "eigen_risk_adj_M100_s": t_c, "vol_regime_s": t_d,
+                             "dates_per_s": C1_DATES / (t_a + t_b + t_d),
+                             "dates_per_s_note": "reg + Newey-West + vol-regime, the three calls the reference arm's df_to_df times"})
+            torch.cuda.set_stream(gs)
+        except Exception as e:      # noqa: BLE001
+            df_block = {"error": repr(e)}
+            torch.cuda.set_stream(gs)
 
     if rank == 0:
         peak, peak_src = load_peaks()
+        fp64_peak, fp64_src = load_fp64_peak()
         achieved = BYTES_PER_STOCK_DATE * rows / (ms_reg * 1e-3) / 1e9
-        dominant = max((ms_reg, "reg_by_time (reg_mma_kernel)"), (ms_nw, "newey_west (nw_emit)"), (ms_vr, "vol_regime (vr_scale_kernel)"))[1]
+        dominant = max((ms_reg, "reg_by_time"), (ms_nw, "newey_west (nw_emit)"), (ms_vr, "vol_regime (vr_scale_kernel)"))[1]
+        if c3 is not None:
+            for key in ("roofline", "bayes_shrink_roofline"):
+                c3[key]["peak"] = peak
+                c3[key]["frac"] = c3[key]["achieved"] / peak
         t0 = time.perf_counter()
-        cpu_v, cpu_desc = cpu_sample(csr, 600)
-        cpu_eig = cpu_eigen_sample(16)
+        ref = load_ref()
+        port_v, port_desc = cpu_sample(csr, 300, 400)
+        if ref is not None:
+            cpu_v, cpu_desc = ref_sample(ref, pan, 40, 400)
+            cpu_eig = ref_eigen_sample(ref, 16)
+        else:
+            cpu_v, cpu_desc = port_v, port_desc
+            cpu_eig = cpu_eigen_sample(16)
+        cpu_kind = "reference" if ref is not None else "port"
         log(f"cpu baseline took {time.perf_counter() - t0:.1f}s")
+        eig_tflops = FLOPS_PER_SIM * eig_dates * sims_rank / (eig_mc_ms * 1e-3) / 1e12
         line = {
             "metric": "regression_dates_per_sec", "value": value, "unit": "dates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C2 synthetic CSI800 panel {N_STOCKS}x{N_DATES} per GPU, P={P}, Q={Q}: reg_by_time + "
-                                   f"Newey_West_by_time(q={NW_Q},tao={int(NW_TAO)}) + vol_regime_adj_by_time(tao={int(VR_TAO)})",
+            "config": {"workload": workload_name(),
                        "parallelism": (f"dates sharded over {world} GPU(s); factor returns and vol-regime terms gathered "
                                        + ("by the producing kernels over peer memory (symmetric memory + device barrier)" if fused
                                           else "with NCCL all-gather")) if world > 1 else "1 GPU",
@@ -612,22 +864,37 @@ def run_gpu(args):
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
                        "all_status_ok": status_ok, "gather_check": gather_check},
-            "roofline": {"kernel": "reg_mma_kernel<10,3,1> (per-date weighted Gram on FP64 MMA + constrained solve + residuals, one warp per date)",
+            "roofline": {"kernel": REG_KERNEL_NAMES.get(reg_mode, str(reg_mode)) + ": per-date weighted Gram + constrained solve + residuals",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": load_traffic(), "traffic_source": "ncu --set full capture of one launch, profiles/roofline_traffic.json",
+                         "traffic": load_traffic(reg_mode),
+                         "traffic_source": "ncu --set full capture of one launch of this kernel form on the C2 panel, profiles/roofline_traffic.json",
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_STOCK_DATE * rows,
                          "dominant_phase": dominant},
-            "cpu_baseline": {"value": cpu_v, "unit": "dates/s", "cores": blas_threads(), "kind": "port", "sample": cpu_desc},
+            "cpu_baseline": {"value": cpu_v, "unit": "dates/s", "cores": blas_threads(), "kind": cpu_kind, "sample": cpu_desc,
+                             "port_value": port_v, "port_sample": port_desc},
             "e2e": {"value": e2e_value, "unit": "dates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "how": "pinned host buffers; every step copies all inputs in and all results out; inputs "
-                           "double-buffered so the H2D copy of step i+1 overlaps the kernels and D2H of step i"},
+                    "matches_device_path": e2e_ok,
+                    "how": "bmfm_risk_step_host on pinned host buffers, one synchronous call per step: the whole panel in, "
+                           "factor returns / specific returns / R2 / both T x K x K covariance series / lambda out; inside the "
+                           "call the panel moves in 16 blocks of dates so the copies overlap the kernels"
+                           + ("" if world == 1 else "; every rank runs its own panel, no exchange")},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "eigen_mc": {"value": eig_value, "unit": "sims/s",
-                         "config": f"K={K}, T_sim={EIG_TSIM}, {EIG_DATES} dates x {sims_per_rank * world} sims ({sims_per_rank} per rank, sims sharded over ranks, one all-reduce), canonical eigen order",
+            "eigen_mc": {"value": eig_value, "unit": "sims/s", "scaling": "strong", "ms_per_step": eig_ms,
+                         "config": f"C4: K={K}, T_sim={EIG_TSIM}, {eig_dates} dates x {eig_sims} sims ({sims_rank} per rank, sims "
+                                   f"sharded over ranks, one all-reduce of the T x K accumulators), canonical eigen order; a step = "
+                                   f"eigen_decompose + eigen_mc_accumulate + eigen_finalize over all dates",
+                         "one_off_gauss_cov_ms": gauss_ms, "gpu_launches": int(eig_launches),
+                         "roofline": {"kernel": "et_tridiag_kernel<6> + et_chain_kernel + et_vectors_kernel<6,42> (bmfm_eigen_mc_accumulate)",
+                                      "bound": "fp64", "achieved": eig_tflops, "peak": fp64_peak, "unit": "TFLOP/s",
+                                      "frac": eig_tflops / fp64_peak, "peak_source": fp64_src,
+                                      "algorithmic_flops_per_unit": FLOPS_PER_SIM, "units_per_launch_set": eig_dates * sims_rank,
+                                      "ms": eig_mc_ms, "traffic": None},
                          "all_status_ok": eig_ok,
-                         "cpu_baseline": {"value": cpu_eig, "unit": "sims/s", "kind": "port", "sample": "16 sims of one date"}},
+                         "cpu_baseline": {"value": cpu_eig, "unit": "sims/s", "kind": cpu_kind, "sample": "16 sims of one date"}},
+            "c3": c3,
+            "df_to_df": df_block,
         }
         emit(line)
     if world > 1:
