@@ -72,6 +72,20 @@ int bmfm_ctx_get_option(bmfm_ctx* ctx, const char* name, int* value);
 void bmfm_limits(int* max_Q, int* max_P, int* max_K);
 const char* bmfm_version(void);
 
+/* Device side of the panel packer (replaces the host passes of demo.py:33-35 and
+ * MFM.py:58-61 over the long table).
+ * bmfm_onehot_to_index: the P one-hot industry columns (int64, element (r, p) at onehot[r * row_stride +
+ *   p * col_stride]) -> ind int32 [rows] (-1: no column set), bit-exact.  flags int32 [2] (device) receives the
+ *   number of thread blocks that saw an entry other than 0 / 1 and that saw a row with more than one 1.
+ * bmfm_pack_gather: out[i] = in[order[i]] for cap, ret, ind and the Q style columns (element (r, q) at
+ *   style[r * style_row_stride + q * style_col_stride]); style_out row-major [rows * Q]: the layout
+ *   bmfm_reg_by_time reads.  order int64 [rows] = the (date, industry, stock name) sort permutation. */
+int bmfm_onehot_to_index(bmfm_ctx* ctx, int64_t rows, int P, const int64_t* onehot, int64_t row_stride,
+                         int64_t col_stride, int32_t* ind, int32_t* flags);
+int bmfm_pack_gather(bmfm_ctx* ctx, int64_t rows, int Q, const int64_t* order, const double* cap, const double* ret,
+                     const int32_t* ind, const double* style, int64_t style_row_stride, int64_t style_col_stride,
+                     double* cap_out, double* ret_out, int32_t* ind_out, double* style_out);
+
 /* One whole step with HOST buffers (bench config C2; the e2e leg of bench.py): MFM.reg_by_time (MFM.py:48-76),
  * MFM.Newey_West_by_time (MFM.py:80-101) and the volatility-regime adjustment of MFM.vol_regime_adj_by_time
  * (MFM.py:130-167) applied to the Newey-West covariances.  Inputs as bmfm_reg_by_time_host; outputs

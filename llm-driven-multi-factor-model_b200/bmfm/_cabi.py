@@ -39,6 +39,8 @@ _SIGNATURES = {
     "bmfm_reg_by_time_gather": ([_P, _I, _I, _I, _I] + [_P] * 9 + [_I, _P, C.c_int64], _I),
     "bmfm_vol_regime_bias_gather": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _I, _P, _P], _I),
     "bmfm_reg_by_time_host": ([_P, _I, _I, _I] + [_P] * 10, _I),
+    "bmfm_onehot_to_index": ([_P, C.c_int64, _I, _P, C.c_int64, C.c_int64, _P, _P], _I),
+    "bmfm_pack_gather": ([_P, C.c_int64, _I, _P, _P, _P, _P, _P, C.c_int64, C.c_int64, _P, _P, _P, _P], _I),
     "bmfm_risk_step_host": ([_P, _I, _I, _I] + [_P] * 5 + [_I, _D, _D] + [_P] * 8, _I),
     "bmfm_newey_west_by_time": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_newey_west_scratch_bytes": ([_I, _I, _I], C.c_size_t),
@@ -111,6 +113,11 @@ def ptr(t):
         return C.c_void_p(t.data_ptr())
     assert t.flags["C_CONTIGUOUS"]
     return C.c_void_p(t.ctypes.data)
+
+
+def _raw(t):
+    """Address of a (possibly strided) torch tensor, or NULL."""
+    return None if t is None else C.c_void_p(t.data_ptr())
 
 
 class Context:
@@ -195,6 +202,14 @@ class Context:
                                                  ptr(ind), ptr(style), ptr(factor_ret), ptr(spec), ptr(r2),
                                                  ptr(exposure), ptr(status)))
 
+
+    def onehot_to_index(self, rows, P, onehot, row_stride, col_stride, ind, flags):
+        self.check(self._L.bmfm_onehot_to_index(self._h, int(rows), int(P), _raw(onehot), int(row_stride), int(col_stride),
+                                                ptr(ind), ptr(flags)))
+
+    def pack_gather(self, rows, Q, order, cap, ret, ind, style, srs, scs, cap_o, ret_o, ind_o, style_o):
+        self.check(self._L.bmfm_pack_gather(self._h, int(rows), int(Q), ptr(order), ptr(cap), ptr(ret), ptr(ind), _raw(style),
+                                            int(srs), int(scs), ptr(cap_o), ptr(ret_o), ptr(ind_o), ptr(style_o)))
 
     def risk_step_host(self, T, P, Q, date_off, cap, ret, ind, style, q, tao_nw, tao_vr,
                        factor_ret, spec, r2, status, nw_cov, nw_status, vr_cov, lamb):

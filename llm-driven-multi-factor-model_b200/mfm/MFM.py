@@ -6,7 +6,7 @@ import pandas as pd
 
 from bmfm import _cabi
 from bmfm import ops as _ops
-from bmfm.panel import pack_frame
+from bmfm.panel import pack_frame_device, LazyFrameList
 from mfm.utils import progressbar
 
 
@@ -42,31 +42,34 @@ class MFM():
 
     def reg_by_time(self):
         '''
-        逐时间点进行横截面多因子回归 (MFM.py:48-76) — one kernel launch for all dates
+        逐时间点进行横截面多因子回归 (MFM.py:48-76) — the table is packed on the GPU, one kernel launch for all dates
         '''
-        import torch
         print('===================================逐时间点进行横截面多因子回归===================================')
-        pk = pack_frame(self.data, self.P, self.Q)
         ctx = _cabi.default_context()
-        dv = lambda a: torch.from_numpy(a).cuda()
+        # a P that does not match the table's columns fails the way MFM.py:70 does (ValueError from the constructor)
+        pd.DataFrame(np.empty((0, 1 + self.P + self.Q)), columns=self.columns)
+        # the long table is packed on the GPU and never comes back: the regression reads it where it lies
+        pk = pack_frame_device(self.data, self.P, self.Q, ctx, dates=self.dates)
         fr, spec, r2, status, _ = _ops.reg_by_time_device(
-            ctx, pk.T, pk.P, pk.Q, pk.max_rows, dv(pk.date_off), dv(pk.cap), dv(pk.ret), dv(pk.ind), dv(pk.style))
+            ctx, pk.T, pk.P, pk.Q, pk.max_rows, pk.date_off, pk.cap, pk.ret, pk.ind, pk.style)
         status = status.cpu().numpy()
         if (status == _cabi.ST_NONFINITE).any():
             raise np.linalg.LinAlgError("SVD did not converge")
         fr = fr.cpu().numpy()
-        spec = spec.cpu().numpy()[pk.name_pos]
         r2 = r2.cpu().numpy()
 
         # DataFrame(factor_ret, columns=self.columns) raises ValueError on a P mismatch, like MFM.py:70
         factor_ret = pd.DataFrame(fr, columns=self.columns, index=self.sorted_dates)
         R2 = pd.DataFrame(r2, columns=['R2'], index=self.sorted_dates)
-        specific_ret = []
-        off = pk.date_off
-        for t in range(self.T):
-            a, b = off[t], off[t + 1]
-            specific_ret.append(pd.DataFrame([spec[a:b]], columns=list(pk.names_sorted[a:b]),
-                                             index=[self.sorted_dates[t]]))
+        sorted_dates = self.sorted_dates
+
+        def fetch():
+            # first access to a specific-return frame: one gather on the device, one copy, names by code
+            vals = spec[pk.name_pos].cpu().numpy()
+            names = pk.name_uniques[pk.name_code[pk.ref_order].cpu().numpy()]
+            return vals, names, pk.date_off_host, sorted_dates
+
+        specific_ret = LazyFrameList(self.T, fetch)          # MFM.py:66, built on demand
         self.last_capital = pk.last_capital
         self._status = status
         self.factor_ret = factor_ret

@@ -4,7 +4,8 @@
 
 The reference is pure Python, so "building" it means byte-compiling its four live source files
 (Barra-master/mfm/{__init__,MFM,CrossSection,utils}.py — NOT the stale copies under build/, dist/, mfm-1.0/,
-SURVEY.md §2) where they lie into sourceless ``.pyc`` modules under oracle/_ref/mfm/.  Nothing is edited and
+SURVEY.md §2) where they lie into code objects under oracle/_ref/mfm/ (``.pyc`` content in files named ``*.bc``: snapshots of
+the repository that skip ``*.pyc`` still carry them).  Nothing is edited and
 no source text is copied: the directory holds compiled code objects only, is git-ignored, and travels to the GPU
 box with the snapshot like the built ``.so`` files.  oracle/ref_loader.py imports it there with the
 third-party stand-ins of oracle/ref_stubs.py.  A manifest records the SHA-256 of every source compiled.
@@ -31,7 +32,7 @@ def build(quiet=False):
     manifest = {"python": sys.version.split()[0], "files": {}}
     for f in FILES:
         src = os.path.join(SRC, f)
-        py_compile.compile(src, cfile=os.path.join(dst, f + "c"), dfile="reference:Barra-master/mfm/" + f, doraise=True)
+        py_compile.compile(src, cfile=os.path.join(dst, f[:-3] + ".bc"), dfile="reference:Barra-master/mfm/" + f, doraise=True)
         manifest["files"][f] = hashlib.sha256(open(src, "rb").read()).hexdigest()
     with open(os.path.join(OUT, "MANIFEST.json"), "w") as fh:
         json.dump(manifest, fh, indent=1)

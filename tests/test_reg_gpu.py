@@ -242,6 +242,65 @@ def test_mfm_dropin_reg_by_time(golden_dir):
     assert list(spec[0].columns) == sorted(spec[0].columns)
 
 
+def test_device_packer_matches_host_packer():
+    """pack_frame_device (row work on the GPU) against pack_frame (host numpy / pandas) on a shuffled ragged panel
+    with rows that have no industry: same storage order, same arrays bit for bit, same name mapping; the checks on the
+    one-hot block raise the same errors; a P that does not fit the table raises ValueError as MFM.py:70 does."""
+    import contextlib
+    import io
+    from bmfm.panel import pack_frame, pack_frame_device
+    from bmfm.synth import make_panel
+    from mfm.MFM import MFM
+    pan = make_panel(T=25, N=90, P=6, Q=4, seed=77, ragged=0.1)
+    df = pan.to_frame(shuffle_seed=9)
+    df.loc[df.index[::13], pan.industry_names] = 0               # rows with no industry column set
+    h = pack_frame(df, pan.P, pan.Q)
+    d = pack_frame_device(df, pan.P, pan.Q)
+    assert (d.T, d.rows, d.max_rows) == (h.T, h.rows, h.max_rows)
+    assert np.array_equal(d.date_off_host, h.date_off) and d.sorted_dates.equals(h.sorted_dates)
+    for name in ("cap", "ret", "ind", "style"):
+        assert np.array_equal(getattr(d, name).cpu().numpy(), getattr(h, name)), name
+    assert np.array_equal(d.name_pos.cpu().numpy(), h.name_pos)
+    assert np.array_equal(d.name_uniques[d.name_code[d.ref_order].cpu().numpy()], h.names_sorted)
+    assert np.array_equal(d.last_capital, h.last_capital)
+    bad = df.copy()
+    bad.iloc[3, 5] = 2
+    with pytest.raises(NotImplementedError, match="0/1"):
+        pack_frame_device(bad, pan.P, pan.Q)
+    bad = df.copy()
+    bad.iloc[3, 4:4 + pan.P] = 1
+    with pytest.raises(NotImplementedError, match="more than one"):
+        pack_frame_device(bad, pan.P, pan.Q)
+    with contextlib.redirect_stdout(io.StringIO()), pytest.raises(ValueError):
+        MFM(df, pan.P - 1, pan.Q).reg_by_time()
+
+
+def test_lazy_specific_return_list(golden_dir):
+    """reg_by_time's list of one-row DataFrames is built on demand: it must behave like the reference's list
+    (len, truth value, indexing incl. negative and slices, iteration, pd.concat as demo.py:78 uses it)."""
+    import contextlib
+    import io
+    import pandas as pd
+    from bmfm.synth import make_panel
+    from mfm.MFM import MFM
+    g = np.load(os.path.join(golden_dir, "pipeline.npz"))
+    pan = make_panel(T=90, N=48, P=4, Q=3, seed=41, ragged=0.05, scale_log10=(-1, 1))
+    with contextlib.redirect_stdout(io.StringIO()):
+        fr, spec, r2 = MFM(pan.to_frame(shuffle_seed=3), pan.P, pan.Q).reg_by_time()
+    assert isinstance(spec, list) and len(spec) == 90 and bool(spec)
+    last = spec[-1]
+    assert isinstance(last, pd.DataFrame) and last.shape[0] == 1 and last.index[0] == fr.index[-1]
+    assert spec[89] is last and spec[-1] is last                    # built once
+    assert [f.shape[1] for f in spec[3:6]] == [int(n) for n in np.diff(g["date_off"])[3:6]]
+    off = g["date_off"]
+    assert relerr(spec[7].values[0], g["specific_ret"][off[7]:off[8]]) < TOL
+    allf = pd.concat(spec)
+    assert allf.shape[0] == 90 and list(allf.index) == list(fr.index)
+    flat = np.concatenate([f.values[0] for f in spec])
+    assert relerr(flat, g["specific_ret"]) < TOL
+    assert sum(1 for _ in reversed(spec)) == 90
+
+
 def test_fused_gather_entry_points_single_gpu(ops):
     """bmfm_reg_by_time_gather / bmfm_vol_regime_bias_gather with this GPU as its own (only) peer: the
     kernels' peer stores must land in the gathered buffers at the rank offset."""
