@@ -87,8 +87,7 @@ REG_KERNEL_NAMES = {1: "reg_fast_kernel<10> (CTA per date, date resident in shar
                     2: "reg_stream_kernel<10> (warp per date, register Gram)",
                     3: "reg_mma_kernel<10,3,1> (FP64-MMA Gram, one warp per date)",
                     5: "reg_mma_kernel<10,2,2> (FP64-MMA Gram, two warps per date)",
-                    4: "reg_mma_kernel<10,2,4> (FP64-MMA Gram, four warps per date)",
-                    6: "reg_bulk_kernel<10> (CTA per date, bulk-copied date resident in shared memory)"}
+                    4: "reg_mma_kernel<10,2,4> (FP64-MMA Gram, four warps per date)"}
 
 
 def load_traffic(mode):

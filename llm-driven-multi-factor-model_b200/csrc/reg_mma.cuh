@@ -215,7 +215,23 @@ __global__ void __launch_bounds__(RM_WARPS * 32, (NSTAGE >= 3 && WPD == 1) ? 3 :
   const int wq = CTA ? warp : 0;                       // this warp takes chunks wq, wq + WPD, ...
   const int t_first = CTA ? (int)blockIdx.x : (int)blockIdx.x * nwarps + warp;
   const int t_step = CTA ? (int)gridDim.x : (int)gridDim.x * nwarps;
-  for (int t = t_first; t < p.T; t += t_step) {
+  // Dates beyond the first one of each warp (CTA) are handed out through a global counter in the order the warps
+  // finish: with T not a multiple of the number of warp slots a static stride would leave some SMs with twice the
+  // second-round work of others.
+  int* s_next = reinterpret_cast<int*>(sbase + SK.flag) + 2;
+  auto next_date = [&](int t) -> int {
+    if (p.next_date == nullptr) return t + t_step;
+    if (CTA) {
+      __syncthreads();
+      if (tid == 0) *s_next = t_step + atomicAdd(p.next_date, 1);
+      __syncthreads();
+      return *s_next;
+    }
+    int v = 0;
+    if (lane == 0) v = t_step + atomicAdd(p.next_date, 1);
+    return __shfl_sync(0xffffffffu, v, 0);
+  };
+  for (int t = t_first; t < p.T; t = next_date(t)) {
     const long long a = p.date_off[t];
     const int n = (int)(p.date_off[t + 1] - a);
     const double nan = __longlong_as_double(0x7ff8000000000000LL);

@@ -35,7 +35,7 @@ r2 = torch.empty(T, dtype=torch.float64, device="cuda")
 st = torch.empty(T, dtype=torch.int32, device="cuda")
 ctx = _cabi.default_context()
 ctx.set_option("reg_mode", MODE)
-for name in ("reg_smma", "reg_warps", "reg_ctas"):
+for name in ("reg_smma", "reg_warps", "reg_ctas", "reg_static"):
     if os.environ.get("BENCH_" + name.upper()):
         ctx.set_option(name, int(os.environ["BENCH_" + name.upper()]))
 GATHER = int(os.environ.get("BENCH_GATHER", "0"))
