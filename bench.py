@@ -432,6 +432,7 @@ def run_gpu(args):
     # are filled by the producing kernels themselves over NVLink (fused all-gather); NCCL is the fallback
     fused = world > 1 and os.environ.get("BENCH_FUSED", "1") == "1"
     nw_shard = os.environ.get("BENCH_NW_SHARD", "1") == "1"
+    vr_shard = os.environ.get("BENCH_VR_SHARD", "1") == "1"
     h_fr = h_wbv = h_tot = None
     if fused:
         try:
@@ -449,6 +450,10 @@ def run_gpu(args):
             tot_sym = symm.empty((world, nw_ns), dtype=torch.float64, device=dev)
             h_tot = symm.rendezvous(tot_sym, group=dist.group.WORLD)
             tot_peers = [int(x) for x in h_tot.buffer_ptrs]
+            # sharded vol-regime: two totals per rank instead of 2 x T gathered terms and a scan over all dates
+            vrt_sym = symm.empty((world, 2), dtype=torch.float64, device=dev)
+            h_vrt = symm.rendezvous(vrt_sym, group=dist.group.WORLD)
+            vrt_peers = [int(x) for x in h_vrt.buffer_ptrs]
         except Exception as e:      # noqa: BLE001
             log(f"symmetric memory unavailable ({e!r}); using NCCL all-gathers")
             fused = False
@@ -523,6 +528,10 @@ def run_gpu(args):
     def vol_regime():
         if world == 1:
             ctx.vol_regime_adj_by_time(T, K, VR_TAO, fr, nw, nw_st, vr, lamb)
+        elif fused and vr_shard:
+            ctx.vol_regime_shard_totals(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wbv[0], wbv[1], rank, vrt_peers)
+            h_vrt.barrier()
+            ctx.vol_regime_shard_scale(T, K, wbv[0], wbv[1], vrt_sym, rank, nw, nw_st, vr, lamb[lo:lo + T])
         elif fused:
             ctx.vol_regime_bias_gather(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wb_peers, wv_peers)
             h_wbv.barrier()
@@ -610,7 +619,15 @@ def run_gpu(args):
     # multi-GPU: the fused (peer-memory) gather must give what the NCCL all-gather gives
     gather_check = None
     if fused:
-        lamb_fused = lamb.clone()
+        lamb_fused = lamb[lo:lo + T].clone()
+        vr_same = True
+        if vr_shard:
+            # the two-totals exchange against the gathered per-date terms + a scan over all dates on every rank
+            ctx.vol_regime_bias_gather(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wb_peers, wv_peers)
+            h_wbv.barrier()
+            lamb_ref = torch.empty(T_all, dtype=torch.float64, device=dev)
+            ctx.vol_regime_scale(T_all, lo, T, K, wb_all, wv_all, nw, nw_st, None, lamb_ref)
+            vr_same = bool(((lamb_fused - lamb_ref[lo:lo + T]).abs().max() <= 1e-13 * lamb_ref.abs().max()).item())
         fr_all_fused = fr_all.clone()
         ref_all = torch.empty((T_all, K), dtype=torch.float64, device=dev)
         dist.all_gather_into_tensor(ref_all, fr)
@@ -622,6 +639,10 @@ def run_gpu(args):
         ok_t = torch.tensor([1 if ok else 0], device=dev)
         dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
         gather_check = "peer-memory gather == NCCL all-gather (bit-identical on every rank)" if ok_t.item() else "MISMATCH"
+        if vr_shard:
+            ok_t = torch.tensor([1 if vr_same else 0], device=dev)
+            dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+            gather_check += "; vol-regime by two exchanged totals == gathered-terms scan (<1e-13 rel)" if ok_t.item() else "; sharded vol-regime MISMATCH"
         del lamb_fused
         if nw_shard:
             # the sharded Newey-West against the pass that reduces the whole gathered series on every rank

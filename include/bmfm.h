@@ -221,6 +221,19 @@ int bmfm_vol_regime_bias_gather(bmfm_ctx* ctx, int T_total, int t0, int n, int K
 int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, int K, const double* wb_all,
                           const double* wv_all, const double* cov_block,
                           const int32_t* cov_status_block, double* out_cov_block, double* lamb_all);
+/* The same adjustment by exchanged block totals: lamb_t^2 (MFM.py:156-160) is a ratio of two prefix sums, so a rank
+ * needs only TWO doubles from every earlier rank.  _shard_totals computes this rank's per-date terms wb / wv [n]
+ * (kept local) and stores their sums into doubles (2 rank, 2 rank + 1) of every buffer in peer_totals (HOST array of
+ * n_peer device pointers to [2 * n_rank] doubles, peer-mapped); after a cross-rank barrier _shard_scale scans this
+ * rank's dates from the sum of the earlier ranks' pairs (`totals`: this rank's own buffer) and scales its block;
+ * lamb_block [n]. */
+int bmfm_vol_regime_shard_totals(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                                 const double* factor_ret_block, const double* cov_block,
+                                 const int32_t* cov_status_block, double* wb, double* wv, int rank, int n_peer,
+                                 double* const* peer_totals);
+int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const double* wb, const double* wv, const double* totals,
+                                int rank, const double* cov_block, const int32_t* cov_status_block,
+                                double* out_cov_block, double* lamb_block);
 
 /*
  * Eigenfactor Monte-Carlo adjustment, utils.eigen_risk_adj (Barra-master/mfm/utils.py:55-92)

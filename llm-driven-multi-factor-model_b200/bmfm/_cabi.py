@@ -50,6 +50,8 @@ _SIGNATURES = {
     "bmfm_newey_west_shard_emit": ([_P, _I, _I, _I, _D, _P, _I, _I, _I, _P, _P, _P, _P], _I),
     "bmfm_vol_regime_bias": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_vol_regime_scale": ([_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P], _I),
+    "bmfm_vol_regime_shard_totals": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _P, _P, _I, _I, _P], _I),
+    "bmfm_vol_regime_shard_scale": ([_P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P], _I),
     "bmfm_newey_west_by_time_noalloc": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_vol_regime_adj_by_time": ([_P, _I, _I, _D, _P, _P, _P, _P, _P], _I),
     "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
@@ -250,6 +252,16 @@ class Context:
     def vol_regime_scale(self, T_total, t0, n, K, wb_all, wv_all, cov_block, status_block, out_block, lamb_all):
         self.check(self._L.bmfm_vol_regime_scale(self._h, T_total, t0, n, K, ptr(wb_all), ptr(wv_all),
                                                  ptr(cov_block), ptr(status_block), ptr(out_block), ptr(lamb_all)))
+
+    def vol_regime_shard_totals(self, T_total, t0, n, K, tao, fr_block, cov_block, status_block, wb, wv, rank, peer_totals):
+        arr = (C.c_void_p * len(peer_totals))(*[int(x) for x in peer_totals])
+        self.check(self._L.bmfm_vol_regime_shard_totals(self._h, T_total, t0, n, K, float(tao), ptr(fr_block),
+                                                        ptr(cov_block), ptr(status_block), ptr(wb), ptr(wv), rank,
+                                                        len(peer_totals), arr))
+
+    def vol_regime_shard_scale(self, n, K, wb, wv, totals, rank, cov_block, status_block, out_block, lamb_block):
+        self.check(self._L.bmfm_vol_regime_shard_scale(self._h, n, K, ptr(wb), ptr(wv), ptr(totals), rank, ptr(cov_block),
+                                                       ptr(status_block), ptr(out_block), ptr(lamb_block)))
 
     def newey_west_by_time_noalloc(self, T, K, q, tao, fr, cov, status):
         """Newey-West with the library's built-in fixed scratch: for callers that may not allocate

@@ -73,6 +73,10 @@ class SymmetricGather:
             self.tot_peers = [int(x) for x in self.h_tot.buffer_ptrs]
         self.fr_all = symm.empty((T_total, K), dtype=torch.float64, device=device)
         self.h_fr = symm.rendezvous(self.fr_all, group=g)
+        # sharded vol-regime: two totals per rank (bmfm_vol_regime_shard_totals / _scale)
+        self.vr_totals = symm.empty((self.world, 2), dtype=torch.float64, device=device)
+        self.h_vrt = symm.rendezvous(self.vr_totals, group=g)
+        self.vrt_peers = [int(x) for x in self.h_vrt.buffer_ptrs]
         self.wbv = symm.empty((2, T_total), dtype=torch.float64, device=device)
         self.h_wbv = symm.rendezvous(self.wbv, group=g)
         self.fr_peers = [int(x) for x in self.h_fr.buffer_ptrs]
@@ -210,9 +214,15 @@ class RiskPipeline:
         cov, cov_st = nw, nw_st
         if eigen is not None:
             cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])
-        ctx.vol_regime_bias_gather(T_total, t0, n, K, tao_vr, fr, cov, cov_st, sg.wb_peers, sg.wv_peers)
-        sg.h_wbv.barrier()
-        vr, lamb_all = self.b.vr_scale(T_total, t0, sg.wbv[0], sg.wbv[1], cov, cov_st)
+        # lamb is a ratio of two prefix sums: every rank keeps its per-date terms and only the two block totals cross
+        # NVLink; lamb_all holds this rank's dates (NaN elsewhere)
+        wb = torch.empty(n, dtype=torch.float64, device=dev)
+        wv = torch.empty(n, dtype=torch.float64, device=dev)
+        ctx.vol_regime_shard_totals(T_total, t0, n, K, tao_vr, fr, cov, cov_st, wb, wv, self.rank, sg.vrt_peers)
+        sg.h_vrt.barrier()
+        vr = torch.empty_like(cov)
+        lamb_all = torch.full((T_total,), float("nan"), dtype=torch.float64, device=dev)
+        ctx.vol_regime_shard_scale(n, K, wb, wv, sg.vr_totals, self.rank, cov, cov_st, vr, lamb_all[t0:t0 + n])
         return {"factor_ret": fr, "factor_ret_all": sg.fr_all, "specific_ret": spec, "R2": r2, "status": status,
                 "nw": nw, "nw_status": nw_st, "cov": cov, "cov_status": cov_st, "vr": vr,
                 "lamb_all": lamb_all, "t0": t0, "n": n}

@@ -127,6 +127,76 @@ __global__ void __launch_bounds__(256) vr_scale_kernel(int T, int KK, const doub
   }
 }
 
+// ---- date-sharded form without the replicated scan ------------------------------------------------
+// lamb_t^2 is a ratio of two prefix sums over the dates up to t, so a rank needs from every EARLIER rank only the
+// two totals of its block.  vr_block_totals_kernel reduces this rank's terms and stores the pair into slot `rank` of
+// every rank's record buffer (peer memory); vr_scan_carry_kernel then scans the rank's own dates starting from the
+// sum of the earlier ranks' pairs.
+struct VrTotPeers {
+  int n;
+  double* tot[8];
+};
+
+__global__ void __launch_bounds__(1024) vr_block_totals_kernel(int n, const double* wb, const double* wv, int rank,
+                                                               VrTotPeers peers) {
+  __shared__ double s_b[32], s_v[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double pb = 0.0, pv = 0.0;
+  for (int t = tid; t < n; t += blockDim.x) { pb += wb[t]; pv += wv[t]; }
+  pb = warp_sum(pb);
+  pv = warp_sum(pv);
+  if (lane == 0) { s_b[warp] = pb; s_v[warp] = pv; }
+  __syncthreads();
+  if (warp == 0) {
+    pb = lane < (blockDim.x >> 5) ? s_b[lane] : 0.0;
+    pv = lane < (blockDim.x >> 5) ? s_v[lane] : 0.0;
+    pb = warp_sum(pb);
+    pv = warp_sum(pv);
+    if (lane < peers.n) {
+      peers.tot[lane][2 * rank] = pb;
+      peers.tot[lane][2 * rank + 1] = pv;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024) vr_scan_carry_kernel(int n, const double* wb, const double* wv,
+                                                             const double* totals, int rank, double* lamb) {
+  __shared__ double s_b[32], s_v[32];
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  double cb = 0.0, cv = 0.0;
+  for (int r = 0; r < rank; ++r) { cb += totals[2 * r]; cv += totals[2 * r + 1]; }
+  const int per = (n + nt - 1) / nt;
+  const int lo = min(n, tid * per), hi = min(n, lo + per);
+  double pb = 0.0, pv = 0.0;
+  for (int t = lo; t < hi; ++t) { pb += wb[t]; pv += wv[t]; }
+  double ib = pb, iv = pv;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const double ab = __shfl_up_sync(0xffffffffu, ib, off), av = __shfl_up_sync(0xffffffffu, iv, off);
+    if (lane >= off) { ib += ab; iv += av; }
+  }
+  if (lane == 31) { s_b[warp] = ib; s_v[warp] = iv; }
+  __syncthreads();
+  if (warp == 0) {
+    double wbt = lane < (nt >> 5) ? s_b[lane] : 0.0, wvt = lane < (nt >> 5) ? s_v[lane] : 0.0;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const double ab = __shfl_up_sync(0xffffffffu, wbt, off), av = __shfl_up_sync(0xffffffffu, wvt, off);
+      if (lane >= off) { wbt += ab; wvt += av; }
+    }
+    s_b[lane] = wbt;
+    s_v[lane] = wvt;
+  }
+  __syncthreads();
+  double rb = cb + (warp > 0 ? s_b[warp - 1] : 0.0) + (ib - pb);
+  double rv = cv + (warp > 0 ? s_v[warp - 1] : 0.0) + (iv - pv);
+  for (int t = lo; t < hi; ++t) {
+    rb += wb[t];
+    rv += wv[t];
+    lamb[t] = rv > 0.0 ? sqrt(rb / rv) : 0.0;
+  }
+}
+
 }  // namespace bmfm
 
 using namespace bmfm;
@@ -214,6 +284,56 @@ extern "C" int bmfm_vol_regime_scale(bmfm_ctx* ctx, int T_total, int t0, int n, 
   ctx->launches++;
   if (out_cov_block && n > 0) {
     vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_all + t0, out_cov_block);
+    ctx->launches++;
+  }
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// Date-sharded vol-regime by exchanged block totals (two doubles per rank) instead of gathered per-date terms:
+//   1. bmfm_vol_regime_shard_totals: the terms wb / wv [n] of this rank's block (kept local) and their two sums,
+//      stored into doubles (2 rank, 2 rank + 1) of every buffer in peer_totals (HOST array of n_peer device pointers
+//      to [2 * n_rank] doubles, peer-mapped);
+//   2. the caller runs a cross-rank barrier;
+//   3. bmfm_vol_regime_shard_scale: lamb of this rank's dates from its own terms and the totals of the ranks before
+//      it (`totals`: this rank's own record buffer), then its block scaled.  lamb_block [n].
+extern "C" int bmfm_vol_regime_shard_totals(bmfm_ctx* ctx, int T_total, int t0, int n, int K, double tao,
+                                            const double* factor_ret_block, const double* cov_block,
+                                            const int32_t* cov_status_block, double* wb, double* wv, int rank,
+                                            int n_peer, double* const* peer_totals) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T_total >= 0 && t0 >= 0 && n >= 0 && t0 + n <= T_total && K > 0 && tao > 0 && rank >= 0, "bad sizes");
+  BMFM_ARG(ctx, n_peer >= 1 && n_peer <= 8 && peer_totals, "bad peer list");
+  BMFM_ARG(ctx, n == 0 || (factor_ret_block && cov_block && wb && wv), "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  VrPeers nopeers;
+  nopeers.n = 0;
+  if (n > 0) {
+    vr_bias_kernel<<<(n * 32 + 255) / 256, 256, 0, ctx->stream>>>(n, K, tao, factor_ret_block, cov_block,
+                                                                cov_status_block, wb, wv, t0, T_total, nopeers);
+    ctx->launches++;
+  }
+  VrTotPeers tp;
+  tp.n = n_peer;
+  for (int r = 0; r < 8; ++r) tp.tot[r] = r < n_peer ? peer_totals[r] : nullptr;
+  vr_block_totals_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, rank, tp);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const double* wb, const double* wv,
+                                           const double* totals, int rank, const double* cov_block,
+                                           const int32_t* cov_status_block, double* out_cov_block, double* lamb_block) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, n >= 0 && K > 0 && rank >= 0, "bad sizes");
+  if (n == 0) return BMFM_OK;
+  BMFM_ARG(ctx, wb && wv && totals && lamb_block, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  vr_scan_carry_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, totals, rank, lamb_block);
+  ctx->launches++;
+  if (out_cov_block) {
+    vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_block, out_cov_block);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());

@@ -380,3 +380,38 @@ def test_backend_record_exchange_path(ops):
         assert np.array_equal(st.cpu().numpy(), st_full[lo:hi])
         ok = st_full[lo:hi] == 0
         assert np.max(np.abs(cov.cpu().numpy()[ok] - cov_full[lo:hi][ok])) < 1e-12 * scale
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,K,world", [(500, 17, 3), (2000, 42, 8), (90, 6, 4)])
+def test_sharded_vol_regime_exchanges_two_totals(ops, T, K, world):
+    """bmfm_vol_regime_shard_totals / _scale: every 'rank' scans only its own dates, the carry-in is the sum of the
+    earlier ranks' (sum wb, sum wv) pairs.  Emulated on one GPU with a single shared record buffer; must agree with
+    the un-sharded pass (a different association of the prefix sums: rounding only)."""
+    import torch
+    from bmfm import _cabi, dist as bd
+    from bmfm.synth import make_factor_returns
+    ctx = _cabi.default_context()
+    fr = make_factor_returns(T, K, seed=T)
+    cov, st = ops.newey_west_by_time(fr, 2, 60.0)
+    want, lamb_want = ops.vol_regime_adj_by_time(fr, np.nan_to_num(cov), st, 21.0)
+    dv = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_fr, d_cov, d_st = dv(fr), dv(np.nan_to_num(cov)), dv(st.astype(np.int32))
+    totals = torch.full((world, 2), float("nan"), dtype=torch.float64, device="cuda")
+    ranges = [bd.shard_range(T, r, world) for r in range(world)]
+    terms = []
+    for r, (lo, hi) in enumerate(ranges):
+        wb = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+        wv = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+        ctx.vol_regime_shard_totals(T, lo, hi - lo, K, 21.0, d_fr[lo:hi].contiguous(), d_cov[lo:hi].contiguous(),
+                                    d_st[lo:hi].contiguous(), wb, wv, r, [totals.data_ptr()])
+        terms.append((wb, wv))
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(totals).all())
+    for r, (lo, hi) in enumerate(ranges):
+        out = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
+        lamb = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+        ctx.vol_regime_shard_scale(hi - lo, K, terms[r][0], terms[r][1], totals, r, d_cov[lo:hi].contiguous(),
+                                   d_st[lo:hi].contiguous(), out, lamb)
+        assert relerr(lamb.cpu().numpy(), lamb_want[lo:hi]) < 1e-13
+        assert relerr(out.cpu().numpy(), want[lo:hi]) < 1e-13
