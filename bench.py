@@ -433,6 +433,9 @@ def run_gpu(args):
     fused = world > 1 and os.environ.get("BENCH_FUSED", "1") == "1"
     nw_shard = os.environ.get("BENCH_NW_SHARD", "1") == "1"
     vr_shard = os.environ.get("BENCH_VR_SHARD", "1") == "1"
+    # per-producer flags instead of the two later barriers: measured slower than the barriers on 8 GPUs (0.253 against
+    # 0.244 ms per step), so off by default; BENCH_FLAGS=1 selects them
+    use_flags = os.environ.get("BENCH_FLAGS", "0") == "1" and nw_shard and vr_shard
     h_fr = h_wbv = h_tot = None
     if fused:
         try:
@@ -454,6 +457,14 @@ def run_gpu(args):
             vrt_sym = symm.empty((world, 2), dtype=torch.float64, device=dev)
             h_vrt = symm.rendezvous(vrt_sym, group=dist.group.WORLD)
             vrt_peers = [int(x) for x in h_vrt.buffer_ptrs]
+            # per-producer flags: a rank waits only for the ranks before it, inside the consuming kernels
+            if use_flags:
+                flg_sym = symm.empty((64,), dtype=torch.int64, device=dev)
+                flg_sym.zero_()
+                h_flg = symm.rendezvous(flg_sym, group=dist.group.WORLD)
+                torch.cuda.synchronize()
+                dist.barrier()
+                ctx.set_peer_flags(rank, [int(x) for x in h_flg.buffer_ptrs])
         except Exception as e:      # noqa: BLE001
             log(f"symmetric memory unavailable ({e!r}); using NCCL all-gathers")
             fused = False
@@ -512,7 +523,8 @@ def run_gpu(args):
         if fused and nw_shard:
             # every rank reduces its own dates only; the ranks exchange one 44 KB state record each
             ctx.newey_west_shard_totals(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, rank, tot_peers)
-            h_tot.barrier()
+            if not use_flags:
+                h_tot.barrier()
             ctx.newey_west_shard_emit(T_all, K, NW_Q, NW_TAO, fr_all, lo, lo + T, rank,
                                       [(r + 1) * T for r in range(rank)], tot_sym, nw, nw_st)
         else:
@@ -530,7 +542,8 @@ def run_gpu(args):
             ctx.vol_regime_adj_by_time(T, K, VR_TAO, fr, nw, nw_st, vr, lamb)
         elif fused and vr_shard:
             ctx.vol_regime_shard_totals(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wbv[0], wbv[1], rank, vrt_peers)
-            h_vrt.barrier()
+            if not use_flags:
+                h_vrt.barrier()
             ctx.vol_regime_shard_scale(T, K, wbv[0], wbv[1], vrt_sym, rank, nw, nw_st, vr, lamb[lo:lo + T])
         elif fused:
             ctx.vol_regime_bias_gather(T_all, lo, T, K, VR_TAO, fr, nw, nw_st, wb_peers, wv_peers)
@@ -877,9 +890,12 @@ def run_gpu(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(),
-                       "parallelism": (f"dates sharded over {world} GPU(s); factor returns and vol-regime terms gathered "
-                                       + ("by the producing kernels over peer memory (symmetric memory + device barrier)" if fused
-                                          else "with NCCL all-gather")) if world > 1 else "1 GPU",
+                       "parallelism": (f"dates sharded over {world} GPU(s); "
+                                       + ("factor returns stored into every rank's series by the regression kernel over peer memory "
+                                          "(one device barrier per step); Newey-West state records and vol-regime block totals "
+                                          "published to the later ranks through per-producer flags" if fused and use_flags
+                                          else "factor returns and exchange records stored over peer memory, device barriers" if fused
+                                          else "NCCL all-gathers")) if world > 1 else "1 GPU",
                        "timed_as": "CUDA graph replays of one captured step (phase_ms from 3 extra eager steps after the warm-up)" if graph is not None else "eager launches",
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},

@@ -68,6 +68,13 @@ long long bmfm_launch_count(const bmfm_ctx* ctx);
  * bmfm_ctx_get_option also reads "last_reg_mode": the kernel form the last regression call launched. */
 int bmfm_ctx_set_option(bmfm_ctx* ctx, const char* name, int value);
 int bmfm_ctx_get_option(bmfm_ctx* ctx, const char* name, int* value);
+/* Per-producer flags for the date-sharded exchanges (multi-GPU; no counterpart in the reference).  flag_bufs: HOST
+ * array of n_rank device pointers, one ZEROED block of 64 int64 per rank in peer-mapped memory (flag_bufs[rank] = this
+ * rank's own).  Once registered, bmfm_newey_west_shard_totals / _emit and bmfm_vol_regime_shard_totals / _scale
+ * publish their records' epochs to the later ranks and wait only for the earlier ranks, inside the kernels; the
+ * caller drops its cross-rank barriers between those calls and keeps ONE all-rank barrier per step (so that no rank
+ * gets a whole step ahead).  n_rank = 0 unregisters. */
+int bmfm_ctx_set_peer_flags(bmfm_ctx* ctx, int rank, int n_rank, int64_t* const* flag_bufs);
 /* compiled limits: max styles Q, max industries P, max factors K */
 void bmfm_limits(int* max_Q, int* max_P, int* max_K);
 const char* bmfm_version(void);

@@ -33,6 +33,7 @@ _SIGNATURES = {
     "bmfm_launch_count": ([_P], C.c_longlong),
     "bmfm_ctx_set_option": ([_P, C.c_char_p, _I], _I),
     "bmfm_ctx_get_option": ([_P, C.c_char_p, C.POINTER(_I)], _I),
+    "bmfm_ctx_set_peer_flags": ([_P, _I, _I, _P], _I),
     "bmfm_limits": ([C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)], None),
     "bmfm_version": ([], C.c_char_p),
     "bmfm_reg_by_time": ([_P, _I, _I, _I, _I] + [_P] * 10, _I),
@@ -151,6 +152,13 @@ class Context:
 
     def sync(self):
         self.check(self._L.bmfm_ctx_sync(self._h))
+
+    def set_peer_flags(self, rank, flag_ptrs):
+        """Register the ranks' flag blocks (device addresses, 64 zeroed int64 each, peer-mapped): the sharded
+        Newey-West / vol-regime calls then synchronise through them instead of caller-side barriers."""
+        n = len(flag_ptrs)
+        arr = (C.c_void_p * max(1, n))(*[int(x) for x in flag_ptrs])
+        self.check(self._L.bmfm_ctx_set_peer_flags(self._h, int(rank), n, arr))
 
     def set_option(self, name, value):
         """Experiment switch of this context (include/bmfm.h: bmfm_ctx_set_option)."""

@@ -23,6 +23,9 @@ struct bmfm_ctx {
   cudaStream_t copy_in, copy_out;
   cudaEvent_t pipe_ev[40];
   bool pipe_ready;
+  // per-producer flags of the date-sharded exchanges (bmfm_ctx_set_peer_flags); n_flag_peers = 0: not registered
+  int flag_rank, n_flag_peers;
+  long long* peer_flags[8];
   // per-context experiment switches (bmfm_ctx_set_option); 0 / negative = library default
   int opt_reg_mode, opt_reg_smma, opt_reg_warps, opt_reg_ctas, opt_nw_chunks, opt_eig_mode, opt_eig_fail_every, opt_eig_c_blocks, opt_reg_static;
   int last_reg_mode;   // kernel form the last bmfm_reg_by_time call launched (bmfm_ctx_get_option "last_reg_mode")
@@ -46,6 +49,57 @@ struct bmfm_ctx {
       return BMFM_E_ARG;                                                            \
     }                                                                               \
   } while (0)
+
+// ---- per-producer flags of the date-sharded exchanges -------------------------------------------------------
+// Every rank owns a block of BMFM_FLAG_WORDS 64-bit words in peer-mapped memory:
+//   [ch * 8 + s]   epoch of the newest record that rank s has published on channel ch (written by rank s)
+//   [32 + ch]      this rank's own epoch on channel ch            (local)
+//   [40 + ch]      CTAs of this rank's producer kernel that have finished, all steps   (local)
+//   [48]           set when a wait gave up                        (local)
+// A producer bumps its epoch and writes it into the flag word of every LATER rank after its record stores; a
+// consumer waits until the words of all EARLIER ranks have reached its own epoch.  Nobody waits for a later rank.
+constexpr int BMFM_FLAG_WORDS = 64;
+constexpr int BMFM_CH_NW = 0, BMFM_CH_VR = 1;
+struct BmfmFlagPeers {
+  int rank, n;
+  long long* f[8];     // f[rank] is this rank's own block
+};
+
+__device__ __forceinline__ void bmfm_flag_publish(const BmfmFlagPeers& fp, int ch, long long epoch) {
+  __threadfence_system();
+  for (int r = fp.rank + 1; r < fp.n; ++r) {
+    volatile long long* w = fp.f[r] + ch * 8 + fp.rank;
+    *w = epoch;
+  }
+  __threadfence_system();
+}
+
+// one thread: wait for the records of all earlier ranks (bounded: a lost producer must not hang the GPU)
+__device__ __forceinline__ void bmfm_flag_wait(const BmfmFlagPeers& fp, int ch) {
+  volatile long long* mine = fp.f[fp.rank];
+  const long long want = mine[32 + ch];
+  for (int s = 0; s < fp.rank; ++s) {
+    long long spins = 0;
+    while (mine[ch * 8 + s] < want) {
+      if (++spins > (1LL << 26)) { mine[48] = 1; break; }
+      __nanosleep(64);
+    }
+  }
+  __threadfence_system();
+}
+
+// the registered flag blocks as a kernel argument (n = 0 when none are registered or the rank does not match)
+inline BmfmFlagPeers bmfm_flag_peers(const bmfm_ctx* ctx, int rank, int n_peer_expected) {
+  BmfmFlagPeers fp;
+  fp.rank = rank;
+  fp.n = 0;
+  for (int r = 0; r < 8; ++r) fp.f[r] = nullptr;
+  if (ctx->n_flag_peers > 1 && ctx->flag_rank == rank && (n_peer_expected == 0 || n_peer_expected == ctx->n_flag_peers)) {
+    fp.n = ctx->n_flag_peers;
+    for (int r = 0; r < fp.n; ++r) fp.f[r] = ctx->peer_flags[r];
+  }
+  return fp;
+}
 
 // host helpers (ctx.cu)
 int bmfm_ws_reserve(bmfm_ctx* ctx, size_t bytes);             // ctx->ws >= bytes

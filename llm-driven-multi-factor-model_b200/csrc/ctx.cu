@@ -45,6 +45,20 @@ extern "C" int bmfm_ctx_set_option(bmfm_ctx* c, const char* name, int value) {
   return BMFM_OK;
 }
 
+// Per-producer flags for the date-sharded Newey-West / vol-regime exchanges: flag_bufs = HOST array of n_rank device
+// pointers, one zero-initialised block of 64 int64 per rank in peer-mapped memory (flag_bufs[rank] = this rank's own).
+// Once registered, bmfm_newey_west_shard_totals / _emit and bmfm_vol_regime_shard_totals / _scale publish and wait
+// through these flags and the caller drops its cross-rank barriers between them (it keeps ONE all-rank barrier per
+// step, e.g. the one after the regression, so that no rank runs a whole step ahead).  n_rank = 0 unregisters.
+extern "C" int bmfm_ctx_set_peer_flags(bmfm_ctx* c, int rank, int n_rank, int64_t* const* flag_bufs) {
+  if (!c) return BMFM_E_ARG;
+  BMFM_ARG(c, n_rank >= 0 && n_rank <= 8 && (n_rank == 0 || (flag_bufs && rank >= 0 && rank < n_rank)), "bad peer flags");
+  c->flag_rank = rank;
+  c->n_flag_peers = n_rank;
+  for (int r = 0; r < 8; ++r) c->peer_flags[r] = r < n_rank ? (long long*)flag_bufs[r] : nullptr;
+  return BMFM_OK;
+}
+
 extern "C" int bmfm_ctx_get_option(bmfm_ctx* c, const char* name, int* value) {
   if (!c || !name || !value) return BMFM_E_ARG;
   int* slot = bmfm_opt_slot(c, name);

@@ -44,6 +44,7 @@ struct NwParams {
   const double* carry;
   int n_peer, rank;
   double* peer_totals[8];
+  BmfmFlagPeers flags;   // per-producer flags (n = 0: the caller runs a barrier instead)
   double lam;
   const double* fr;   // [T][K]
   double* cov;        // [T][K][K]
@@ -181,17 +182,36 @@ __global__ void __launch_bounds__(32 * NW_SCAN_GROUPS) nw_chunk_scan(NwParams p)
   const int g_last = p.c_used > 0 ? (p.c_used - 1) / per : 0;
   if (p.n_peer > 0 && act && g == g_last)
     for (int r = 0; r < p.n_peer; ++r) p.peer_totals[r][(size_t)p.rank * ns + e] = run;
+  if (p.n_peer > 0 && p.flags.n > 0) {
+    // the CTA that finishes last publishes the record's epoch to the later ranks
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      long long* mine = p.flags.f[p.flags.rank];
+      const unsigned long long done = atomicAdd(reinterpret_cast<unsigned long long*>(mine + 40 + BMFM_CH_NW), 1ULL) + 1ULL;
+      if (done % gridDim.x == 0) {
+        __threadfence_system();
+        const long long ep = (long long)(done / gridDim.x);
+        *reinterpret_cast<volatile long long*>(mine + 32 + BMFM_CH_NW) = ep;
+        bmfm_flag_publish(p.flags, BMFM_CH_NW, ep);
+      }
+    }
+  }
 }
 
 // carry-in of a date-sharded rank: decayed sum of the earlier ranks' zero-start totals,
 //   carry = sum_{r' < rank} lam^(t0 - end_{r'}) total_{r'}      (end_{r'} = one past rank r' 's last row)
 struct NwEnds { long long v[8]; };
 __global__ void nw_carry_kernel(int ns, int rank, double lam, const double* totals, NwEnds ends, long long t0,
-                                double* carry) {
+                                double* carry, BmfmFlagPeers fp) {
+  if (fp.n > 0) {
+    if (threadIdx.x == 0) bmfm_flag_wait(fp, BMFM_CH_NW);
+    __syncthreads();
+  }
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= ns) return;
   double s = 0.0;
-  for (int r = 0; r < rank; ++r) s = fma(pow(lam, (double)(t0 - ends.v[r])), totals[(size_t)r * ns + e], s);
+  for (int r = 0; r < rank; ++r) s = fma(pow(lam, (double)(t0 - ends.v[r])), __ldcg(totals + (size_t)r * ns + e), s);
   carry[e] = s;
 }
 
@@ -461,7 +481,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
-  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0;
+  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;
   if (t0 < 0) t0 = 0;
   if (t1 > T) t1 = T;
   p.t0 = t0; p.t1 = t1;
@@ -583,7 +603,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = factor_ret; p.cov = cov; p.status = status;
   p.t0 = 0; p.t1 = T;
-  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0;
+  p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;
   p.state = nw_static_ptr[ctx->device];
   return nw_run(ctx, p);
 }
@@ -617,7 +637,7 @@ static int nw_shard_params(bmfm_ctx* ctx, NwParams& p, int T_total, int K, int q
   p.lam = pow(0.5, 1.0 / tao);
   p.fr = fr_all; p.cov = nullptr; p.status = nullptr;
   p.row0 = t0; p.t0 = t0; p.t1 = t1;
-  p.carry = nullptr; p.n_peer = 0; p.rank = 0;
+  p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;
   const size_t ns = (size_t)nw_nstate(K, q);
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   const int rc = bmfm_ws_reserve(ctx, ((size_t)(p.nchunks > 0 ? p.nchunks : 1) * ns + ns) * sizeof(double));
@@ -642,6 +662,7 @@ extern "C" int bmfm_newey_west_shard_totals(bmfm_ctx* ctx, int T_total, int K, i
   if (rc) return rc;
   p.n_peer = n_peer; p.rank = rank;
   for (int r = 0; r < 8; ++r) p.peer_totals[r] = r < n_peer ? peer_totals[r] : nullptr;
+  p.flags = bmfm_flag_peers(ctx, rank, n_peer);
   return nw_run_totals(ctx, p);
 }
 
@@ -663,7 +684,8 @@ extern "C" int bmfm_newey_west_shard_emit(bmfm_ctx* ctx, int T_total, int K, int
     NwEnds ends;
     for (int r = 0; r < 8; ++r) ends.v[r] = r < rank ? (long long)range_ends[r] : 0;
     const int ns = nw_nstate(K, q);
-    nw_carry_kernel<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(ns, rank, p.lam, totals, ends, (long long)t0, carry);
+    nw_carry_kernel<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(ns, rank, p.lam, totals, ends, (long long)t0, carry,
+                                                               bmfm_flag_peers(ctx, rank, 0));
     ctx->launches++;
     p.carry = carry;
   }

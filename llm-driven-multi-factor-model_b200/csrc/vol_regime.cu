@@ -138,7 +138,7 @@ struct VrTotPeers {
 };
 
 __global__ void __launch_bounds__(1024) vr_block_totals_kernel(int n, const double* wb, const double* wv, int rank,
-                                                               VrTotPeers peers) {
+                                                               VrTotPeers peers, BmfmFlagPeers fp) {
   __shared__ double s_b[32], s_v[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double pb = 0.0, pv = 0.0;
@@ -156,15 +156,29 @@ __global__ void __launch_bounds__(1024) vr_block_totals_kernel(int n, const doub
       peers.tot[lane][2 * rank] = pb;
       peers.tot[lane][2 * rank + 1] = pv;
     }
+    if (fp.n > 0) {
+      __syncwarp();
+      if (lane == 0) {
+        volatile long long* mine = fp.f[fp.rank];
+        const long long e = mine[32 + BMFM_CH_VR] + 1;
+        mine[32 + BMFM_CH_VR] = e;
+        bmfm_flag_publish(fp, BMFM_CH_VR, e);
+      }
+    }
   }
 }
 
 __global__ void __launch_bounds__(1024) vr_scan_carry_kernel(int n, const double* wb, const double* wv,
-                                                             const double* totals, int rank, double* lamb) {
+                                                             const double* totals, int rank, double* lamb,
+                                                             BmfmFlagPeers fp) {
   __shared__ double s_b[32], s_v[32];
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  if (fp.n > 0) {
+    if (tid == 0) bmfm_flag_wait(fp, BMFM_CH_VR);
+    __syncthreads();
+  }
   double cb = 0.0, cv = 0.0;
-  for (int r = 0; r < rank; ++r) { cb += totals[2 * r]; cv += totals[2 * r + 1]; }
+  for (int r = 0; r < rank; ++r) { cb += __ldcg(totals + 2 * r); cv += __ldcg(totals + 2 * r + 1); }
   const int per = (n + nt - 1) / nt;
   const int lo = min(n, tid * per), hi = min(n, lo + per);
   double pb = 0.0, pv = 0.0;
@@ -316,7 +330,7 @@ extern "C" int bmfm_vol_regime_shard_totals(bmfm_ctx* ctx, int T_total, int t0, 
   VrTotPeers tp;
   tp.n = n_peer;
   for (int r = 0; r < 8; ++r) tp.tot[r] = r < n_peer ? peer_totals[r] : nullptr;
-  vr_block_totals_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, rank, tp);
+  vr_block_totals_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, rank, tp, bmfm_flag_peers(ctx, rank, n_peer));
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
@@ -330,7 +344,7 @@ extern "C" int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const do
   if (n == 0) return BMFM_OK;
   BMFM_ARG(ctx, wb && wv && totals && lamb_block, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  vr_scan_carry_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, totals, rank, lamb_block);
+  vr_scan_carry_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, totals, rank, lamb_block, bmfm_flag_peers(ctx, rank, 0));
   ctx->launches++;
   if (out_cov_block) {
     vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_block, out_cov_block);
