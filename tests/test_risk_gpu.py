@@ -415,3 +415,62 @@ def test_sharded_vol_regime_exchanges_two_totals(ops, T, K, world):
                                    d_st[lo:hi].contiguous(), out, lamb)
         assert relerr(lamb.cpu().numpy(), lamb_want[lo:hi]) < 1e-13
         assert relerr(out.cpu().numpy(), want[lo:hi]) < 1e-13
+
+
+@pytest.mark.gpu
+def test_sharded_exchanges_through_per_producer_flags(ops):
+    """bmfm_ctx_set_peer_flags: with the ranks' flag blocks registered, the sharded Newey-West and vol-regime calls
+    publish their records' epochs to the later ranks and wait for the earlier ones inside the kernels (no caller-side
+    barrier).  Three emulated ranks with a context and a flag block each on one GPU, two steps in a row (epochs 1
+    and 2); results must equal the barrier form's."""
+    import torch
+    from bmfm import _cabi, dist as bd
+    from bmfm.synth import make_factor_returns
+    T, K, q, tao, world = 420, 11, 2, 50.0, 3
+    fr = make_factor_returns(T, K, seed=19)
+    cov_full, st_full = ops.newey_west_by_time(fr, q, tao)
+    vr_full, lamb_full = ops.vol_regime_adj_by_time(fr, np.nan_to_num(cov_full), st_full, 21.0)
+    d_fr = torch.from_numpy(fr).cuda()
+    ctxs = [_cabi.Context(0) for _ in range(world)]
+    flags = [torch.zeros(64, dtype=torch.int64, device="cuda") for _ in range(world)]
+    for r in range(world):
+        ctxs[r].set_peer_flags(r, [f.data_ptr() for f in flags])
+    ns = ctxs[0].newey_west_state_doubles(K, q)
+    nw_tot = torch.zeros((world, ns), dtype=torch.float64, device="cuda")
+    vr_tot = torch.zeros((world, 2), dtype=torch.float64, device="cuda")
+    ranges = [bd.shard_range(T, r, world) for r in range(world)]
+    ends = [hi for (_, hi) in ranges]
+    scale = np.nanmax(np.abs(cov_full))
+    for step in (1, 2):
+        covs = []
+        for r, (lo, hi) in enumerate(ranges):          # producers first: on ONE GPU a consumer must not spin before them
+            ctxs[r].newey_west_shard_totals(T, K, q, tao, d_fr, lo, hi, r, [nw_tot.data_ptr()])
+        for r, (lo, hi) in enumerate(ranges):
+            cov = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
+            st = torch.empty(hi - lo, dtype=torch.int32, device="cuda")
+            ctxs[r].newey_west_shard_emit(T, K, q, tao, d_fr, lo, hi, r, ends[:r], nw_tot, cov, st)
+            covs.append((cov, st))
+        terms = []
+        for r, (lo, hi) in enumerate(ranges):
+            wb = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+            wv = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+            ctxs[r].vol_regime_shard_totals(T, lo, hi - lo, K, 21.0, d_fr[lo:hi].contiguous(), torch.nan_to_num(covs[r][0]),
+                                            covs[r][1], wb, wv, r, [vr_tot.data_ptr()])
+            terms.append((wb, wv))
+        for r, (lo, hi) in enumerate(ranges):
+            out = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
+            lamb = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
+            ctxs[r].vol_regime_shard_scale(hi - lo, K, terms[r][0], terms[r][1], vr_tot, r, torch.nan_to_num(covs[r][0]),
+                                           covs[r][1], out, lamb)
+            torch.cuda.synchronize()
+            ok = st_full[lo:hi] == 0
+            assert np.array_equal(covs[r][1].cpu().numpy(), st_full[lo:hi])
+            assert np.max(np.abs(covs[r][0].cpu().numpy()[ok] - cov_full[lo:hi][ok])) < 1e-12 * scale
+            assert relerr(lamb.cpu().numpy(), lamb_full[lo:hi]) < 1e-13
+        for r in range(world):
+            f = flags[r].cpu().numpy()
+            assert f[48] == 0                                           # no wait gave up
+            assert f[32] == step and f[33] == step                      # own epochs on both channels
+            assert all(f[s] == step for s in range(r)) and all(f[8 + s] == step for s in range(r))
+    for c in ctxs:
+        c.close()
