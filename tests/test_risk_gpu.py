@@ -444,7 +444,7 @@ def test_sharded_exchanges_through_per_producer_flags(ops):
     for step in (1, 2):
         covs = []
         for r, (lo, hi) in enumerate(ranges):          # producers first: on ONE GPU a consumer must not spin before them
-            ctxs[r].newey_west_shard_totals(T, K, q, tao, d_fr, lo, hi, r, [nw_tot.data_ptr()])
+            ctxs[r].newey_west_shard_totals(T, K, q, tao, d_fr, lo, hi, r, [nw_tot.data_ptr()] * world)
         for r, (lo, hi) in enumerate(ranges):
             cov = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
             st = torch.empty(hi - lo, dtype=torch.int32, device="cuda")
@@ -455,7 +455,7 @@ def test_sharded_exchanges_through_per_producer_flags(ops):
             wb = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
             wv = torch.empty(hi - lo, dtype=torch.float64, device="cuda")
             ctxs[r].vol_regime_shard_totals(T, lo, hi - lo, K, 21.0, d_fr[lo:hi].contiguous(), torch.nan_to_num(covs[r][0]),
-                                            covs[r][1], wb, wv, r, [vr_tot.data_ptr()])
+                                            covs[r][1], wb, wv, r, [vr_tot.data_ptr()] * world)
             terms.append((wb, wv))
         for r, (lo, hi) in enumerate(ranges):
             out = torch.empty((hi - lo, K, K), dtype=torch.float64, device="cuda")
