@@ -1253,6 +1253,14 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   if (mode < 1 || mode > 5) {
     int wpd = (max_rows > 0 && max_rows <= 1024) ? 1 : 2;
     const long long slots = (long long)ctx->sm_count * 12;      // warps the SMs hold with one warp per date
+    // pass C re-reads a date when its solve is done: with one warp per date the dates in flight (slots x rows x
+    // ~100 B) must stay in L2 for that.  At 800 x 2500 they are 142 MB and 64% of the second pass goes back to HBM
+    // (ncu: 341 MB of DRAM traffic for 216 MB of algorithmic bytes); two warps per date halve the dates in flight:
+    // 241 MB (1.12x) at the same kernel time.
+    {
+      const long long inflight = (p.T < slots ? p.T : slots) * (long long)(max_rows > 0 ? max_rows : 1024) * (Q * 8 + 28);
+      if (wpd == 1 && inflight > (64LL << 20)) wpd = 2;
+    }
     while (wpd < 4 && (long long)p.T * wpd * 2 <= slots) wpd *= 2;
     mode = wpd == 1 ? 3 : (wpd == 2 ? 5 : 4);
   }
