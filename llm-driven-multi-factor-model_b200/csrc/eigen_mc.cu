@@ -562,7 +562,7 @@ static int et_run(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, const 
     ctx->launches++;
   }
   const size_t smem_b = (size_t)2 * K * ET_BTHREADS * 8;
-  const size_t smem_c = ((size_t)G * (et_slot_doubles<NT>() + 2) + (size_t)G * LD) * 8;
+  const size_t smem_c = ((size_t)2 * G * (et_slot_doubles<NT>() + 2) + (size_t)G * LD) * 8;   // two slot sets
   BMFM_CUDA(ctx, cudaFuncSetAttribute(et_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
   BMFM_CUDA(ctx, cudaFuncSetAttribute(et_vectors_kernel<NT, N, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
   int occ_a = 1, occ_c = 1;
@@ -601,16 +601,17 @@ static int et_dispatch(bmfm_ctx* ctx, int T, int K, int nsim, const double* C, c
   const int NT = (K + 7) / 8;
   // the factor counts of the reference's own runs get compile-time loop bounds: 42 = 1 + 31 + 10 (BASELINE
   // configs), 39 = 1 + 28 + 10 (demo.py:38)
-  if (K == 42) return ctx->opt_eig_c_blocks == 2 ? et_run<6, 42, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate)
-                                                  : et_run<6, 42, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-  if (K == 39) return et_run<5, 39, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+  // (two slot sets of three problems are 81 KB of shared memory: two CTAs per SM, so the 255-register build)
+  if (K == 42) return ctx->opt_eig_c_blocks == 3 ? et_run<6, 42, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate)
+                                                  : et_run<6, 42, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+  if (K == 39) return et_run<5, 39, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
   switch (NT) {
-    case 1: return et_run<1, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 2: return et_run<2, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 3: return et_run<3, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 4: return et_run<4, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 5: return et_run<5, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
-    case 6: return et_run<6, 0, 3>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 1: return et_run<1, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 2: return et_run<2, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 3: return et_run<3, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 4: return et_run<4, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 5: return et_run<5, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
+    case 6: return et_run<6, 0, 2>(ctx, T, K, nsim, C, D0, status, perm, vsum, accumulate);
   }
   snprintf(ctx->err, sizeof(ctx->err), "K=%d exceeds the register-tile solver (K <= %d)", K, 8 * ET_MAX_NT);
   return BMFM_E_UNSUPPORTED;

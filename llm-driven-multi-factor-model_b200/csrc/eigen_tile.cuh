@@ -290,11 +290,13 @@ __global__ void __launch_bounds__(ET_WARPS * 32) et_tridiag_kernel(EtBatch b) {
 __device__ inline bool et_ql_values(double* d, double* e2, int st, int n) {
   const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
   int budget = 60 * n;
+  int m = -1;          // end of the unreduced block that starts at l (first negligible off-diagonal), -1: not known
   for (int l = 0; l < n;) {
-    int m = l;
-    for (; m < n - 1; ++m) {
-      const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
-      if (e2[m * st] <= eps2 * dd * dd) break;
+    if (m < l) {       // a scan per converged eigenvalue; between the sweeps of one block the split is tracked below
+      for (m = l; m < n - 1; ++m) {
+        const double dd = fabs(d[m * st]) + fabs(d[(m + 1) * st]);
+        if (e2[m * st] <= eps2 * dd * dd) break;
+      }
     }
     if (m < n - 1) e2[m * st] = 0.0;
     if (m == l) { ++l; continue; }
@@ -323,24 +325,41 @@ __device__ inline bool et_ql_values(double* d, double* e2, int st, int n) {
     double c = 1.0, sn = 0.0;
     double gamma = d[m * st] - sigma;
     p = gamma * gamma;
-    double bb = e2[(m - 1) * st], alpha = d[(m - 1) * st];
-    for (int i = m - 1; i >= l; --i) {
-      const double bb_nx = i > l ? e2[(i - 1) * st] : 0.0, alpha_nx = i > l ? d[(i - 1) * st] : 0.0;
+    double* pd = d + (size_t)(m - 1) * st;
+    double* pe = e2 + (size_t)(m - 1) * st;
+    double bb = *pe, alpha = *pd;
+    double d_up = 0.0;                // final d[i + 2] of the previous step (for the split test)
+    int msplit = -1;
+    for (int i = m - 1; i >= l; --i, pd -= st, pe -= st) {
+      const double bb_nx = i > l ? pe[-st] : 0.0, alpha_nx = i > l ? pd[-st] : 0.0;
       const double r = p + bb;
-      if (i != m - 1) e2[(i + 1) * st] = sn * r;
+      const double e_new = sn * r;                // e2[i + 1]
       const double oldc = c;
       const double ir = r > 0.0 ? et_rcp(r) : 0.0;
       c = p * ir;
       sn = bb * ir;
       const double oldgam = gamma;
       gamma = c * (alpha - sigma) - sn * oldgam;
-      d[(i + 1) * st] = oldgam + (alpha - gamma);
+      const double d_new = oldgam + (alpha - gamma);     // d[i + 1]
+      pd[st] = d_new;
+      if (i != m - 1) {
+        pe[st] = e_new;
+        const double dd = fabs(d_new) + fabs(d_up);
+        if (e_new <= eps2 * dd * dd) msplit = i + 1;      // i decreases: the last hit is the smallest index
+      }
+      d_up = d_new;
       p = c != 0.0 ? gamma * gamma * et_rcp(c) : oldc * bb;
       bb = bb_nx;
       alpha = alpha_nx;
     }
-    e2[l * st] = sn * p;
-    d[l * st] = sigma + gamma;
+    {
+      const double e_new = sn * p, d_new = sigma + gamma;
+      e2[l * st] = e_new;
+      d[l * st] = d_new;
+      const double dd = fabs(d_new) + fabs(d_up);
+      if (e_new <= eps2 * dd * dd) msplit = l;
+    }
+    if (msplit >= 0) m = msplit;
   }
   return true;
 }
@@ -392,17 +411,10 @@ __global__ void __launch_bounds__(ET_CTHREADS, MINB) et_vectors_kernel(EtBatch b
   const int tid = threadIdx.x;
   const int slot = tid / n, j = tid - slot * n;        // threads >= G * n idle in the per-eigenpair part
   const bool active = slot < G;
+  // two sets of G slots: while a round is computed from one set the next round's problems arrive in the other
+  // (cp.async), so the ~12 KB per problem that come from L2 / HBM are not waited for
   double* S0 = reinterpret_cast<double*>(smem);
-  double* vacc = S0 + (size_t)G * SLOT;                // [G][LD] accumulators
-  double* my = S0 + (size_t)(active ? slot : 0) * SLOT;
-  const double* s_d = my;
-  const double* s_e = s_d + LD;
-  const double* s_d0 = s_e + LD;
-  const double* s_lam = s_d0 + LD;
-  const double* s_hinv = s_lam + LD;
-  double* s_ratio = my + 5 * LD;
-  int* s_rank = reinterpret_cast<int*>(s_ratio + LD);   // LD ints
-  const double* s_V = s_ratio + 2 * LD;
+  double* vacc = S0 + (size_t)2 * G * SLOT;            // [G][LD] accumulators
   const int per = (b.nm + nblk - 1) / nblk;
   for (int w = blockIdx.x; w < b.nd * nblk; w += gridDim.x) {
     const int dt = w / nblk, blk = w - dt * nblk, t = b.t0 + dt;
@@ -411,27 +423,47 @@ __global__ void __launch_bounds__(ET_CTHREADS, MINB) et_vectors_kernel(EtBatch b
     __syncthreads();
     for (int e = tid; e < G * LD; e += ET_CTHREADS) vacc[e] = 0.0;
     const int mi_lo = blk * per, mi_hi = min(b.nm, mi_lo + per);
-    for (int mi0 = mi_lo; mi0 < mi_hi; mi0 += G) {
-      __syncthreads();
-      // stage the round's problems (all threads): d, e, lam, hinv, V; D0 of the date
+    auto stage = [&](int mi0, int buf) {
+      // d, e, lam, hinv, V of the round's problems and D0 of the date -> slot set `buf` (asynchronous copies)
       for (int sl = 0; sl < G; ++sl) {
         const int mi = mi0 + sl;
         if (mi >= mi_hi) break;
         const int p = dt * b.nm + mi;
-        double* dst = S0 + (size_t)sl * SLOT;
+        double* dst = S0 + (size_t)(buf * G + sl) * SLOT;
         for (int k = tid; k < LD; k += ET_CTHREADS) {
-          dst[k] = b.de[(size_t)k * b.P + p];
-          dst[LD + k] = b.de[(size_t)(LD + k) * b.P + p];
-          dst[2 * LD + k] = k < n ? b.D0[(size_t)t * n + k] : 0.0;
-          dst[3 * LD + k] = b.lam[(size_t)k * b.P + p];
-          dst[4 * LD + k] = b.hinv[(size_t)p * LD + k];
+          cp_async_8(dst + k, b.de + (size_t)k * b.P + p);
+          cp_async_8(dst + LD + k, b.de + (size_t)(LD + k) * b.P + p);
+          if (k < n) cp_async_8(dst + 2 * LD + k, b.D0 + (size_t)t * n + k);
+          else dst[2 * LD + k] = 0.0;
+          cp_async_8(dst + 3 * LD + k, b.lam + (size_t)k * b.P + p);
+          cp_async_8(dst + 4 * LD + k, b.hinv + (size_t)p * LD + k);
         }
-        const double2* src = reinterpret_cast<const double2*>(b.V + (size_t)p * et_vsz(NT));
-        double2* dv = reinterpret_cast<double2*>(dst + 7 * LD);
-        const int nv = n >= 3 ? et_vrow(NT, n - 2) / 2 : 0;         // reflector rows 0 .. n-3
-        for (int e = tid; e < nv; e += ET_CTHREADS) dv[e] = src[e];
+        const double* src = b.V + (size_t)p * et_vsz(NT);
+        double* dv = dst + 7 * LD;
+        const int nv = n >= 3 ? et_vrow(NT, n - 2) / 2 : 0;         // reflector rows 0 .. n-3, in 16-byte pieces
+        for (int e = tid; e < nv; e += ET_CTHREADS) cp_async_16(dv + 2 * e, src + 2 * e);
+      }
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    int buf = 0;
+    stage(mi_lo, 0);
+    for (int mi0 = mi_lo; mi0 < mi_hi; mi0 += G, buf ^= 1) {
+      if (mi0 + G < mi_hi) {
+        stage(mi0 + G, buf ^ 1);                         // the other set was released by the barrier that ended the last round
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+      } else {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
       }
       __syncthreads();
+      double* my = S0 + (size_t)(buf * G + (active ? slot : 0)) * SLOT;
+      const double* s_d = my;
+      const double* s_e = s_d + LD;
+      const double* s_d0 = s_e + LD;
+      const double* s_lam = s_d0 + LD;
+      const double* s_hinv = s_lam + LD;
+      double* s_ratio = my + 5 * LD;
+      int* s_rank = reinterpret_cast<int*>(s_ratio + LD);   // LD ints
+      const double* s_V = s_ratio + 2 * LD;
       const int mi = mi0 + slot;
       const bool work = active && mi < mi_hi;
       double ratio = 0.0, lam = 0.0;
@@ -572,6 +604,7 @@ __global__ void __launch_bounds__(ET_CTHREADS, MINB) et_vectors_kernel(EtBatch b
         for (int i = 0; i < n; ++i)
           if (s_rank[i] == j) vacc[slot * LD + j] += s_ratio[i];
       }
+      __syncthreads();          // the round's slot set may be refilled
     }
     __syncthreads();
     for (int k = tid; k < n; k += ET_CTHREADS) {
