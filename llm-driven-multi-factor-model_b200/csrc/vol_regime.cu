@@ -46,7 +46,10 @@ __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const
   cnt = __reduce_add_sync(0xffffffffu, cnt);
   nanvar = __any_sync(0xffffffffu, nanvar);
   if (lane == 0) {
-    const double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);   // B_t^2
+    // B_t^2; the reference takes sqrt(mean) and squares it again (MFM.py:149,160), so a negative mean (a negative
+    // variance on the diagonal) is NaN there and poisons every later lamb
+    double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);
+    if (b2 < 0.0) b2 = __longlong_as_double(0x7ff8000000000000LL);
     const double w = pow(0.5, (double)(T_total - 1 - (t_off + t)) / tao);
     // rows whose variance vector holds a NaN are excluded from both sums (MFM.py:158)
     const double ob = nanvar ? 0.0 : w * b2, ov = nanvar ? 0.0 : w;

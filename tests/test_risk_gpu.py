@@ -474,3 +474,20 @@ def test_sharded_exchanges_through_per_producer_flags(ops):
             assert all(f[s] == step for s in range(r)) and all(f[8 + s] == step for s in range(r))
     for c in ctxs:
         c.close()
+
+
+@pytest.mark.gpu
+def test_vol_regime_negative_variance_poisons_later_dates(ops):
+    """A date whose mean f^2 / var is negative (a negative variance on the diagonal): the reference's sqrt makes its
+    bias NaN and every later lamb with it (MFM.py:149,160); dates before it are untouched."""
+    from bmfm.synth import make_factor_returns
+    from oracle import barra_oracle as orc
+    T, K = 40, 5
+    fr = make_factor_returns(T, K, seed=2)
+    cov = np.stack([np.cov(fr.T) for _ in range(T)])
+    cov[25, 0, 0] = -1e-12                       # f^2 / var hugely negative for factor 0 on date 25
+    out, lamb = ops.vol_regime_adj_by_time(fr, cov, np.zeros(T, dtype=np.int32), 9.0)
+    wv, wl = orc.vol_regime_adj_by_time(fr, [cov[t] for t in range(T)], 9.0)
+    assert np.isnan(lamb[25:]).all() and np.isfinite(lamb[:25]).all()
+    assert relerr(lamb, np.array(wl)) < TOL
+    assert relerr(out[10], wv[10]) < TOL and np.isnan(out[30]).all()

@@ -70,6 +70,48 @@ def test_noalloc_leaves_free_device_memory_unchanged():
     ctx.close()
 
 
+def test_noalloc_long_series_uses_longer_chunks():
+    """T = 30 000 at K = 42, q = 2: the ordinary chunk length would need more chunk states than the fixed array
+    holds, so the entry point lengthens the chunks (more shared memory per CTA of the emit kernel) — the one path
+    on which its limits matter.  Checked against the regular entry point on a sample of dates."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.synth import make_factor_returns
+    ctx = _cabi.default_context()
+    T, K, q, tao = 30000, 42, 2, 252.0
+    d_fr = torch.from_numpy(make_factor_returns(T, K, seed=6) + 0.001).cuda()
+    st_a = torch.empty(T, dtype=torch.int32, device="cuda")
+    st_b = torch.empty(T, dtype=torch.int32, device="cuda")
+    cov_a = torch.empty((T, K, K), dtype=torch.float64, device="cuda")
+    ctx.newey_west_by_time_noalloc(T, K, q, tao, d_fr, cov_a, st_a)
+    pick = torch.tensor(sorted(set(list(range(0, T, 997)) + [K, K + 1, T - 1])), device="cuda")
+    got = cov_a[pick].cpu().numpy()
+    del cov_a
+    cov_b = torch.empty((T, K, K), dtype=torch.float64, device="cuda")
+    ctx.newey_west_by_time(T, K, q, tao, d_fr, cov_b, st_b)
+    want = cov_b[pick].cpu().numpy()
+    assert torch.equal(st_a, st_b)
+    ok = st_b[pick].cpu().numpy() == 0
+    assert ok.any()
+    assert np.abs(got[ok] - want[ok]).max() <= 1e-11 * np.abs(want[ok]).max()
+
+
+def test_noalloc_refuses_series_past_its_limit():
+    """Just past the documented limit (about T = 85 000 at K = 42, q = 2) the call is refused with a message and
+    nothing is launched."""
+    import torch
+    from bmfm import _cabi
+    ctx = _cabi.default_context()
+    T, K = 90000, 42
+    fr = torch.zeros((T, K), dtype=torch.float64, device="cuda")
+    cov = torch.empty((1,), dtype=torch.float64, device="cuda")      # never touched: the call is refused first
+    st = torch.empty(T, dtype=torch.int32, device="cuda")
+    n0 = ctx.launches
+    with pytest.raises(_cabi.BmfmError, match="fixed"):
+        ctx.newey_west_by_time_noalloc(T, K, 2, 252.0, fr, cov, st)
+    assert ctx.launches == n0
+
+
 def test_noalloc_rejects_oversized_problems():
     import torch
     from bmfm import _cabi
