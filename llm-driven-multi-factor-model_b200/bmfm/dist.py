@@ -143,6 +143,27 @@ class GpuBackend:
         self.ctx.vol_regime_scale(T_total, t0, n, K, wb_all, wv_all, cov_block, status_block, out, lamb)
         return out, lamb
 
+    def vr_shard_totals(self, T_total, t0, fr_block, cov_block, status_block, tao, rank, world):
+        """Per-date terms of this rank's block (kept) and their two sums as a [2] tensor
+        (bmfm_vol_regime_shard_totals with this GPU's own buffer as the only destination)."""
+        import torch
+        n, K = fr_block.shape
+        wb = torch.empty(n, dtype=torch.float64, device=fr_block.device)
+        wv = torch.empty(n, dtype=torch.float64, device=fr_block.device)
+        buf = torch.zeros((world, 2), dtype=torch.float64, device=fr_block.device)
+        self.ctx.vol_regime_shard_totals(T_total, t0, n, K, tao, fr_block, cov_block, status_block, wb, wv, rank,
+                                         [buf.data_ptr()])
+        return wb, wv, buf[rank]
+
+    def vr_shard_scale(self, wb, wv, totals, rank, cov_block, status_block):
+        """lamb of this rank's dates from its own terms and the earlier ranks' totals ([world, 2]); scaled block."""
+        import torch
+        n, K = cov_block.shape[0], cov_block.shape[1]
+        out = torch.empty_like(cov_block)
+        lamb = torch.empty(n, dtype=torch.float64, device=cov_block.device)
+        self.ctx.vol_regime_shard_scale(n, K, wb, wv, totals.contiguous(), rank, cov_block, status_block, out, lamb)
+        return out, lamb
+
 
 class RiskPipeline:
     """reg_by_time -> Newey_West_by_time -> [eigen_risk_adj_by_time] -> vol_regime_adj_by_time with the
@@ -153,12 +174,13 @@ class RiskPipeline:
         self.rank, self.world, self.group = rank, world, group
 
     def run(self, counts, P, Q, max_rows, off, cap, ret, ind, style, q=2, tao_nw=252, tao_vr=84,
-            eigen=None, symmetric=None, shard_nw=False):
+            eigen=None, symmetric=None, shard_nw=False, shard_vr=False):
         """`counts[r]` = number of dates owned by rank r (date order = rank order); the panel arrays are
         this rank's block.  `eigen` = None (vol-regime directly on the Newey-West covariances, BASELINE
         config 2) or dict(T_sim=, M=, scale_coef=).  `shard_nw`: Newey-West by exchanged state records (see
-        bmfm_newey_west_shard_totals) instead of the whole-series pass.  Returns a dict of this rank's blocks +
-        lamb_all."""
+        bmfm_newey_west_shard_totals) instead of the whole-series pass.  `shard_vr`: vol-regime by two exchanged
+        block totals per rank (bmfm_vol_regime_shard_totals) instead of gathered per-date terms; lamb_all then holds
+        this rank's dates only (NaN elsewhere).  Returns a dict of this rank's blocks + lamb_all."""
         T_total = int(sum(counts))
         t0 = int(sum(counts[: self.rank]))
         n = int(counts[self.rank])
@@ -180,10 +202,18 @@ class RiskPipeline:
         cov, cov_st = nw, nw_st
         if eigen is not None:
             cov, cov_st = self.b.eigen(nw, nw_st, eigen["T_sim"], eigen["M"], eigen["scale_coef"])
-        wb, wv = self.b.vr_bias(T_total, t0, fr, cov, cov_st, tao_vr)
-        wb_all = all_gather_rows(wb, counts, self.group)
-        wv_all = all_gather_rows(wv, counts, self.group)
-        vr, lamb_all = self.b.vr_scale(T_total, t0, wb_all, wv_all, cov, cov_st)
+        if shard_vr and self.world > 1:
+            import torch
+            wb, wv, tot = self.b.vr_shard_totals(T_total, t0, fr, cov, cov_st, tao_vr, self.rank, self.world)
+            totals = all_gather_rows(tot.reshape(1, 2), [1] * self.world, self.group)
+            vr, lamb = self.b.vr_shard_scale(wb, wv, totals, self.rank, cov, cov_st)
+            lamb_all = torch.full((T_total,), float("nan"), dtype=lamb.dtype, device=lamb.device)
+            lamb_all[t0:t0 + n] = lamb
+        else:
+            wb, wv = self.b.vr_bias(T_total, t0, fr, cov, cov_st, tao_vr)
+            wb_all = all_gather_rows(wb, counts, self.group)
+            wv_all = all_gather_rows(wv, counts, self.group)
+            vr, lamb_all = self.b.vr_scale(T_total, t0, wb_all, wv_all, cov, cov_st)
         return {"factor_ret": fr, "factor_ret_all": fr_all, "specific_ret": spec, "R2": r2, "status": status,
                 "nw": nw, "nw_status": nw_st, "cov": cov, "cov_status": cov_st, "vr": vr,
                 "lamb_all": lamb_all, "t0": t0, "n": n}

@@ -82,22 +82,25 @@ def progressbar(cur, total, txt):
 
 def group_mean_std(x):
     '''
-    计算一组的加权平均和波动率 (utils.py:133-139)
+    计算一组的加权平均和波动率 (utils.py:133-139): cap-weighted mean and population std of one cap group.
+    Host helper kept so that code importing it from mfm.utils keeps working; bayes_shrink below does not
+    call it (the whole shrinkage runs in one kernel).  `x`: anything with .volatility and .capital.
     '''
-    m = sum(x.volatility * x.capital) / sum(x.capital)
-    s = np.sqrt(np.mean((x.volatility - m) ** 2))
-    return ([m, s])
+    vol = np.asarray(x.volatility, dtype=np.float64)
+    cap = np.asarray(x.capital, dtype=np.float64)
+    m = float(np.dot(vol, cap) / cap.sum())
+    return ([m, float(np.sqrt(np.mean(np.square(vol - m))))])
 
 
 def shrink(x, group_weight_mean, q):
     '''
-    计算shrink估计量 (utils.py:142-150)
+    计算shrink估计量 (utils.py:142-150) for one row `x` (keys 'volatility', 'group'); `group_weight_mean[g]` is
+    the [mean, std] pair of group g as group_mean_std returns it.  Host helper for API compatibility only.
     '''
-    a = q * np.abs(x['volatility'] - group_weight_mean[x['group']][0])
-    b = group_weight_mean[x['group']][1]
-    v = a / (a + b)
-    SH_est = v * group_weight_mean[x['group']][0] + (1 - v) * np.abs(x['volatility'])
-    return (SH_est)
+    m, s = group_weight_mean[x['group']][0], group_weight_mean[x['group']][1]
+    dist = q * abs(x['volatility'] - m)
+    v = dist / (dist + s)
+    return (v * m + (1 - v) * abs(x['volatility']))
 
 
 def bayes_shrink(volatility, capital, ngroup=10, q=1):

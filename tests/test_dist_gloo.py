@@ -151,6 +151,19 @@ class OracleBackend:
         return torch.from_numpy(out), torch.from_numpy(lamb)
 
 
+    # -- vol-regime by exchanged block totals (the form of bmfm_vol_regime_shard_totals / _scale) --
+    def vr_shard_totals(self, T_total, t0, fr_block, cov_block, status_block, tao, rank, world):
+        wb, wv = self.vr_bias(T_total, t0, fr_block, cov_block, status_block, tao)
+        return wb, wv, torch.stack([wb.sum(), wv.sum()])
+
+    def vr_shard_scale(self, wb, wv, totals, rank, cov_block, status_block):
+        cb, cv = totals[:rank, 0].sum().item(), totals[:rank, 1].sum().item()
+        nb, nv = cb + np.cumsum(wb.numpy()), cv + np.cumsum(wv.numpy())
+        with np.errstate(invalid="ignore", divide="ignore"):
+            lamb = np.where(nv > 0, np.sqrt(nb / np.where(nv > 0, nv, 1)), 0.0)
+        return torch.from_numpy(cov_block.numpy() * (lamb ** 2)[:, None, None]), torch.from_numpy(lamb)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -163,7 +176,7 @@ def _panel():
     return make_panel(T=40, N=30, P=3, Q=2, seed=77, ragged=0.1)
 
 
-def _worker(rank, world, port, q, shard_nw=False):
+def _worker(rank, world, port, q, shard_nw=False, shard_vr=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -179,7 +192,7 @@ def _worker(rank, world, port, q, shard_nw=False):
         pipe = bd.RiskPipeline(OracleBackend(), rank, world)
         res = pipe.run(counts, pan.P, pan.Q, pan.N, off, tt(csr["cap"][a:b]), tt(csr["ret"][a:b]),
                        tt(csr["ind"][a:b]), tt(csr["style"][a:b]), q=2, tao_nw=15, tao_vr=8,
-                       eigen=dict(T_sim=30, M=4, scale_coef=1.4), shard_nw=shard_nw)
+                       eigen=dict(T_sim=30, M=4, scale_coef=1.4), shard_nw=shard_nw, shard_vr=shard_vr)
         # config-4 style: all dates on every rank, simulations sharded
         fr_all = res["factor_ret_all"]
         nw_all, st_all = OracleBackend().newey_west_range(fr_all, 0, T, 2, 15)
@@ -221,13 +234,13 @@ def test_newey_west_recurrence_and_record_exchange():
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("shard_nw", [False, True])
-def test_sharded_pipeline_matches_single_process(shard_nw):
+@pytest.mark.parametrize("shard_nw,shard_vr", [(False, False), (True, False), (True, True)])
+def test_sharded_pipeline_matches_single_process(shard_nw, shard_vr):
     world = 2
     port = _free_port()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q, shard_nw)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, shard_nw, shard_vr)) for r in range(world)]
     for p in procs:
         p.start()
     got = {}
@@ -255,7 +268,11 @@ def test_sharded_pipeline_matches_single_process(shard_nw):
         t0, n = res["t0"], res["n"]
         assert close(res["factor_ret"], fr[t0:t0 + n])
         assert close(res["factor_ret_all"], fr)
-        assert close(res["lamb_all"], np.array(lamb), 1e-10)
+        if shard_vr:       # the two-totals exchange leaves every rank with the lamb of its own dates
+            assert close(res["lamb_all"][t0:t0 + n], np.array(lamb)[t0:t0 + n], 1e-10)
+            assert np.isnan(np.delete(res["lamb_all"], np.arange(t0, t0 + n))).all()
+        else:
+            assert close(res["lamb_all"], np.array(lamb), 1e-10)
         for i in range(n):
             t = t0 + i
             assert (res["nw_status"][i] == 0) == (nw[t] is not None)
