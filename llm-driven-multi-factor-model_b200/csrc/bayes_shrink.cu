@@ -21,11 +21,30 @@ constexpr int BS_MAX_GROUPS = 64;
 constexpr int BS_ST_DUP_EDGES = 5;
 constexpr int BS_BIN_BITS = 11, BS_BINS = 1 << BS_BIN_BITS;   // histogram of the multi-select
 constexpr int BS_COLL_MAX = 2048;                              // members of needed bins ranked by counting
+constexpr int BS_MAXR = 16;                                    // rows per thread: 16384 rows per date at 1024 threads
+constexpr int BS_GFAST = 10;                                   // groups handled by register accumulators (deciles)
 
 // order-preserving map double -> uint64
 __device__ __forceinline__ unsigned long long bs_key(double x) {
   const unsigned long long u = (unsigned long long)__double_as_longlong(x);
   return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+
+// sum over the warp of 16 values per lane by recursive halving: lanes 2 e and 2 e + 1 both return the total of
+// value e (15 + 1 shuffles instead of 16 x 5)
+__device__ __forceinline__ double bs_reduce_scatter16(double (&a)[16], int lane) {
+#pragma unroll
+  for (int s2 = 0; s2 < 4; ++s2) {
+    const int off = 16 >> s2, H = 8 >> s2;
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const double lo = a[i], hi = a[i + H];
+      const double send = upper ? lo : hi, keep = upper ? hi : lo;
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return a[0] + __shfl_xor_sync(0xffffffffu, a[0], 1);
 }
 
 struct BsParams {
@@ -62,7 +81,7 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
   int* s_slotoff = s_slotbin + 2 * BS_MAX_GROUPS + 2;                 // [+1]
   int* s_fill = s_slotoff + 2 * BS_MAX_GROUPS + 3;
   int* s_ctl = s_fill + 2 * BS_MAX_GROUPS + 2;                        // nslots, ncoll, spare
-  const int tid = threadIdx.x, nt = blockDim.x, G = p.ngroup;
+  const int tid = threadIdx.x, nt = blockDim.x, G = p.ngroup, lane = threadIdx.x & 31;
   for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
     const long long a = p.date_off[t];
     const int n = (int)(p.date_off[t + 1] - a);
@@ -217,63 +236,134 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
       __syncthreads();
       continue;
     }
-    // pass 1: group sums
+    // The decile code of every row is found once and kept in registers (a thread owns rows tid, tid + nt, ...: at
+    // most BS_MAXR of them).
     const double e0 = s_edges[0];
-    for (int i = tid; i < n; i += nt) {
-      const double c = p.cap[a + i], v = p.vol[a + i];
-      int cnt = 0;
-      for (int k = 0; k <= G; ++k) cnt += s_edges[k] < c;   // searchsorted(edges, c, 'left')
-      int g = cnt - 1;
-      if (c == e0) g = 0;
-      if (g >= 0 && g < G) {
-        atomicAdd(&my[4 * g + 0], v * c);
-        atomicAdd(&my[4 * g + 1], c);
-        atomicAdd(&my[4 * g + 2], 1.0);
+    signed char gcode[BS_MAXR];
+#pragma unroll
+    for (int j = 0; j < BS_MAXR; ++j) {
+      const int i = tid + j * nt;
+      int g = -1;
+      if (i < n) {
+        const double c = p.cap[a + i];
+        int cnt = 0;
+        for (int k = 0; k <= G; ++k) cnt += s_edges[k] < c;   // searchsorted(edges, c, 'left')
+        g = cnt - 1;
+        if (c == e0) g = 0;
+        if (g >= G) g = -1;
       }
+      gcode[j] = (signed char)g;
     }
-    __syncthreads();
-    for (int e = tid; e < 4 * G; e += nt) {
-      if ((e & 3) == 3) continue;
-      double acc = 0.0;
-      for (int w = 0; w < nwarps; ++w) acc += s_wsum[(size_t)w * G * 4 + e];
-      s_gsum[e] = acc;
-    }
-    __syncthreads();
-    // pass 2: dispersion about the group mean
-    for (int i = tid; i < n; i += nt) {
-      const double c = p.cap[a + i], v = p.vol[a + i];
-      int cnt = 0;
-      for (int k = 0; k <= G; ++k) cnt += s_edges[k] < c;
-      int g = cnt - 1;
-      if (c == e0) g = 0;
-      if (g >= 0 && g < G) {
-        const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
-        const double d = v - m;
-        atomicAdd(&my[4 * g + 3], d * d);
+    if (G <= BS_GFAST) {
+      // group sums without atomics: every lane adds its rows into one register accumulator per group (predicated
+      // adds: the ~10 groups are hit by every row, shared-memory atomics on them are compare-and-swap loops that
+      // collide all the time), then a recursive-halving reduction inside the warp and one store per warp.  One
+      // sweep over the thread's rows per kind of sum keeps the accumulators at 16 registers pairs.
+#pragma unroll 1
+      for (int which = 0; which < 3; ++which) {
+        double acc[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e] = 0.0;
+#pragma unroll
+        for (int j = 0; j < BS_MAXR; ++j) {
+          const int i = tid + j * nt;
+          if (i < n) {
+            const double c = p.cap[a + i];
+            const double x = which == 0 ? p.vol[a + i] * c : (which == 1 ? c : 1.0);
+            const int g = gcode[j];
+#pragma unroll
+            for (int k = 0; k < BS_GFAST; ++k) acc[k] += g == k ? x : 0.0;
+          }
+        }
+        const double tot = bs_reduce_scatter16(acc, lane);
+        if ((lane & 1) == 0 && (lane >> 1) < G) my[4 * (lane >> 1) + which] = tot;
+      }
+      __syncthreads();
+      for (int e = tid; e < 4 * G; e += nt) {
+        if ((e & 3) == 3) continue;
+        double s2 = 0.0;
+        for (int w = 0; w < nwarps; ++w) s2 += s_wsum[(size_t)w * G * 4 + e];
+        s_gsum[e] = s2;
+      }
+      __syncthreads();
+      // dispersion about the group mean
+      {
+        double acc[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e] = 0.0;
+#pragma unroll
+        for (int j = 0; j < BS_MAXR; ++j) {
+          const int i = tid + j * nt;
+          const int g = gcode[j];
+          if (i < n && g >= 0) {
+            const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
+            const double d = p.vol[a + i] - m;
+            const double dd = d * d;
+#pragma unroll
+            for (int k = 0; k < BS_GFAST; ++k) acc[k] += g == k ? dd : 0.0;
+          }
+        }
+        const double tot = bs_reduce_scatter16(acc, lane);
+        if ((lane & 1) == 0 && (lane >> 1) < G) my[4 * (lane >> 1) + 3] = tot;
+      }
+    } else {
+      // many groups: per-warp shared tables and atomics
+      for (int j = 0; j < BS_MAXR; ++j) {
+        const int i = tid + j * nt;
+        const int g = gcode[j];
+        if (i < n && g >= 0) {
+          const double c = p.cap[a + i], v = p.vol[a + i];
+          atomicAdd(&my[4 * g + 0], v * c);
+          atomicAdd(&my[4 * g + 1], c);
+          atomicAdd(&my[4 * g + 2], 1.0);
+        }
+      }
+      __syncthreads();
+      for (int e = tid; e < 4 * G; e += nt) {
+        if ((e & 3) == 3) continue;
+        double s2 = 0.0;
+        for (int w = 0; w < nwarps; ++w) s2 += s_wsum[(size_t)w * G * 4 + e];
+        s_gsum[e] = s2;
+      }
+      __syncthreads();
+      for (int j = 0; j < BS_MAXR; ++j) {
+        const int i = tid + j * nt;
+        const int g = gcode[j];
+        if (i < n && g >= 0) {
+          const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
+          const double d = p.vol[a + i] - m;
+          atomicAdd(&my[4 * g + 3], d * d);
+        }
       }
     }
     __syncthreads();
     for (int g = tid; g < G; g += nt) {
-      double acc = 0.0;
-      for (int w = 0; w < nwarps; ++w) acc += s_wsum[(size_t)w * G * 4 + 4 * g + 3];
-      s_gsum[4 * g + 3] = acc;
+      double s2 = 0.0;
+      for (int w = 0; w < nwarps; ++w) s2 += s_wsum[(size_t)w * G * 4 + 4 * g + 3];
+      s_gsum[4 * g + 3] = s2;
     }
     __syncthreads();
-    for (int i = tid; i < n; i += nt) {
-      const double c = p.cap[a + i], v = p.vol[a + i];
-      int cnt = 0;
-      for (int k = 0; k <= G; ++k) cnt += s_edges[k] < c;
-      int g = cnt - 1;
-      if (c == e0) g = 0;
-      double o = __longlong_as_double(0x7ff8000000000000LL);
-      if (g >= 0 && g < G) {
-        const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
-        const double s = sqrt(s_gsum[4 * g + 3] / s_gsum[4 * g + 2]);
-        const double aa = p.q * fabs(v - m);
-        const double w = aa / (aa + s);
-        o = w * m + (1.0 - w) * fabs(v);
+    // per group: mean and std once, then the shrink of every row (utils.py:146-149)
+    if (tid < G) {
+      s_gsum[4 * tid + 0] = s_gsum[4 * tid + 0] / s_gsum[4 * tid + 1];
+      s_gsum[4 * tid + 3] = sqrt(s_gsum[4 * tid + 3] / s_gsum[4 * tid + 2]);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < BS_MAXR; ++j) {
+      const int i = tid + j * nt;
+      if (i < n) {
+        const int g = gcode[j];
+        double o = __longlong_as_double(0x7ff8000000000000LL);
+        if (g >= 0) {
+          const double v = p.vol[a + i];
+          const double m = s_gsum[4 * g + 0], sd = s_gsum[4 * g + 3];
+          const double aa = p.q * fabs(v - m);
+          const double w = aa / (aa + sd);
+          o = w * m + (1.0 - w) * fabs(v);
+        }
+        p.out[a + i] = o;
       }
-      p.out[a + i] = o;
     }
     if (tid == 0) p.status[t] = BMFM_ST_OK;
     __syncthreads();
@@ -310,7 +400,9 @@ extern "C" int bmfm_bayes_shrink(bmfm_ctx* ctx, int T, int max_rows_per_date, co
     volatile double pct = y * 100.0;
     p.quant[k] = pct / 100.0;
   }
-  int nthreads = npad >= 2048 ? 1024 : (npad >= 512 ? 256 : 128);
+  // (two CTAs of 512 threads per SM overlap one date's barrier-separated phases with another's; a thread owns at most
+  //  BS_MAXR rows)
+  int nthreads = npad > 8192 ? 1024 : (npad >= 2048 ? 512 : (npad >= 512 ? 256 : 128));
   const size_t smem = ((size_t)npad + BS_MAX_GROUPS + 1 + 4 * BS_MAX_GROUPS) * 8 + 16 + (size_t)(nthreads / 32) * ngroup * 4 * 8 +
                       (size_t)(2 * BS_MAX_GROUPS + 2 + 2) * 8 + (size_t)(2 * BS_BINS + 1 + 6 * (2 * BS_MAX_GROUPS + 3) + 8) * 4;
   if (smem > (size_t)ctx->max_smem_optin) {
