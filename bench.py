@@ -17,6 +17,8 @@ Further blocks of the same JSON line:
               scaling), one all-reduce of the T x K accumulators; sims/s and a roofline against the measured FP64 peak;
   "c3"        configs[2]: ONE 5000 x 3750 panel sharded by date over the ranks (strong scaling): regression +
               Bayesian shrinkage of a specific-risk estimate, dates/s and HBM fractions;
+  "c5"        configs[4]: descriptor build for 5000 stocks x 3750 days (returns, BETA/HSIGMA, DASTD, CMRA by stock;
+              winsorize, composite, orthogonalize by date; one all-to-all between them when N > 1), stock-days/s;
   "df_to_df"  configs[0] ("C1", 300 x 1400, P = 28): DataFrame in, DataFrames out through the drop-in MFM class.
 
 One JSON line on stdout (rank 0).  --impl reference times the REFERENCE's own code (oracle/_ref: its mfm
@@ -838,6 +840,102 @@ def run_gpu(args):
         del c_ind, c_cap, c_style, c_ret, c_spec, c_sh, c_vol
         torch.cuda.empty_cache()
 
+    # ---- config C5: descriptor build for 5000 stocks x 3750 days: daily returns, EWMA BETA/HSIGMA (252-day window,
+    #      63-day half-life), DASTD, CMRA on per-stock series (stocks sharded over the ranks), one all-to-all that
+    #      turns [days, my stocks] into [my days, all stocks], then winsorize x4, the volatility composite and its
+    #      orthogonalisation against BETA and SIZE per date (factor_calculator.py:79-234, post_processing.py:7-70) ----
+    c5 = None
+    if os.environ.get("BENCH_C5", "1") == "1":
+        torch.cuda.empty_cache()
+        S5, L5 = C3_STOCKS, C3_DATES
+        s_lo, s_hi = rank * S5 // world, (rank + 1) * S5 // world
+        Sr = s_hi - s_lo
+        d_cut = [r * L5 // world for r in range(world + 1)]
+        Lr = d_cut[rank + 1] - d_cut[rank]
+        g = torch.Generator(device=dev)
+        g.manual_seed(20240005)                     # the market series is the same on every rank
+        mret = 0.012 * torch.randn(L5, dtype=torch.float64, device=dev, generator=g)
+        mret[0] = float("nan")
+        g.manual_seed(20240005 + 1 + rank)
+        sb = 0.4 + 1.2 * torch.rand(Sr, dtype=torch.float64, device=dev, generator=g)
+        sret = sb[None, :] * torch.nan_to_num(mret)[:, None] + 0.02 * torch.randn((L5, Sr), dtype=torch.float64, device=dev, generator=g)
+        d_close = (10.0 * torch.exp(torch.cumsum(torch.log1p(sret.clamp(-0.2, 0.2)), 0))).contiguous()
+        d_mkt = mret[:, None].expand(L5, Sr).contiguous()
+        d_lcap = (15.0 + 1.5 * torch.randn(S5, dtype=torch.float64, device=dev, generator=g))[None, :].expand(Lr, S5).contiguous().reshape(-1)
+        del sret
+        d_ret, d_lr = torch.empty_like(d_close), torch.empty_like(d_close)
+        roll = [torch.empty_like(d_close) for _ in range(4)]            # BETA, HSIGMA, DASTD, CMRA as [days, my stocks]
+        recv = [torch.empty((world * Lr, Sr), dtype=torch.float64, device=dev) for _ in range(4)] if world > 1 else None
+        cols = [torch.empty(Lr * S5, dtype=torch.float64, device=dev) for _ in range(4)]     # [my days, all stocks]
+        wz = [torch.empty(Lr * S5, dtype=torch.float64, device=dev) for _ in range(4)]
+        d_vol, d_volo = torch.empty(Lr * S5, dtype=torch.float64, device=dev), torch.empty(Lr * S5, dtype=torch.float64, device=dev)
+        off5 = torch.arange(Lr + 1, dtype=torch.int64, device=dev) * S5
+        in_split = [d_cut[r + 1] - d_cut[r] for r in range(world)]
+        ev5 = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+        def c5_step(timed=False):
+            if timed:
+                ev5[0].record()
+            ctx.prepare_returns(L5, Sr, d_close, d_ret, d_lr)
+            ctx.beta_hsigma(L5, Sr, d_ret, d_mkt, 252, 63, 42, roll[0], roll[1])
+            ctx.dastd(L5, Sr, d_ret, d_mkt, 252, 42, 42, roll[2])
+            ctx.cmra(L5, Sr, d_lr, 252, roll[3])
+            if timed:
+                ev5[1].record()
+            if world > 1:
+                for j in range(4):
+                    dist.all_to_all_single(recv[j], roll[j], output_split_sizes=[Lr] * world, input_split_sizes=in_split)
+                    cols[j].view(Lr, world, Sr).copy_(recv[j].view(world, Lr, Sr).permute(1, 0, 2))
+                src = cols
+            else:
+                src = [r_.view(-1) for r_ in roll]
+            if timed:
+                ev5[2].record()
+            for j in range(4):
+                ctx.winsorize(Lr, off5, src[j], 2.5, wz[j])
+            ctx.composite(Lr * S5, [wz[2], wz[3], wz[1]], [0.74, 0.16, 0.10], d_vol)
+            ctx.orthogonalize(Lr, off5, d_vol, [wz[0], d_lcap], d_volo)
+            if timed:
+                ev5[3].record()
+
+        if S5 % world:
+            c5 = {"skipped": f"{S5} stocks do not split evenly over {world} ranks"}
+        else:
+            for _ in range(3):
+                c5_step()
+            barrier()
+            n_c5 = max(3, min(args.steps, 10))
+            ph = np.zeros(3)
+            for _ in range(n_c5):
+                c5_step(timed=True)
+                torch.cuda.synchronize()
+                ph += [ev5[i].elapsed_time(ev5[i + 1]) for i in range(3)]
+            barrier()
+            tm = torch.tensor(list(ph / n_c5), dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            r_ms, x_ms, p_ms = (float(x) for x in tm.tolist())
+            c5_ms = r_ms + x_ms + p_ms
+            fin = float(torch.isfinite(d_volo.view(Lr, S5)[-1]).double().mean().item())
+            # algorithmic bytes per stock-day: returns 8 in + 16 out; BETA/HSIGMA 16 in + 16 out; DASTD 16 + 8; CMRA 8 + 8;
+            # winsorize 4 x 16; composite 24 + 8; orthogonalize 24 + 8  (the market return is a [days, stocks] panel
+            # in this ABI, read like a second input column)
+            roll_bytes, post_bytes = 96, 128
+            c5 = {"value": S5 * L5 / (c5_ms * 1e-3), "unit": "stock-days/s", "scaling": "strong", "ms_per_step": c5_ms,
+                  "config": f"C5: {S5} stocks x {L5} days generated on the device; prepare_returns + beta_hsigma(252, hl 63) + dastd + cmra "
+                            f"on [days, {Sr} stocks] per rank, "
+                            + ("one NCCL all-to-all per column to [days / ranks, all stocks], " if world > 1 else "")
+                            + "winsorize x4 + volatility composite + orthogonalize(volatility | BETA, SIZE) per date; "
+                            f"{L5 * S5 * 8 / 1e6:.0f} MB per column, larger than L2",
+                  "phase_ms": {"rolling": r_ms, "exchange": x_ms, "post_processing": p_ms},
+                  "rolling_roofline": {"kernel": "prepare_returns + beta_hsigma + dastd + cmra kernels", "bound": "hbm", "unit": "GB/s",
+                                       "achieved": roll_bytes * L5 * Sr / (r_ms * 1e-3) / 1e9, "algorithmic_bytes_per_stock_day": roll_bytes},
+                  "post_roofline": {"kernel": "winsorize x4 + composite + orthogonalize kernels", "bound": "hbm", "unit": "GB/s",
+                                    "achieved": post_bytes * Lr * S5 / (p_ms * 1e-3) / 1e9, "algorithmic_bytes_per_stock_day": post_bytes},
+                  "finite_share_last_date": fin}
+        del d_close, d_mkt, d_ret, d_lr, roll, recv, cols, wz, d_vol, d_volo, d_lcap
+        torch.cuda.empty_cache()
+
     # ---- config C1, DataFrame in / DataFrames out through the drop-in MFM class (rank 0) ----
     df_block = None
     if rank == 0 and os.environ.get("BENCH_DF", "1") == "1":
@@ -873,6 +971,10 @@ def run_gpu(args):
             for key in ("roofline", "bayes_shrink_roofline"):
                 c3[key]["peak"] = peak
                 c3[key]["frac"] = c3[key]["achieved"] / peak
+        if c5 is not None and "value" in c5:
+            for key in ("rolling_roofline", "post_roofline"):
+                c5[key]["peak"] = peak
+                c5[key]["frac"] = c5[key]["achieved"] / peak
         t0 = time.perf_counter()
         ref = load_ref()
         port_v, port_desc = cpu_sample(csr, 300, 400)
@@ -930,6 +1032,7 @@ def run_gpu(args):
                          "all_status_ok": eig_ok,
                          "cpu_baseline": {"value": cpu_eig, "unit": "sims/s", "kind": cpu_kind, "sample": "16 sims of one date"}},
             "c3": c3,
+            "c5": c5,
             "df_to_df": df_block,
         }
         emit(line)
