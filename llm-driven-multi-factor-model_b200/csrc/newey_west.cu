@@ -28,7 +28,7 @@
 namespace bmfm {
 
 constexpr int NW_MAX_Q = 4;
-constexpr int NW_LOCAL_THREADS = 512;   // chunk-total kernel: one state element per thread
+constexpr int NW_LOCAL_THREADS = 256;   // chunk-total kernel: one 2 x 2 block of every lag matrix (or one vector element) per thread
 constexpr int NW_EMIT_THREADS = 128;    // emit kernel: one 2 x 2 block of the covariance per thread
 constexpr int NW_TARGET_CHUNKS = 144;   // chunks per series aimed at (state traffic ~ nchunks * 44 KB at K = 42)
 constexpr int NW_EMIT_SMEM = 56 * 1024; // shared memory the emit kernel may use (several CTAs per SM)
@@ -45,7 +45,8 @@ struct NwParams {
   int n_peer, rank;
   double* peer_totals[8];
   BmfmFlagPeers flags;   // per-producer flags (n = 0: the caller runs a barrier instead)
-  double lam;
+  double lam, log_lam;
+  double fC, fLast, fPer;   // lam^C, lam^(length of the last chunk), lam^(C * chunks per scan part): set by nw_run_totals
   const double* fr;   // [T][K]
   double* cov;        // [T][K][K]
   int* status;        // [T]
@@ -67,8 +68,9 @@ __host__ inline int nw_pick_chunk(int T, int K, int q, int target_opt = 0) {
   return C;
 }
 
-// stage rows r0-q .. r1-1 of the series (zeros before row 0) in shared memory
-__device__ __forceinline__ void nw_stage_rows(const NwParams& p, double* sx, int r0, int len) {
+// stage rows r0-q .. r1-1 of the series (zeros before row 0) in shared memory: issue only, the caller waits
+// (cp_async_wait_all + __syncthreads) after whatever else it can do meanwhile
+__device__ __forceinline__ void nw_stage_rows_issue(const NwParams& p, double* sx, int r0, int len) {
   // rows r0-q .. r0+len-1 are one contiguous piece of the series; cp.async keeps every copy in flight at once
   // (a load-then-store loop would pay one global-memory latency per row)
   const int K = p.K, q = p.q;
@@ -84,30 +86,64 @@ __device__ __forceinline__ void nw_stage_rows(const NwParams& p, double* sx, int
   } else {
     for (int e = threadIdx.x; e < n; e += blockDim.x) cp_async_8(dst + e, src + e);
   }
+}
+__device__ __forceinline__ void nw_stage_rows(const NwParams& p, double* sx, int r0, int len) {
+  nw_stage_rows_issue(p, sx, r0, len);
   cp_async_wait_all();
 }
 
-// kernel 1: chunk totals from a zero start, one state element per thread (grid: chunks x element blocks)
+// kernel 1: chunk totals from a zero start (grid: chunks x item blocks).  Work items of a chunk: the KB x KB
+// 2 x 2 blocks of the moment matrices (KB = ceil(K/2); one thread carries its block of ALL 1+q lag matrices, so the
+// rows it reads are shared between 4 (1+q) accumulators), then the (1+2q) K vector elements, then the 1+q scalars.
+template <int QL>
 __global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int q = QL;
   double* sx = reinterpret_cast<double*>(smem_raw);   // [(C+q)][K]
-  const int c = blockIdx.x, K = p.K, q = p.q;
+  const int c = blockIdx.x, K = p.K;
   const int r0 = p.row0 + c * p.C, r1 = min(p.T, r0 + p.C), len = r1 - r0;
   double* st = p.state + (size_t)c * nw_nstate(K, q);
   nw_stage_rows(p, sx, r0, len);
   __syncthreads();
   const double lam = p.lam;
+  const int KB = (K + 1) >> 1, nblk = KB * KB;
   const int nm = (1 + q) * K * K, nv = (1 + 2 * q) * K;
-  const int e = blockIdx.y * blockDim.x + threadIdx.x;
-  if (e < nm) {
-    const int i = e / (K * K), ab = e - i * K * K, a = ab / K, b = ab - a * K;
-    const double* xa = sx + (q - i) * K + a;   // row j - i (zero rows before row 0)
-    const double* xb = sx + q * K + b;         // row j
-    double s = 0.0;
-    for (int j = 0; j < len; ++j) s = fma(s, lam, xa[j * K] * xb[j * K]);
-    st[e] = s;
-  } else if (e < nm + nv) {
-    const int v = (e - nm) / K, k = (e - nm) - v * K;
+  int e = blockIdx.y * blockDim.x + threadIdx.x;
+  if (e < nblk) {
+    const int ba = e / KB, bb = e - ba * KB;
+    const int a = 2 * ba, b = 2 * bb;
+    const bool aok = a + 1 < K, bok = b + 1 < K;
+    const int a1 = aok ? a + 1 : a, b1 = bok ? b + 1 : b;
+    double s[QL + 1][2][2];
+#pragma unroll
+    for (int i = 0; i <= QL; ++i) s[i][0][0] = s[i][0][1] = s[i][1][0] = s[i][1][1] = 0.0;
+    const double* xr = sx + q * K;            // row j; row j - i is i rows above (zero rows before row 0)
+    for (int j = 0; j < len; ++j, xr += K) {
+      const double vb0 = xr[b], vb1 = xr[b1];
+#pragma unroll
+      for (int i = 0; i <= QL; ++i) {
+        const double la0 = xr[a - i * K], la1 = xr[a1 - i * K];
+        s[i][0][0] = fma(s[i][0][0], lam, la0 * vb0);
+        s[i][0][1] = fma(s[i][0][1], lam, la0 * vb1);
+        s[i][1][0] = fma(s[i][1][0], lam, la1 * vb0);
+        s[i][1][1] = fma(s[i][1][1], lam, la1 * vb1);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i <= QL; ++i) {
+      double* m = st + (size_t)i * K * K;
+      m[a * K + b] = s[i][0][0];
+      if (bok) m[a * K + b1] = s[i][0][1];
+      if (aok) {
+        m[a1 * K + b] = s[i][1][0];
+        if (bok) m[a1 * K + b1] = s[i][1][1];
+      }
+    }
+    return;
+  }
+  e -= nblk;
+  if (e < nv) {
+    const int v = e / K, k = e - v * K;
     double s = 0.0;
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
@@ -117,15 +153,15 @@ __global__ void __launch_bounds__(NW_LOCAL_THREADS) nw_chunk_local(NwParams p) {
       else add = sx[(q + j - (v - q)) * K + k];
       s = fma(s, lam, add);
     }
-    st[e] = s;
-  } else if (e < nm + nv + 1 + q) {
-    const int i = e - nm - nv;
+    st[nm + e] = s;
+  } else if (e < nv + 1 + q) {
+    const int i = e - nv;
     double s = 0.0;
     for (int r = r0; r < r1; ++r) {
       s *= lam;
       if (r >= i) s += 1.0;
     }
-    st[e] = s;
+    st[nm + e] = s;
   }
 }
 
@@ -144,9 +180,9 @@ __global__ void __launch_bounds__(32 * NW_SCAN_GROUPS) nw_chunk_scan(NwParams p)
   const int per = max(1, (p.nchunks + NW_SCAN_GROUPS - 1) / NW_SCAN_GROUPS);   // from nchunks, not c_used: a date range
                                                                                  // then adds in the same order as the whole series
   const int c_lo = min(p.c_used, g * per), c_hi = min(p.c_used, c_lo + per);
-  const double fC = pow(p.lam, (double)p.C);
-  // the last chunk may be shorter than C: the running state before it decays by lam^len
-  const double fLast = pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C));
+  // lam^C, and lam^len for the last chunk, which may be shorter than C (computed once on the host: a pow per
+  // thread was a third of this kernel's instructions)
+  const double fC = p.fC, fLast = p.fLast;
   double* col = p.state + (act ? e : 0);
   double run = 0.0;
   for (int c0 = c_lo; c0 < c_hi; c0 += 8) {
@@ -162,7 +198,7 @@ __global__ void __launch_bounds__(32 * NW_SCAN_GROUPS) nw_chunk_scan(NwParams p)
   // state at the start of this thread's part: every earlier part holds exactly `per` full chunks
   double start = 0.0;
   {
-    const double fPer = pow(fC, (double)per);
+    const double fPer = p.fPer;
     for (int h = 0; h < g; ++h) start = fma(start, fPer, s_part[h][ex]);
   }
   run = start;
@@ -241,34 +277,76 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
   const double* cr = p.carry;                                           // sharded form: decayed state of earlier ranks
   const double fcar = cr ? pow(lam, (double)(r0 - p.row0)) : 0.0;
 #define NW_LD(idx) (cr ? fma(fcar, cr[idx], st[idx]) : st[idx])
-  nw_stage_rows(p, sx, r0, len);
-  __syncthreads();
-  // the scalar sums Z, Z_i do not depend on the data: closed form per date (one thread per date),
-  //   Z after j+1 more rows = Z_start lam^(j+1) + (1 - lam^cnt) / (1 - lam),  cnt = rows counted so far
+  nw_stage_rows_issue(p, sx, r0, len);
+  // ---- while the rows are in flight: everything that does not need them ----
+  // this thread's 2 x 2 block of V (rows a, a+1 and columns b, b+1 share their loads).  V is symmetric: only blocks
+  // on or above the block diagonal are computed (row-major enumeration of the upper triangle of the KB x KB block
+  // grid), each thread also stores the transpose of its block
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  const int KB = (K + 1) >> 1;
+  const int e = blockIdx.y * nt + tid;
+  const bool eact = e < KB * (KB + 1) / 2;
+  int ba = 0, rem = eact ? e : 0;
+  while (rem >= KB - ba) { rem -= KB - ba; ++ba; }
+  const int a = 2 * ba, b = 2 * (ba + rem);
+  const int a1 = a + 1 < K ? a + 1 : a, b1 = b + 1 < K ? b + 1 : b;     // clamped partner (stores are guarded)
+  const bool aok = a + 1 < K, bok = b + 1 < K;
+  const int ia[2] = {a, a1}, ib[2] = {b, b1};
+  double a0[2][2], bab[QN][2][2], bba[QN][2][2], wl[QN];
+  if (eact) {          // start state of the block (global loads, L2)
+#pragma unroll
+    for (int x = 0; x < 2; ++x)
+#pragma unroll
+      for (int y = 0; y < 2; ++y) {
+        a0[x][y] = NW_LD(ia[x] * K + ib[y]);
+#pragma unroll
+        for (int i = 0; i < QL; ++i) {
+          bab[i][x][y] = NW_LD((1 + i) * K * K + ia[x] * K + ib[y]);
+          bba[i][x][y] = NW_LD((1 + i) * K * K + ib[y] * K + ia[x]);
+        }
+      }
+  }
+  // start state of the vector sums of factor k = tid (further k of a thread, K > blockDim, are loaded in the loop)
+  double S0 = 0.0, R0[QN], P0[QN];
+  if (tid < K) {
+    S0 = NW_LD(nm + tid);
+#pragma unroll
+    for (int i = 0; i < QL; ++i) {
+      R0[i] = NW_LD(nm + (1 + i) * K + tid);
+      P0[i] = NW_LD(nm + (1 + q + i) * K + tid);
+    }
+  }
+  // the scalar sums Z, Z_i do not depend on the data: closed form per date (one thread per date).  With L = r + 1
+  // rows so far, Z = (1 - lam^L) / (1 - lam) and Z_i the same with L - i rows (those with index >= i);
+  // 1 - lam^n = -expm1(n log lam) keeps full precision when n log lam is small
   for (int j = tid; j < len; j += nt) {
-    const double lj = pow(lam, (double)(j + 1));
-    const double inv1 = 1.0 / (1.0 - lam);
-    const double Z0 = fma(NW_LD(nm + (1 + 2 * q) * K), lj, (1.0 - lj) * inv1);
-    const double iz = 1.0 / Z0;
+    const int L = r0 + j + 1;
+    const double inv1 = -1.0 / expm1(p.log_lam);
+    const double iz = 1.0 / (-expm1((double)L * p.log_lam) * inv1);
     double zs = 0.0;
 #pragma unroll
     for (int i = 0; i < QL; ++i) {
       const int lag = i + 1;
-      const int cnt = max(0, r0 + j + 1 - max(r0, lag));          // rows r >= lag among r0 .. r0+j
-      const double Zl = fma(NW_LD(nm + (1 + 2 * q) * K + lag), lj, (1.0 - pow(lam, (double)cnt)) * inv1);
+      const double Zl = L > lag ? -expm1((double)(L - lag) * p.log_lam) * inv1 : 0.0;
       zs = fma(1.0 - (double)lag / (1.0 + q), Zl, zs);
     }
     siz[j] = iz;
     scc[j] = 1.0 - 2.0 * zs * iz;
   }
+  cp_async_wait_all();
   __syncthreads();
   for (int k = tid; k < K; k += nt) {
-    double S = NW_LD(nm + k);
+    double S = S0;
     double R[QN], Pv[QN];
 #pragma unroll
-    for (int i = 0; i < QL; ++i) {
-      R[i] = NW_LD(nm + (1 + i) * K + k);
-      Pv[i] = NW_LD(nm + (1 + q + i) * K + k);
+    for (int i = 0; i < QL; ++i) { R[i] = R0[i]; Pv[i] = P0[i]; }
+    if (k != tid) {
+      S = NW_LD(nm + k);
+#pragma unroll
+      for (int i = 0; i < QL; ++i) {
+        R[i] = NW_LD(nm + (1 + i) * K + k);
+        Pv[i] = NW_LD(nm + (1 + q + i) * K + k);
+      }
     }
     for (int j = 0; j < len; ++j) {
       const int r = r0 + j;
@@ -288,32 +366,8 @@ __global__ void __launch_bounds__(NW_EMIT_THREADS) nw_emit(NwParams p) {
     }
   }
   __syncthreads();
-  // one 2 x 2 block of V per thread: rows a, a+1 and columns b, b+1 share their loads
-  const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  const int KB = (K + 1) >> 1;
-  // V is symmetric: only blocks on or above the block diagonal are computed (row-major enumeration of the
-  // upper triangle of the KB x KB block grid), each thread also stores the transpose of its block
-  const int e = blockIdx.y * nt + tid;
-  if (e < KB * (KB + 1) / 2) {
-    int ba = 0, rem = e;
-    while (rem >= KB - ba) { rem -= KB - ba; ++ba; }
-    const int a = 2 * ba, b = 2 * (ba + rem);
-    const int a1 = a + 1 < K ? a + 1 : a, b1 = b + 1 < K ? b + 1 : b;     // clamped partner (stores are guarded)
-    const bool aok = a + 1 < K, bok = b + 1 < K;
+  if (eact) {
     const bool keven = (K & 1) == 0 && (reinterpret_cast<uintptr_t>(p.cov) & 15) == 0;
-    const int ia[2] = {a, a1}, ib[2] = {b, b1};
-    double a0[2][2], bab[QN][2][2], bba[QN][2][2], wl[QN];
-#pragma unroll
-    for (int x = 0; x < 2; ++x)
-#pragma unroll
-      for (int y = 0; y < 2; ++y) {
-        a0[x][y] = NW_LD(ia[x] * K + ib[y]);
-#pragma unroll
-        for (int i = 0; i < QL; ++i) {
-          bab[i][x][y] = NW_LD((1 + i) * K * K + ia[x] * K + ib[y]);
-          bba[i][x][y] = NW_LD((1 + i) * K * K + ib[y] * K + ia[x]);
-        }
-      }
 #pragma unroll
     for (int i = 0; i < QL; ++i) wl[i] = 1.0 - (double)(i + 1) / (1.0 + q);
     const int jlo = max(0, p.t0 - r0), jhi = min(len, p.t1 - r0);   // dates of this chunk that are emitted
@@ -403,6 +457,16 @@ static int nw_launch_emit(bmfm_ctx* ctx, const NwParams& p, int nchunks_emit, si
   return BMFM_OK;
 }
 
+template <int QL>
+static int nw_launch_local(bmfm_ctx* ctx, const NwParams& p, size_t smem_local) {
+  if (smem_local > 48 * 1024)
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local<QL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
+  const int KB = (p.K + 1) / 2;
+  const int items = KB * KB + (1 + 2 * QL) * p.K + 1 + QL;
+  nw_chunk_local<QL><<<dim3(p.c_used, (items + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
+  return BMFM_OK;
+}
+
 // chunk totals + scan for a filled-in NwParams (C, nchunks, state, row0 and the date range set by the caller)
 static int nw_run_totals(bmfm_ctx* ctx, NwParams& p) {
   const int K = p.K, q = p.q;
@@ -416,10 +480,22 @@ static int nw_run_totals(bmfm_ctx* ctx, NwParams& p) {
   }
   if (c_last < p.c_first && p.n_peer == 0) return BMFM_OK;
   const int ns = nw_nstate(K, q);
+  p.fC = pow(p.lam, (double)p.C);
+  p.fLast = pow(p.lam, (double)(p.T - p.row0 - (p.nchunks - 1) * p.C));
+  {
+    const int per = (p.nchunks + NW_SCAN_GROUPS - 1) / NW_SCAN_GROUPS;      // chunks per scan part, as in nw_chunk_scan
+    p.fPer = pow(p.fC, (double)(per > 1 ? per : 1));
+  }
   if (p.c_used > 0) {
-    if (smem_local > 48 * 1024)
-      BMFM_CUDA(ctx, cudaFuncSetAttribute(nw_chunk_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_local));
-    nw_chunk_local<<<dim3(p.c_used, (ns + NW_LOCAL_THREADS - 1) / NW_LOCAL_THREADS), NW_LOCAL_THREADS, smem_local, ctx->stream>>>(p);
+    int rc = BMFM_E_UNSUPPORTED;
+    switch (q) {
+      case 0: rc = nw_launch_local<0>(ctx, p, smem_local); break;
+      case 1: rc = nw_launch_local<1>(ctx, p, smem_local); break;
+      case 2: rc = nw_launch_local<2>(ctx, p, smem_local); break;
+      case 3: rc = nw_launch_local<3>(ctx, p, smem_local); break;
+      case 4: rc = nw_launch_local<4>(ctx, p, smem_local); break;
+    }
+    if (rc) return rc;
     ctx->launches++;
   }
   nw_chunk_scan<<<(ns + 31) / 32, 32 * NW_SCAN_GROUPS, 0, ctx->stream>>>(p);
@@ -480,6 +556,7 @@ static int nw_launch(bmfm_ctx* ctx, int T, int K, int q, double tao, const doubl
   p.C = nw_pick_chunk(T, K, q, ctx->opt_nw_chunks);
   p.nchunks = (T + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
+  p.log_lam = log(p.lam);
   p.fr = fr; p.cov = cov; p.status = status; p.state = scratch;
   p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;
   if (t0 < 0) t0 = 0;
@@ -601,6 +678,7 @@ extern "C" int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int 
     }
   }
   p.lam = pow(0.5, 1.0 / tao);
+  p.log_lam = log(p.lam);
   p.fr = factor_ret; p.cov = cov; p.status = status;
   p.t0 = 0; p.t1 = T;
   p.row0 = 0; p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;
@@ -635,6 +713,7 @@ static int nw_shard_params(bmfm_ctx* ctx, NwParams& p, int T_total, int K, int q
   p.C = nw_pick_chunk(n > 0 ? n : 1, K, q);
   p.nchunks = (n + p.C - 1) / p.C;
   p.lam = pow(0.5, 1.0 / tao);
+  p.log_lam = log(p.lam);
   p.fr = fr_all; p.cov = nullptr; p.status = nullptr;
   p.row0 = t0; p.t0 = t0; p.t1 = t1;
   p.carry = nullptr; p.n_peer = 0; p.rank = 0; p.flags.n = 0;

@@ -214,6 +214,92 @@ __global__ void __launch_bounds__(1024) vr_scan_carry_kernel(int n, const double
   }
 }
 
+// Scan and scale in one launch: CTA b owns the dates [b D, (b+1) D).  lamb_t^2 is a ratio of two prefix sums, so the
+// CTA first adds the terms of all earlier dates (and, date-sharded, the totals of the earlier ranks) — a few loads
+// per thread from L2, all in flight together — then walks its own dates and streams their matrices.  This replaces
+// a one-CTA scan kernel (6 us at T = 2500, all other SMs idle) and the launch after it.
+constexpr int VR_FUSED_MAXD = 32;
+__global__ void __launch_bounds__(256) vr_scan_scale_kernel(int n, int KK, int D, const double* __restrict__ wb,
+                                                            const double* __restrict__ wv, const double* totals, int rank,
+                                                            BmfmFlagPeers fp, const double* cov, const int* cov_status,
+                                                            double* lamb, double* out) {
+  __shared__ double s_b[8], s_v[8], s_wb[VR_FUSED_MAXD], s_wv[VR_FUSED_MAXD], s_l2[VR_FUSED_MAXD];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int d0 = blockIdx.x * D, d1 = min(n, d0 + D);
+  if (fp.n > 0) {
+    if (tid == 0) bmfm_flag_wait(fp, BMFM_CH_VR);
+    __syncthreads();
+  }
+  double pb = 0.0, pv = 0.0;
+  if (tid < rank) { pb = __ldcg(totals + 2 * tid); pv = __ldcg(totals + 2 * tid + 1); }
+  for (int t = tid; t < d0; t += 1024) {
+    double xb[4], xv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int tt = t + 256 * j;
+      xb[j] = tt < d0 ? wb[tt] : 0.0;
+      xv[j] = tt < d0 ? wv[tt] : 0.0;
+    }
+    pb += (xb[0] + xb[1]) + (xb[2] + xb[3]);
+    pv += (xv[0] + xv[1]) + (xv[2] + xv[3]);
+  }
+  if (tid < d1 - d0) { s_wb[tid] = wb[d0 + tid]; s_wv[tid] = wv[d0 + tid]; }
+  pb = warp_sum(pb);
+  pv = warp_sum(pv);
+  if (lane == 0) { s_b[warp] = pb; s_v[warp] = pv; }
+  __syncthreads();
+  if (tid == 0) {
+    double rb = 0.0, rv = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { rb += s_b[w]; rv += s_v[w]; }
+    for (int j = 0; j < d1 - d0; ++j) {
+      rb += s_wb[j];
+      rv += s_wv[j];
+      const double l = rv > 0.0 ? sqrt(rb / rv) : 0.0;
+      lamb[d0 + j] = l;
+      s_l2[j] = l * l;
+    }
+  }
+  __syncthreads();
+  if (out == nullptr) return;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int t = d0; t < d1; ++t) {
+    const bool have = cov_status == nullptr || cov_status[t] == BMFM_ST_OK || cov_status[t] == BMFM_ST_PINV;
+    const double l2 = s_l2[t - d0];
+    const double* src = cov + (size_t)t * KK;
+    double* dst = out + (size_t)t * KK;
+    if ((KK & 1) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+      const double2* s2 = reinterpret_cast<const double2*>(src);
+      const int half = KK >> 1;
+      for (int base = tid; base < half; base += 1024) {
+        double2 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[j] = make_double2(nan, nan);
+          if (have && base + 256 * j < half) v[j] = __ldcs(s2 + base + 256 * j);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (base + 256 * j < half) {
+            if (have) { v[j].x *= l2; v[j].y *= l2; }
+            st_stream2(dst + 2 * (base + 256 * j), v[j].x, v[j].y);
+          }
+      }
+    } else {
+      for (int e = tid; e < KK; e += 256) st_stream(dst + e, have ? __ldcs(src + e) * l2 : nan);
+    }
+  }
+}
+
+// dates per CTA of vr_scan_scale_kernel: about eight CTAs per SM
+static inline int vr_fused_dates(const bmfm_ctx* ctx, int n) {
+  const int ctas = 8 * (ctx->sm_count > 0 ? ctx->sm_count : 148);
+  int D = (n + ctas - 1) / ctas;
+  if (D < 1) D = 1;
+  if (D > VR_FUSED_MAXD) D = VR_FUSED_MAXD;
+  return D;
+}
+
 }  // namespace bmfm
 
 using namespace bmfm;
@@ -234,10 +320,11 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
   nopeers.n = 0;
   vr_bias_kernel<<<(T * 32 + 255) / 256, 256, 0, ctx->stream>>>(T, K, tao, factor_ret, cov, cov_status, wb, wv, 0, T, nopeers);
   ctx->launches++;
-  vr_scan_kernel<<<1, 1024, 0, ctx->stream>>>(T, wb, wv, lamb);
-  ctx->launches++;
-  if (out_cov) {
-    vr_scale_kernel<<<T, 256, 0, ctx->stream>>>(T, K * K, cov, cov_status, lamb, out_cov);
+  {
+    const int D = vr_fused_dates(ctx, T);
+    BmfmFlagPeers noflags;
+    noflags.n = 0;
+    vr_scan_scale_kernel<<<(T + D - 1) / D, 256, 0, ctx->stream>>>(T, K * K, D, wb, wv, nullptr, 0, noflags, cov, cov_status, lamb, out_cov);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());
@@ -347,10 +434,10 @@ extern "C" int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const do
   if (n == 0) return BMFM_OK;
   BMFM_ARG(ctx, wb && wv && totals && lamb_block, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  vr_scan_carry_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, totals, rank, lamb_block, bmfm_flag_peers(ctx, rank, 0));
-  ctx->launches++;
-  if (out_cov_block) {
-    vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_block, out_cov_block);
+  {
+    const int D = vr_fused_dates(ctx, n);
+    vr_scan_scale_kernel<<<(n + D - 1) / D, 256, 0, ctx->stream>>>(n, K * K, D, wb, wv, totals, rank, bmfm_flag_peers(ctx, rank, 0),
+                                                                  cov_block, cov_status_block, lamb_block, out_cov_block);
     ctx->launches++;
   }
   BMFM_CUDA(ctx, cudaGetLastError());
