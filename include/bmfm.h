@@ -212,6 +212,13 @@ int bmfm_newey_west_by_time_noalloc(bmfm_ctx* ctx, int T, int K, int q, double t
 int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double tao, const double* factor_ret,
                                 const double* cov, const int32_t* cov_status, double* out_cov,
                                 double* lamb);
+/* Dates [t0, t1) of the same adjustment (MFM.py:149-163) when the dates before t0 went through earlier calls with
+ * the same wb / wv ([T] doubles each, device, kept by the caller between the calls; no need to clear them): what
+ * bmfm_risk_step_host uses to adjust each block of dates as soon as its covariances exist.  All pointers address
+ * the full series; calling it for consecutive blocks that cover [0, T) gives the rows of the call above. */
+int bmfm_vol_regime_adj_range(bmfm_ctx* ctx, int T, int t0, int t1, int K, double tao, const double* factor_ret,
+                              const double* cov, const int32_t* cov_status, double* wb, double* wv,
+                              double* out_cov, double* lamb);
 /* The same pass split for date-sharded runs (MFM.py:149-163): _bias gives this rank's block
  * (n dates from global date t0 of T_total) of weighted bias terms wb = w_t B_t^2, wv = w_t; the
  * caller gathers them over ranks in date order; _scale turns the gathered terms into lamb_all

@@ -55,6 +55,7 @@ _SIGNATURES = {
     "bmfm_vol_regime_shard_scale": ([_P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P], _I),
     "bmfm_newey_west_by_time_noalloc": ([_P, _I, _I, _I, _D, _P, _P, _P], _I),
     "bmfm_vol_regime_adj_by_time": ([_P, _I, _I, _D, _P, _P, _P, _P, _P], _I),
+    "bmfm_vol_regime_adj_range": ([_P, _I, _I, _I, _I, _D, _P, _P, _P, _P, _P, _P, _P], _I),
     "bmfm_gauss_cov": ([_P, _I, _I, _I, _I, _P], _I),
     "bmfm_eigen_decompose": ([_P, _I, _I, _P, _P, _P, _P, _P], _I),
     "bmfm_eigen_mc_accumulate": ([_P, _I, _I, _I, _P, _P, _P, _P, _I], _I),
@@ -280,6 +281,11 @@ class Context:
     def vol_regime_adj_by_time(self, T, K, tao, fr, cov, cov_status, out_cov, lamb):
         self.check(self._L.bmfm_vol_regime_adj_by_time(self._h, T, K, float(tao), ptr(fr), ptr(cov),
                                                        ptr(cov_status), ptr(out_cov), ptr(lamb)))
+
+    def vol_regime_adj_range(self, T, t0, t1, K, tao, fr, cov, cov_status, wb, wv, out_cov, lamb):
+        """Dates [t0, t1) of vol_regime_adj_by_time; wb / wv [T] persist between the calls (full-series pointers)."""
+        self.check(self._L.bmfm_vol_regime_adj_range(self._h, T, t0, t1, K, float(tao), ptr(fr), ptr(cov),
+                                                     ptr(cov_status), ptr(wb), ptr(wv), ptr(out_cov), ptr(lamb)))
 
     def eigenfactor_bias_stat(self, T, K, predlen, cov, cov_status, fr, bias_stat, b_out=None):
         self.check(self._L.bmfm_eigenfactor_bias_stat(self._h, T, K, int(predlen), ptr(cov), ptr(cov_status), ptr(fr),

@@ -221,6 +221,7 @@ extern "C" int bmfm_risk_step_host(bmfm_ctx* ctx, int T, int P, int Q, const int
   DEVBUF(11, T * 4);
   DEVBUF(12, T * K * K * 8);
   DEVBUF(13, T * 8);
+  DEVBUF(9, 2 * T * 8);
   const int64_t* d_off = (const int64_t*)ctx->stage[0];
   double* d_cap = (double*)ctx->stage[1];
   double* d_ret = (double*)ctx->stage[2];
@@ -234,6 +235,7 @@ extern "C" int bmfm_risk_step_host(bmfm_ctx* ctx, int T, int P, int Q, const int
   int32_t* d_nwst = (int32_t*)ctx->stage[11];
   double* d_vr = (double*)ctx->stage[12];
   double* d_lamb = (double*)ctx->stage[13];
+  double* d_wb = (double*)ctx->stage[9];        // vol-regime bias terms of the dates done so far (wb | wv)
   cudaEvent_t* ev = ctx->pipe_ev;
   // whatever the compute stream still does with the staging buffers comes first
   BMFM_CUDA(ctx, cudaEventRecord(ev[39], ctx->stream));
@@ -256,25 +258,26 @@ extern "C" int bmfm_risk_step_host(bmfm_ctx* ctx, int T, int P, int Q, const int
     int rc = bmfm_reg_by_time(ctx, t1 - t0, P, Q, max_rows, d_off + t0, d_cap, d_ret, d_ind, d_style, d_fr + (size_t)t0 * K,
                               d_spec, d_r2 + t0, nullptr, d_st + t0);
     if (rc) return rc;
+    // the covariances of a date need only the factor returns up to it: Newey-West and the vol-regime adjustment of
+    // this block run now (the range forms re-reduce the earlier dates' moments, microseconds against the 200+ us a
+    // block takes to arrive), and the block's results leave while later blocks are still coming in
+    rc = bmfm_newey_west_by_time_range(ctx, T, (int)K, q, tao_nw, d_fr, t0, t1, d_nw + (size_t)t0 * K * K, d_nwst + t0);
+    if (rc) return rc;
+    rc = bmfm_vol_regime_adj_range(ctx, T, t0, t1, (int)K, tao_vr, d_fr, d_nw, d_nwst, d_wb, d_wb + T, d_vr, d_lamb);
+    if (rc) return rc;
     BMFM_CUDA(ctx, cudaEventRecord(ev[16 + c], ctx->stream));
     BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[16 + c], 0));
     if (r1 > r0)
       BMFM_CUDA(ctx, cudaMemcpyAsync(specific_ret + r0, d_spec + r0, (r1 - r0) * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+    if (t1 > t0) {
+      BMFM_CUDA(ctx, cudaMemcpyAsync(nw_cov + (size_t)t0 * K * K, d_nw + (size_t)t0 * K * K, (size_t)(t1 - t0) * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+      BMFM_CUDA(ctx, cudaMemcpyAsync(vr_cov + (size_t)t0 * K * K, d_vr + (size_t)t0 * K * K, (size_t)(t1 - t0) * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+    }
   }
   BMFM_CUDA(ctx, cudaMemcpyAsync(factor_ret, d_fr, T * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
   BMFM_CUDA(ctx, cudaMemcpyAsync(r2, d_r2, T * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
   BMFM_CUDA(ctx, cudaMemcpyAsync(status, d_st, T * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
-  int rc = bmfm_newey_west_by_time(ctx, T, (int)K, q, tao_nw, d_fr, d_nw, d_nwst);
-  if (rc) return rc;
-  BMFM_CUDA(ctx, cudaEventRecord(ev[32], ctx->stream));
-  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[32], 0));
-  BMFM_CUDA(ctx, cudaMemcpyAsync(nw_cov, d_nw, T * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
   BMFM_CUDA(ctx, cudaMemcpyAsync(nw_status, d_nwst, T * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
-  rc = bmfm_vol_regime_adj_by_time(ctx, T, (int)K, tao_vr, d_fr, d_nw, d_nwst, d_vr, d_lamb);
-  if (rc) return rc;
-  BMFM_CUDA(ctx, cudaEventRecord(ev[33], ctx->stream));
-  BMFM_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ev[33], 0));
-  BMFM_CUDA(ctx, cudaMemcpyAsync(vr_cov, d_vr, T * K * K * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
   BMFM_CUDA(ctx, cudaMemcpyAsync(lamb, d_lamb, T * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
   BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
   BMFM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -219,13 +219,13 @@ __global__ void __launch_bounds__(1024) vr_scan_carry_kernel(int n, const double
 // per thread from L2, all in flight together — then walks its own dates and streams their matrices.  This replaces
 // a one-CTA scan kernel (6 us at T = 2500, all other SMs idle) and the launch after it.
 constexpr int VR_FUSED_MAXD = 32;
-__global__ void __launch_bounds__(256) vr_scan_scale_kernel(int n, int KK, int D, const double* __restrict__ wb,
+__global__ void __launch_bounds__(256) vr_scan_scale_kernel(int t_first, int n, int KK, int D, const double* __restrict__ wb,
                                                             const double* __restrict__ wv, const double* totals, int rank,
                                                             BmfmFlagPeers fp, const double* cov, const int* cov_status,
                                                             double* lamb, double* out) {
   __shared__ double s_b[8], s_v[8], s_wb[VR_FUSED_MAXD], s_wv[VR_FUSED_MAXD], s_l2[VR_FUSED_MAXD];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int d0 = blockIdx.x * D, d1 = min(n, d0 + D);
+  const int d0 = t_first + blockIdx.x * D, d1 = min(n, d0 + D);      // dates [t_first, n) of the arrays are this launch's
   if (fp.n > 0) {
     if (tid == 0) bmfm_flag_wait(fp, BMFM_CH_VR);
     __syncthreads();
@@ -324,9 +324,35 @@ extern "C" int bmfm_vol_regime_adj_by_time(bmfm_ctx* ctx, int T, int K, double t
     const int D = vr_fused_dates(ctx, T);
     BmfmFlagPeers noflags;
     noflags.n = 0;
-    vr_scan_scale_kernel<<<(T + D - 1) / D, 256, 0, ctx->stream>>>(T, K * K, D, wb, wv, nullptr, 0, noflags, cov, cov_status, lamb, out_cov);
+    vr_scan_scale_kernel<<<(T + D - 1) / D, 256, 0, ctx->stream>>>(0, T, K * K, D, wb, wv, nullptr, 0, noflags, cov, cov_status, lamb, out_cov);
     ctx->launches++;
   }
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// Dates [t0, t1) of a series of T dates whose earlier dates were already processed by calls of this function with
+// the same wb / wv arrays ([T] each, device, kept by the caller between the calls): the pipelined host entry point
+// adjusts each block of dates as soon as its covariances exist.  All pointers address the FULL series.
+extern "C" int bmfm_vol_regime_adj_range(bmfm_ctx* ctx, int T, int t0, int t1, int K, double tao, const double* factor_ret,
+                                         const double* cov, const int32_t* cov_status, double* wb, double* wv,
+                                         double* out_cov, double* lamb) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && t0 >= 0 && t1 >= t0 && t1 <= T && K > 0 && tao > 0, "bad sizes");
+  if (t1 == t0) return BMFM_OK;
+  BMFM_ARG(ctx, factor_ret && cov && wb && wv && lamb, "NULL pointer");
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int n = t1 - t0;
+  VrPeers nopeers;
+  nopeers.n = 0;
+  vr_bias_kernel<<<(n * 32 + 255) / 256, 256, 0, ctx->stream>>>(n, K, tao, factor_ret + (size_t)t0 * K, cov + (size_t)t0 * K * K,
+                                                              cov_status ? cov_status + t0 : nullptr, wb + t0, wv + t0, t0, T, nopeers);
+  ctx->launches++;
+  const int D = vr_fused_dates(ctx, n);
+  BmfmFlagPeers noflags;
+  noflags.n = 0;
+  vr_scan_scale_kernel<<<(n + D - 1) / D, 256, 0, ctx->stream>>>(t0, t1, K * K, D, wb, wv, nullptr, 0, noflags, cov, cov_status, lamb, out_cov);
+  ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;
 }
@@ -436,7 +462,7 @@ extern "C" int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const do
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
   {
     const int D = vr_fused_dates(ctx, n);
-    vr_scan_scale_kernel<<<(n + D - 1) / D, 256, 0, ctx->stream>>>(n, K * K, D, wb, wv, totals, rank, bmfm_flag_peers(ctx, rank, 0),
+    vr_scan_scale_kernel<<<(n + D - 1) / D, 256, 0, ctx->stream>>>(0, n, K * K, D, wb, wv, totals, rank, bmfm_flag_peers(ctx, rank, 0),
                                                                   cov_block, cov_status_block, lamb_block, out_cov_block);
     ctx->launches++;
   }

@@ -491,3 +491,38 @@ def test_vol_regime_negative_variance_poisons_later_dates(ops):
     assert np.isnan(lamb[25:]).all() and np.isfinite(lamb[:25]).all()
     assert relerr(lamb, np.array(wl)) < TOL
     assert relerr(out[10], wv[10]) < TOL and np.isnan(out[30]).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,K,cuts", [(97, 6, (0, 1, 40, 41, 97)), (300, 42, (0, 128, 300)), (50, 5, (0, 50))])
+def test_vol_regime_range_blocks_equal_whole_series(ops, T, K, cuts):
+    """bmfm_vol_regime_adj_range over consecutive blocks of dates (what the pipelined host step calls) gives the rows
+    of the whole-series call; one date without a covariance in the middle."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.synth import make_factor_returns
+    from oracle import barra_oracle as orc
+    fr = make_factor_returns(T, K, seed=11)
+    covs, st = ops.newey_west_by_time(fr, 1, 30.0)
+    st = st.copy()
+    st[T // 2] = 1                                     # an empty DataFrame in the reference
+    want_cov, want_l = orc.vol_regime_adj_by_time(fr, [covs[t] if st[t] == 0 else None for t in range(T)], 12.0)
+    ctx = _cabi.default_context()
+    dv = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_fr, d_cov, d_st = dv(fr), dv(covs), dv(st.astype(np.int32))
+    wb = torch.full((T,), float("nan"), dtype=torch.float64, device="cuda")     # nothing has to be cleared
+    wv = torch.full((T,), float("nan"), dtype=torch.float64, device="cuda")
+    out = torch.empty_like(d_cov)
+    lamb = torch.empty(T, dtype=torch.float64, device="cuda")
+    for t0, t1 in zip(cuts[:-1], cuts[1:]):
+        ctx.vol_regime_adj_range(T, t0, t1, K, 12.0, d_fr, d_cov, d_st, wb, wv, out, lamb)
+    torch.cuda.synchronize()
+    whole_cov, whole_l = ops.vol_regime_adj_by_time(fr, covs, st.astype(np.int32), 12.0)
+    got_l, got = lamb.cpu().numpy(), out.cpu().numpy()
+    assert record(f"vol_regime.range.lamb.T{T}", relerr(got_l, np.array(want_l))) < TOL
+    assert relerr(got_l, whole_l) < 1e-14
+    for t in range(T):
+        if st[t] == 0 and np.isfinite(covs[t]).all():
+            assert relerr(got[t], want_cov[t]) < TOL
+        else:
+            assert np.isnan(got[t]).all()
