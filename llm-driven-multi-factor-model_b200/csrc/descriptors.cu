@@ -120,54 +120,65 @@ __global__ void __launch_bounds__(128) ew_window_kernel(int L, int S, int W, int
 }
 
 // CMRA: ln(1 + max Z) - ln(1 + min Z), Z = exp(cumsum(log_ret over the window)) - 1, all W rows present.
-// = max - min of the running sum over the window (the window's start offset cancels).  Sliding
-// max/min by the block decomposition of van Herk / Gil-Werman: a thread owns (stock, block of W
-// rows); it needs the suffix extrema of the previous block (kept in thread-local arrays, all
-// threads index them uniformly) and the running prefix extrema of its own block.
+// = max - min of the running sum over the window (any common offset cancels).  Sliding max/min by the block
+// decomposition of van Herk / Gil-Werman: a thread owns (stock, block of W rows); with the running sum measured
+// from the END of the previous block, it needs the suffix extrema of the previous block (one backward pass over
+// it: R_j = -(sum of the rows after j), kept in thread-local arrays that all threads index uniformly) and the
+// running prefix extrema of its own block.  Loads are taken eight rows at a time so that they overlap.
+constexpr int CMRA_U = 8;
 __global__ void __launch_bounds__(128) cmra_kernel(int L, int S, int W, const double* log_ret, double* out) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= S) return;
   const int b = blockIdx.y;
   const int r0 = b * W, r1 = min(L, r0 + W);
+  const double qn = qnan();
   double smax[CMRA_MAX_WINDOW], smin[CMRA_MAX_WINDOW];
-  // relative running sum P starts at the first row of the previous block; NaN rows add 0 and are remembered
-  int lastnan = -1;          // largest row index with NaN seen so far (>= p0), -1 if none
-  double Pend = 0.0;         // P at the end of the previous block
+  int lastnan = -1;          // largest row index with NaN seen so far (>= r0 - W), -1 if none
   if (b > 0) {
     const int p0 = r0 - W;
-    double P = 0.0;
-    for (int j = 0; j < W; ++j) {
-      const double v = log_ret[(size_t)(p0 + j) * S + s];
-      if (isnan(v)) lastnan = p0 + j; else P += v;
-      smax[j] = P;           // P_j, overwritten below by the suffix extrema
-    }
-    Pend = P;
-    double mx = -INFINITY, mn = INFINITY;
-    for (int j = W - 1; j >= 0; --j) {
-      const double Pj = smax[j];
-      mx = fmax(mx, Pj);
-      mn = fmin(mn, Pj);
-      smax[j] = mx;
-      smin[j] = mn;
+    double Q = 0.0, mx = -INFINITY, mn = INFINITY;     // Q: sum of the rows after j
+    for (int jb = W - 1; jb >= 0; jb -= CMRA_U) {
+      double v[CMRA_U];
+#pragma unroll
+      for (int u = 0; u < CMRA_U; ++u) v[u] = jb - u >= 0 ? log_ret[(size_t)(p0 + jb - u) * S + s] : qn;
+#pragma unroll
+      for (int u = 0; u < CMRA_U; ++u) {
+        const int j = jb - u;
+        if (j >= 0) {
+          mx = fmax(mx, -Q);
+          mn = fmin(mn, -Q);
+          smax[j] = mx;
+          smin[j] = mn;
+          if (isnan(v[u])) { if (lastnan < 0) lastnan = p0 + j; } else Q += v[u];
+        }
+      }
     }
   }
-  double P = Pend, pmax = -INFINITY, pmin = INFINITY;
-  for (int r = r0; r < r1; ++r) {
-    const double v = log_ret[(size_t)r * S + s];
-    if (isnan(v)) lastnan = r; else P += v;
-    pmax = fmax(pmax, P);
-    pmin = fmin(pmin, P);
-    const int ws = r - W + 1;          // first row of the window
-    double o = qnan();
-    if (ws >= 0 && lastnan < ws) {
-      double mx = pmax, mn = pmin;
-      if (ws < r0) {                   // the window reaches into the previous block
-        mx = fmax(mx, smax[ws - (r0 - W)]);
-        mn = fmin(mn, smin[ws - (r0 - W)]);
+  double P = 0.0, pmax = -INFINITY, pmin = INFINITY;
+  for (int rb = r0; rb < r1; rb += CMRA_U) {
+    double v[CMRA_U];
+#pragma unroll
+    for (int u = 0; u < CMRA_U; ++u) v[u] = rb + u < r1 ? log_ret[(size_t)(rb + u) * S + s] : qn;
+#pragma unroll
+    for (int u = 0; u < CMRA_U; ++u) {
+      const int r = rb + u;
+      if (r < r1) {
+        if (isnan(v[u])) lastnan = r; else P += v[u];
+        pmax = fmax(pmax, P);
+        pmin = fmin(pmin, P);
+        const int ws = r - W + 1;          // first row of the window
+        double o = qn;
+        if (ws >= 0 && lastnan < ws) {
+          double mx = pmax, mn = pmin;
+          if (ws < r0) {                   // the window reaches into the previous block
+            mx = fmax(mx, smax[ws - (r0 - W)]);
+            mn = fmin(mn, smin[ws - (r0 - W)]);
+          }
+          o = mx - mn;
+        }
+        st_stream(out + (size_t)r * S + s, o);
       }
-      o = mx - mn;
     }
-    st_stream(out + (size_t)r * S + s, o);
   }
 }
 

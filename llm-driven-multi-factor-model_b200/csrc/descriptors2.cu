@@ -22,32 +22,57 @@ __device__ __forceinline__ double qnan2() { return __longlong_as_double(0x7ff800
 // oldest row has weight 1 (factor_calculator.py:137-144: weights_arr[:len(window)]); NaN rows are dropped with
 // their weights; NaN unless >= minp valid rows.  The normalisation cancels any common factor of the weights,
 // so a chunk uses decay^(row - a0) with a0 = first row of the chunk's first window.
+// Rows are taken eight at a time: the sixteen loads of a batch (entering and leaving rows) are issued before the
+// serial updates, so a thread keeps 128 B in flight instead of 16 B (one thread per stock and chunk is ~75 000
+// threads at 5000 x 3750: a single load each does not cover the memory latency).
+constexpr int DESC2_U = 8;
 __global__ void __launch_bounds__(128) rstr_kernel(int L, int S, int W, int lag, int minp, double decay,
                                                    const double* x, double* out) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= S) return;
   const int r0 = blockIdx.y * DESC2_CHUNK, r1 = min(L, r0 + DESC2_CHUNK);
   const int a0 = max(0, r0 - W + 1);
+  const double qn = qnan2();
   double num = 0.0, den = 0.0;
   int cnt = 0;
   double wadd = 1.0;                       // decay^(row - a0) of the row being added
-  for (int r = a0; r < r0; ++r) {          // rows of the first window that precede the chunk
-    const double v = r >= lag ? x[(size_t)(r - lag) * S + s] : qnan2();
-    if (!isnan(v)) { num = fma(wadd, v, num); den += wadd; ++cnt; }
-    wadd *= decay;
+  for (int rb = a0; rb < r0; rb += DESC2_U) {     // rows of the first window that precede the chunk
+    double v[DESC2_U];
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      const int r = rb + j;
+      v[j] = (r < r0 && r >= lag) ? x[(size_t)(r - lag) * S + s] : qn;
+    }
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      if (rb + j < r0) {
+        if (!isnan(v[j])) { num = fma(wadd, v[j], num); den += wadd; ++cnt; }
+        wadd *= decay;
+      }
+    }
   }
   double wrem = 1.0;                       // decay^(row - a0) of the row being removed
-  for (int r = r0; r < r1; ++r) {
-    const double v = r >= lag ? x[(size_t)(r - lag) * S + s] : qnan2();
-    if (!isnan(v)) { num = fma(wadd, v, num); den += wadd; ++cnt; }
-    wadd *= decay;
-    const int gone = r - W;                // row that left the window
-    if (gone >= a0) {
-      const double u = gone >= lag ? x[(size_t)(gone - lag) * S + s] : qnan2();
-      if (!isnan(u)) { num = fma(-wrem, u, num); den -= wrem; --cnt; }
-      wrem *= decay;
+  for (int rb = r0; rb < r1; rb += DESC2_U) {
+    double v[DESC2_U], u[DESC2_U];
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      const int r = rb + j, gone = r - W;  // gone: row that left the window
+      v[j] = (r < r1 && r >= lag) ? x[(size_t)(r - lag) * S + s] : qn;
+      u[j] = (r < r1 && gone >= a0 && gone >= lag) ? x[(size_t)(gone - lag) * S + s] : qn;
     }
-    st_stream(out + (size_t)r * S + s, cnt >= minp ? num / den : qnan2());
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      const int r = rb + j;
+      if (r < r1) {
+        if (!isnan(v[j])) { num = fma(wadd, v[j], num); den += wadd; ++cnt; }
+        wadd *= decay;
+        if (r - W >= a0) {
+          if (!isnan(u[j])) { num = fma(-wrem, u[j], num); den -= wrem; --cnt; }
+          wrem *= decay;
+        }
+        st_stream(out + (size_t)r * S + s, cnt >= minp ? num / den : qn);
+      }
+    }
   }
 }
 
@@ -87,33 +112,54 @@ __global__ void __launch_bounds__(128) roll_logsum3_kernel(int L, int S, Roll3 q
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= S) return;
   const int r0 = blockIdx.y * DESC2_CHUNK, r1 = min(L, r0 + DESC2_CHUNK);
+  const double qn = qnan2();
   double sum[3] = {0.0, 0.0, 0.0};
   int cnt[3] = {0, 0, 0}, nnz[3] = {0, 0, 0}, a0[3];
 #pragma unroll
   for (int w = 0; w < 3; ++w) a0[w] = max(0, r0 - q.W[w] + 1);
   const int amin = min(a0[0], min(a0[1], a0[2]));
-  for (int r = amin; r < r0; ++r) {
-    const double v = x[(size_t)r * S + s] / divisor;
-    if (!isnan(v)) {
+  for (int rb = amin; rb < r0; rb += DESC2_U) {
+    double v[DESC2_U];
 #pragma unroll
-      for (int w = 0; w < 3; ++w)
-        if (r >= a0[w]) { sum[w] += v; ++cnt[w]; nnz[w] += v != 0.0; }
+    for (int j = 0; j < DESC2_U; ++j) v[j] = rb + j < r0 ? x[(size_t)(rb + j) * S + s] : qn;
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      const double vv = v[j] / divisor;
+      if (!isnan(vv)) {
+#pragma unroll
+        for (int w = 0; w < 3; ++w)
+          if (rb + j >= a0[w]) { sum[w] += vv; ++cnt[w]; nnz[w] += vv != 0.0; }
+      }
     }
   }
-  for (int r = r0; r < r1; ++r) {
-    const double v = x[(size_t)r * S + s] / divisor;
-    const bool vok = !isnan(v);
+  for (int rb = r0; rb < r1; rb += DESC2_U) {
+    double v[DESC2_U], u[3][DESC2_U];
 #pragma unroll
-    for (int w = 0; w < 3; ++w) {
-      if (vok) { sum[w] += v; ++cnt[w]; nnz[w] += v != 0.0; }
-      const int gone = r - q.W[w];
-      if (gone >= a0[w]) {
-        const double u = x[(size_t)gone * S + s] / divisor;
-        if (!isnan(u)) { sum[w] -= u; --cnt[w]; nnz[w] -= u != 0.0; }
+    for (int j = 0; j < DESC2_U; ++j) {
+      const int r = rb + j;
+      v[j] = r < r1 ? x[(size_t)r * S + s] : qn;
+#pragma unroll
+      for (int w = 0; w < 3; ++w) {
+        const int gone = r - q.W[w];
+        u[w][j] = (r < r1 && gone >= a0[w]) ? x[(size_t)gone * S + s] : qn;
       }
-      double o = qnan2();
-      if (cnt[w] >= q.minp[w] && nnz[w] > 0 && sum[w] != 0.0) o = log(sum[w]);
-      st_stream(q.out[w] + (size_t)r * S + s, o);
+    }
+#pragma unroll
+    for (int j = 0; j < DESC2_U; ++j) {
+      const int r = rb + j;
+      if (r < r1) {
+        const double vv = v[j] / divisor;
+        const bool vok = !isnan(vv);
+#pragma unroll
+        for (int w = 0; w < 3; ++w) {
+          if (vok) { sum[w] += vv; ++cnt[w]; nnz[w] += vv != 0.0; }
+          const double uu = u[w][j] / divisor;       // NaN when nothing leaves (r - W before the first window)
+          if (!isnan(uu)) { sum[w] -= uu; --cnt[w]; nnz[w] -= uu != 0.0; }
+          double o = qn;
+          if (cnt[w] >= q.minp[w] && nnz[w] > 0 && sum[w] != 0.0) o = log(sum[w]);
+          st_stream(q.out[w] + (size_t)r * S + s, o);
+        }
+      }
     }
   }
 }

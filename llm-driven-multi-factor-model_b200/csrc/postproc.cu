@@ -85,127 +85,205 @@ struct OrthoParams {
   double* out;
 };
 
-// tiny symmetric eigen-solver (cyclic Jacobi, one thread): pinv solve of G c = b, numpy cutoff
-__device__ void pinv_solve_small(int m, double* G, double* b, double* c) {
-  double V[(PP_MAX_K + 1) * (PP_MAX_K + 1)];
-  for (int i = 0; i < m; ++i)
-    for (int j = 0; j < m; ++j) V[i * m + j] = i == j ? 1.0 : 0.0;
+// tiny symmetric eigen-solver (cyclic Jacobi, one thread): pinv solve of G c = b, numpy cutoff.  M is a template
+// parameter so that every index is a compile-time constant after unrolling and the matrices live in registers.
+template <int M>
+__device__ __forceinline__ void pinv_solve_small(double (&G)[M * M], const double (&b)[M], double (&c)[M]) {
+  double V[M * M];
+#pragma unroll
+  for (int i = 0; i < M; ++i)
+#pragma unroll
+    for (int j = 0; j < M; ++j) V[i * M + j] = i == j ? 1.0 : 0.0;
   for (int sweep = 0; sweep < 30; ++sweep) {
     int rot = 0;
-    for (int p = 0; p < m - 1; ++p)
-      for (int q = p + 1; q < m; ++q) {
-        const double apq = G[p * m + q], app = G[p * m + p], aqq = G[q * m + q];
+#pragma unroll
+    for (int p = 0; p < M - 1; ++p)
+#pragma unroll
+      for (int q = p + 1; q < M; ++q) {
+        const double apq = G[p * M + q], app = G[p * M + p], aqq = G[q * M + q];
         if (fabs(apq) > 1.1102230246251565e-16 * sqrt(fabs(app * aqq)) && fabs(apq) > 1e-290) {
           rot++;
           const double tau = (aqq - app) / (2.0 * apq);
           const double tt = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
           const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = tt * cs;
-          for (int k2 = 0; k2 < m; ++k2) {
-            const double gkp = G[k2 * m + p], gkq = G[k2 * m + q];
-            G[k2 * m + p] = cs * gkp - sn * gkq;
-            G[k2 * m + q] = sn * gkp + cs * gkq;
-            const double vkp = V[k2 * m + p], vkq = V[k2 * m + q];
-            V[k2 * m + p] = cs * vkp - sn * vkq;
-            V[k2 * m + q] = sn * vkp + cs * vkq;
+#pragma unroll
+          for (int k2 = 0; k2 < M; ++k2) {
+            const double gkp = G[k2 * M + p], gkq = G[k2 * M + q];
+            G[k2 * M + p] = cs * gkp - sn * gkq;
+            G[k2 * M + q] = sn * gkp + cs * gkq;
+            const double vkp = V[k2 * M + p], vkq = V[k2 * M + q];
+            V[k2 * M + p] = cs * vkp - sn * vkq;
+            V[k2 * M + q] = sn * vkp + cs * vkq;
           }
-          for (int k2 = 0; k2 < m; ++k2) {
-            const double gpk = G[p * m + k2], gqk = G[q * m + k2];
-            G[p * m + k2] = cs * gpk - sn * gqk;
-            G[q * m + k2] = sn * gpk + cs * gqk;
+#pragma unroll
+          for (int k2 = 0; k2 < M; ++k2) {
+            const double gpk = G[p * M + k2], gqk = G[q * M + k2];
+            G[p * M + k2] = cs * gpk - sn * gqk;
+            G[q * M + k2] = sn * gpk + cs * gqk;
           }
         }
       }
     if (!rot) break;
   }
   double mx = 0.0;
-  for (int i = 0; i < m; ++i) mx = fmax(mx, fabs(G[i * m + i]));
-  for (int i = 0; i < m; ++i) c[i] = 0.0;
-  for (int e = 0; e < m; ++e) {
-    const double lam = G[e * m + e];
+#pragma unroll
+  for (int i = 0; i < M; ++i) mx = fmax(mx, fabs(G[i * M + i]));
+#pragma unroll
+  for (int i = 0; i < M; ++i) c[i] = 0.0;
+#pragma unroll
+  for (int e = 0; e < M; ++e) {
+    const double lam = G[e * M + e];
     if (!(fabs(lam) > 1e-15 * mx)) continue;
     double dot = 0.0;
-    for (int i = 0; i < m; ++i) dot += V[i * m + e] * b[i];
-    for (int i = 0; i < m; ++i) c[i] += V[i * m + e] * dot / lam;
+#pragma unroll
+    for (int i = 0; i < M; ++i) dot += V[i * M + e] * b[i];
+#pragma unroll
+    for (int i = 0; i < M; ++i) c[i] += V[i * M + e] * dot / lam;
   }
 }
 
-// residual of y ~ 1 + X on complete-case rows, NaN elsewhere; all-NaN when n < k + 2 (:56)
+// residual of y ~ 1 + X on complete-case rows, NaN elsewhere; all-NaN when n < k + 2 (:56).  One CTA per date,
+// three passes over the date's rows (count / Gram / residuals): the first reads HBM, the other two hit L1/L2.
+// KX regressors at compile time (register arrays), all sums of a pass reduced together (two barriers).
+template <int KX>
 __global__ void __launch_bounds__(256) orthogonalize_kernel(OrthoParams p) {
-  __shared__ double s_red[32];
-  __shared__ double s_coef[PP_MAX_K + 2];
-  __shared__ double s_shift[PP_MAX_K + 1];
-  __shared__ int s_first;
-  const int k = p.k, m = k + 1;
+  constexpr int M = KX + 1, NG = M * (M + 1) / 2, NR = NG + M;
+  __shared__ double s_part[8][NR];
+  __shared__ double s_tot[NR];
+  __shared__ double s_coef[M];
+  __shared__ int s_cnt[8], s_fst[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const double nan = __longlong_as_double(0x7ff8000000000000LL);
   for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
     const long long a = p.date_off[t];
     const int n = (int)(p.date_off[t + 1] - a);
-    if (threadIdx.x == 0) s_first = n;
-    __syncthreads();
-    double cnt = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      bool ok = !isnan(p.y[a + i]);
-      for (int j = 0; j < k; ++j) ok = ok && !isnan(p.X[j][a + i]);
-      if (ok) { cnt += 1.0; atomicMin(&s_first, i); }
+    const double* y = p.y + a;
+    const double* X[KX];
+#pragma unroll
+    for (int j = 0; j < KX; ++j) X[j] = p.X[j] + a;
+    // pass 1: complete rows, and the first of them
+    int cnt = 0, first = n;
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4][M];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 256 * u;
+#pragma unroll
+        for (int j = 0; j < KX; ++j) v[u][j] = i < n ? X[j][i] : nan;
+        v[u][KX] = i < n ? y[i] : nan;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        bool ok = true;
+#pragma unroll
+        for (int j = 0; j < M; ++j) ok = ok && !isnan(v[u][j]);
+        if (ok) { cnt++; first = min(first, i0 + 256 * u); }
+      }
     }
-    cnt = block_sum(cnt, s_red);
-    if (cnt < (double)(k + 2)) {
-      for (int i = threadIdx.x; i < n; i += blockDim.x) p.out[a + i] = nan;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    first = __reduce_min_sync(0xffffffffu, first);
+    if (lane == 0) { s_cnt[warp] = cnt; s_fst[warp] = first; }
+    __syncthreads();
+    cnt = 0; first = n;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { cnt += s_cnt[w]; first = min(first, s_fst[w]); }
+    if (cnt < KX + 2) {
+      for (int i = tid; i < n; i += 256) p.out[a + i] = nan;
       __syncthreads();
       continue;
     }
     // shift every column by its first complete row: residuals are unchanged (intercept), conditioning improves
-    if (threadIdx.x < k) s_shift[threadIdx.x] = p.X[threadIdx.x][a + s_first];
-    if (threadIdx.x == k) s_shift[k] = p.y[a + s_first];
-    __syncthreads();
-    // Gram of [1, X - shift] and right-hand side, upper triangle accumulated per thread
-    double g[(PP_MAX_K + 1) * (PP_MAX_K + 2) / 2];
-    double rb[PP_MAX_K + 1];
-    for (int e = 0; e < m * (m + 1) / 2; ++e) g[e] = 0.0;
-    for (int e = 0; e < m; ++e) rb[e] = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      double row[PP_MAX_K + 1];
-      row[0] = 1.0;
-      const double yy = p.y[a + i] - s_shift[k];
-      bool ok = !isnan(yy);
-      for (int j = 0; j < k; ++j) { row[1 + j] = p.X[j][a + i] - s_shift[j]; ok = ok && !isnan(row[1 + j]); }
-      if (!ok) continue;
-      int e = 0;
-      for (int r = 0; r < m; ++r) {
-        for (int c = r; c < m; ++c) { g[e] = fma(row[r], row[c], g[e]); ++e; }
-        rb[r] = fma(row[r], yy, rb[r]);
+    double sh[M];
+#pragma unroll
+    for (int j = 0; j < KX; ++j) sh[j] = X[j][first];
+    sh[KX] = y[first];
+    // pass 2: Gram of [1, X - shift] (upper triangle) and right-hand side
+    double acc[NR];
+#pragma unroll
+    for (int e = 0; e < NR; ++e) acc[e] = 0.0;
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4][M];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 256 * u;
+#pragma unroll
+        for (int j = 0; j < KX; ++j) v[u][j] = i < n ? X[j][i] : nan;
+        v[u][KX] = i < n ? y[i] : nan;
       }
-    }
-    __shared__ double s_G[(PP_MAX_K + 1) * (PP_MAX_K + 1)];
-    __shared__ double s_b[PP_MAX_K + 1];
-    {
-      int e = 0;
-      for (int r = 0; r < m; ++r)
-        for (int c = r; c < m; ++c) {
-          const double v = block_sum(g[e++], s_red);
-          if (threadIdx.x == 0) { s_G[r * m + c] = v; s_G[c * m + r] = v; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        double row[M];
+        row[0] = 1.0;
+        const double yy = v[u][KX] - sh[KX];
+        bool ok = !isnan(yy);
+#pragma unroll
+        for (int j = 0; j < KX; ++j) { row[1 + j] = v[u][j] - sh[j]; ok = ok && !isnan(row[1 + j]); }
+        if (ok) {
+          int e = 0;
+#pragma unroll
+          for (int r = 0; r < M; ++r) {
+#pragma unroll
+            for (int c = r; c < M; ++c) { acc[e] = fma(row[r], row[c], acc[e]); ++e; }
+            acc[NG + r] = fma(row[r], yy, acc[NG + r]);
+          }
         }
-      for (int r = 0; r < m; ++r) {
-        const double v = block_sum(rb[r], s_red);
-        if (threadIdx.x == 0) s_b[r] = v;
       }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double G[(PP_MAX_K + 1) * (PP_MAX_K + 1)], b[PP_MAX_K + 1], c[PP_MAX_K + 1];
-      for (int e = 0; e < m * m; ++e) G[e] = s_G[e];
-      for (int e = 0; e < m; ++e) b[e] = s_b[e];
-      pinv_solve_small(m, G, b, c);
-      for (int e = 0; e < m; ++e) s_coef[e] = c[e];
+#pragma unroll
+    for (int e = 0; e < NR; ++e) {
+      const double v = warp_sum(acc[e]);
+      if (lane == 0) s_part[warp][e] = v;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      double r = p.y[a + i] - s_shift[k] - s_coef[0];
-      for (int j = 0; j < k; ++j) r = fma(-s_coef[1 + j], p.X[j][a + i] - s_shift[j], r);
-      st_stream(p.out + a + i, r);    // NaN inputs propagate: incomplete rows come out NaN
+    if (tid < NR) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) v += s_part[w][tid];
+      s_tot[tid] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double G[M * M], b[M], c[M];
+      int e = 0;
+#pragma unroll
+      for (int r = 0; r < M; ++r)
+#pragma unroll
+        for (int cc = r; cc < M; ++cc) { const double v = s_tot[e++]; G[r * M + cc] = v; G[cc * M + r] = v; }
+#pragma unroll
+      for (int r = 0; r < M; ++r) b[r] = s_tot[NG + r];
+      pinv_solve_small<M>(G, b, c);
+#pragma unroll
+      for (int r = 0; r < M; ++r) s_coef[r] = c[r];
+    }
+    __syncthreads();
+    double cf[M];
+#pragma unroll
+    for (int r = 0; r < M; ++r) cf[r] = s_coef[r];
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4][M];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 256 * u;
+#pragma unroll
+        for (int j = 0; j < KX; ++j) v[u][j] = i < n ? X[j][i] : nan;
+        v[u][KX] = i < n ? y[i] : nan;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 256 * u;
+        double r = v[u][KX] - sh[KX] - cf[0];
+#pragma unroll
+        for (int j = 0; j < KX; ++j) r = fma(-cf[1 + j], v[u][j] - sh[j], r);
+        if (i < n) st_stream(p.out + a + i, r);    // NaN inputs propagate: incomplete rows come out NaN
+      }
     }
     __syncthreads();
   }
+}
+
+template <int KX>
+static void ortho_launch(bmfm_ctx* ctx, const OrthoParams& p, int grid) {
+  orthogonalize_kernel<KX><<<grid, 256, 0, ctx->stream>>>(p);
 }
 
 }  // namespace bmfm
@@ -262,7 +340,14 @@ extern "C" int bmfm_orthogonalize(bmfm_ctx* ctx, int T, const int64_t* date_off,
   p.y = y; p.out = out;
   for (int j = 0; j < k; ++j) p.X[j] = X[j];
   int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
-  orthogonalize_kernel<<<grid, 256, 0, ctx->stream>>>(p);
+  switch (k) {
+    case 1: ortho_launch<1>(ctx, p, grid); break;
+    case 2: ortho_launch<2>(ctx, p, grid); break;
+    case 3: ortho_launch<3>(ctx, p, grid); break;
+    case 4: ortho_launch<4>(ctx, p, grid); break;
+    case 5: ortho_launch<5>(ctx, p, grid); break;
+    default: ortho_launch<6>(ctx, p, grid); break;
+  }
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());
   return BMFM_OK;

@@ -50,7 +50,7 @@ __global__ void vr_bias_kernel(int T, int K, double tao, const double* fr, const
     // variance on the diagonal) is NaN there and poisons every later lamb
     double b2 = cnt > 0 ? sum / cnt : __longlong_as_double(0x7ff8000000000000LL);
     if (b2 < 0.0) b2 = __longlong_as_double(0x7ff8000000000000LL);
-    const double w = pow(0.5, (double)(T_total - 1 - (t_off + t)) / tao);
+    const double w = exp2(-(double)(T_total - 1 - (t_off + t)) / tao);      // 0.5^((T-1-t)/tao)
     // rows whose variance vector holds a NaN are excluded from both sums (MFM.py:158)
     const double ob = nanvar ? 0.0 : w * b2, ov = nanvar ? 0.0 : w;
     if (wb) { wb[t] = ob; wv[t] = ov; }
