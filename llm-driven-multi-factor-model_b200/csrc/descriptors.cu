@@ -25,21 +25,37 @@ namespace bmfm {
 constexpr int DESC_CHUNK = 256;      // rows per (stock, chunk) work item
 constexpr int DESC_MAX_WINDOW = 1024;
 constexpr int CMRA_MAX_WINDOW = 256;
+constexpr int EW_U = 4;              // steps of the EW window kernels whose loads are issued together
 
 __device__ __forceinline__ double qnan() { return __longlong_as_double(0x7ff8000000000000LL); }
 
 // ret = close / close.shift(1) - 1 ; log_ret = log(close) - log(close.shift(1))   (:50-51, pandas 3: no fill)
-__global__ void prepare_returns_kernel(int L, int S, const double* close, double* ret, double* log_ret) {
-  const size_t total = (size_t)L * S;
-  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-    double r = qnan(), lr = qnan();
-    if (e >= (size_t)S) {
-      const double c1 = close[e], c0 = close[e - S];
-      r = __dsub_rn(__ddiv_rn(c1, c0), 1.0);
-      lr = __dsub_rn(log(c1), log(c0));
+// A thread walks PR_ROWS consecutive rows of one stock, so each log(close) is computed once and used for two rows
+// (the logs are most of this kernel's instructions); stocks are the fast index, every access stays coalesced.
+constexpr int PR_ROWS = 8;
+__global__ void __launch_bounds__(256) prepare_returns_kernel(int L, int S, const double* close, double* ret, double* log_ret) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  const int r0 = blockIdx.y * PR_ROWS;
+  double c[PR_ROWS + 1];
+  c[0] = r0 > 0 ? close[(size_t)(r0 - 1) * S + s] : qnan();
+#pragma unroll
+  for (int j = 0; j < PR_ROWS; ++j) c[j + 1] = r0 + j < L ? close[(size_t)(r0 + j) * S + s] : qnan();
+  double lprev = log_ret ? log(c[0]) : 0.0;
+#pragma unroll
+  for (int j = 0; j < PR_ROWS; ++j) {
+    const int r = r0 + j;
+    if (r < L) {
+      double rr = qnan(), lr = qnan();
+      const double lcur = log_ret ? log(c[j + 1]) : 0.0;
+      if (r > 0) {
+        rr = __dsub_rn(__ddiv_rn(c[j + 1], c[j]), 1.0);
+        lr = __dsub_rn(lcur, lprev);
+      }
+      lprev = lcur;
+      if (ret) st_stream(ret + (size_t)r * S + s, rr);
+      if (log_ret) st_stream(log_ret + (size_t)r * S + s, lr);
     }
-    if (ret) ret[e] = r;
-    if (log_ret) log_ret[e] = lr;
   }
 }
 
@@ -57,64 +73,72 @@ __global__ void __launch_bounds__(128) ew_window_kernel(int L, int S, int W, int
   const int s0 = max(0, r0 - W);        // warm-up start: the window of row r0-1 is rows [s0, r0)
   double Sw = 0, Sx = 0, Sy = 0, Sxx = 0, Sxy = 0, Syy = 0;
   int n = 0;
-  // the four values of a step (arriving row, leaving row) do not depend on the running sums: they are
-  // fetched one step ahead so that their latency overlaps the arithmetic of the current step
+  // the four values of a step (arriving row, leaving row) do not depend on the running sums: the loads of
+  // EW_U steps are issued together, ahead of the serial updates (one thread per stock and chunk cannot cover
+  // the memory latency with a single step's loads in flight)
   const double qn = qnan();
-  double y_nx = ret[(size_t)s0 * S + s], x_nx = mkt[(size_t)s0 * S + s], yl_nx = qn, xl_nx = qn;
-  for (int r = s0; r < r1; ++r) {
-    const double y = y_nx, x = x_nx, yl = yl_nx, xl = xl_nx;
-    if (r + 1 < r1) {
-      y_nx = ret[(size_t)(r + 1) * S + s];
-      x_nx = mkt[(size_t)(r + 1) * S + s];
-      const int rn = r + 1 - W;
-      yl_nx = rn >= s0 ? ret[(size_t)rn * S + s] : qn;
-      xl_nx = rn >= s0 ? mkt[(size_t)rn * S + s] : qn;
+  for (int rb = s0; rb < r1; rb += EW_U) {
+    double yb[EW_U], xb[EW_U], ylb[EW_U], xlb[EW_U];
+#pragma unroll
+    for (int j = 0; j < EW_U; ++j) {
+      const int r = rb + j, rl = r - W;
+      const bool in = r < r1, lv = in && rl >= s0;
+      yb[j] = in ? ret[(size_t)r * S + s] : qn;
+      xb[j] = in ? mkt[(size_t)r * S + s] : qn;
+      ylb[j] = lv ? ret[(size_t)rl * S + s] : qn;
+      xlb[j] = lv ? mkt[(size_t)rl * S + s] : qn;
     }
-    const int rl = r - W;
-    if (rl >= s0) {
-      // the oldest row of the previous window leaves; among n valid rows it had rank n-1
-      if (!isnan(yl) && !isnan(xl)) {
-        const double wg = pw[n - 1];
-        if (MODE == 0) {
-          Sw -= wg; Sx = fma(-wg, xl, Sx); Sy = fma(-wg, yl, Sy);
-          Sxx = fma(-wg * xl, xl, Sxx); Sxy = fma(-wg * xl, yl, Sxy); Syy = fma(-wg * yl, yl, Syy);
-        } else {
-          const double e = yl - xl;
-          Sw -= wg; Sx = fma(-wg, e, Sx); Sxx = fma(-wg * e, e, Sxx);
-        }
-        n -= 1;
-      }
-    }
-    if (!isnan(y) && !isnan(x)) {
-      if (MODE == 0) {
-        Sw = fma(Sw, lam, 1.0); Sx = fma(Sx, lam, x); Sy = fma(Sy, lam, y);
-        Sxx = fma(Sxx, lam, x * x); Sxy = fma(Sxy, lam, x * y); Syy = fma(Syy, lam, y * y);
-      } else {
-        const double e = y - x;
-        Sw = fma(Sw, lam, 1.0); Sx = fma(Sx, lam, e); Sxx = fma(Sxx, lam, e * e);
-      }
-      n += 1;
-    }
-    if (n == 0) { Sw = Sx = Sy = Sxx = Sxy = Syy = 0.0; }   // drop accumulated rounding when the window empties
-    if (r >= r0) {
-      double o0 = qnan(), o1 = qnan();
-      if (n >= minp) {
-        if (MODE == 0) {
-          // WLS of y on [1, x] with un-normalised weights (:96-102); HSIGMA = sqrt(sum w e^2 / (n - 2))
-          const double det = Sw * Sxx - Sx * Sx;
-          const double beta = (Sw * Sxy - Sx * Sy) / det;
-          const double alpha = (Sy - beta * Sx) / Sw;
-          const double sse = Syy - alpha * Sy - beta * Sxy;
-          o0 = beta;
-          o1 = sqrt(fmax(sse, 0.0) / (double)(n - 2));
-        } else {
-          // normalised weights: sqrt(sum w (x - mu)^2), mu = sum w x (:173-180)
-          const double mu = Sx / Sw;
-          o0 = sqrt(fmax(Sxx / Sw - mu * mu, 0.0));
+#pragma unroll
+    for (int j = 0; j < EW_U; ++j) {
+      const int r = rb + j;
+      if (r >= r1) break;
+      const double y = yb[j], x = xb[j], yl = ylb[j], xl = xlb[j];
+      const int rl = r - W;
+      if (rl >= s0) {
+        // the oldest row of the previous window leaves; among n valid rows it had rank n-1
+        if (!isnan(yl) && !isnan(xl)) {
+          const double wg = pw[n - 1];
+          if (MODE == 0) {
+            Sw -= wg; Sx = fma(-wg, xl, Sx); Sy = fma(-wg, yl, Sy);
+            Sxx = fma(-wg * xl, xl, Sxx); Sxy = fma(-wg * xl, yl, Sxy); Syy = fma(-wg * yl, yl, Syy);
+          } else {
+            const double e = yl - xl;
+            Sw -= wg; Sx = fma(-wg, e, Sx); Sxx = fma(-wg * e, e, Sxx);
+          }
+          n -= 1;
         }
       }
-      st_stream(out0 + (size_t)r * S + s, o0);
-      if (MODE == 0) st_stream(out1 + (size_t)r * S + s, o1);
+      if (!isnan(y) && !isnan(x)) {
+        if (MODE == 0) {
+          Sw = fma(Sw, lam, 1.0); Sx = fma(Sx, lam, x); Sy = fma(Sy, lam, y);
+          Sxx = fma(Sxx, lam, x * x); Sxy = fma(Sxy, lam, x * y); Syy = fma(Syy, lam, y * y);
+        } else {
+          const double e = y - x;
+          Sw = fma(Sw, lam, 1.0); Sx = fma(Sx, lam, e); Sxx = fma(Sxx, lam, e * e);
+        }
+        n += 1;
+      }
+      if (n == 0) { Sw = Sx = Sy = Sxx = Sxy = Syy = 0.0; }   // drop accumulated rounding when the window empties
+      if (r >= r0) {
+        double o0 = qnan(), o1 = qnan();
+        if (n >= minp) {
+          if (MODE == 0) {
+            // WLS of y on [1, x] with un-normalised weights (:96-102); HSIGMA = sqrt(sum w e^2 / (n - 2))
+            const double det = Sw * Sxx - Sx * Sx;
+            const double beta = (Sw * Sxy - Sx * Sy) / det;
+            const double alpha = (Sy - beta * Sx) / Sw;
+            const double sse = Syy - alpha * Sy - beta * Sxy;
+            o0 = beta;
+            o1 = sqrt(fmax(sse, 0.0) / (double)(n - 2));
+          } else {
+            // normalised weights: sqrt(sum w (x - mu)^2), mu = sum w x (:173-180)
+            const double mu = Sx / Sw;
+            o0 = sqrt(fmax(Sxx / Sw - mu * mu, 0.0));
+          }
+        }
+        st_stream(out0 + (size_t)r * S + s, o0);
+        if (MODE == 0) st_stream(out1 + (size_t)r * S + s, o1);
+      }
     }
   }
 }
@@ -191,8 +215,7 @@ extern "C" int bmfm_prepare_returns(bmfm_ctx* ctx, int L, int S, const double* c
   BMFM_ARG(ctx, L >= 0 && S >= 0 && close && (ret || log_ret), "bad arguments");
   if (L == 0 || S == 0) return BMFM_OK;
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  const size_t total = (size_t)L * S;
-  int grid = (int)((total + 255) / 256 < (size_t)ctx->sm_count * 16 ? (total + 255) / 256 : (size_t)ctx->sm_count * 16);
+  const dim3 grid((S + 255) / 256, (L + PR_ROWS - 1) / PR_ROWS);
   prepare_returns_kernel<<<grid, 256, 0, ctx->stream>>>(L, S, close, ret, log_ret);
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());

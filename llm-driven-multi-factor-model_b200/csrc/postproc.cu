@@ -15,44 +15,67 @@ namespace bmfm {
 constexpr int PP_MAX_K = 6;       // regressors in orthogonalize (reference uses 1 and 2)
 constexpr int PP_MAX_COMP = 8;    // components of a composite
 
-__device__ __forceinline__ double block_sum(double v, double* s_red) {
-  v = warp_sum(v);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  __syncthreads();
-  if (lane == 0) s_red[warp] = v;
-  __syncthreads();
-  double t = 0.0;
-  for (int w = 0; w < nw; ++w) t += s_red[w];
-  return t;
-}
-
-// clip to mean +- n_std * std; pandas semantics: NaN skipped, ddof = 1, NaN bounds leave values alone
+// clip to mean +- n_std * std; pandas semantics: NaN skipped, ddof = 1, NaN bounds leave values alone.
+// Three passes over the date's rows (sum and count / squared deviations / clip): the first reads HBM, the others
+// hit L1/L2; loads four at a time, the two sums of the first pass reduced together.
 __global__ void __launch_bounds__(256) winsorize_kernel(int T, const long long* date_off, const double* x,
                                                         double n_std, double* out) {
-  __shared__ double s_red[32];
+  __shared__ double s_a[8], s_b[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
   for (int t = blockIdx.x; t < T; t += gridDim.x) {
     const long long a = date_off[t];
     const int n = (int)(date_off[t + 1] - a);
+    const double* xs = x + a;
     double s = 0.0, c = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const double v = x[a + i];
-      if (!isnan(v)) { s += v; c += 1.0; }
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = i0 + 256 * u < n ? xs[i0 + 256 * u] : nan;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (!isnan(v[u])) { s += v[u]; c += 1.0; }
     }
-    s = block_sum(s, s_red);
-    c = block_sum(c, s_red);
+    s = warp_sum(s);
+    c = warp_sum(c);
+    if (lane == 0) { s_a[warp] = s; s_b[warp] = c; }
+    __syncthreads();
+    s = 0.0; c = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { s += s_a[w]; c += s_b[w]; }
+    __syncthreads();
     const double mean = s / c;
     double q = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const double v = x[a + i];
-      if (!isnan(v)) { const double d = mean - v; q = fma(d, d, q); }
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = i0 + 256 * u < n ? xs[i0 + 256 * u] : nan;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (!isnan(v[u])) { const double d = mean - v[u]; q = fma(d, d, q); }
     }
-    q = block_sum(q, s_red);
-    const double sd = c > 1.0 ? sqrt(q / (c - 1.0)) : __longlong_as_double(0x7ff8000000000000LL);
+    q = warp_sum(q);
+    if (lane == 0) s_a[warp] = q;
+    __syncthreads();
+    q = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q += s_a[w];
+    __syncthreads();
+    const double sd = c > 1.0 ? sqrt(q / (c - 1.0)) : nan;
     const double lo = mean - n_std * sd, hi = mean + n_std * sd;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      double v = x[a + i];
-      if (!isnan(v) && !isnan(lo) && !isnan(hi)) v = fmin(fmax(v, lo), hi);
-      st_stream(out + a + i, v);
+    const bool clip = !isnan(lo) && !isnan(hi);
+    for (int i0 = tid; i0 < n; i0 += 4 * 256) {
+      double v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = i0 + 256 * u < n ? xs[i0 + 256 * u] : nan;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (i0 + 256 * u < n) {
+          double w = v[u];
+          if (!isnan(w) && clip) w = fmin(fmax(w, lo), hi);
+          st_stream(out + a + i0 + 256 * u, w);
+        }
+      }
     }
   }
 }
