@@ -414,6 +414,8 @@ def run_gpu(args):
     gs = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(gs)
     ctx = _cabi.Context(local_rank, stream=gs.cuda_stream)
+    if os.environ.get("BENCH_VR_SPLIT"):                  # comparison switch: separate vol-regime scan and scale launches
+        ctx.set_option("vr_split", int(os.environ["BENCH_VR_SPLIT"]))
     nocoll = os.environ.get("BENCH_NO_COLL") == "1"     # timing experiment only (results are wrong)
     use_graph = os.environ.get("BENCH_GRAPH", "1") == "1"     # one captured step replayed (BENCH_GRAPH=0: eager launches)
 
@@ -582,7 +584,10 @@ def run_gpu(args):
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=gs):
                 step_body()
-            graph.replay()
+            # untimed replays on top of the W eager warm-up steps: the first replays of a fresh graph (and the first
+            # back-to-back use of the peer mappings) were seen to run several times slower than the steady state
+            for _ in range(max(args.warmup, 10)):
+                graph.replay()
             barrier()
         except Exception as e:      # noqa: BLE001
             log(f"CUDA graph capture failed ({e!r}); timing eager steps")

@@ -27,7 +27,7 @@ struct bmfm_ctx {
   int flag_rank, n_flag_peers;
   long long* peer_flags[8];
   // per-context experiment switches (bmfm_ctx_set_option); 0 / negative = library default
-  int opt_reg_mode, opt_reg_smma, opt_reg_warps, opt_reg_ctas, opt_nw_chunks, opt_eig_mode, opt_eig_fail_every, opt_eig_c_blocks, opt_reg_static;
+  int opt_reg_mode, opt_reg_smma, opt_reg_warps, opt_reg_ctas, opt_nw_chunks, opt_eig_mode, opt_eig_fail_every, opt_eig_c_blocks, opt_reg_static, opt_vr_split;
   int last_reg_mode;   // kernel form the last bmfm_reg_by_time call launched (bmfm_ctx_get_option "last_reg_mode")
   char err[512];
 };

@@ -29,6 +29,7 @@ static int* bmfm_opt_slot(bmfm_ctx* c, const char* name) {
   if (!strcmp(name, "reg_warps")) return &c->opt_reg_warps;
   if (!strcmp(name, "reg_ctas")) return &c->opt_reg_ctas;
   if (!strcmp(name, "reg_static")) return &c->opt_reg_static;
+  if (!strcmp(name, "vr_split")) return &c->opt_vr_split;
   if (!strcmp(name, "nw_chunks")) return &c->opt_nw_chunks;
   if (!strcmp(name, "eig_mode")) return &c->opt_eig_mode;
   if (!strcmp(name, "eig_fail_every")) return &c->opt_eig_fail_every;

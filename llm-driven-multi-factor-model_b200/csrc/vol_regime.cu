@@ -460,7 +460,14 @@ extern "C" int bmfm_vol_regime_shard_scale(bmfm_ctx* ctx, int n, int K, const do
   if (n == 0) return BMFM_OK;
   BMFM_ARG(ctx, wb && wv && totals && lamb_block, "NULL pointer");
   BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
-  {
+  if (ctx->opt_vr_split) {       // the separate scan and scale launches (comparison switch)
+    vr_scan_carry_kernel<<<1, 1024, 0, ctx->stream>>>(n, wb, wv, totals, rank, lamb_block, bmfm_flag_peers(ctx, rank, 0));
+    ctx->launches++;
+    if (out_cov_block) {
+      vr_scale_kernel<<<n, 256, 0, ctx->stream>>>(n, K * K, cov_block, cov_status_block, lamb_block, out_cov_block);
+      ctx->launches++;
+    }
+  } else {
     const int D = vr_fused_dates(ctx, n);
     vr_scan_scale_kernel<<<(n + D - 1) / D, 256, 0, ctx->stream>>>(0, n, K * K, D, wb, wv, totals, rank, bmfm_flag_peers(ctx, rank, 0),
                                                                   cov_block, cov_status_block, lamb_block, out_cov_block);
