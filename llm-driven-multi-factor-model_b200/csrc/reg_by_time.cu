@@ -1192,6 +1192,7 @@ __global__ void __launch_bounds__(RS_WARPS * 32, RS_CTAS) reg_stream_kernel(RegP
 }
 
 #include "reg_mma.cuh"
+#include "reg_bulk.cuh"
 
 // ---- host side ---------------------------------------------------------------------------------
 template <int Q, int NSTAGE, int WPD>
@@ -1225,6 +1226,28 @@ static int launch_reg_mma(bmfm_ctx* ctx, const RegParams& p) {
   return BMFM_OK;
 }
 
+// the bulk-copy form (reg_mode 6): four warps per date, even Q in 8..10 (others fall back to reg_mode 4)
+template <int Q>
+static int launch_reg_bulk(bmfm_ctx* ctx, const RegParams& p) {
+  if constexpr (Q % 2 == 0 && rm_has_s(Q)) {
+    constexpr int NS = 2;
+    const int smem_s = rb_cta_bytes<Q, NS>(p.P);
+    BMFM_CUDA(ctx, cudaFuncSetAttribute(reg_bulk_kernel<Q, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
+    int per_sm = (228 * 1024) / (smem_s + 1024);
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 4) per_sm = 4;
+    if (ctx->opt_reg_ctas > 0) per_sm = ctx->opt_reg_ctas;
+    int grid = ctx->sm_count * per_sm;
+    if (grid > p.T) grid = p.T;
+    reg_bulk_kernel<Q, NS><<<grid, RB_WARPS * 32, smem_s, ctx->stream>>>(p);
+    ctx->launches++;
+    BMFM_CUDA(ctx, cudaGetLastError());
+    return BMFM_OK;
+  } else {
+    return launch_reg_mma<Q, 2, RM_WARPS>(ctx, p);
+  }
+}
+
 template <int Q>
 static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   const int SMEM_MAX = ctx->max_smem_optin;           // 227 KB on B200
@@ -1250,7 +1273,7 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   // forces a kernel: 1 = CTA kernel with the date resident in shared memory, 2 = warp-per-date kernel with
   // register accumulators (the two earlier designs, kept for comparison).
   int mode = ctx->opt_reg_mode;
-  if (mode < 1 || mode > 5) {
+  if (mode < 1 || mode > 6) {
     int wpd = (max_rows > 0 && max_rows <= 1024) ? 1 : 2;
     const long long slots = (long long)ctx->sm_count * 12;      // warps the SMs hold with one warp per date
     // pass C re-reads a date when its solve is done: with one warp per date the dates in flight (slots x rows x
@@ -1266,9 +1289,10 @@ static int launch_reg(bmfm_ctx* ctx, RegParams p, int max_rows) {
   }
   const bool use_stream = mode == 2;
   ctx->last_reg_mode = p.all_dense ? 0 : mode;
-  if (!p.all_dense && mode >= 3 && mode <= 5) {
+  if (!p.all_dense && mode >= 3 && mode <= 6) {
     const int rc = mode == 3 ? launch_reg_mma<Q, 3, 1>(ctx, p)
-                 : mode == 5 ? launch_reg_mma<Q, 2, 2>(ctx, p) : launch_reg_mma<Q, 2, RM_WARPS>(ctx, p);
+                 : mode == 5 ? launch_reg_mma<Q, 2, 2>(ctx, p)
+                 : mode == 6 ? launch_reg_bulk<Q>(ctx, p) : launch_reg_mma<Q, 2, RM_WARPS>(ctx, p);
     if (rc != BMFM_OK) return rc;
   } else if (!p.all_dense && use_stream) {
     const RegSmem Lw = reg_smem_layout(0, p.P, Q, 1, false);

@@ -68,7 +68,7 @@ def test_short_series_status_not_error(env):
     assert (st.cpu().numpy() == _cabi.ST_SHORT).all() and bool(torch.isnan(cov).all())
 
 
-@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5"])
+@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5", "6"])
 def test_empty_date_inside_a_panel(env, mode, bmfm_option):
     """A date with no rows gets NaN factor returns and BMFM_ST_NONFINITE; its neighbours are unaffected."""
     torch, _cabi, ctx = env

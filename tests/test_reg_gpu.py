@@ -30,7 +30,7 @@ def _case(reg, case):
 
 @pytest.mark.parametrize("case", ["small", "csi", "nostyle_scale"])
 @pytest.mark.parametrize("grouped", [True, False])
-@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5"])     # 1: CTA-per-date kernel, 2: warp-per-date streaming kernel, 3: warp-per-date FP64-MMA kernel
+@pytest.mark.parametrize("mode", ["1", "2", "3", "4", "5", "6"])     # 1: CTA-per-date kernel, 2: warp-per-date streaming kernel, 3: warp-per-date FP64-MMA kernel
 def test_golden_reference_outputs(ops, reg_golden, case, grouped, mode, bmfm_option):
     bmfm_option("reg_mode", mode)
     g = _case(reg_golden, case)
@@ -87,7 +87,7 @@ def test_golden_exposure(ops, reg_golden, case):
     (3, 70, 63, 12, 0.0, (0, 0)),         # compiled limits; N < K -> pinv path
     (2, 5000, 31, 10, 0.02, (-2, 2)),     # full A-share cross-section (config C3): multi-tile path
 ])
-@pytest.mark.parametrize("mode", ["0", "1", "2", "3", "4", "5"])   # auto / CTA-per-date / warp-per-date streaming / warp-per-date FP64-MMA
+@pytest.mark.parametrize("mode", ["0", "1", "2", "3", "4", "5", "6"])   # auto / CTA-per-date / warp-per-date streaming / warp-per-date FP64-MMA
 def test_oracle_parity(ops, T, N, P, Q, ragged, scale, mode, bmfm_option):
     bmfm_option("reg_mode", mode)
     from bmfm.synth import make_panel
@@ -115,7 +115,7 @@ def test_oracle_parity(ops, T, N, P, Q, ragged, scale, mode, bmfm_option):
     (4, 1500, 12, 7),     # two warps per date
     (3, 333, 40, 8),      # more than 32 industries
 ])
-@pytest.mark.parametrize("mode", ["3", "4", "5"])
+@pytest.mark.parametrize("mode", ["3", "4", "5", "6"])
 def test_oracle_parity_rows_not_grouped(ops, T, N, P, Q, mode, bmfm_option):
     """The C-ABI accepts any row order inside a date; the packer's grouping by industry is an optimisation only."""
     bmfm_option("reg_mode", mode)
@@ -340,7 +340,7 @@ def test_fused_gather_entry_points_single_gpu(ops):
     assert wba.sum() == wb.sum()
 
 
-@pytest.mark.parametrize("mode", ["3", "4", "5"])
+@pytest.mark.parametrize("mode", ["3", "4", "5", "6"])
 def test_oracle_parity_shape_sweep(ops, mode, bmfm_option):
     """Odd and even style counts on both sides of the one-tile / two-tile split of the MMA kernel, industry
     counts around the 32-lane boundary, cross-sections shorter than a chunk, ragged dates (unaligned starts)."""

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Time the regression entry point alone on a synthetic panel of a given shape (CUDA events).
 
-    python tools/bench_reg.py N T [mode]        mode: the reg_mode context option (0 auto; 3 / 5 / 4 = FP64-MMA kernel with 1 / 2 / 4 warps per date;
+    python tools/bench_reg.py N T [mode]        mode: the reg_mode context option (0 auto; 3 / 5 / 4 = FP64-MMA kernel with 1 / 2 / 4 warps per date; 6 = 4 warps per date fed by cp.async.bulk;
                                                 1 CTA kernel, 2 register-Gram stream kernel: earlier designs)
     BENCH_UNGROUPED=1: rows not grouped by industry; BENCH_GATHER=n: the fused-gather entry point with n local "peers"
 """
