@@ -254,11 +254,62 @@ __global__ void __launch_bounds__(1024) bayes_shrink_kernel(BsParams p) {
       }
       gcode[j] = (signed char)g;
     }
-    if (G <= BS_GFAST) {
-      // group sums without atomics: every lane adds its rows into one register accumulator per group (predicated
-      // adds: the ~10 groups are hit by every row, shared-memory atomics on them are compare-and-swap loops that
-      // collide all the time), then a recursive-halving reduction inside the warp and one store per warp.  One
-      // sweep over the thread's rows per kind of sum keeps the accumulators at 16 registers pairs.
+    if (G <= BS_GFAST && G * nt <= p.npad) {
+      // group sums without atomics and without a predicated add per (row, group): every thread owns column tid of a
+      // [G][nt] table (the sort buffer, free by now; nt is a multiple of 32, so a warp's accesses never share a bank
+      // whatever the groups) and adds each of its rows into the row of its group — three instructions per row where
+      // one register accumulator per group costs two per (row, group).  The G column sums then go through the same
+      // recursive-halving reduction inside the warp and one store per warp.
+      double* col = s_sort + tid;
+#pragma unroll 1
+      for (int which = 0; which < 3; ++which) {
+        for (int k = 0; k < G; ++k) col[k * nt] = 0.0;
+#pragma unroll
+        for (int j = 0; j < BS_MAXR; ++j) {
+          const int i = tid + j * nt;
+          const int g = gcode[j];
+          if (i < n && g >= 0) {
+            const double c = p.cap[a + i];
+            const double x = which == 0 ? p.vol[a + i] * c : (which == 1 ? c : 1.0);
+            col[g * nt] += x;
+          }
+        }
+        double acc[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e] = e < G ? col[e * nt] : 0.0;
+        const double tot = bs_reduce_scatter16(acc, lane);
+        if ((lane & 1) == 0 && (lane >> 1) < G) my[4 * (lane >> 1) + which] = tot;
+      }
+      __syncthreads();
+      for (int e = tid; e < 4 * G; e += nt) {
+        if ((e & 3) == 3) continue;
+        double s2 = 0.0;
+        for (int w = 0; w < nwarps; ++w) s2 += s_wsum[(size_t)w * G * 4 + e];
+        s_gsum[e] = s2;
+      }
+      __syncthreads();
+      // dispersion about the group mean
+      {
+        for (int k = 0; k < G; ++k) col[k * nt] = 0.0;
+#pragma unroll
+        for (int j = 0; j < BS_MAXR; ++j) {
+          const int i = tid + j * nt;
+          const int g = gcode[j];
+          if (i < n && g >= 0) {
+            const double m = s_gsum[4 * g + 0] / s_gsum[4 * g + 1];
+            const double d = p.vol[a + i] - m;
+            col[g * nt] += d * d;
+          }
+        }
+        double acc[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e] = e < G ? col[e * nt] : 0.0;
+        const double tot = bs_reduce_scatter16(acc, lane);
+        if ((lane & 1) == 0 && (lane >> 1) < G) my[4 * (lane >> 1) + 3] = tot;
+      }
+    } else if (G <= BS_GFAST) {
+      // (short dates, where the sort buffer is smaller than the [G][nt] table) one register accumulator per group
+      // and predicated adds, one sweep over the thread's rows per kind of sum
 #pragma unroll 1
       for (int which = 0; which < 3; ++which) {
         double acc[16];

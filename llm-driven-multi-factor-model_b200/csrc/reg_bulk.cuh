@@ -11,8 +11,9 @@
 // Bulk copies need 16-byte aligned global addresses and sizes.  A date may start at any row, so the 8-byte
 // (cap, ret) and 4-byte (industry) columns are copied from the enclosing 16-byte aligned range and read with a
 // constant per-date shift; style rows are Q * 8 bytes, a multiple of 16 for even Q (the kernel is built for even
-// Q only).  The aligned range can reach up to 12 bytes past the last row of the whole panel, so the LAST date's
-// last super-chunk, and panels whose base pointers are not 16-byte aligned, go through plain loads instead.
+// Q only).  The aligned range can reach up to 12 bytes past the super-chunk's last row: a super-chunk whose range
+// would leave the panel (the last rows of the last dates), and panels whose base pointers are not 16-byte aligned,
+// go through plain loads instead.
 #pragma once
 
 constexpr int RB_WARPS = 4;
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(RB_WARPS * 32, 4) reg_bulk_kernel(RegParams p)
     const long long g0 = a + r0;
     unsigned char* st = ring + (size_t)s * SSB;
     const unsigned st_sa = ring_sa + s * SSB, mb = mbar_sa + 16 * s;
-    const bool bulk = aligned16 && (g0 + m < rows_total || (((g0 + m) & 3) == 0));
+    const bool bulk = aligned16 && ((g0 + m + 3) & ~3LL) <= rows_total;     // the aligned ranges stay inside the panel
     if (bulk) {
       if (tid == 0) {
         const long long c0 = g0 & ~1LL, c1 = (g0 + m + 1) & ~1LL;       // doubles, 16-byte aligned range
