@@ -7,9 +7,10 @@
 //   w_s     = 0.5^((T-1-s)/tao)
 //   lamb_t  = sqrt( sum_{s<=t, var_s valid} w_s B_s^2 / sum_{s<=t, var_s valid} w_s ), 0 when no valid row
 //   out_t   = cov_t * lamb_t^2
-// The reference's O(T^2) python loop is two prefix sums.  Three launches: per-date bias
-// statistic, one-CTA scan over dates, then a streaming scale of T*K*K doubles (HBM-bound:
-// 16 B per matrix element).
+// The reference's O(T^2) python loop is two prefix sums.  Two launches: the per-date bias
+// statistic, then one kernel in which every CTA first adds the terms of all earlier dates and then
+// streams its own dates' matrices (T*K*K doubles, HBM-bound: 16 B per matrix element).  The separate
+// one-CTA scan and scale kernels remain for the gathered multi-GPU form and as a comparison switch.
 #include <math.h>
 #include "bmfm_common.cuh"
 
