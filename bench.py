@@ -17,8 +17,8 @@ Further blocks of the same JSON line:
               scaling), one all-reduce of the T x K accumulators; sims/s and a roofline against the measured FP64 peak;
   "c3"        configs[2]: ONE 5000 x 3750 panel sharded by date over the ranks (strong scaling): regression +
               Bayesian shrinkage of a specific-risk estimate, dates/s and HBM fractions;
-  "c5"        configs[4]: descriptor build for 5000 stocks x 3750 days (returns, BETA/HSIGMA, DASTD, CMRA by stock;
-              winsorize, composite, orthogonalize by date; one all-to-all between them when N > 1), stock-days/s;
+  "c5"        configs[4]: descriptor build for 5000 stocks x 3750 days (returns, BETA/HSIGMA, DASTD, CMRA, then
+              winsorize, composite, orthogonalize; stocks sharded over the ranks, per-date moments all-reduced), stock-days/s;
   "df_to_df"  configs[0] ("C1", 300 x 1400, P = 28): DataFrame in, DataFrames out through the drop-in MFM class.
 
 One JSON line on stdout (rank 0).  --impl reference times the REFERENCE's own code (oracle/_ref: its mfm
@@ -846,17 +846,18 @@ def run_gpu(args):
         torch.cuda.empty_cache()
 
     # ---- config C5: descriptor build for 5000 stocks x 3750 days: daily returns, EWMA BETA/HSIGMA (252-day window,
-    #      63-day half-life), DASTD, CMRA on per-stock series (stocks sharded over the ranks), one all-to-all that
-    #      turns [days, my stocks] into [my days, all stocks], then winsorize x4, the volatility composite and its
-    #      orthogonalisation against BETA and SIZE per date (factor_calculator.py:79-234, post_processing.py:7-70) ----
+    #      63-day half-life), DASTD, CMRA on per-stock series, then winsorize x4, the volatility composite and its
+    #      orthogonalisation against BETA and SIZE per date (factor_calculator.py:79-234, post_processing.py:7-70).
+    #      STOCKS shard over the ranks for every stage: the [days][my stocks] panels of the rolling
+    #      kernels are already grouped by date, the cross-sectional stages all-reduce their per-date moments (four
+    #      small all-reduces per step) and no panel is transposed ----
     c5 = None
     if os.environ.get("BENCH_C5", "1") == "1":
         torch.cuda.empty_cache()
+        from bmfm.dist import winsorize_sharded, orthogonalize_sharded
         S5, L5 = C3_STOCKS, C3_DATES
         s_lo, s_hi = rank * S5 // world, (rank + 1) * S5 // world
         Sr = s_hi - s_lo
-        d_cut = [r * L5 // world for r in range(world + 1)]
-        Lr = d_cut[rank + 1] - d_cut[rank]
         g = torch.Generator(device=dev)
         g.manual_seed(20240005)                     # the market series is the same on every rank
         mret = 0.012 * torch.randn(L5, dtype=torch.float64, device=dev, generator=g)
@@ -866,17 +867,19 @@ def run_gpu(args):
         sret = sb[None, :] * torch.nan_to_num(mret)[:, None] + 0.02 * torch.randn((L5, Sr), dtype=torch.float64, device=dev, generator=g)
         d_close = (10.0 * torch.exp(torch.cumsum(torch.log1p(sret.clamp(-0.2, 0.2)), 0))).contiguous()
         d_mkt = mret[:, None].expand(L5, Sr).contiguous()
-        d_lcap = (15.0 + 1.5 * torch.randn(S5, dtype=torch.float64, device=dev, generator=g))[None, :].expand(Lr, S5).contiguous().reshape(-1)
+        d_lcap = (15.0 + 1.5 * torch.randn(Sr, dtype=torch.float64, device=dev, generator=g))[None, :].expand(L5, Sr).contiguous().reshape(-1)
         del sret
         d_ret, d_lr = torch.empty_like(d_close), torch.empty_like(d_close)
-        roll = [torch.empty_like(d_close) for _ in range(4)]            # BETA, HSIGMA, DASTD, CMRA as [days, my stocks]
-        recv = [torch.empty((world * Lr, Sr), dtype=torch.float64, device=dev) for _ in range(4)] if world > 1 else None
-        cols = [torch.empty(Lr * S5, dtype=torch.float64, device=dev) for _ in range(4)]     # [my days, all stocks]
-        wz = [torch.empty(Lr * S5, dtype=torch.float64, device=dev) for _ in range(4)]
-        d_vol, d_volo = torch.empty(Lr * S5, dtype=torch.float64, device=dev), torch.empty(Lr * S5, dtype=torch.float64, device=dev)
-        off5 = torch.arange(Lr + 1, dtype=torch.int64, device=dev) * S5
-        in_split = [d_cut[r + 1] - d_cut[r] for r in range(world)]
-        ev5 = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        roll = [torch.empty_like(d_close) for _ in range(4)]            # BETA, HSIGMA, DASTD, CMRA as [days][my stocks]
+        wz = [torch.empty(L5 * Sr, dtype=torch.float64, device=dev) for _ in range(4)]
+        d_vol, d_volo = torch.empty(L5 * Sr, dtype=torch.float64, device=dev), torch.empty(L5 * Sr, dtype=torch.float64, device=dev)
+        off5 = torch.arange(L5 + 1, dtype=torch.int64, device=dev) * Sr
+        ev5 = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        n_ar = [0]
+
+        def ar5(t):
+            n_ar[0] += 1
+            dist.all_reduce(t)
 
         def c5_step(timed=False):
             if timed:
@@ -887,21 +890,18 @@ def run_gpu(args):
             ctx.cmra(L5, Sr, d_lr, 252, roll[3])
             if timed:
                 ev5[1].record()
+            src = [r_.view(-1) for r_ in roll]
             if world > 1:
-                for j in range(4):
-                    dist.all_to_all_single(recv[j], roll[j], output_split_sizes=[Lr] * world, input_split_sizes=in_split)
-                    cols[j].view(Lr, world, Sr).copy_(recv[j].view(world, Lr, Sr).permute(1, 0, 2))
-                src = cols
+                winsorize_sharded(ctx, L5, off5, src, 2.5, wz, ar5)
+                ctx.composite(L5 * Sr, [wz[2], wz[3], wz[1]], [0.74, 0.16, 0.10], d_vol)
+                orthogonalize_sharded(ctx, L5, off5, d_vol, [wz[0], d_lcap], d_volo, ar5)
             else:
-                src = [r_.view(-1) for r_ in roll]
+                for j in range(4):
+                    ctx.winsorize(L5, off5, src[j], 2.5, wz[j])
+                ctx.composite(L5 * Sr, [wz[2], wz[3], wz[1]], [0.74, 0.16, 0.10], d_vol)
+                ctx.orthogonalize(L5, off5, d_vol, [wz[0], d_lcap], d_volo)
             if timed:
                 ev5[2].record()
-            for j in range(4):
-                ctx.winsorize(Lr, off5, src[j], 2.5, wz[j])
-            ctx.composite(Lr * S5, [wz[2], wz[3], wz[1]], [0.74, 0.16, 0.10], d_vol)
-            ctx.orthogonalize(Lr, off5, d_vol, [wz[0], d_lcap], d_volo)
-            if timed:
-                ev5[3].record()
 
         if S5 % world:
             c5 = {"skipped": f"{S5} stocks do not split evenly over {world} ranks"}
@@ -910,35 +910,39 @@ def run_gpu(args):
                 c5_step()
             barrier()
             n_c5 = max(3, min(args.steps, 10))
-            ph = np.zeros(3)
+            ph = np.zeros(2)
+            n_ar[0] = 0
             for _ in range(n_c5):
                 c5_step(timed=True)
                 torch.cuda.synchronize()
-                ph += [ev5[i].elapsed_time(ev5[i + 1]) for i in range(3)]
+                ph += [ev5[i].elapsed_time(ev5[i + 1]) for i in range(2)]
             barrier()
             tm = torch.tensor(list(ph / n_c5), dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-            r_ms, x_ms, p_ms = (float(x) for x in tm.tolist())
-            c5_ms = r_ms + x_ms + p_ms
-            fin = float(torch.isfinite(d_volo.view(Lr, S5)[-1]).double().mean().item())
+            r_ms, p_ms = (float(x) for x in tm.tolist())
+            c5_ms = r_ms + p_ms
+            fin = float(torch.isfinite(d_volo.view(L5, Sr)[-1]).double().mean().item())
             # algorithmic bytes per stock-day: returns 8 in + 16 out; BETA/HSIGMA 16 in + 16 out; DASTD 16 + 8; CMRA 8 + 8;
             # winsorize 4 x 16; composite 24 + 8; orthogonalize 24 + 8  (the market return is a [days, stocks] panel
             # in this ABI, read like a second input column)
             roll_bytes, post_bytes = 96, 128
             c5 = {"value": S5 * L5 / (c5_ms * 1e-3), "unit": "stock-days/s", "scaling": "strong", "ms_per_step": c5_ms,
-                  "config": f"C5: {S5} stocks x {L5} days generated on the device; prepare_returns + beta_hsigma(252, hl 63) + dastd + cmra "
-                            f"on [days, {Sr} stocks] per rank, "
-                            + ("one NCCL all-to-all per column to [days / ranks, all stocks], " if world > 1 else "")
-                            + "winsorize x4 + volatility composite + orthogonalize(volatility | BETA, SIZE) per date; "
-                            f"{L5 * S5 * 8 / 1e6:.0f} MB per column, larger than L2",
-                  "phase_ms": {"rolling": r_ms, "exchange": x_ms, "post_processing": p_ms},
+                  "config": f"C5: {S5} stocks x {L5} days generated on the device, {Sr} stocks per rank for every stage: "
+                            f"prepare_returns + beta_hsigma(252, hl 63) + dastd + cmra, then winsorize x4 + volatility "
+                            f"composite + orthogonalize(volatility | BETA, SIZE) per date"
+                            + (f" with the per-date moments all-reduced over the ranks ({n_ar[0] // n_c5} small NCCL "
+                               f"all-reduces per step, no transpose)" if world > 1 else "")
+                            + f"; {L5 * S5 * 8 / 1e6:.0f} MB per column, larger than L2",
+                  "phase_ms": {"rolling": r_ms, "post_processing": p_ms},
                   "rolling_roofline": {"kernel": "prepare_returns + beta_hsigma + dastd + cmra kernels", "bound": "hbm", "unit": "GB/s",
                                        "achieved": roll_bytes * L5 * Sr / (r_ms * 1e-3) / 1e9, "algorithmic_bytes_per_stock_day": roll_bytes},
-                  "post_roofline": {"kernel": "winsorize x4 + composite + orthogonalize kernels", "bound": "hbm", "unit": "GB/s",
-                                    "achieved": post_bytes * Lr * S5 / (p_ms * 1e-3) / 1e9, "algorithmic_bytes_per_stock_day": post_bytes},
+                  "post_roofline": {"kernel": "winsorize x4 + composite + orthogonalize kernels"
+                                              + (" (three passes each around the all-reduces)" if world > 1 else ""),
+                                    "bound": "hbm", "unit": "GB/s",
+                                    "achieved": post_bytes * L5 * Sr / (p_ms * 1e-3) / 1e9, "algorithmic_bytes_per_stock_day": post_bytes},
                   "finite_share_last_date": fin}
-        del d_close, d_mkt, d_ret, d_lr, roll, recv, cols, wz, d_vol, d_volo, d_lcap
+        del d_close, d_mkt, d_ret, d_lr, roll, wz, d_vol, d_volo, d_lcap
         torch.cuda.empty_cache()
 
     # ---- config C1, DataFrame in / DataFrames out through the drop-in MFM class (rank 0) ----

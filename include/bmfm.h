@@ -393,6 +393,28 @@ int bmfm_composite(bmfm_ctx* ctx, int64_t rows, int ncomp, const double* const* 
 int bmfm_orthogonalize(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* y, int k,
                        const double* const* X, double* out);
 
+/*
+ * The same two functions when the STOCKS of every date are sharded over ranks (no counterpart in the
+ * single-process reference).  A rank's table holds its own stocks of every date (date_off over its rows); each pass
+ * leaves per-date sums in a small array that the caller all-reduces (sum) over the ranks before the next pass:
+ *   winsorize:     _sums  -> sums [T][2] (sum of valid values, their number)            all-reduce
+ *                  _sqdev -> sqdev [T] = sum (mean_t - x)^2, mean_t = sum / number       all-reduce
+ *                  _apply with lo / hi [T] = mean -+ n_std sqrt(sqdev / (number - 1)) (NaN bounds: values unchanged)
+ *   orthogonalize: _pass 0 -> out [T][k + 2] (complete rows, sum X_1..X_k, sum y over them)            all-reduce
+ *                  _pass 1 -> out [T][(k+1)(k+2)/2 + k + 1]: upper triangle of the Gram of [1, X - shift_t] and the
+ *                             right-hand side with y - shift_t[k]; shift [T][k + 1] (the column means)   all-reduce
+ *                  _pass 2 -> out = this rank's residuals from the all-reduced gram and count [T] (doubles)
+ * (bmfm/dist.py: winsorize_sharded / orthogonalize_sharded drive them.)
+ */
+int bmfm_winsorize_sums(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, double* sums);
+int bmfm_winsorize_sqdev(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, const double* mean,
+                         double* sqdev);
+int bmfm_winsorize_apply(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, const double* lo,
+                         const double* hi, double* out);
+int bmfm_orthogonalize_pass(bmfm_ctx* ctx, int pass, int T, const int64_t* date_off, const double* y, int k,
+                            const double* const* X, const double* shift, const double* gram, const double* count,
+                            double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -77,6 +77,10 @@ _SIGNATURES = {
     "bmfm_winsorize": ([_P, _I, _P, _P, _D, _P], _I),
     "bmfm_composite": ([_P, C.c_int64, _I, _P, _P, _P], _I),
     "bmfm_orthogonalize": ([_P, _I, _P, _P, _I, _P, _P], _I),
+    "bmfm_winsorize_sums": ([_P, _I, _P, _P, _P], _I),
+    "bmfm_winsorize_sqdev": ([_P, _I, _P, _P, _P, _P], _I),
+    "bmfm_winsorize_apply": ([_P, _I, _P, _P, _P, _P, _P], _I),
+    "bmfm_orthogonalize_pass": ([_P, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P], _I),
 }
 
 
@@ -364,6 +368,22 @@ class Context:
         arr = (C.c_void_p * n)(*[t.data_ptr() for t in comps])
         w = (C.c_double * n)(*[float(x) for x in weights])
         self.check(self._L.bmfm_composite(self._h, rows, n, arr, w, ptr(out)))
+
+    def winsorize_sums(self, T, date_off, x, sums):
+        self.check(self._L.bmfm_winsorize_sums(self._h, T, ptr(date_off), ptr(x), ptr(sums)))
+
+    def winsorize_sqdev(self, T, date_off, x, mean, sqdev):
+        self.check(self._L.bmfm_winsorize_sqdev(self._h, T, ptr(date_off), ptr(x), ptr(mean), ptr(sqdev)))
+
+    def winsorize_apply(self, T, date_off, x, lo, hi, out):
+        self.check(self._L.bmfm_winsorize_apply(self._h, T, ptr(date_off), ptr(x), ptr(lo), ptr(hi), ptr(out)))
+
+    def orthogonalize_pass(self, which, T, date_off, y, Xs, out, shift=None, gram=None, count=None):
+        """Stock-sharded orthogonalize: pass 0 (sums), 1 (Gram about `shift`), 2 (residuals from gram / count)."""
+        k = len(Xs)
+        arr = (C.c_void_p * k)(*[t.data_ptr() for t in Xs])
+        self.check(self._L.bmfm_orthogonalize_pass(self._h, int(which), T, ptr(date_off), ptr(y), k, arr, ptr(shift),
+                                                   ptr(gram), ptr(count), ptr(out)))
 
     def orthogonalize(self, T, date_off, y, Xs, out):
         k = len(Xs)

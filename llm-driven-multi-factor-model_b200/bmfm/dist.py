@@ -264,3 +264,48 @@ def eigen_sharded_by_sims(backend, cov_all, status_all, T_sim, M, scale_coef, ra
     m_lo, m_hi = shard_range(M, rank, world)
     return backend.eigen(cov_all, status_all, T_sim, M, scale_coef, sim_range=(m_lo, m_hi),
                          allreduce=lambda t: all_reduce_sum(t, group))
+
+
+# ---- descriptors: stocks shard, per-date moments are all-reduced -------------------------------
+# The rolling kernels write [days][my stocks] panels, which already are "long tables grouped by date" with this rank's
+# stocks of every date, so the cross-sectional stages run on them in place: every pass leaves per-date sums (KB), one
+# all-reduce per pass makes them the sums over ALL stocks, the next pass uses them.  No bulk transpose of the panels.
+
+def winsorize_sharded(ctx, T, date_off, cols, n_std, outs, allreduce):
+    """winsorize_factors (post_processing.py:7-24) for several columns of a stock-sharded table at once:
+    two all-reduces in total (sums of all columns, then squared deviations of all columns)."""
+    import torch
+    nc, dev = len(cols), cols[0].device
+    sums = torch.empty((nc, T, 2), dtype=torch.float64, device=dev)
+    for i, x in enumerate(cols):
+        ctx.winsorize_sums(T, date_off, x, sums[i])
+    allreduce(sums)
+    cnt = sums[..., 1].contiguous()
+    mean = (sums[..., 0] / cnt).contiguous()
+    q = torch.empty((nc, T), dtype=torch.float64, device=dev)
+    for i, x in enumerate(cols):
+        ctx.winsorize_sqdev(T, date_off, x, mean[i], q[i])
+    allreduce(q)
+    nan = torch.full_like(q, float("nan"))
+    sd = torch.where(cnt > 1.0, torch.sqrt(q / (cnt - 1.0)), nan)        # pandas std, ddof = 1
+    lo, hi = (mean - n_std * sd).contiguous(), (mean + n_std * sd).contiguous()
+    for i, x in enumerate(cols):
+        ctx.winsorize_apply(T, date_off, x, lo[i], hi[i], outs[i])
+    return outs
+
+
+def orthogonalize_sharded(ctx, T, date_off, y, Xs, out, allreduce):
+    """orthogonalize_factors (post_processing.py:47-70) for one dependent column of a stock-sharded table: the
+    complete-row count and column sums, then the Gram about the column means — two all-reduces."""
+    import torch
+    k, dev = len(Xs), y.device
+    sums = torch.empty((T, k + 2), dtype=torch.float64, device=dev)
+    ctx.orthogonalize_pass(0, T, date_off, y, Xs, sums)
+    allreduce(sums)
+    count = sums[:, 0].contiguous()
+    shift = torch.nan_to_num(sums[:, 1:] / count[:, None]).contiguous()    # column means (0 where a date has no complete row)
+    gram = torch.empty((T, (k + 1) * (k + 2) // 2 + k + 1), dtype=torch.float64, device=dev)
+    ctx.orthogonalize_pass(1, T, date_off, y, Xs, gram, shift=shift)
+    allreduce(gram)
+    ctx.orthogonalize_pass(2, T, date_off, y, Xs, out, shift=shift, gram=gram, count=count)
+    return out

@@ -304,6 +304,189 @@ __global__ void __launch_bounds__(256) orthogonalize_kernel(OrthoParams p) {
   }
 }
 
+// ---- stock-sharded forms (descriptors shard by stock, per-date moments are all-reduced) -----------
+// A rank holds a block of STOCKS of every date (the [days][my stocks] panels the rolling kernels write are already
+// "grouped by date").  The per-date statistics then need every rank's rows: each pass below leaves its per-date sums
+// in a small array, the caller all-reduces it (KB), and the next pass uses the totals.  No bulk transpose.
+
+// pass 1 of winsorize: out[2 t] = sum of the valid values, out[2 t + 1] = their number
+__global__ void __launch_bounds__(256) winsorize_sums_kernel(int T, const long long* date_off, const double* x, double* out) {
+  __shared__ double s_a[8], s_b[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const long long a = date_off[t];
+    const int n = (int)(date_off[t + 1] - a);
+    double s = 0.0, c = 0.0;
+    for (int i = tid; i < n; i += 256) {
+      const double v = x[a + i];
+      if (!isnan(v)) { s += v; c += 1.0; }
+    }
+    s = warp_sum(s);
+    c = warp_sum(c);
+    if (lane == 0) { s_a[warp] = s; s_b[warp] = c; }
+    __syncthreads();
+    if (tid == 0) {
+      s = 0.0; c = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { s += s_a[w]; c += s_b[w]; }
+      out[2 * t] = s;
+      out[2 * t + 1] = c;
+    }
+    __syncthreads();
+  }
+}
+
+// pass 2: out[t] = sum over the valid values of (mean_t - x)^2
+__global__ void __launch_bounds__(256) winsorize_sqdev_kernel(int T, const long long* date_off, const double* x,
+                                                              const double* mean, double* out) {
+  __shared__ double s_a[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const long long a = date_off[t];
+    const int n = (int)(date_off[t + 1] - a);
+    const double m = mean[t];
+    double q = 0.0;
+    for (int i = tid; i < n; i += 256) {
+      const double v = x[a + i];
+      if (!isnan(v)) { const double d = m - v; q = fma(d, d, q); }
+    }
+    q = warp_sum(q);
+    if (lane == 0) s_a[warp] = q;
+    __syncthreads();
+    if (tid == 0) {
+      q = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) q += s_a[w];
+      out[t] = q;
+    }
+    __syncthreads();
+  }
+}
+
+// pass 3: clip to [lo_t, hi_t]; NaN bounds leave the values alone (as the single-GPU kernel)
+__global__ void __launch_bounds__(256) winsorize_apply_kernel(int T, const long long* date_off, const double* x,
+                                                              const double* lo, const double* hi, double* out) {
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const long long a = date_off[t];
+    const int n = (int)(date_off[t + 1] - a);
+    const double l = lo[t], h = hi[t];
+    const bool clip = !isnan(l) && !isnan(h);
+    for (int i = threadIdx.x; i < n; i += 256) {
+      double v = x[a + i];
+      if (!isnan(v) && clip) v = fmin(fmax(v, l), h);
+      st_stream(out + a + i, v);
+    }
+  }
+}
+
+// orthogonalize, pass 1 (MODE 0): out[t][0] = complete rows, out[t][1 + j] = sum of X_j, out[t][1 + KX] = sum of y over
+// them.  Pass 2 (MODE 1): Gram of [1, X - shift_t] (upper triangle) and right-hand side with y - shift_t[KX], NR sums.
+template <int KX, int MODE>
+__global__ void __launch_bounds__(256) ortho_sums_kernel(OrthoParams p, const double* shift, double* out) {
+  constexpr int M = KX + 1, NG = M * (M + 1) / 2;
+  constexpr int NR = MODE == 0 ? KX + 2 : NG + M;
+  __shared__ double s_part[8][NR];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    double sh[M];
+#pragma unroll
+    for (int j = 0; j < M; ++j) sh[j] = MODE == 1 ? shift[(size_t)t * M + j] : 0.0;
+    double acc[NR];
+#pragma unroll
+    for (int e = 0; e < NR; ++e) acc[e] = 0.0;
+    for (int i = tid; i < n; i += 256) {
+      double row[M];
+      row[0] = 1.0;
+      const double yy = p.y[a + i] - sh[KX];
+      bool ok = !isnan(yy);
+#pragma unroll
+      for (int j = 0; j < KX; ++j) { row[1 + j] = p.X[j][a + i] - sh[j]; ok = ok && !isnan(row[1 + j]); }
+      if (ok) {
+        if (MODE == 0) {
+          acc[0] += 1.0;
+#pragma unroll
+          for (int j = 0; j < KX; ++j) acc[1 + j] += row[1 + j];
+          acc[1 + KX] += yy;
+        } else {
+          int e = 0;
+#pragma unroll
+          for (int r = 0; r < M; ++r) {
+#pragma unroll
+            for (int c = r; c < M; ++c) { acc[e] = fma(row[r], row[c], acc[e]); ++e; }
+            acc[NG + r] = fma(row[r], yy, acc[NG + r]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < NR; ++e) {
+      const double v = warp_sum(acc[e]);
+      if (lane == 0) s_part[warp][e] = v;
+    }
+    __syncthreads();
+    if (tid < NR) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) v += s_part[w][tid];
+      out[(size_t)t * NR + tid] = v;
+    }
+    __syncthreads();
+  }
+}
+
+// pass 3: solve from the all-reduced Gram (every rank the same numbers) and write this rank's residuals
+template <int KX>
+__global__ void __launch_bounds__(256) ortho_apply_kernel(OrthoParams p, const double* shift, const double* gram,
+                                                          const double* count) {
+  constexpr int M = KX + 1, NG = M * (M + 1) / 2, NR = NG + M;
+  __shared__ double s_coef[M];
+  const int tid = threadIdx.x;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int t = blockIdx.x; t < p.T; t += gridDim.x) {
+    const long long a = p.date_off[t];
+    const int n = (int)(p.date_off[t + 1] - a);
+    if (count[t] < (double)(KX + 2)) {
+      for (int i = tid; i < n; i += 256) p.out[a + i] = nan;
+      continue;
+    }
+    if (tid == 0) {
+      double G[M * M], b[M], c[M];
+      const double* g = gram + (size_t)t * NR;
+      int e = 0;
+#pragma unroll
+      for (int r = 0; r < M; ++r)
+#pragma unroll
+        for (int cc = r; cc < M; ++cc) { const double v = g[e++]; G[r * M + cc] = v; G[cc * M + r] = v; }
+#pragma unroll
+      for (int r = 0; r < M; ++r) b[r] = g[NG + r];
+      pinv_solve_small<M>(G, b, c);
+#pragma unroll
+      for (int r = 0; r < M; ++r) s_coef[r] = c[r];
+    }
+    __syncthreads();
+    double cf[M], sh[M];
+#pragma unroll
+    for (int r = 0; r < M; ++r) { cf[r] = s_coef[r]; sh[r] = shift[(size_t)t * M + r]; }
+    for (int i = tid; i < n; i += 256) {
+      double r = p.y[a + i] - sh[KX] - cf[0];
+#pragma unroll
+      for (int j = 0; j < KX; ++j) r = fma(-cf[1 + j], p.X[j][a + i] - sh[j], r);
+      st_stream(p.out + a + i, r);
+    }
+    __syncthreads();
+  }
+}
+
+template <int KX>
+static void ortho_shard_launch(bmfm_ctx* ctx, const OrthoParams& p, int grid, int pass, const double* shift,
+                               const double* gram, const double* count, double* out) {
+  if (pass == 0) ortho_sums_kernel<KX, 0><<<grid, 256, 0, ctx->stream>>>(p, nullptr, out);
+  else if (pass == 1) ortho_sums_kernel<KX, 1><<<grid, 256, 0, ctx->stream>>>(p, shift, out);
+  else ortho_apply_kernel<KX><<<grid, 256, 0, ctx->stream>>>(p, shift, gram, count);
+}
+
 template <int KX>
 static void ortho_launch(bmfm_ctx* ctx, const OrthoParams& p, int grid) {
   orthogonalize_kernel<KX><<<grid, 256, 0, ctx->stream>>>(p);
@@ -370,6 +553,79 @@ extern "C" int bmfm_orthogonalize(bmfm_ctx* ctx, int T, const int64_t* date_off,
     case 4: ortho_launch<4>(ctx, p, grid); break;
     case 5: ortho_launch<5>(ctx, p, grid); break;
     default: ortho_launch<6>(ctx, p, grid); break;
+  }
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// ---- stock-sharded post-processing: the three passes of winsorize and orthogonalize around the caller's all-reduce ----
+extern "C" int bmfm_winsorize_sums(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, double* sums) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && date_off && x && sums, "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  winsorize_sums_kernel<<<grid, 256, 0, ctx->stream>>>(T, reinterpret_cast<const long long*>(date_off), x, sums);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_winsorize_sqdev(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, const double* mean,
+                                    double* sqdev) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && date_off && x && mean && sqdev, "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  winsorize_sqdev_kernel<<<grid, 256, 0, ctx->stream>>>(T, reinterpret_cast<const long long*>(date_off), x, mean, sqdev);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+extern "C" int bmfm_winsorize_apply(bmfm_ctx* ctx, int T, const int64_t* date_off, const double* x, const double* lo,
+                                    const double* hi, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && date_off && x && lo && hi && out, "bad arguments");
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  winsorize_apply_kernel<<<grid, 256, 0, ctx->stream>>>(T, reinterpret_cast<const long long*>(date_off), x, lo, hi, out);
+  ctx->launches++;
+  BMFM_CUDA(ctx, cudaGetLastError());
+  return BMFM_OK;
+}
+
+// pass 0: sums [T][k + 2] (complete rows, sum X_1..X_k, sum y);  pass 1: gram [T][(k+1)(k+2)/2 + k + 1] about
+// shift [T][k + 1];  pass 2: residuals from the (all-reduced) gram and count [T] (doubles).
+extern "C" int bmfm_orthogonalize_pass(bmfm_ctx* ctx, int pass, int T, const int64_t* date_off, const double* y, int k,
+                                       const double* const* X, const double* shift, const double* gram,
+                                       const double* count, double* out) {
+  if (!ctx) return BMFM_E_ARG;
+  BMFM_ARG(ctx, T >= 0 && k >= 1 && pass >= 0 && pass <= 2 && date_off && y && X && out, "bad arguments");
+  BMFM_ARG(ctx, pass == 0 || shift, "shift missing");
+  BMFM_ARG(ctx, pass < 2 || (gram && count), "gram / count missing");
+  if (k > PP_MAX_K) {
+    snprintf(ctx->err, sizeof(ctx->err), "k=%d exceeds compiled limit %d", k, PP_MAX_K);
+    return BMFM_E_UNSUPPORTED;
+  }
+  if (T == 0) return BMFM_OK;
+  BMFM_CUDA(ctx, cudaSetDevice(ctx->device));
+  OrthoParams p;
+  p.T = T; p.k = k;
+  p.date_off = reinterpret_cast<const long long*>(date_off);
+  p.y = y; p.out = out;
+  for (int j = 0; j < k; ++j) p.X[j] = X[j];
+  const int grid = T < ctx->sm_count * 8 ? T : ctx->sm_count * 8;
+  switch (k) {
+    case 1: ortho_shard_launch<1>(ctx, p, grid, pass, shift, gram, count, out); break;
+    case 2: ortho_shard_launch<2>(ctx, p, grid, pass, shift, gram, count, out); break;
+    case 3: ortho_shard_launch<3>(ctx, p, grid, pass, shift, gram, count, out); break;
+    case 4: ortho_shard_launch<4>(ctx, p, grid, pass, shift, gram, count, out); break;
+    case 5: ortho_shard_launch<5>(ctx, p, grid, pass, shift, gram, count, out); break;
+    default: ortho_shard_launch<6>(ctx, p, grid, pass, shift, gram, count, out); break;
   }
   ctx->launches++;
   BMFM_CUDA(ctx, cudaGetLastError());

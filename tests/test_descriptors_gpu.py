@@ -400,3 +400,96 @@ def test_two_column_elementwise_ops(ops):
     got = ops.rolling_sum(panel, 5, 2)
     want = np.column_stack([orc.rolling_sum(panel[:, s], 5, 2) for s in range(panel.shape[1])])
     assert np.array_equal(np.isnan(got), np.isnan(want)) and relerr(got, want) < 1e-14
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [1, 3])
+def test_stock_sharded_post_processing_equals_whole_table(world):
+    """the cross-sectional stages on a table whose STOCKS are split over ranks, with the per-date
+    moments summed over the ranks between the passes (here: the shards of one GPU, summed by hand), give what the
+    single-table entry points give; NaN runs, a date with too few complete rows, a date with a constant column."""
+    import torch
+    from bmfm import _cabi
+    from bmfm.dist import winsorize_sharded, orthogonalize_sharded
+    from util import record
+    rng = np.random.default_rng(5)
+    T, S = 40, 61
+    cols = [rng.normal(3.0 * j, 1.0 + j, size=(T, S)) for j in range(3)]
+    for c in cols:
+        c[rng.random((T, S)) < 0.06] = np.nan
+    cols[0][7, :] = np.nan                     # a date with no complete row
+    cols[1][9, 3:] = np.nan                    # a date with three complete rows at most (k + 2 = 4 needed)
+    cols[2][11, :] = 2.5                       # a constant regressor: rank-deficient Gram, pinv
+    ctx = _cabi.default_context()
+    dv = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    off_full = dv(np.arange(T + 1, dtype=np.int64) * S)
+    full = [dv(c.reshape(-1)) for c in cols]
+    want_w = [torch.empty_like(f) for f in full]
+    for f, w in zip(full, want_w):
+        ctx.winsorize(T, off_full, f, 2.5, w)
+    want_o = torch.empty_like(full[0])
+    ctx.orthogonalize(T, off_full, full[0], [full[1], full[2]], want_o)
+    # the shards: contiguous blocks of stocks, each a [T][S_r] table of its own
+    cuts = [S * r // world for r in range(world + 1)]
+    shards = [[dv(c[:, cuts[r]:cuts[r + 1]].reshape(-1)) for c in cols] for r in range(world)]
+    offs = [dv(np.arange(T + 1, dtype=np.int64) * (cuts[r + 1] - cuts[r])) for r in range(world)]
+
+    # the all-reduce of `world` ranks that run in lockstep, emulated: every rank's call is recorded and replayed
+    # with the sum once all ranks have reached the same pass
+    import threading
+    barrier = threading.Barrier(world)
+    slots, lock = {}, threading.Lock()
+
+    def make_allreduce(rank):
+        step = [0]
+
+        def allreduce(t):
+            key = step[0]
+            step[0] += 1
+            with lock:
+                slots.setdefault(key, []).append(t)
+            barrier.wait()
+            if rank == 0:
+                tot = torch.stack(slots[key]).sum(0)
+                for x in slots[key]:
+                    x.copy_(tot)
+                torch.cuda.synchronize()
+            barrier.wait()
+        return allreduce
+
+    got_w = [[torch.empty_like(x) for x in shards[r]] for r in range(world)]
+    got_o = [torch.empty_like(shards[r][0]) for r in range(world)]
+    errs = []
+
+    ctxs = [_cabi.Context(0) for _ in range(world)]         # one context per rank (host thread)
+
+    def run(rank):
+        try:
+            ar = make_allreduce(rank)
+            c = ctxs[rank]
+            winsorize_sharded(c, T, offs[rank], shards[rank], 2.5, got_w[rank], ar)
+            orthogonalize_sharded(c, T, offs[rank], shards[rank][0], [shards[rank][1], shards[rank][2]], got_o[rank], ar)
+        except Exception as e:      # noqa: BLE001
+            errs.append(e)
+            barrier.abort()
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    torch.cuda.synchronize()
+    for c in ctxs:
+        c.close()
+    for j in range(3):
+        got = np.concatenate([got_w[r][j].cpu().numpy().reshape(T, -1) for r in range(world)], axis=1)
+        want = want_w[j].cpu().numpy().reshape(T, S)
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        assert relerr(got, want) < 1e-13, j
+    got = np.concatenate([got_o[r].cpu().numpy().reshape(T, -1) for r in range(world)], axis=1)
+    want = want_o.cpu().numpy().reshape(T, S)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    assert np.isnan(got[7]).all() and np.isnan(got[9]).all()
+    ok = np.isfinite(want)
+    assert record(f"orthogonalize.sharded.w{world}", relerr(got[ok], want[ok])) < 1e-9
