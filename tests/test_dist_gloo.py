@@ -284,3 +284,120 @@ def test_sharded_pipeline_matches_single_process(shard_nw, shard_vr):
         for t in range(pan.T):       # simulations sharded, all-reduced
             if er[t] is not None:
                 assert close(er_sims[t], er[t], 1e-10)
+
+
+# ---- descriptors sharded by stock: the host logic of winsorize_sharded / orthogonalize_sharded ----------------------
+class OraclePostprocCtx:
+    """The six pass entry points of the C-ABI (bmfm_winsorize_sums / _sqdev / _apply, bmfm_orthogonalize_pass) restated
+    in numpy on CPU tensors (test only): same arguments, same per-date sums."""
+
+    @staticmethod
+    def _dates(date_off):
+        off = date_off.numpy()
+        return [(int(off[t]), int(off[t + 1])) for t in range(len(off) - 1)]
+
+    def winsorize_sums(self, T, date_off, x, sums):
+        for t, (a, b) in enumerate(self._dates(date_off)):
+            v = x.numpy()[a:b]
+            ok = ~np.isnan(v)
+            sums[t, 0], sums[t, 1] = float(v[ok].sum()), float(ok.sum())
+
+    def winsorize_sqdev(self, T, date_off, x, mean, sqdev):
+        for t, (a, b) in enumerate(self._dates(date_off)):
+            v = x.numpy()[a:b]
+            ok = ~np.isnan(v)
+            sqdev[t] = float(((float(mean[t]) - v[ok]) ** 2).sum())
+
+    def winsorize_apply(self, T, date_off, x, lo, hi, out):
+        for t, (a, b) in enumerate(self._dates(date_off)):
+            v = x.numpy()[a:b].copy()
+            l, h = float(lo[t]), float(hi[t])
+            if not (np.isnan(l) or np.isnan(h)):
+                ok = ~np.isnan(v)
+                v[ok] = np.minimum(np.maximum(v[ok], l), h)
+            out.numpy()[a:b] = v
+
+    def orthogonalize_pass(self, which, T, date_off, y, Xs, out, shift=None, gram=None, count=None):
+        k = len(Xs)
+        for t, (a, b) in enumerate(self._dates(date_off)):
+            yy = y.numpy()[a:b]
+            X = np.column_stack([c.numpy()[a:b] for c in Xs])
+            ok = ~(np.isnan(yy) | np.isnan(X).any(axis=1))
+            if which == 0:
+                out[t] = torch.from_numpy(np.concatenate([[ok.sum()], X[ok].sum(0), [yy[ok].sum()]]))
+                continue
+            sh = shift[t].numpy()
+            A = np.column_stack([np.ones(ok.sum()), X[ok] - sh[:k]])
+            r = yy[ok] - sh[k]
+            if which == 1:
+                G = A.T @ A
+                out[t] = torch.from_numpy(np.concatenate([G[np.triu_indices(k + 1)], A.T @ r]))
+                continue
+            res = np.full(b - a, np.nan)
+            if float(count[t]) >= k + 2:
+                g = gram[t].numpy()
+                G = np.zeros((k + 1, k + 1))
+                G[np.triu_indices(k + 1)] = g[:(k + 1) * (k + 2) // 2]
+                G = G + np.triu(G, 1).T
+                coef = np.linalg.pinv(G) @ g[(k + 1) * (k + 2) // 2:]
+                Afull = np.column_stack([np.ones(b - a), X - sh[:k]])
+                res = (yy - sh[k]) - Afull @ coef
+            out.numpy()[a:b] = res
+
+
+def _postproc_table():
+    rng = np.random.default_rng(31)
+    T, S = 12, 23
+    cols = [rng.normal(2.0 * j, 1.0 + j, size=(T, S)) for j in range(3)]
+    for c in cols:
+        c[rng.random((T, S)) < 0.08] = np.nan
+    cols[1][4, 2:] = np.nan            # fewer than k + 2 complete rows on date 4
+    return T, S, cols
+
+
+def _postproc_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        T, S, cols = _postproc_table()
+        lo, hi = S * rank // world, S * (rank + 1) // world
+        mine = [torch.from_numpy(np.ascontiguousarray(c[:, lo:hi]).reshape(-1)) for c in cols]
+        off = torch.arange(T + 1, dtype=torch.int64) * (hi - lo)
+        ctx = OraclePostprocCtx()
+        wz = [torch.empty_like(x) for x in mine]
+        bd.winsorize_sharded(ctx, T, off, mine, 2.5, wz, lambda t: dist.all_reduce(t))
+        res = torch.empty_like(mine[0])
+        bd.orthogonalize_sharded(ctx, T, off, mine[0], [mine[1], mine[2]], res, lambda t: dist.all_reduce(t))
+        q.put((rank, [w.numpy().reshape(T, -1) for w in wz], res.numpy().reshape(T, -1)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_stock_sharded_post_processing_gloo():
+    """Two ranks, each with half of the stocks of every date: the drivers of bmfm/dist.py with gloo all-reduces
+    reproduce the oracle's winsorize / orthogonalize of the whole table."""
+    world, port = 2, _free_port()
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    procs = [ctxm.Process(target=_postproc_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict()
+    for _ in range(world):
+        r, wz, res = q.get(timeout=120)
+        got[r] = (wz, res)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    T, S, cols = _postproc_table()
+    for j in range(3):
+        have = np.concatenate([got[r][0][j] for r in range(world)], axis=1)
+        want = np.stack([orc.winsorize(cols[j][t]) for t in range(T)])
+        assert np.array_equal(np.isnan(have), np.isnan(want))
+        assert np.nanmax(np.abs(have - want)) < 1e-12
+    have = np.concatenate([got[r][1] for r in range(world)], axis=1)
+    want = np.stack([orc.orthogonalize(cols[0][t], np.column_stack([cols[1][t], cols[2][t]])) for t in range(T)])
+    assert np.array_equal(np.isnan(have), np.isnan(want))
+    assert np.isnan(have[4]).all()
+    assert np.nanmax(np.abs(have - want)) < 1e-10
