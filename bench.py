@@ -580,13 +580,18 @@ def run_gpu(args):
         barrier()
         # one step (kernels + NCCL collectives) captured once and replayed: removes the host-side launch and
         # collective-enqueue gaps that dominate a sub-millisecond multi-GPU step
+        # several steps per graph (a divisor of K, so that exactly K steps are timed): one graph launch costs the
+        # host tens of microseconds, and with eight processes on one box a late launch on any rank stalls all of
+        # them at the next device barrier
+        g_unroll = next(u for u in (10, 5, 4, 2, 1) if args.steps % u == 0)
         try:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=gs):
-                step_body()
+                for _ in range(g_unroll):
+                    step_body()
             # untimed replays on top of the W eager warm-up steps: the first replays of a fresh graph (and the first
             # back-to-back use of the peer mappings) were seen to run several times slower than the steady state
-            for _ in range(max(args.warmup, 10)):
+            for _ in range(max(2, (max(args.warmup, 10) + g_unroll - 1) // g_unroll)):
                 graph.replay()
             barrier()
         except Exception as e:      # noqa: BLE001
@@ -599,9 +604,13 @@ def run_gpu(args):
     launches0 = ctx.launches
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
+    # the barrier comes LAST before the timed region: anything a single rank does between the barrier and its start
+    # event (rank 0 initialises NVML for the clock sampler, tens of ms) is time the other ranks spend inside the region
+    # waiting for it at the first device barrier — with K = 20 that was 2.3 ms of a 4.6 ms region on eight GPUs
+    barrier()
     t_start.record()
     if graph is not None:
-        for i in range(args.steps):
+        for i in range(args.steps // g_unroll):
             graph.replay()
     else:
         for i in range(args.warmup, args.warmup + args.steps):
@@ -1007,7 +1016,7 @@ def run_gpu(args):
                                           "published to the later ranks through per-producer flags" if fused and use_flags
                                           else "factor returns and exchange records stored over peer memory, device barriers" if fused
                                           else "NCCL all-gathers")) if world > 1 else "1 GPU",
-                       "timed_as": "CUDA graph replays of one captured step (phase_ms from 3 extra eager steps after the warm-up)" if graph is not None else "eager launches",
+                       "timed_as": (f"CUDA graph replays, {g_unroll} captured step(s) per graph (phase_ms from 3 extra eager steps after the warm-up)") if graph is not None else "eager launches",
                        "l2": f"inputs larger than L2: panel {h2d / 1e6:.0f} MB + {2 * T * K * K * 8 / 1e6:.0f} MB of covariance output per GPU per step vs 126 MB L2",
                        "phase_ms": {"reg_by_time": ms_reg, "newey_west": ms_nw, "vol_regime": ms_vr},
                        "all_status_ok": status_ok, "gather_check": gather_check},
